@@ -1,0 +1,126 @@
+/*
+ * pctts.h -- C ABI of libpctts.so, the B200 (sm_100a) backend of the PercivalTTS WGAN-GP training step.
+ *
+ * The reference (gillesdegottex/percivaltts) has no FFI of its own on this path: its only process->device boundary
+ * is Keras `train_on_batch` / `predict` inside percivaltts/backend_tensorflow.py's global tf.Session
+ * (backend_tensorflow.py:38-39; call sites optimizertts_wgan.py:220,236, modeltts.py:68-69).  libpctts.so replaces the
+ * TensorFlow/cuDNN library calls that session dispatched; each entry point below names the reference op it stands for.
+ * INTEGRATION.md shows the ctypes stub a maintainer would add to bind them.
+ *
+ * Conventions: plain pointers and sizes only; every pointer is a DEVICE pointer unless stated; tensors are fp32,
+ * batch-major, channels innermost ([B,T,feat], NHWC maps [N,T,F,C], Keras kernel layouts [in,out] / [W,in,out] /
+ * [KH,KW,in,out]); caller owns all buffers; calls are asynchronous on `stream` (a cudaStream_t passed as void*);
+ * return value 0 = ok, >0 = cudaError_t, <0 = PCTTS_E* argument error.  Nothing allocates.
+ */
+#ifndef PCTTS_H
+#define PCTTS_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PCTTS_ABI_VERSION 1
+
+/* epilogue flags shared by the GEMM and conv2d entry points */
+#define PCTTS_EPI_BIAS 1        /* + bias[n]                                   (Dense/Conv use_bias=True)            */
+#define PCTTS_EPI_LRELU 2       /* LeakyReLU(alpha=0.3)                        networktts.py:62,119,125               */
+#define PCTTS_EPI_SIGMOID 4     /* sigmoid                                     modeltts_common.py:121                 */
+#define PCTTS_EPI_DLRELU_AUX 8  /* * LeakyReLU'(aux) with aux = the layer's stored OUTPUT (y>0 <=> x>0)               */
+#define PCTTS_EPI_ACCUM 16      /* C += result                                                                        */
+#define PCTTS_EPI_ATOMIC 32     /* atomicAdd(C, result) (overlapping virtual rows: Conv1D data gradient)              */
+#define PCTTS_EPI_ADDMOD 64     /* + addmod[m % addrows, n]  (critic: ctx-branch term shared by the 3 applications)   */
+
+int pctts_abi_version(void);
+/* 0 when device `dev` is compute capability 10.x (B200); else PCTTS_EUNSUPPORTED / cudaError. Host call. */
+int pctts_device_check(int dev);
+
+/* ---- dense contractions: keras Dense (networktts.py:59-63,196-197), Conv1D as virtual-im2col GEMM (networktts.py:116-120),
+ *      LSTM input projections (networktts.py:90-94), and all their data / weight gradients ------------------------------- */
+/* C = epilogue(alpha * op(A) op(B)); op(A) is MxK, op(B) is KxN.  A stored matrix X is addressed as
+ * X[(r / segX) * segstrideX + (r % segX) * ldX + c] (segX <= 0: X[r*ldX + c]); `aux` uses C's addressing. */
+int pctts_gemm_f32(int transA, int transB, int M, int N, int K, float alpha,
+                   const float* A, long lda, int segA, long segstrideA,
+                   const float* B, long ldb, int segB, long segstrideB,
+                   float* C, long ldc, int segC, long segstrideC,
+                   const float* bias, const float* aux, const float* addmod, int addrows,
+                   int flags, void* stream);
+
+/* ---- Conv2D 'same', stride 1, NHWC, HWIO (networktts.py:122-126; modeltts_common.py:98,100; networks_critic.py:67) ------ */
+/* y[n,t,f,:] = epilogue(sum_{kt,kf,ci} x[n,t+kt-pad_t,f+kf-pad_f,ci] w[kt,kf,ci,:]).  xpitch/ypitch/auxpitch = floats between
+ * consecutive t rows, *batch = floats between consecutive n (lets the first / last layer read / write the spectral columns
+ * of a [B,T,1+S+NM] feature tensor in place, networks_critic.py:58, modeltts_common.py:101,123).  The data gradient is this
+ * same call with pctts_conv2d_flip_weights() kernels, swapped channel counts and pad = K-1-pad. */
+int pctts_conv2d_fwd(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T, int F,
+                     int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch, long auxpitch,
+                     long xbatch, long ybatch, long auxbatch, int flags, void* stream);
+int pctts_conv2d_flip_weights(const float* w, float* wt, int KH, int KW, int CIN, int COUT, void* stream);
+long pctts_conv2d_wgrad_workspace(int NB, int T, int CIN, int COUT, int KH, int KW); /* floats; host call */
+/* dw[kt,kf,ci,co] (+)= scale * sum_{n,t,f} x[n,t+kt-pad_t,f+kf-pad_f,ci] dy[n,t,f,co]   (deterministic two-stage) */
+int pctts_conv2d_wgrad(const float* x, const float* dy, float* dw, float* workspace, int NB, int T, int F, int CIN, int COUT,
+                       int KH, int KW, int pad_t, int pad_f, long xpitch, long dypitch, long xbatch, long dybatch, float scale,
+                       int accumulate, void* stream);
+
+/* ---- BatchNormalization(axis=-1) + LeakyReLU (networktts.py:61-62,118-119,124-125), data [rows, C] ------------------- */
+long pctts_colreduce_workspace_bytes(long rows, int C);            /* host call; zero the workspace once after allocation */
+void* pctts_colreduce_sums_ptr(void* workspace, long rows, int C); /* host call; double sums[2][C] inside the workspace
+                                                                      (all-reduce these across ranks for sync-BN) */
+int pctts_bn_stats(const float* x, long rows, int C, void* workspace, void* stream);  /* sums = [sum x, sum x^2] */
+int pctts_bn_finalize(void* workspace, long rows, int C, double count, float eps, float momentum, float* mean, float* invstd,
+                      float* moving_mean, float* moving_var, void* stream);          /* moving_* may be NULL (frozen) */
+int pctts_bn_apply(const float* x, float* y, const float* mean, const float* invstd_or_var, const float* gamma,
+                   const float* beta, long rows, int C, float eps, int use_var, int lrelu, void* stream);
+int pctts_bn_bwd_reduce(const float* x, const float* dy, const float* mean, const float* invstd, const float* gamma,
+                        const float* beta, long rows, int C, int lrelu, void* workspace, void* stream);
+int pctts_bn_bwd_apply(const float* x, const float* dy, float* dx, const float* mean, const float* invstd, const float* gamma,
+                       const float* beta, long rows, int C, double count, int lrelu, float* dgamma, float* dbeta,
+                       float grad_scale, int accumulate, void* workspace, void* stream); /* dgamma/dbeta *= grad_scale
+                       (1/world when the sums were all-reduced and the flat gradient is summed over ranks afterwards) */
+int pctts_colsum(const float* x, long rows, int C, float* out, int accumulate, void* workspace, void* stream);
+
+/* ---- LSTM / Bidirectional(LSTM) recurrence (networktts.py:72-96): persistent cluster kernel, U resident in smem -------- */
+/* zx* = x.W + b  [B,T,4H] (gate order i,f,c,o); U* [H,4H]; hout [B,T,ldh] (direction d -> columns d*H..); the gates and c buffers are
+ * written when non-NULL (needed by the backward).  ndir = 1 (LSTM) or 2 (Bidirectional: direction 1 runs time-reversed). */
+int pctts_lstm_fwd(const float* zx0, const float* zx1, const float* U0, const float* U1, float* hout, float* gates0,
+                   float* gates1, float* c0, float* c1, int B, int T, int H, int ndir, int ldh, int cluster_size,
+                   int batch_chunk, void* stream);
+/* BPTT: dz* [B,T,4H] = gradients wrt the gate pre-activations; weight gradients follow as GEMMs on dz. */
+int pctts_lstm_bwd(const float* dhout, const float* U0, const float* U1, const float* gates0, const float* gates1,
+                   const float* c0, const float* c1, float* dz0, float* dz1, int B, int T, int H, int ndir, int ldh,
+                   int cluster_size, int batch_chunk, void* stream);
+
+/* ---- WGAN-GP pieces (optimizertts_wgan.py:44-79) ------------------------------------------------------------------------ */
+/* s0 [3B,T,S] = [real | fake | alpha*real+(1-alpha)*fake] restricted to feature columns off..off+S-1  (:44-51, critic :58) */
+int pctts_critic_pack_inputs(const float* real, const float* fake, const float* alpha, float* s0, int B, int T, int O, int S,
+                             int off, void* stream);
+int pctts_fill_segments(float* p, long n0, float v0, long n1, float v1, long n2, float v2, void* stream);
+int pctts_sum_scaled(const float* x, long n, double scale, float* losses, int slot, void* stream);   /* wasserstein_loss :70-71 */
+int pctts_gp_norms(const float* g, int B, long per_sample, float* ss, void* stream);                 /* :59-64 */
+int pctts_gp_scale(const float* g, const float* ss, float* r0, int B, long per_sample, float lambda, int Bglobal,
+                   float* losses, int gp_slot, void* stream);                                        /* :66-68 and d/dg */
+int pctts_loss_combine(float* losses, int out, int a, float ca, int b, float cb, int c, float cc, void* stream);
+long pctts_lse_workspace_bytes(void);  /* host call; zero once */
+int pctts_lse_loss_grad(const float* pred, const float* real, const float* w, float* dpred, long rows, int O,
+                        double scale_loss, float scale_grad, float* losses, int slot, void* workspace, void* stream); /* :73-79 */
+/* Keras Adam (:145,172): reads *step, uses t=*step+1, then increments *step (device int) */
+int pctts_adam(float* p, const float* g, float* m, float* v, long n, float lr, float beta1, float beta2, float eps, int* step,
+               void* stream);
+
+/* ---- small movers -------------------------------------------------------------------------------------------------------- */
+int pctts_add(float* out, const float* a, const float* b, long n, void* stream);
+int pctts_sigmoid_bwd(const float* dy, long lddy, const float* y, long ldy, float* dz, long lddz, long rows, int cols, void* stream);
+int pctts_copy2d(float* dst, long ldd, const float* src, long lds, long rows, int cols, int accumulate, void* stream);
+int pctts_pad_time(float* dst, const float* src, int B, int T, int C, int left, int right, void* stream);
+int pctts_uniform(float* out, int n, unsigned long long seed, unsigned long long* counter, void* stream); /* K.random_uniform :50 */
+
+/* ---- PML band compression (vocoders.py:134-166,202; pulsemodel/analysis.py:336,366; tables from sigproc.py) -------------- */
+/* out[t,k] = (1-w[k]) f(in[t,idx[k]]) + w[k] f(in[t,idx[k]+1]),  f = log|.| when log_abs else identity */
+int pctts_pml_linbnd2fwbnd(const float* in, const int* idx, const float* wgt, float* out, long T, int nbins, int K, int log_abs,
+                           void* stream);
+/* out[t,i] = interp(in[t,:], idx[i] + w[i]) linear (smooth=0) or Catmull-Rom (smooth=1); exp() applied when do_exp */
+int pctts_pml_fwbnd2linbnd(const float* in, const int* idx, const float* wgt, float* out, long T, int K, int nbins, int smooth,
+                           int do_exp, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -250,7 +250,7 @@ def conv1d_same(x, k, bias=None):
     W = k.shape[0]
     left = (W - 1) // 2
     xp = F.pad(x.permute(0, 2, 1), (left, W - 1 - left))
-    y = F.conv1d(xp, k.permute(2, 1, 0), bias)
+    y = F.conv1d(xp.contiguous(), k.permute(2, 1, 0).contiguous(), bias)
     return y.permute(0, 2, 1)
 
 
@@ -259,7 +259,7 @@ def conv2d_same(x, k, bias=None):
     KH, KW = k.shape[0], k.shape[1]
     lt, lf = (KH - 1) // 2, (KW - 1) // 2
     xp = F.pad(x.permute(0, 3, 1, 2), (lf, KW - 1 - lf, lt, KH - 1 - lt))
-    y = F.conv2d(xp, k.permute(3, 2, 0, 1), bias)
+    y = F.conv2d(xp.contiguous(), k.permute(3, 2, 0, 1).contiguous(), bias)
     return y.permute(0, 2, 3, 1)
 
 

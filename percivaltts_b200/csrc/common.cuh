@@ -1,0 +1,59 @@
+// Shared device/host helpers for the percivaltts_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define PCTTS_LRELU_ALPHA 0.3f   // networktts.py:62,119,125 ; networks_critic.py:68
+
+// status codes returned through the C ABI (0 = ok, >0 = cudaError_t, <0 = argument errors)
+#define PCTTS_OK 0
+#define PCTTS_EINVAL (-1)
+#define PCTTS_EUNSUPPORTED (-2)
+
+#define PCTTS_LAUNCH_CHECK()                          \
+    do {                                              \
+        cudaError_t e__ = cudaGetLastError();         \
+        if (e__ != cudaSuccess) return (int)e__;      \
+    } while (0)
+
+#define PCTTS_CUDA(call)                              \
+    do {                                              \
+        cudaError_t e__ = (call);                     \
+        if (e__ != cudaSuccess) return (int)e__;      \
+    } while (0)
+
+__device__ __forceinline__ float lrelu_f(float x) { return x > 0.f ? x : PCTTS_LRELU_ALPHA * x; }
+// derivative of LeakyReLU written in terms of the *output* (sign-preserving, so y>0 <=> x>0)
+__device__ __forceinline__ float dlrelu_from_out(float y) { return y > 0.f ? 1.f : PCTTS_LRELU_ALPHA; }
+__device__ __forceinline__ float sigmoid_f(float x) { return 1.f / (1.f + __expf(-x)); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// block-wide sum (all threads get the result); scratch must hold >= 32 doubles
+__device__ __forceinline__ double block_sum_d(double v, double* scratch) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    v = warp_sum_d(v);
+    __syncthreads();
+    if (lane == 0) scratch[wid] = v;
+    __syncthreads();
+    const int nw = (blockDim.x + 31) >> 5;
+    double r = (threadIdx.x < nw) ? scratch[threadIdx.x] : 0.0;
+    if (wid == 0) {
+        r = warp_sum_d(r);
+        if (lane == 0) scratch[0] = r;
+    }
+    __syncthreads();
+    r = scratch[0];
+    return r;
+}
+
+static inline int pctts_div_up(long a, long b) { return (int)((a + b - 1) / b); }

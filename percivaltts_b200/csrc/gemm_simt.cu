@@ -1,0 +1,189 @@
+// fp32 SIMT GEMM with segmented row addressing and fused epilogues.
+//
+// This is the exact-fp32 contraction used for every Dense / Conv1D product of the reference graph
+// (networktts.py:59-63 pFC, :116-120 pCNN1D, LSTM input projections networktts.py:90-94) and for their
+// data / weight gradients.  The tcgen05 path (gemm_tc.cu) replaces it for the large contractions.
+//
+// A stored matrix is described by (ptr, ld, seg, segstride): element (r, c) lives at
+//     ptr[(r / seg) * segstride + (r % seg) * ld + c]          (seg <= 0: plain ptr[r*ld + c])
+// which lets a zero-padded [B, T+W-1, C] buffer be read as the *virtual* im2col matrix of a 'same'
+// Conv1D (row (b,t) = the W*C contiguous floats starting at xp[b, t, 0]; ld = C, seg = T,
+// segstride = (T+W-1)*C) without materialising it.
+#include "common.cuh"
+#include "pctts.h"
+
+namespace {
+
+struct Mat {
+    const float* p;
+    long ld;
+    int seg;
+    long segstride;
+};
+
+__device__ __forceinline__ long row_off(const Mat& m, int r) {
+    if (m.seg > 0) {
+        int s = r / m.seg;
+        return (long)s * m.segstride + (long)(r - s * m.seg) * m.ld;
+    }
+    return (long)r * m.ld;
+}
+
+constexpr int BM = 128, BN = 64, BK = 16, NT = 256;
+constexpr int TM = 8, TN = 4;
+
+struct Epi {
+    const float* bias;      // [N] or null
+    const float* aux;       // lrelu-derivative source (same addressing as C) or null
+    const float* addmod;    // [addrows, N] contiguous, added as addmod[m % addrows, n], or null
+    int addrows;
+    int flags;
+    float alpha;            // scales the accumulator before everything else
+};
+
+template <bool TA, bool TB>
+__global__ void __launch_bounds__(NT) gemm_f32_kernel(int M, int N, int K, Mat A, Mat B, Mat C, Epi e) {
+    __shared__ __align__(16) float As[BK][BM + 4];
+    __shared__ __align__(16) float Bs[BK][BN + 4];
+    const int tid = threadIdx.x;
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    const int ty = tid / 16, tx = tid % 16;
+
+    float acc[TM][TN];
+#pragma unroll
+    for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+
+    // per-thread global row offsets that do not depend on the k-block
+    long a_off[8];
+    bool a_ok[8];
+    if (!TA) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            int m = m0 + tid / 16 + 16 * i;
+            a_ok[i] = m < M;
+            a_off[i] = a_ok[i] ? row_off(A, m) : 0;
+        }
+    }
+    long b_off[4];
+    bool b_ok[4];
+    if (TB) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int n = n0 + tid / 16 + 16 * i;
+            b_ok[i] = n < N;
+            b_off[i] = b_ok[i] ? row_off(B, n) : 0;
+        }
+    }
+
+    for (int k0 = 0; k0 < K; k0 += BK) {
+        float ra[8], rb[4];
+        if (!TA) {
+            const int k = k0 + (tid % 16);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) ra[i] = (a_ok[i] && k < K) ? __ldg(A.p + a_off[i] + k) : 0.f;
+        } else {
+            const int m = m0 + (tid % 128);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                int k = k0 + tid / 128 + 2 * i;
+                ra[i] = (m < M && k < K) ? __ldg(A.p + row_off(A, k) + m) : 0.f;
+            }
+        }
+        if (!TB) {
+            const int n = n0 + (tid % 64);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                int k = k0 + tid / 64 + 4 * i;
+                rb[i] = (n < N && k < K) ? __ldg(B.p + row_off(B, k) + n) : 0.f;
+            }
+        } else {
+            const int k = k0 + (tid % 16);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) rb[i] = (b_ok[i] && k < K) ? __ldg(B.p + b_off[i] + k) : 0.f;
+        }
+        __syncthreads();   // previous tile fully consumed
+        if (!TA) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) As[tid % 16][tid / 16 + 16 * i] = ra[i];
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) As[tid / 128 + 2 * i][tid % 128] = ra[i];
+        }
+        if (!TB) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) Bs[tid / 64 + 4 * i][tid % 64] = rb[i];
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) Bs[tid % 16][tid / 16 + 16 * i] = rb[i];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < BK; ++kk) {
+            float4 a0 = *reinterpret_cast<const float4*>(&As[kk][ty * TM]);
+            float4 a1 = *reinterpret_cast<const float4*>(&As[kk][ty * TM + 4]);
+            float4 b0 = *reinterpret_cast<const float4*>(&Bs[kk][tx * TN]);
+            const float a[TM] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float b[TN] = {b0.x, b0.y, b0.z, b0.w};
+#pragma unroll
+            for (int i = 0; i < TM; ++i)
+#pragma unroll
+                for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+    }
+
+    float* Cp = const_cast<float*>(C.p);
+#pragma unroll
+    for (int i = 0; i < TM; ++i) {
+        const int m = m0 + ty * TM + i;
+        if (m >= M) continue;
+        const long coff = row_off(C, m);
+#pragma unroll
+        for (int j = 0; j < TN; ++j) {
+            const int n = n0 + tx * TN + j;
+            if (n >= N) continue;
+            float v = acc[i][j] * e.alpha;
+            if (e.flags & PCTTS_EPI_BIAS) v += __ldg(e.bias + n);
+            if (e.flags & PCTTS_EPI_ADDMOD) v += __ldg(e.addmod + (long)(m % e.addrows) * N + n);
+            if (e.flags & PCTTS_EPI_LRELU) v = lrelu_f(v);
+            if (e.flags & PCTTS_EPI_SIGMOID) v = sigmoid_f(v);
+            if (e.flags & PCTTS_EPI_DLRELU_AUX) v *= dlrelu_from_out(e.aux[coff + n]);   // aux may alias C (tangent sweep)
+            if (e.flags & PCTTS_EPI_ATOMIC) {
+                atomicAdd(Cp + coff + n, v);
+            } else {
+                if (e.flags & PCTTS_EPI_ACCUM) v += Cp[coff + n];
+                Cp[coff + n] = v;
+            }
+        }
+    }
+}
+
+int launch(int ta, int tb, int M, int N, int K, Mat A, Mat B, Mat C, Epi e, cudaStream_t st) {
+    if (M <= 0 || N <= 0) return PCTTS_OK;
+    if (K < 0) return PCTTS_EINVAL;
+    dim3 grid(pctts_div_up(N, BN), pctts_div_up(M, BM));
+    if (!ta && !tb) gemm_f32_kernel<false, false><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e);
+    else if (!ta && tb) gemm_f32_kernel<false, true><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e);
+    else if (ta && !tb) gemm_f32_kernel<true, false><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e);
+    else gemm_f32_kernel<true, true><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
+}  // namespace
+
+extern "C" int pctts_gemm_f32(int transA, int transB, int M, int N, int K, float alpha,
+                              const float* A, long lda, int segA, long segstrideA,
+                              const float* B, long ldb, int segB, long segstrideB,
+                              float* C, long ldc, int segC, long segstrideC,
+                              const float* bias, const float* aux, const float* addmod, int addrows,
+                              int flags, void* stream) {
+    if (!A || !B || !C) return PCTTS_EINVAL;
+    if ((flags & PCTTS_EPI_BIAS) && !bias) return PCTTS_EINVAL;
+    if ((flags & PCTTS_EPI_DLRELU_AUX) && !aux) return PCTTS_EINVAL;
+    if ((flags & PCTTS_EPI_ADDMOD) && (!addmod || addrows <= 0)) return PCTTS_EINVAL;
+    Mat a{A, lda, segA, segstrideA}, b{B, ldb, segB, segstrideB}, c{C, ldc, segC, segstrideC};
+    Epi e{bias, aux, addmod, addrows, flags, alpha};
+    return launch(transA, transB, M, N, K, a, b, c, e, (cudaStream_t)stream);
+}

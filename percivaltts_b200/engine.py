@@ -1,0 +1,503 @@
+"""
+Host-side execution engine of the WGAN-GP step: explicit forward / backward / double-backward schedules of the
+generator and the critic, written against the kernel interface of percivaltts_b200/ops.py (libpctts.so).
+
+torch is used for device memory only: no autograd, no torch operators on the data path.  Every gradient below is
+derived by hand and checked against the CPU oracle in tests/.
+
+Reference graph:  generator percivaltts/modeltts_common.py:61-126, critic percivaltts/networks_critic.py:44-96,
+layer builders percivaltts/networktts.py:59-126, losses / step graphs percivaltts/optimizertts_wgan.py:44-79,107-213.
+"""
+from collections import OrderedDict
+
+import numpy as np
+import torch
+
+from . import arch as A
+from .ops import EPI_LRELU, EPI_SIGMOID, EPI_ACCUM
+
+
+class LocalSync(object):
+    """Single-replica stand-in for the data-parallel exchange (see parallel.DistSync)."""
+    world = 1
+    rank = 0
+
+    def allreduce(self, t):
+        return t
+
+
+class ParamStore(object):
+    """Flat fp32 buffers (parameters, gradients, Adam slots) with named views; non-trainable BN moving
+    statistics live in a second flat buffer.  One flat gradient buffer = one NCCL all-reduce per step."""
+
+    def __init__(self, ops, shapes):
+        self.ops = ops
+        self.shapes = list(shapes)
+        ntrain = sum(int(np.prod(s)) for _, s, t in self.shapes if t)
+        nstate = sum(int(np.prod(s)) for _, s, t in self.shapes if not t)
+        self.flat = ops.zeros(max(ntrain, 1))
+        self.grad = ops.zeros(max(ntrain, 1))
+        self.m = ops.zeros(max(ntrain, 1))
+        self.v = ops.zeros(max(ntrain, 1))
+        self.state = ops.zeros(max(nstate, 1))
+        self.step = ops.zeros(1, dtype=torch.int32)
+        self.ntrain, self.nstate = ntrain, nstate
+        self.p, self.g = OrderedDict(), OrderedDict()
+        ot = os_ = 0
+        for name, shape, trainable in self.shapes:
+            n = int(np.prod(shape))
+            if trainable:
+                self.p[name] = self.flat[ot:ot + n].view(*shape)
+                self.g[name] = self.grad[ot:ot + n].view(*shape)
+                ot += n
+            else:
+                self.p[name] = self.state[os_:os_ + n].view(*shape)
+                os_ += n
+
+    def count_params(self):
+        return self.ntrain + self.nstate
+
+    def load(self, weights):
+        """weights: name -> array-like (numpy or torch); every inventory entry must be present."""
+        for name, shape, _ in self.shapes:
+            w = torch.as_tensor(np.asarray(weights[name])).to(self.flat.dtype).reshape(*shape)
+            self.p[name].copy_(w)
+
+    def export(self):
+        return OrderedDict((name, self.p[name].detach().cpu().numpy().copy()) for name, _, _ in self.shapes)
+
+    def export_grads(self):
+        return OrderedDict((name, self.g[name].detach().cpu().numpy().copy()) for name in self.g)
+
+    def adam(self, lr, beta1, beta2, eps=1e-7):
+        if self.ntrain:
+            self.ops.adam(self.flat[:self.ntrain], self.grad[:self.ntrain], self.m[:self.ntrain], self.v[:self.ntrain],
+                          lr, beta1, beta2, eps, self.step)
+
+
+def _im2col_view(xp, T, W):
+    """Virtual im2col of a time-padded [B, T+W-1, C] buffer: row (b,t) = the W*C floats starting at xp[b,t,0]."""
+    B, Tp, C = xp.shape
+    return xp.as_strided((B, T, W * C), (Tp * C, C, 1))
+
+
+class _BN(object):
+    """Buffers of one BatchNormalization(axis=-1)+LeakyReLU application on a [rows, C] pre-activation."""
+
+    def __init__(self, ops, prefix, rows, C):
+        self.prefix, self.rows, self.C = prefix, rows, C
+        self.mean = ops.zeros(C)
+        self.invstd = ops.zeros(C)
+
+
+class Generator(object):
+    """DCNNF0SpecNoiseFeatures (modeltts_common.py:61-126): ctx [B,T,ctxsize] -> [B,T,1+spec+nm]."""
+
+    def __init__(self, ops, arch, params=None):
+        if arch.gen_nbcnnlayers < 1:
+            raise ValueError('arch_gen_nbcnnlayers must be >= 1 on the B200 path')
+        self.ops, self.a = ops, arch
+        self.params = params if params is not None else ParamStore(ops, A.generator_param_shapes(arch))
+        self._plans = {}
+
+    # ---- buffers ----------------------------------------------------------------------------------------------
+    def plan(self, B, T, with_backward=True):
+        key = (B, T, bool(with_backward))
+        pl = self._plans.get(key)
+        if pl is None:
+            pl = self._plans[key] = self._make_plan(B, T, with_backward)
+        return pl
+
+    def _make_plan(self, B, T, bwd):
+        o, a = self.ops, self.a
+        H, S, NM, O, Fl, W = a.hiddenwidth, a.spec_size, a.nm_size, a.outsize, a.gen_nbfilters, a.ctx_winlen
+        M = B * T
+        pl = dict(B=B, T=T, M=M)
+        cin = a.ctxsize
+        pl['ctx_xp'], pl['ctx_z'], pl['ctx_y'], pl['ctx_bn'] = [], [], [], []
+        for i in range(a.ctx_nbcnnlayers):
+            pl['ctx_xp'].append(o.zeros(B, T + W - 1, cin))
+            pl['ctx_z'].append(o.empty(M, H))
+            pl['ctx_y'].append(o.empty(M, H))
+            pl['ctx_bn'].append(_BN(o, 'g.ctx.cnn%d.bn' % i, M, H))
+            cin = H
+        pl['fc_z'] = [o.empty(M, H) for _ in range(2)]
+        pl['fc_y'] = [o.empty(M, H) for _ in range(2)]
+        pl['fc_bn'] = [_BN(o, 'g.ctx.fc%d.bn' % i, M, H) for i in range(2)]
+        pl['zx'] = [o.empty(B, T, 4 * H) for _ in range(2)]
+        pl['hout'] = o.empty(B, T, 2 * H)
+        pl['gates'] = [o.empty(B, T, 4 * H) for _ in range(2)] if bwd else None
+        pl['cstate'] = [o.empty(B, T, H) for _ in range(2)] if bwd else None
+        pl['s'] = o.empty(M, S)
+        L = a.gen_nbcnnlayers
+        pl['cv_z'] = [o.empty(B, T, S, Fl) for _ in range(L)]
+        pl['cv_a'] = [o.empty(B, T, S, Fl) for _ in range(L)]
+        pl['cv_bn'] = [_BN(o, 'g.spec.cnn%d.bn' % i, M * S, Fl) for i in range(L)]
+        Ln = L // 2
+        pl['nm_z'] = [o.empty(M, H) for _ in range(Ln)]
+        pl['nm_y'] = [o.empty(M, H) for _ in range(Ln)]
+        pl['nm_bn'] = [_BN(o, 'g.nm.fc%d.bn' % i, M, H) for i in range(Ln)]
+        if bwd:
+            pl['d_lctx'] = o.empty(M, H)
+            pl['dA'] = o.empty(M, H)           # ping-pong [M,H] gradient buffers
+            pl['dB'] = o.empty(M, H)
+            pl['dz_nm'] = o.empty(M, NM)
+            pl['dspec'] = o.empty(M, S)
+            pl['df0'] = o.empty(M, 1)
+            pl['dmapA'] = o.empty(B, T, S, Fl)
+            pl['dmapB'] = o.empty(B, T, S, Fl)
+            pl['ds'] = o.empty(M, S)
+            pl['dhout'] = o.empty(B, T, 2 * H)
+            pl['dzl'] = [o.empty(B, T, 4 * H) for _ in range(2)]
+            pl['wflip'] = [o.empty(a.gen_winlen, a.spec_freqlen, Fl, 1 if i == 0 else Fl) for i in range(L)]
+            pl['wflip_out'] = o.empty(a.gen_winlen, a.spec_freqlen, 1, Fl)
+            if a.ctx_nbcnnlayers > 1:
+                pl['ctx_dzp'] = o.zeros(B, T + W - 1, H)
+                pl['ctx_kflip'] = o.empty(W, 1, H, H)
+        return pl
+
+    # ---- forward ----------------------------------------------------------------------------------------------
+    def _bn_fwd(self, z2, y2, bn, training, update_stats, sync):
+        o, p = self.ops, self.params.p
+        g, b = p[bn.prefix + '.gamma'], p[bn.prefix + '.beta']
+        mm, mv = p[bn.prefix + '.moving_mean'], p[bn.prefix + '.moving_var']
+        if training:
+            ws = o.bn_stats(z2)
+            sync.allreduce(ws.sums)
+            o.bn_finalize(ws, bn.rows * sync.world, A.BN_EPS, A.BN_MOMENTUM, bn.mean, bn.invstd,
+                          mm if update_stats else None, mv if update_stats else None)
+            o.bn_apply(z2, y2, bn.mean, bn.invstd, g, b, A.BN_EPS, 0, 1)
+        else:
+            o.bn_apply(z2, y2, mm, mv, g, b, A.BN_EPS, 1, 1)
+
+    def forward(self, pl, ctx, out, training=True, update_stats=False, sync=None):
+        """ctx [B,T,ctxsize] -> out [B,T,O] (both contiguous device tensors).  training: BN uses batch statistics
+        (all-reduced through `sync`); update_stats: also move the BN moving averages (generator step only)."""
+        o, a, p = self.ops, self.a, self.params.p
+        sync = sync or LocalSync()
+        B, T, M = pl['B'], pl['T'], pl['M']
+        H, S, O, Fl, W = a.hiddenwidth, a.spec_size, a.outsize, a.gen_nbfilters, a.ctx_winlen
+        left = (W - 1) // 2
+        x = ctx
+        for i in range(a.ctx_nbcnnlayers):                                   # pCNN1D (networktts.py:116-120)
+            xp = pl['ctx_xp'][i]
+            o.pad_time(xp, x, left, W - 1 - left)
+            k = p['g.ctx.cnn%d.kernel' % i]
+            o.gemm(_im2col_view(xp, T, W), k.view(-1, H), pl['ctx_z'][i])
+            self._bn_fwd(pl['ctx_z'][i], pl['ctx_y'][i], pl['ctx_bn'][i], training, update_stats, sync)
+            x = pl['ctx_y'][i].view(B, T, H)
+        x2 = x.reshape(M, -1)
+        for i in range(2):                                                   # pFC (networktts.py:59-63)
+            o.gemm(x2, p['g.ctx.fc%d.kernel' % i], pl['fc_z'][i])
+            self._bn_fwd(pl['fc_z'][i], pl['fc_y'][i], pl['fc_bn'][i], training, update_stats, sync)
+            x2 = pl['fc_y'][i]
+        lctx = x2
+        out2 = out.view(M, O)
+        # F0: Bidirectional LSTM + Dense(1)   (modeltts_common.py:82-84, networktts.py:85-96)
+        for d, dn in enumerate(('fw', 'bw')):
+            o.gemm(lctx, p['g.f0.blstm.%s.kernel' % dn], pl['zx'][d].view(M, 4 * H), bias=p['g.f0.blstm.%s.bias' % dn])
+        o.lstm_fwd(pl['zx'], [p['g.f0.blstm.fw.recurrent'], p['g.f0.blstm.bw.recurrent']], pl['hout'], pl['gates'],
+                   pl['cstate'])
+        o.gemm(pl['hout'].view(M, 2 * H), p['g.f0.out.kernel'], out2[:, 0:1], bias=p['g.f0.out.bias'])
+        # Spec: Dense projection, [B,T,S,1] map, pCNN2D stack, Conv2D(1)   (modeltts_common.py:95-101)
+        o.gemm(lctx, p['g.spec.proj.kernel'], pl['s'], bias=p['g.spec.proj.bias'])
+        amap = pl['s'].view(B, T, S, 1)
+        for i in range(a.gen_nbcnnlayers):
+            o.conv2d(amap, p['g.spec.cnn%d.kernel' % i], pl['cv_z'][i])
+            self._bn_fwd(pl['cv_z'][i].view(M * S, Fl), pl['cv_a'][i].view(M * S, Fl), pl['cv_bn'][i], training,
+                         update_stats, sync)
+            amap = pl['cv_a'][i]
+        o.conv2d(amap, p['g.spec.out.kernel'], out[:, :, 1:1 + S].unsqueeze(-1), bias=p['g.spec.out.bias'])
+        # NM: pFC x (L//2), Dense(sigmoid)   (modeltts_common.py:117-121)
+        n2 = lctx
+        for i in range(a.gen_nbcnnlayers // 2):
+            o.gemm(n2, p['g.nm.fc%d.kernel' % i], pl['nm_z'][i])
+            self._bn_fwd(pl['nm_z'][i], pl['nm_y'][i], pl['nm_bn'][i], training, update_stats, sync)
+            n2 = pl['nm_y'][i]
+        o.gemm(n2, p['g.nm.out.kernel'], out2[:, 1 + S:], bias=p['g.nm.out.bias'], flags=EPI_SIGMOID)
+        pl['lctx'], pl['ctx_in'] = lctx, ctx
+        return out
+
+    # ---- backward ---------------------------------------------------------------------------------------------
+    def _bn_bwd(self, z2, dy2, dz2, bn, sync):
+        o, p, g = self.ops, self.params.p, self.params.g
+        gam, bet = p[bn.prefix + '.gamma'], p[bn.prefix + '.beta']
+        ws = o.bn_bwd_reduce(z2, dy2, bn.mean, bn.invstd, gam, bet, 1)
+        sync.allreduce(ws.sums)
+        # dgamma / dbeta come from the all-reduced sums, i.e. every rank holds the global value: pre-divide by world so
+        # that the all-reduce(sum) of the flat gradient buffer does not count them `world` times
+        o.bn_bwd_apply(ws, z2, dy2, dz2, bn.mean, bn.invstd, gam, bet, bn.rows * sync.world, 1,
+                       g[bn.prefix + '.gamma'], g[bn.prefix + '.beta'], grad_scale=1.0 / sync.world)
+
+    def backward(self, pl, out, dout, sync=None):
+        """dout = d(loss)/d(out) [B,T,O]; fills params.g for every trainable generator parameter."""
+        o, a, p, g = self.ops, self.a, self.params.p, self.params.g
+        sync = sync or LocalSync()
+        B, T, M = pl['B'], pl['T'], pl['M']
+        H, S, NM, O, Fl, W = a.hiddenwidth, a.spec_size, a.nm_size, a.outsize, a.gen_nbfilters, a.ctx_winlen
+        L, Ln = a.gen_nbcnnlayers, a.gen_nbcnnlayers // 2
+        lctx, dl = pl['lctx'], pl['d_lctx']
+        out2, dout2 = out.view(M, O), dout.view(M, O)
+        # ---- NM branch
+        nlast = pl['nm_y'][Ln - 1] if Ln > 0 else lctx
+        o.sigmoid_bwd(dout2[:, 1 + S:], out2[:, 1 + S:], pl['dz_nm'])
+        o.gemm(nlast, pl['dz_nm'], g['g.nm.out.kernel'], transA=True)
+        o.colsum(pl['dz_nm'], g['g.nm.out.bias'])
+        dcur = dl if Ln == 0 else pl['dA']
+        o.gemm(pl['dz_nm'], p['g.nm.out.kernel'], dcur, transB=True)
+        for i in range(Ln - 1, -1, -1):
+            xin = pl['nm_y'][i - 1] if i > 0 else lctx
+            dz = pl['dB'] if dcur is pl['dA'] else pl['dA']
+            self._bn_bwd(pl['nm_z'][i], dcur, dz, pl['nm_bn'][i], sync)
+            o.gemm(xin, dz, g['g.nm.fc%d.kernel' % i], transA=True)
+            dnext = dl if i == 0 else dcur
+            o.gemm(dz, p['g.nm.fc%d.kernel' % i], dnext, transB=True)
+            dcur = dnext
+        # ---- Spec branch
+        o.copy2d(pl['dspec'], dout2[:, 1:1 + S])
+        dmap = pl['dspec'].view(B, T, S, 1)
+        o.conv2d_wgrad(pl['cv_a'][L - 1], dmap, g['g.spec.out.kernel'])
+        o.colsum(pl['dspec'].view(M * S, 1), g['g.spec.out.bias'])
+        o.conv2d_flip(p['g.spec.out.kernel'], pl['wflip_out'])
+        da = pl['dmapA']
+        o.conv2d(dmap, pl['wflip_out'], da)
+        for i in range(L - 1, -1, -1):
+            dz = pl['dmapB'] if da is pl['dmapA'] else pl['dmapA']
+            self._bn_bwd(pl['cv_z'][i].view(M * S, Fl), da.view(M * S, Fl), dz.view(M * S, Fl), pl['cv_bn'][i], sync)
+            ain = pl['cv_a'][i - 1] if i > 0 else pl['s'].view(B, T, S, 1)
+            o.conv2d_wgrad(ain, dz, g['g.spec.cnn%d.kernel' % i])
+            o.conv2d_flip(p['g.spec.cnn%d.kernel' % i], pl['wflip'][i])
+            dnext = (pl['dmapB'] if dz is pl['dmapA'] else pl['dmapA']) if i > 0 else pl['ds'].view(B, T, S, 1)
+            o.conv2d(dz, pl['wflip'][i], dnext)
+            da = dnext
+        o.gemm(lctx, pl['ds'], g['g.spec.proj.kernel'], transA=True)
+        o.colsum(pl['ds'], g['g.spec.proj.bias'])
+        o.gemm(pl['ds'], p['g.spec.proj.kernel'], dl, transB=True, flags=EPI_ACCUM)
+        # ---- F0 branch
+        o.copy2d(pl['df0'], dout2[:, 0:1])
+        hout2 = pl['hout'].view(M, 2 * H)
+        o.gemm(hout2, pl['df0'], g['g.f0.out.kernel'], transA=True)
+        o.colsum(pl['df0'], g['g.f0.out.bias'])
+        o.gemm(pl['df0'], p['g.f0.out.kernel'], pl['dhout'].view(M, 2 * H), transB=True)
+        U = [p['g.f0.blstm.fw.recurrent'], p['g.f0.blstm.bw.recurrent']]
+        o.lstm_bwd(pl['dhout'], U, pl['gates'], pl['cstate'], pl['dzl'])
+        for d, dn in enumerate(('fw', 'bw')):
+            dz2 = pl['dzl'][d].view(M, 4 * H)
+            o.gemm(lctx, dz2, g['g.f0.blstm.%s.kernel' % dn], transA=True)
+            o.colsum(dz2, g['g.f0.blstm.%s.bias' % dn])
+            gU = g['g.f0.blstm.%s.recurrent' % dn]
+            if T > 1:
+                hd = pl['hout'][:, :, d * H:(d + 1) * H]
+                if d == 0:      # forward direction: the state feeding step t is h[t-1]
+                    o.gemm(hd[:, 0:T - 1], pl['dzl'][d][:, 1:T], gU, transA=True)
+                else:           # backward direction: the state feeding step t is h[t+1]
+                    o.gemm(hd[:, 1:T], pl['dzl'][d][:, 0:T - 1], gU, transA=True)
+            else:
+                o.fill_segments(gU.view(-1), gU.numel(), 0.0)
+            o.gemm(dz2, p['g.f0.blstm.%s.kernel' % dn], dl, transB=True, flags=EPI_ACCUM)
+        # ---- ctx trunk: pFC x2 then pCNN1D stack
+        dcur = dl
+        for i in (1, 0):
+            if i > 0:
+                xin = pl['fc_y'][i - 1]
+            else:
+                xin = pl['ctx_y'][-1] if a.ctx_nbcnnlayers > 0 else pl['ctx_in'].view(M, -1)
+            dz = pl['dB'] if dcur is not pl['dB'] else pl['dA']
+            self._bn_bwd(pl['fc_z'][i], dcur, dz, pl['fc_bn'][i], sync)
+            o.gemm(xin, dz, g['g.ctx.fc%d.kernel' % i], transA=True)
+            if i > 0 or a.ctx_nbcnnlayers > 0:
+                dnext = pl['dA'] if dz is pl['dB'] else pl['dB']
+                o.gemm(dz, p['g.ctx.fc%d.kernel' % i], dnext, transB=True)
+                dcur = dnext
+        left = (W - 1) // 2
+        for i in range(a.ctx_nbcnnlayers - 1, -1, -1):
+            dz = pl['dB'] if dcur is not pl['dB'] else pl['dA']
+            self._bn_bwd(pl['ctx_z'][i], dcur, dz, pl['ctx_bn'][i], sync)
+            k = p['g.ctx.cnn%d.kernel' % i]
+            o.gemm(_im2col_view(pl['ctx_xp'][i], T, W), dz, g['g.ctx.cnn%d.kernel' % i].view(-1, H), transA=True)
+            if i > 0:
+                # data gradient = 'same' correlation of dz with the time-flipped, in/out-transposed kernel
+                o.pad_time(pl['ctx_dzp'], dz.view(B, T, H), W - 1 - left, left)
+                o.conv2d_flip(k.view(W, 1, H, H), pl['ctx_kflip'])
+                dnext = pl['dA'] if dz is pl['dB'] else pl['dB']
+                o.gemm(_im2col_view(pl['ctx_dzp'], T, W), pl['ctx_kflip'].view(W * H, H), dnext)
+                dcur = dnext
+
+
+class Critic(object):
+    """Critic (networks_critic.py:44-96): (features [B,T,O], ctx [B,T,ctxsize]) -> [B,T,1].
+
+    `napp` applications that share the ctx input are batched along the sample axis of the spectral branch
+    ([real | fake | interpolated] in the critic step); the ctx branch is evaluated once and its contribution to the
+    first post layer is added per application (the reference recomputes it for each application,
+    optimizertts_wgan.py:131-137 -- same values, one third of the work)."""
+
+    def __init__(self, ops, arch, params=None):
+        if arch.gen_nbcnnlayers < 1:
+            raise ValueError('arch_gen_nbcnnlayers must be >= 1 on the B200 path')
+        self.ops, self.a = ops, arch
+        self.params = params if params is not None else ParamStore(ops, A.critic_param_shapes(arch))
+        self._plans = {}
+
+    def plan(self, napp, B, T):
+        key = (napp, B, T)
+        pl = self._plans.get(key)
+        if pl is None:
+            pl = self._plans[key] = self._make_plan(napp, B, T)
+        return pl
+
+    def _make_plan(self, napp, B, T):
+        o, a = self.ops, self.a
+        H, S, Fl, W, L = a.hiddenwidth, a.spec_size, a.gen_nbfilters, a.ctx_winlen, a.gen_nbcnnlayers
+        M, nB = B * T, napp * B
+        nM = nB * T
+        pl = dict(B=B, T=T, M=M, napp=napp, nB=nB, nM=nM)
+        cin = a.ctxsize
+        pl['ctx_xp'], pl['ctx_y'] = [], []
+        for i in range(a.ctx_nbcnnlayers):
+            pl['ctx_xp'].append(o.zeros(B, T + W - 1, cin))
+            pl['ctx_y'].append(o.empty(M, H))
+            cin = H
+        pl['fc_y'] = [o.empty(M, H) for _ in range(2)]
+        pl['ctxterm'] = o.empty(M, H)
+        pl['a'] = [o.empty(nB, T, S, Fl) for _ in range(L)]
+        pl['p'] = [o.empty(nM, H) for _ in range(3)]
+        pl['d'] = o.empty(nM, 1)
+        pl['dd'] = o.empty(nM, 1)
+        pl['dp'] = [o.empty(nM, H) for _ in range(3)]
+        pl['da'] = [o.empty(nB, T, S, Fl) for _ in range(L)]
+        pl['wflip'] = [o.empty(a.gen_winlen, a.spec_freqlen, Fl, 1 if i == 0 else Fl) for i in range(L)]
+        pl['dct'] = o.empty(M, H)
+        pl['dcA'] = o.empty(M, H)
+        pl['dcB'] = o.empty(M, H)
+        if a.ctx_nbcnnlayers > 1:
+            pl['ctx_dzp'] = o.zeros(B, T + W - 1, H)
+            pl['ctx_kflip'] = o.empty(W, 1, H, H)
+        return pl
+
+    def forward(self, pl, s0, ctx):
+        """s0: spectral input map view [napp*B, T, S, 1]; ctx [B,T,ctxsize].  -> pl['d'] [napp*B*T, 1]."""
+        o, a, p = self.ops, self.a, self.params.p
+        B, T, M, nM = pl['B'], pl['T'], pl['M'], pl['nM']
+        H, S, Fl, W, L = a.hiddenwidth, a.spec_size, a.gen_nbfilters, a.ctx_winlen, a.gen_nbcnnlayers
+        SF = S * Fl
+        left = (W - 1) // 2
+        # ctx branch, once per batch (networks_critic.py:80-85)
+        x = ctx
+        for i in range(a.ctx_nbcnnlayers):
+            xp = pl['ctx_xp'][i]
+            o.pad_time(xp, x, left, W - 1 - left)
+            o.gemm(_im2col_view(xp, T, W), p['c.ctx.cnn%d.kernel' % i].view(-1, H), pl['ctx_y'][i],
+                   bias=p['c.ctx.cnn%d.bias' % i], flags=EPI_LRELU)
+            x = pl['ctx_y'][i].view(B, T, H)
+        x2 = x.reshape(M, -1)
+        for i in range(2):
+            o.gemm(x2, p['c.ctx.fc%d.kernel' % i], pl['fc_y'][i], bias=p['c.ctx.fc%d.bias' % i], flags=EPI_LRELU)
+            x2 = pl['fc_y'][i]
+        w0 = p['c.post.fc0.kernel']
+        o.gemm(x2, w0[SF:], pl['ctxterm'], bias=p['c.post.fc0.bias'])
+        # spectral branch on all applications (networks_critic.py:58-70)
+        amap = s0
+        for i in range(L):
+            o.conv2d(amap, p['c.spec.cnn%d.kernel' % i], pl['a'][i], bias=p['c.spec.cnn%d.bias' % i], flags=EPI_LRELU)
+            amap = pl['a'][i]
+        # post layers (networks_critic.py:89-96); concat([spec, ctx]) . W0 = spec . W0[:SF] + ctx . W0[SF:]
+        o.gemm(amap.view(nM, SF), w0[:SF], pl['p'][0], addmod=pl['ctxterm'], flags=EPI_LRELU)
+        for i in (1, 2):
+            o.gemm(pl['p'][i - 1], p['c.post.fc%d.kernel' % i], pl['p'][i], bias=p['c.post.fc%d.bias' % i], flags=EPI_LRELU)
+        o.gemm(pl['p'][2], p['c.out.kernel'], pl['d'], bias=p['c.out.bias'])
+        pl['s0'], pl['ctx_in'], pl['ctx_last'] = s0, ctx, x2
+        return pl['d']
+
+    def backward_to_input(self, pl, g_out, g_rows=None, accumulate=False):
+        """Back-propagate pl['dd'] (d objective / d critic output, [nM,1]) to the spectral input.  The per-layer
+        pre-activation gradients stay in pl['dp'] / pl['da'] for param_grads().  g_out: [n,T,S,1] view receiving the
+        input gradient of the applications `g_rows` (slice over the napp*B sample axis; default all)."""
+        o, a, p = self.ops, self.a, self.params.p
+        nM = pl['nM']
+        S, Fl, L = a.spec_size, a.gen_nbfilters, a.gen_nbcnnlayers
+        SF = S * Fl
+        o.gemm(pl['dd'], p['c.out.kernel'], pl['dp'][2], transB=True, aux=pl['p'][2])
+        o.gemm(pl['dp'][2], p['c.post.fc2.kernel'], pl['dp'][1], transB=True, aux=pl['p'][1])
+        o.gemm(pl['dp'][1], p['c.post.fc1.kernel'], pl['dp'][0], transB=True, aux=pl['p'][0])
+        o.gemm(pl['dp'][0], p['c.post.fc0.kernel'][:SF], pl['da'][L - 1].view(nM, SF), transB=True,
+               aux=pl['a'][L - 1].view(nM, SF))
+        for i in range(L - 1, -1, -1):
+            o.conv2d_flip(p['c.spec.cnn%d.kernel' % i], pl['wflip'][i])
+        for i in range(L - 1, 0, -1):
+            o.conv2d(pl['da'][i], pl['wflip'][i], pl['da'][i - 1], aux=pl['a'][i - 1])
+        src = pl['da'][0] if g_rows is None else pl['da'][0][g_rows]
+        o.conv2d(src, pl['wflip'][0], g_out, flags=EPI_ACCUM if accumulate else 0)
+
+    def tangent_forward(self, pl, rows):
+        """Forward-mode sweep of the linearised critic (LeakyReLU masks frozen) on the applications `rows`, whose
+        input tangent has been written over pl['s0'][rows].  The tangents overwrite the stored activations of those
+        rows in place, so that param_grads() sees [a | a | tangent] as one batched layer input."""
+        o, a, p = self.ops, self.a, self.params.p
+        T = pl['T']
+        S, Fl, L = a.spec_size, a.gen_nbfilters, a.gen_nbcnnlayers
+        SF = S * Fl
+        tmap = pl['s0'][rows]
+        n = tmap.shape[0] * T
+        r2 = slice(rows.start * T, rows.stop * T)
+        for i in range(L):
+            y = pl['a'][i][rows]
+            o.conv2d(tmap, p['c.spec.cnn%d.kernel' % i], y, aux=y)
+            tmap = y
+        o.gemm(tmap.view(n, SF), p['c.post.fc0.kernel'][:SF], pl['p'][0][r2], aux=pl['p'][0][r2])
+        for i in (1, 2):
+            o.gemm(pl['p'][i - 1][r2], p['c.post.fc%d.kernel' % i], pl['p'][i][r2], aux=pl['p'][i][r2])
+
+    def param_grads(self, pl, first_order_apps=2):
+        """Gradients of every critic parameter from the stored layer inputs (activations, or tangents on the GP rows)
+        and pre-activation gradients.  Kernels use all napp applications; biases and the ctx branch only the first
+        `first_order_apps` (the gradient penalty reaches neither: optimizertts_wgan.py:57-68 differentiates through
+        piecewise-constant masks)."""
+        o, a, p, g = self.ops, self.a, self.params.p, self.params.g
+        B, T, M, nM = pl['B'], pl['T'], pl['M'], pl['nM']
+        H, S, Fl, W, L = a.hiddenwidth, a.spec_size, a.gen_nbfilters, a.ctx_winlen, a.gen_nbcnnlayers
+        SF = S * Fl
+        fM = first_order_apps * M
+        for i in range(L):
+            ain = pl['a'][i - 1] if i > 0 else pl['s0']
+            o.conv2d_wgrad(ain, pl['da'][i], g['c.spec.cnn%d.kernel' % i])
+            o.colsum(pl['da'][i].view(nM * S, Fl)[:fM * S], g['c.spec.cnn%d.bias' % i])
+        o.gemm(pl['a'][L - 1].view(nM, SF), pl['dp'][0], g['c.post.fc0.kernel'][:SF], transA=True)
+        for i in (1, 2):
+            o.gemm(pl['p'][i - 1], pl['dp'][i], g['c.post.fc%d.kernel' % i], transA=True)
+            o.colsum(pl['dp'][i][:fM], g['c.post.fc%d.bias' % i])
+        o.gemm(pl['p'][2], pl['dd'], g['c.out.kernel'], transA=True)
+        o.colsum(pl['dd'][:fM], g['c.out.bias'])
+        # ctx branch: its term enters the first post layer of every first-order application
+        dct = pl['dct']
+        if first_order_apps == 1:
+            o.copy2d(dct, pl['dp'][0][:M])
+        else:
+            o.add(dct, pl['dp'][0][:M], pl['dp'][0][M:2 * M])
+            for k in range(2, first_order_apps):
+                o.copy2d(dct, pl['dp'][0][k * M:(k + 1) * M], accumulate=True)
+        o.colsum(dct, g['c.post.fc0.bias'])
+        o.gemm(pl['ctx_last'], dct, g['c.post.fc0.kernel'][SF:], transA=True)
+        dcur = pl['dcA']
+        o.gemm(dct, p['c.post.fc0.kernel'][SF:], dcur, transB=True, aux=pl['fc_y'][1])
+        for i in (1, 0):
+            if i > 0:
+                xin = pl['fc_y'][0]
+            else:
+                xin = pl['ctx_y'][-1] if a.ctx_nbcnnlayers > 0 else pl['ctx_in'].view(M, -1)
+            o.gemm(xin, dcur, g['c.ctx.fc%d.kernel' % i], transA=True)
+            o.colsum(dcur, g['c.ctx.fc%d.bias' % i])
+            if i > 0 or a.ctx_nbcnnlayers > 0:
+                dnext = pl['dcB'] if dcur is pl['dcA'] else pl['dcA']
+                o.gemm(dcur, p['c.ctx.fc%d.kernel' % i], dnext, transB=True, aux=xin)
+                dcur = dnext
+        left = (W - 1) // 2
+        for i in range(a.ctx_nbcnnlayers - 1, -1, -1):
+            o.gemm(_im2col_view(pl['ctx_xp'][i], T, W), dcur, g['c.ctx.cnn%d.kernel' % i].view(-1, H), transA=True)
+            o.colsum(dcur, g['c.ctx.cnn%d.bias' % i])
+            if i > 0:
+                o.pad_time(pl['ctx_dzp'], dcur.view(B, T, H), W - 1 - left, left)
+                o.conv2d_flip(p['c.ctx.cnn%d.kernel' % i].view(W, 1, H, H), pl['ctx_kflip'])
+                dnext = pl['dcB'] if dcur is pl['dcA'] else pl['dcA']
+                o.gemm(_im2col_view(pl['ctx_dzp'], T, W), pl['ctx_kflip'].view(W * H, H), dnext, aux=pl['ctx_y'][i - 1])
+                dcur = dnext

@@ -1,0 +1,319 @@
+"""
+Tensor-level wrappers around the C ABI of libpctts.so (include/pctts.h).
+
+Every method takes torch CUDA tensors (used only as typed device memory), derives raw pointers / leading dimensions
+from the views, and launches the hand-written sm_100a kernel on torch's current CUDA stream.  No method has a
+PyTorch or CPU fallback: constructing `CudaOps` without a B200 and a built libpctts.so raises.
+
+The engine (percivaltts_b200/engine.py) is written against this interface; tests/cpu_ops_double.py implements the
+same interface with plain torch on the CPU *for testing the host logic only* (it is not importable from the package).
+"""
+import torch
+
+from . import _lib
+
+EPI_BIAS, EPI_LRELU, EPI_SIGMOID, EPI_DLRELU_AUX, EPI_ACCUM, EPI_ATOMIC, EPI_ADDMOD = 1, 2, 4, 8, 16, 32, 64
+
+
+def _mat(t):
+    """(ptr, ld, seg, segstride, rows, cols) of a 2-D [R,C] or segmented 3-D [S,R,C] fp32 view, unit inner stride."""
+    assert t.dtype == torch.float32, t.dtype
+    if t.dim() == 2:
+        R, C = t.shape
+        assert C == 1 or t.stride(1) == 1, ('inner stride', t.stride())
+        ld = t.stride(0) if R > 1 else max(C, 1)
+        return t.data_ptr(), ld, 0, 0, R, C
+    assert t.dim() == 3, t.shape
+    S, R, C = t.shape
+    assert C == 1 or t.stride(2) == 1, ('inner stride', t.stride())
+    ld = t.stride(1) if R > 1 else max(C, 1)
+    return t.data_ptr(), ld, R, t.stride(0), S * R, C
+
+
+def _map4(t):
+    """(ptr, batch stride, row pitch) of an NHWC map view [N,T,F,C] whose (F,C) plane is dense."""
+    assert t.dtype == torch.float32 and t.dim() == 4, (t.dtype, t.shape)
+    N, T, F, C = t.shape
+    assert (C == 1 or t.stride(3) == 1) and (F == 1 or t.stride(2) == C), ('map strides', t.shape, t.stride())
+    return t.data_ptr(), t.stride(0), t.stride(1)
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+class ReduceWorkspace(object):
+    """Scratch of the deterministic two-stage column reductions; `sums` is the fp64 [2,C] result (all-reducible)."""
+
+    def __init__(self, lib, rows, C, device):
+        nbytes = lib.pctts_colreduce_workspace_bytes(rows, C)
+        self.buf = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+        off = lib.pctts_colreduce_sums_ptr(self.buf.data_ptr(), rows, C) - self.buf.data_ptr()
+        self.sums = self.buf[off:off + 16 * C].view(torch.float64).view(2, C)
+        self.rows, self.C = rows, C
+
+    @property
+    def ptr(self):
+        return self.buf.data_ptr()
+
+
+class CudaOps(object):
+    name = 'cuda'
+
+    def __init__(self, device=None):
+        if not torch.cuda.is_available():
+            raise _lib.PcttsError('percivaltts_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback')
+        self.lib = _lib.load()
+        self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
+        _lib.check(self.lib.pctts_device_check(self.device.index or 0), 'pctts_device_check')
+        self._red = {}
+        self._wg = {}
+        self._lse_ws = None
+        self.launches = 0          # number of C-ABI kernel-launching calls (reset by the caller)
+
+    # -- helpers ---------------------------------------------------------------------------------------------
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _ck(self, rc, what):
+        self.launches += 1
+        _lib.check(rc, what)
+
+    def reduce_ws(self, rows, C):
+        key = (int(rows), int(C))
+        ws = self._red.get(key)
+        if ws is None:
+            ws = self._red[key] = ReduceWorkspace(self.lib, key[0], key[1], self.device)
+        return ws
+
+    def empty(self, *shape, dtype=torch.float32):
+        return torch.empty(*shape, dtype=dtype, device=self.device)
+
+    def zeros(self, *shape, dtype=torch.float32):
+        return torch.zeros(*shape, dtype=dtype, device=self.device)
+
+    # -- dense contractions ----------------------------------------------------------------------------------
+    def gemm(self, A, B, C, transA=False, transB=False, alpha=1.0, bias=None, aux=None, addmod=None, flags=0):
+        """C = epilogue(alpha * op(A) op(B)); A/B/C are 2-D or segmented 3-D views (see _mat)."""
+        pa, lda, sa, ssa, ra, ca = _mat(A)
+        pb, ldb, sb, ssb, rb, cb = _mat(B)
+        pc, ldc, sc, ssc, rc_, cc = _mat(C)
+        M, K = (ca, ra) if transA else (ra, ca)
+        Kb, N = (cb, rb) if transB else (rb, cb)
+        assert K == Kb and rc_ == M and cc == N, ('gemm shapes', A.shape, B.shape, C.shape, transA, transB)
+        addrows = 0
+        if bias is not None:
+            flags |= EPI_BIAS
+            assert bias.numel() == N and bias.is_contiguous()
+        if aux is not None:
+            flags |= EPI_DLRELU_AUX
+            pa2, ldx, sx, ssx, rx, cx = _mat(aux)
+            assert (ldx, sx, ssx, rx, cx) == (ldc, sc, ssc, rc_, cc), 'aux must share the addressing of C'
+        if addmod is not None:
+            flags |= EPI_ADDMOD
+            assert addmod.dim() == 2 and addmod.shape[1] == N and addmod.is_contiguous()
+            addrows = addmod.shape[0]
+        self._ck(self.lib.pctts_gemm_f32(int(transA), int(transB), M, N, K, float(alpha), pa, lda, sa, ssa, pb, ldb, sb, ssb,
+                                         pc, ldc, sc, ssc, _ptr(bias), _ptr(aux), _ptr(addmod), addrows, flags,
+                                         self._stream()), 'pctts_gemm_f32')
+
+    # -- 2-D convolutions ------------------------------------------------------------------------------------
+    def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0):
+        """y = epilogue(conv2d_same(x, w)); x [N,T,F,Cin], w [KH,KW,Cin,Cout] contiguous, y/aux [N,T,F,Cout] views."""
+        N, T, F, CIN = x.shape
+        KH, KW, ci, COUT = w.shape
+        assert ci == CIN and tuple(y.shape) == (N, T, F, COUT) and w.is_contiguous()
+        pad_t, pad_f = ((KH - 1) // 2, (KW - 1) // 2) if pad is None else pad
+        px, xb, xp = _map4(x)
+        py, yb, yp = _map4(y)
+        pa, ab, ap = (None, 0, 0)
+        if bias is not None:
+            flags |= EPI_BIAS
+        if aux is not None:
+            flags |= EPI_DLRELU_AUX
+            assert tuple(aux.shape) == tuple(y.shape)
+            pa, ab, ap = _map4(aux)
+        self._ck(self.lib.pctts_conv2d_fwd(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
+                                           xp, yp, ap, xb, yb, ab, flags, self._stream()), 'pctts_conv2d_fwd')
+
+    def conv2d_flip(self, w, wt):
+        KH, KW, CIN, COUT = w.shape
+        assert tuple(wt.shape) == (KH, KW, COUT, CIN) and w.is_contiguous() and wt.is_contiguous()
+        self._ck(self.lib.pctts_conv2d_flip_weights(w.data_ptr(), wt.data_ptr(), KH, KW, CIN, COUT, self._stream()),
+                 'pctts_conv2d_flip_weights')
+
+    def conv2d_wgrad(self, x, dy, dw, scale=1.0, accumulate=False, pad=None):
+        N, T, F, CIN = x.shape
+        KH, KW, ci, COUT = dw.shape
+        assert ci == CIN and tuple(dy.shape) == (N, T, F, COUT) and dw.is_contiguous()
+        pad_t, pad_f = ((KH - 1) // 2, (KW - 1) // 2) if pad is None else pad
+        key = (N, T, CIN, COUT, KH, KW)
+        ws = self._wg.get(key)
+        if ws is None:
+            ws = self._wg[key] = self.empty(self.lib.pctts_conv2d_wgrad_workspace(*key))
+        px, xb, xp = _map4(x)
+        pd, db, dp = _map4(dy)
+        self._ck(self.lib.pctts_conv2d_wgrad(px, pd, dw.data_ptr(), ws.data_ptr(), N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
+                                             xp, dp, xb, db, float(scale), int(accumulate), self._stream()),
+                 'pctts_conv2d_wgrad')
+
+    # -- batch normalisation ---------------------------------------------------------------------------------
+    def bn_stats(self, x):
+        """-> ReduceWorkspace whose .sums = [sum x, sum x^2] over the rows of the contiguous [rows, C] tensor x."""
+        rows, C = x.shape
+        assert x.is_contiguous()
+        ws = self.reduce_ws(rows, C)
+        self._ck(self.lib.pctts_bn_stats(x.data_ptr(), rows, C, ws.ptr, self._stream()), 'pctts_bn_stats')
+        return ws
+
+    def bn_finalize(self, ws, count, eps, momentum, mean, invstd, moving_mean=None, moving_var=None):
+        self._ck(self.lib.pctts_bn_finalize(ws.ptr, ws.rows, ws.C, float(count), float(eps), float(momentum), mean.data_ptr(),
+                                            invstd.data_ptr(), _ptr(moving_mean), _ptr(moving_var), self._stream()),
+                 'pctts_bn_finalize')
+
+    def bn_apply(self, x, y, mean, invstd_or_var, gamma, beta, eps, use_var, lrelu):
+        rows, C = x.shape
+        assert x.is_contiguous() and y.is_contiguous()
+        self._ck(self.lib.pctts_bn_apply(x.data_ptr(), y.data_ptr(), mean.data_ptr(), invstd_or_var.data_ptr(),
+                                         gamma.data_ptr(), beta.data_ptr(), rows, C, float(eps), int(use_var), int(lrelu),
+                                         self._stream()), 'pctts_bn_apply')
+
+    def bn_bwd_reduce(self, x, dy, mean, invstd, gamma, beta, lrelu):
+        rows, C = x.shape
+        assert x.is_contiguous() and dy.is_contiguous()
+        ws = self.reduce_ws(rows, C)
+        self._ck(self.lib.pctts_bn_bwd_reduce(x.data_ptr(), dy.data_ptr(), mean.data_ptr(), invstd.data_ptr(), gamma.data_ptr(),
+                                              beta.data_ptr(), rows, C, int(lrelu), ws.ptr, self._stream()),
+                 'pctts_bn_bwd_reduce')
+        return ws
+
+    def bn_bwd_apply(self, ws, x, dy, dx, mean, invstd, gamma, beta, count, lrelu, dgamma, dbeta, grad_scale=1.0,
+                     accumulate=False):
+        rows, C = x.shape
+        assert dx.is_contiguous()
+        self._ck(self.lib.pctts_bn_bwd_apply(x.data_ptr(), dy.data_ptr(), dx.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                                             gamma.data_ptr(), beta.data_ptr(), rows, C, float(count), int(lrelu),
+                                             _ptr(dgamma), _ptr(dbeta), float(grad_scale), int(accumulate), ws.ptr,
+                                             self._stream()),
+                 'pctts_bn_bwd_apply')
+
+    def colsum(self, x, out, accumulate=False):
+        rows, C = x.shape
+        assert x.is_contiguous() and out.numel() == C
+        ws = self.reduce_ws(rows, C)
+        self._ck(self.lib.pctts_colsum(x.data_ptr(), rows, C, out.data_ptr(), int(accumulate), ws.ptr, self._stream()),
+                 'pctts_colsum')
+
+    # -- LSTM ------------------------------------------------------------------------------------------------
+    def lstm_fwd(self, zx, U, hout, gates=None, cstate=None, cluster_size=8, batch_chunk=2):
+        """zx/U/gates/cstate: lists with one entry per direction (1 or 2); hout [B,T,ndir*H]."""
+        ndir = len(zx)
+        B, T, H4 = zx[0].shape
+        H = H4 // 4
+        g = gates if gates is not None else [None] * ndir
+        c = cstate if cstate is not None else [None] * ndir
+        z1, u1, g1, c1 = (zx[1], U[1], g[1], c[1]) if ndir == 2 else (None, None, None, None)
+        for t in list(zx) + list(U):
+            assert t.is_contiguous()
+        assert hout.is_contiguous() and hout.shape[2] == ndir * H
+        self._ck(self.lib.pctts_lstm_fwd(zx[0].data_ptr(), _ptr(z1), U[0].data_ptr(), _ptr(u1), hout.data_ptr(), _ptr(g[0]),
+                                         _ptr(g1), _ptr(c[0]), _ptr(c1), B, T, H, ndir, hout.shape[2], cluster_size,
+                                         batch_chunk, self._stream()), 'pctts_lstm_fwd')
+
+    def lstm_bwd(self, dhout, U, gates, cstate, dz, cluster_size=8, batch_chunk=2):
+        ndir = len(U)
+        B, T, H4 = gates[0].shape
+        H = H4 // 4
+        u1, g1, c1, d1 = (U[1], gates[1], cstate[1], dz[1]) if ndir == 2 else (None, None, None, None)
+        assert dhout.is_contiguous()
+        self._ck(self.lib.pctts_lstm_bwd(dhout.data_ptr(), U[0].data_ptr(), _ptr(u1), gates[0].data_ptr(), _ptr(g1),
+                                         cstate[0].data_ptr(), _ptr(c1), dz[0].data_ptr(), _ptr(d1), B, T, H, ndir,
+                                         dhout.shape[2], cluster_size, batch_chunk, self._stream()), 'pctts_lstm_bwd')
+
+    # -- WGAN-GP pieces --------------------------------------------------------------------------------------
+    def critic_pack_inputs(self, real, fake, alpha, s0, S, off):
+        B, T, O = real.shape
+        assert real.is_contiguous() and fake.is_contiguous() and s0.is_contiguous() and tuple(s0.shape) == (3 * B, T, S)
+        self._ck(self.lib.pctts_critic_pack_inputs(real.data_ptr(), fake.data_ptr(), alpha.data_ptr(), s0.data_ptr(), B, T, O, S,
+                                                   off, self._stream()), 'pctts_critic_pack_inputs')
+
+    def fill_segments(self, p, n0, v0, n1=0, v1=0.0, n2=0, v2=0.0):
+        assert p.is_contiguous() and p.numel() == n0 + n1 + n2
+        self._ck(self.lib.pctts_fill_segments(p.data_ptr(), n0, float(v0), n1, float(v1), n2, float(v2), self._stream()),
+                 'pctts_fill_segments')
+
+    def sum_scaled(self, x, scale, losses, slot):
+        assert x.is_contiguous()
+        self._ck(self.lib.pctts_sum_scaled(x.data_ptr(), x.numel(), float(scale), losses.data_ptr(), slot, self._stream()),
+                 'pctts_sum_scaled')
+
+    def gp_norms(self, g, ss):
+        B = g.shape[0]
+        assert g.is_contiguous() and ss.numel() >= B
+        self._ck(self.lib.pctts_gp_norms(g.data_ptr(), B, g.numel() // B, ss.data_ptr(), self._stream()), 'pctts_gp_norms')
+
+    def gp_scale(self, g, ss, r0, lam, Bglobal, losses, slot):
+        B = g.shape[0]
+        assert g.is_contiguous() and r0.is_contiguous()
+        self._ck(self.lib.pctts_gp_scale(g.data_ptr(), ss.data_ptr(), r0.data_ptr(), B, g.numel() // B, float(lam), int(Bglobal),
+                                         losses.data_ptr(), slot, self._stream()), 'pctts_gp_scale')
+
+    def loss_combine(self, losses, out, a, ca, b=-1, cb=0.0, c=-1, cc=0.0):
+        self._ck(self.lib.pctts_loss_combine(losses.data_ptr(), out, a, float(ca), b, float(cb), c, float(cc), self._stream()),
+                 'pctts_loss_combine')
+
+    def lse_loss_grad(self, pred, real, w, dpred, scale_loss, scale_grad, losses, slot):
+        O = pred.shape[-1]
+        rows = pred.numel() // O
+        assert pred.is_contiguous() and real.is_contiguous() and (dpred is None or dpred.is_contiguous())
+        if self._lse_ws is None:
+            self._lse_ws = torch.zeros(self.lib.pctts_lse_workspace_bytes(), dtype=torch.uint8, device=self.device)
+        self._ck(self.lib.pctts_lse_loss_grad(pred.data_ptr(), real.data_ptr(), _ptr(w), _ptr(dpred), rows, O, float(scale_loss),
+                                              float(scale_grad), losses.data_ptr(), slot, self._lse_ws.data_ptr(),
+                                              self._stream()), 'pctts_lse_loss_grad')
+
+    def adam(self, p, g, m, v, lr, beta1, beta2, eps, step):
+        assert p.is_contiguous() and g.is_contiguous() and step.dtype == torch.int32
+        self._ck(self.lib.pctts_adam(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), float(lr), float(beta1),
+                                     float(beta2), float(eps), step.data_ptr(), self._stream()), 'pctts_adam')
+
+    # -- small movers ----------------------------------------------------------------------------------------
+    def add(self, out, a, b):
+        assert out.is_contiguous() and a.is_contiguous() and b.is_contiguous()
+        self._ck(self.lib.pctts_add(out.data_ptr(), a.data_ptr(), b.data_ptr(), out.numel(), self._stream()), 'pctts_add')
+
+    def sigmoid_bwd(self, dy, y, dz):
+        rows, cols = dy.shape
+        self._ck(self.lib.pctts_sigmoid_bwd(dy.data_ptr(), dy.stride(0), y.data_ptr(), y.stride(0), dz.data_ptr(), dz.stride(0),
+                                            rows, cols, self._stream()), 'pctts_sigmoid_bwd')
+
+    def copy2d(self, dst, src, accumulate=False):
+        rows, cols = dst.shape
+        assert tuple(src.shape) == (rows, cols)
+        self._ck(self.lib.pctts_copy2d(dst.data_ptr(), dst.stride(0), src.data_ptr(), src.stride(0), rows, cols, int(accumulate),
+                                       self._stream()), 'pctts_copy2d')
+
+    def pad_time(self, dst, src, left, right):
+        B, T, C = src.shape
+        assert dst.is_contiguous() and src.is_contiguous() and tuple(dst.shape) == (B, T + left + right, C)
+        self._ck(self.lib.pctts_pad_time(dst.data_ptr(), src.data_ptr(), B, T, C, left, right, self._stream()), 'pctts_pad_time')
+
+    def uniform(self, out, seed, counter):
+        assert counter.dtype == torch.int64
+        self._ck(self.lib.pctts_uniform(out.data_ptr(), out.numel(), int(seed), counter.data_ptr(), self._stream()),
+                 'pctts_uniform')
+
+    # -- PML band compression --------------------------------------------------------------------------------
+    def pml_linbnd2fwbnd(self, x, idx, wgt, out, log_abs):
+        T, nbins = x.shape
+        K = out.shape[1]
+        assert x.is_contiguous() and out.is_contiguous() and idx.dtype == torch.int32
+        self._ck(self.lib.pctts_pml_linbnd2fwbnd(x.data_ptr(), idx.data_ptr(), wgt.data_ptr(), out.data_ptr(), T, nbins, K,
+                                                 int(log_abs), self._stream()), 'pctts_pml_linbnd2fwbnd')
+
+    def pml_fwbnd2linbnd(self, x, idx, wgt, out, smooth, do_exp):
+        T, K = x.shape
+        nbins = out.shape[1]
+        assert x.is_contiguous() and out.is_contiguous() and idx.dtype == torch.int32
+        self._ck(self.lib.pctts_pml_fwbnd2linbnd(x.data_ptr(), idx.data_ptr(), wgt.data_ptr(), out.data_ptr(), T, K, nbins,
+                                                 int(smooth), int(do_exp), self._stream()), 'pctts_pml_fwbnd2linbnd')

@@ -1,0 +1,168 @@
+"""
+Device-side WGAN-GP step: the two compiled Keras graphs of OptimizerTTSWGAN.prepare()
+(reference percivaltts/optimizertts_wgan.py:107-213) restated as explicit kernel schedules, plus the
+train_on_batch() policy (:216-241).
+
+  critic step      loss = mean(-D(real)) + mean(+D(fake)) + lambda * mean_b (1 - ||dD(xhat)/dxhat||_2)^2      (:131-154)
+  generator step   loss = mean(w_wgan) * mean(-D(G(ctx))) + mean((y - G(ctx))^2 * w_ls)   ('WLSWGAN', :180-213)
+                   loss = mean(-D(G(ctx)))                                                 ('WGAN',    :174-178)
+
+Data parallel: every rank holds `B` utterances of the global batch; all means are over the global batch (local sums
+are scaled by 1/global count and the flat gradient buffers are all-reduced with SUM before Adam).
+"""
+import numpy as np
+import torch
+
+from . import arch as A
+from .engine import Generator, Critic, LocalSync
+
+# slots of the device loss vector
+L_REAL, L_FAKE, L_GP, L_CRITIC, L_GW, L_GLS, L_GEN = 0, 1, 2, 3, 4, 5, 6
+NLOSS = 8
+
+
+def critic_runs(generator_updates):
+    """optimizertts_wgan.py:225-228"""
+    return 10 if (generator_updates < 25 or generator_updates % 500 == 0) else 5
+
+
+class WGANStepper(object):
+    def __init__(self, ops, arch, generator=None, critic=None, errtype='WLSWGAN', sync=None,
+                 critic_lr=1e-4, critic_beta1=0.5, critic_beta2=0.9, gen_lr=1e-3, gen_beta1=0.5, gen_beta2=0.9,
+                 gp_lambda=10.0, w_ls=None, w_wgan_mean=1.0, adam_eps=1e-7, seed=123):
+        if errtype not in ('WGAN', 'WLSWGAN'):
+            raise ValueError('unknown errtype ' + str(errtype))
+        self.ops, self.a, self.errtype = ops, arch, errtype
+        self.sync = sync or LocalSync()
+        self.G = generator or Generator(ops, arch)
+        self.C = critic or Critic(ops, arch)
+        self.copt = (critic_lr, critic_beta1, critic_beta2)
+        self.gopt = (gen_lr, gen_beta1, gen_beta2)
+        self.adam_eps = adam_eps
+        self.lam = float(gp_lambda)
+        self.wbar = float(w_wgan_mean)
+        self.w_ls = None
+        if errtype == 'WLSWGAN':
+            if w_ls is None:
+                raise ValueError('WLSWGAN needs the LSE weight vector')
+            self.w_ls = ops.zeros(arch.outsize)
+            self.w_ls.copy_(torch.as_tensor(np.asarray(w_ls, dtype=np.float64)).to(self.w_ls.dtype))
+        self.losses = ops.zeros(NLOSS)
+        self.seed = int(seed) + 7919 * self.sync.rank     # independent alpha streams per replica
+        self.counter = ops.zeros(1, dtype=torch.int64)
+        self._bufs = {}
+
+    def buffers(self, B, T):
+        key = (B, T)
+        b = self._bufs.get(key)
+        if b is None:
+            o, a = self.ops, self.a
+            b = self._bufs[key] = dict(
+                fake=o.empty(B, T, a.outsize), s0=o.empty(3 * B, T, a.spec_size), alpha=o.zeros(B),
+                g=o.empty(B, T, a.spec_size, 1), ss=o.zeros(B), dpred=o.empty(B, T, a.outsize))
+        return b
+
+    # ------------------------------------------------------------------------------------------------------------
+    def critic_step(self, X, Y, alpha=None, apply=True):
+        """One critic update on device tensors X [B,T,ctx], Y [B,T,O].  alpha [B] overrides the random
+        interpolation weights (RandomWeightedAverage, optimizertts_wgan.py:44-51)."""
+        o, a, sync = self.ops, self.a, self.sync
+        B, T, _ = X.shape
+        M, S = B * T, a.spec_size
+        bf = self.buffers(B, T)
+        gpl = self.G.plan(B, T)
+        # frozen generator, learning phase 1: batch statistics, no moving-average update (:121-128)
+        self.G.forward(gpl, X, bf['fake'], training=True, update_stats=False, sync=sync)
+        if alpha is None:
+            o.uniform(bf['alpha'], self.seed, self.counter)
+            alpha = bf['alpha']
+        o.critic_pack_inputs(Y, bf['fake'], alpha, bf['s0'], S, 1)
+        cpl = self.C.plan(3, B, T)
+        s0 = bf['s0'].view(3 * B, T, S, 1)
+        d = self.C.forward(cpl, s0, X)
+        ng = float(M * sync.world)
+        o.sum_scaled(d[0:M], -1.0 / ng, self.losses, L_REAL)          # wasserstein_loss with y_true = -1 (:152)
+        o.sum_scaled(d[M:2 * M], 1.0 / ng, self.losses, L_FAKE)       # y_true = +1 (:153)
+        # d(objective)/d(D): -1/N on real rows, +1/N on fake rows; the interpolated rows carry K.gradients' implicit
+        # all-ones seed of sum(D(xhat)) (:57)
+        o.fill_segments(cpl['dd'].view(-1), M, -1.0 / ng, M, 1.0 / ng, M, 1.0)
+        rows = slice(2 * B, 3 * B)
+        self.C.backward_to_input(cpl, bf['g'], g_rows=rows)
+        o.gp_norms(bf['g'].view(B, T * S), bf['ss'])                   # ||g_b||^2 (:59-64)
+        # tangent seed = lambda * d(mean_b (1-||g_b||)^2)/dg, written over the (no longer needed) xhat rows of s0
+        o.gp_scale(bf['g'].view(B, T * S), bf['ss'], bf['s0'][rows].view(B, T * S), self.lam, B * sync.world, self.losses, L_GP)
+        self.C.tangent_forward(cpl, rows)
+        self.C.param_grads(cpl, first_order_apps=2)
+        o.loss_combine(self.losses, L_CRITIC, L_REAL, 1.0, L_FAKE, 1.0, L_GP, self.lam)   # loss_weights [1,1,lambda] (:150)
+        if apply:
+            sync.allreduce(self.C.params.grad)
+            self.C.params.adam(*self.copt, eps=self.adam_eps)
+
+    def generator_step(self, X, Y, apply=True):
+        """One generator update (BN moving statistics move here, like in the reference's generator_model)."""
+        o, a, sync = self.ops, self.a, self.sync
+        B, T, _ = X.shape
+        M, S, O = B * T, a.spec_size, a.outsize
+        bf = self.buffers(B, T)
+        gpl = self.G.plan(B, T)
+        pred = bf['fake']
+        self.G.forward(gpl, X, pred, training=True, update_stats=True, sync=sync)
+        cpl = self.C.plan(1, B, T)
+        d = self.C.forward(cpl, pred[:, :, 1:1 + S].unsqueeze(-1), X)
+        ng = float(M * sync.world)
+        o.sum_scaled(d, -1.0 / ng, self.losses, L_GW)
+        dpred = bf['dpred']
+        if self.errtype == 'WLSWGAN':
+            o.lse_loss_grad(pred, Y, self.w_ls, dpred, 1.0 / (ng * O), 1.0 / (ng * O), self.losses, L_GLS)   # (:73-79)
+            o.loss_combine(self.losses, L_GEN, L_GW, self.wbar, L_GLS, 1.0)                                  # (:213)
+            seed = -self.wbar / ng
+        else:
+            o.fill_segments(dpred.view(-1), dpred.numel(), 0.0)
+            o.loss_combine(self.losses, L_GEN, L_GW, 1.0)
+            seed = -1.0 / ng
+        o.fill_segments(cpl['dd'].view(-1), M, seed)
+        self.C.backward_to_input(cpl, dpred[:, :, 1:1 + S].unsqueeze(-1), accumulate=True)
+        self.G.backward(gpl, pred, dpred, sync=sync)
+        if apply:
+            sync.allreduce(self.G.params.grad)
+            self.G.params.adam(*self.gopt, eps=self.adam_eps)
+
+    def evaluate_losses(self, X, Y, alpha=None):
+        """Critic and generator objectives on one batch in inference mode (BN moving statistics), no update:
+        what critic_model.evaluate / generator_model.evaluate return in update_validation_cost (:244-262)."""
+        o, a = self.ops, self.a
+        B, T, _ = X.shape
+        M, S, O = B * T, a.spec_size, a.outsize
+        bf = self.buffers(B, T)
+        gpl = self.G.plan(B, T)
+        nosync = LocalSync()
+        self.G.forward(gpl, X, bf['fake'], training=False, sync=nosync)
+        if alpha is None:
+            o.uniform(bf['alpha'], self.seed, self.counter)
+            alpha = bf['alpha']
+        o.critic_pack_inputs(Y, bf['fake'], alpha, bf['s0'], S, 1)
+        cpl = self.C.plan(3, B, T)
+        d = self.C.forward(cpl, bf['s0'].view(3 * B, T, S, 1), X)
+        ng = float(M)
+        o.sum_scaled(d[0:M], -1.0 / ng, self.losses, L_REAL)
+        o.sum_scaled(d[M:2 * M], 1.0 / ng, self.losses, L_FAKE)
+        o.sum_scaled(d[M:2 * M], -1.0 / ng, self.losses, L_GW)
+        o.fill_segments(cpl['dd'].view(-1), M, 0.0, M, 0.0, M, 1.0)
+        rows = slice(2 * B, 3 * B)
+        self.C.backward_to_input(cpl, bf['g'], g_rows=rows)
+        o.gp_norms(bf['g'].view(B, T * S), bf['ss'])
+        o.gp_scale(bf['g'].view(B, T * S), bf['ss'], bf['s0'][rows].view(B, T * S), self.lam, B, self.losses, L_GP)
+        o.loss_combine(self.losses, L_CRITIC, L_REAL, 1.0, L_FAKE, 1.0, L_GP, self.lam)
+        if self.errtype == 'WLSWGAN':
+            o.lse_loss_grad(bf['fake'], Y, self.w_ls, None, 1.0 / (ng * O), 0.0, self.losses, L_GLS)
+            o.loss_combine(self.losses, L_GEN, L_GW, self.wbar, L_GLS, 1.0)
+        else:
+            o.loss_combine(self.losses, L_GEN, L_GW, 1.0)
+
+    def predict(self, X, out=None):
+        """Generator inference forward (BN moving statistics): ModelTTS.predict (modeltts.py:68-69)."""
+        B, T, _ = X.shape
+        gpl = self.G.plan(B, T, with_backward=False)
+        if out is None:
+            out = self.ops.empty(B, T, self.a.outsize)
+        return self.G.forward(gpl, X, out, training=False, sync=LocalSync())
