@@ -33,6 +33,8 @@ extern "C" {
 int pctts_abi_version(void);
 /* 0 when device `dev` is compute capability 10.x (B200); else PCTTS_EUNSUPPORTED / cudaError. Host call. */
 int pctts_device_check(int dev);
+/* number of kernels this library has launched (or recorded into a CUDA graph under capture) so far. Host call. */
+long pctts_launch_count(void);
 
 /* ---- dense contractions: keras Dense (networktts.py:59-63,196-197), Conv1D as virtual-im2col GEMM (networktts.py:116-120),
  *      LSTM input projections (networktts.py:90-94), and all their data / weight gradients ------------------------------- */
@@ -44,6 +46,14 @@ int pctts_gemm_f32(int transA, int transB, int M, int N, int K, float alpha,
                    float* C, long ldc, int segC, long segstrideC,
                    const float* bias, const float* aux, const float* addmod, int addrows,
                    int flags, void* stream);
+
+/* Split-K form for long reductions with few output tiles (weight gradients dW = X^T dZ: M,N ~ 256, K = B*T rows).
+ * `workspace` holds splits*M*N floats; flags: 0 or PCTTS_EPI_ACCUM; two-stage, deterministic. */
+int pctts_gemm_splitk_f32(int transA, int transB, int M, int N, int K, float alpha,
+                          const float* A, long lda, int segA, long segstrideA,
+                          const float* B, long ldb, int segB, long segstrideB,
+                          float* C, long ldc, int segC, long segstrideC,
+                          int flags, int splits, float* workspace, void* stream);
 
 /* ---- Conv2D 'same', stride 1, NHWC, HWIO (networktts.py:122-126; modeltts_common.py:98,100; networks_critic.py:67) ------ */
 /* y[n,t,f,:] = epilogue(sum_{kt,kf,ci} x[n,t+kt-pad_t,f+kf-pad_f,ci] w[kt,kf,ci,:]).  xpitch/ypitch/auxpitch = floats between

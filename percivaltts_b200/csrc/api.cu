@@ -1,6 +1,11 @@
 // Library-level entry points of libpctts.so: ABI version and device capability check.
 #include "common.cuh"
 #include "pctts.h"
+#include <atomic>
+
+static std::atomic<long> g_launches{0};
+void pctts_note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+extern "C" long pctts_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 extern "C" int pctts_abi_version(void) { return PCTTS_ABI_VERSION; }
 

@@ -10,8 +10,12 @@
 #define PCTTS_EINVAL (-1)
 #define PCTTS_EUNSUPPORTED (-2)
 
+// every kernel launch of the library is counted (pctts_launch_count): evidence for bench.py's gpu_launches
+void pctts_note_launch();
+
 #define PCTTS_LAUNCH_CHECK()                          \
     do {                                              \
+        pctts_note_launch();                          \
         cudaError_t e__ = cudaGetLastError();         \
         if (e__ != cudaSuccess) return (int)e__;      \
     } while (0)

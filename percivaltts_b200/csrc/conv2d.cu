@@ -244,21 +244,21 @@ __global__ void conv2d_wgrad_generic(const float* __restrict__ x, const float* _
     }
 }
 
+// one warp per weight element: lanes stride over the per-CTA partials, butterfly sum in a fixed order
 __global__ void reduce_partials_kernel(const float* __restrict__ partial, float* __restrict__ out, int nblk, int NW,
                                        float scale, int accumulate) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
     if (i >= NW) return;
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-    int b = 0;
-    for (; b + 3 < nblk; b += 4) {
+    float s0 = 0.f, s1 = 0.f;
+    int b = lane;
+    for (; b + 32 < nblk; b += 64) {
         s0 += partial[(long)b * NW + i];
-        s1 += partial[(long)(b + 1) * NW + i];
-        s2 += partial[(long)(b + 2) * NW + i];
-        s3 += partial[(long)(b + 3) * NW + i];
+        s1 += partial[(long)(b + 32) * NW + i];
     }
-    for (; b < nblk; ++b) s0 += partial[(long)b * NW + i];
-    const float v = ((s0 + s1) + (s2 + s3)) * scale;
-    out[i] = accumulate ? out[i] + v : v;
+    if (b < nblk) s0 += partial[(long)b * NW + i];
+    const float v = warp_sum(s0 + s1) * scale;
+    if (lane == 0) out[i] = accumulate ? out[i] + v : v;
 }
 
 template <int CIN, int COUT, int KH, int KW>
@@ -357,7 +357,7 @@ extern "C" int pctts_conv2d_wgrad(const float* x, const float* dy, float* dw, fl
         rc = PCTTS_OK;
     }
     if (rc != PCTTS_OK) return rc;
-    reduce_partials_kernel<<<pctts_div_up(NW, 128), 128, 0, st>>>(workspace, dw, nblk, NW, scale, accumulate);
+    reduce_partials_kernel<<<pctts_div_up(NW, 8), 256, 0, st>>>(workspace, dw, nblk, NW, scale, accumulate);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

@@ -42,7 +42,8 @@ struct Epi {
 };
 
 template <bool TA, bool TB>
-__global__ void __launch_bounds__(NT) gemm_f32_kernel(int M, int N, int K, Mat A, Mat B, Mat C, Epi e) {
+__global__ void __launch_bounds__(NT) gemm_f32_kernel(int M, int N, int K, Mat A, Mat B, Mat C, Epi e, int kchunk,
+                                                       float* __restrict__ partial) {
     __shared__ __align__(16) float As[BK][BM + 4];
     __shared__ __align__(16) float Bs[BK][BN + 4];
     const int tid = threadIdx.x;
@@ -77,18 +78,21 @@ __global__ void __launch_bounds__(NT) gemm_f32_kernel(int M, int N, int K, Mat A
         }
     }
 
-    for (int k0 = 0; k0 < K; k0 += BK) {
+    // split-K: CTA z owns k in [z*kchunk, (z+1)*kchunk) and writes raw sums to partial[z][M][N] (kchunk % BK == 0)
+    const int kbeg = partial ? blockIdx.z * kchunk : 0;
+    const int kend = partial ? min(K, kbeg + kchunk) : K;
+    for (int k0 = kbeg; k0 < kend; k0 += BK) {
         float ra[8], rb[4];
         if (!TA) {
             const int k = k0 + (tid % 16);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) ra[i] = (a_ok[i] && k < K) ? __ldg(A.p + a_off[i] + k) : 0.f;
+            for (int i = 0; i < 8; ++i) ra[i] = (a_ok[i] && k < kend) ? __ldg(A.p + a_off[i] + k) : 0.f;
         } else {
             const int m = m0 + (tid % 128);
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 int k = k0 + tid / 128 + 2 * i;
-                ra[i] = (m < M && k < K) ? __ldg(A.p + row_off(A, k) + m) : 0.f;
+                ra[i] = (m < M && k < kend) ? __ldg(A.p + row_off(A, k) + m) : 0.f;
             }
         }
         if (!TB) {
@@ -96,12 +100,12 @@ __global__ void __launch_bounds__(NT) gemm_f32_kernel(int M, int N, int K, Mat A
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 int k = k0 + tid / 64 + 4 * i;
-                rb[i] = (n < N && k < K) ? __ldg(B.p + row_off(B, k) + n) : 0.f;
+                rb[i] = (n < N && k < kend) ? __ldg(B.p + row_off(B, k) + n) : 0.f;
             }
         } else {
             const int k = k0 + (tid % 16);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) rb[i] = (b_ok[i] && k < K) ? __ldg(B.p + b_off[i] + k) : 0.f;
+            for (int i = 0; i < 4; ++i) rb[i] = (b_ok[i] && k < kend) ? __ldg(B.p + b_off[i] + k) : 0.f;
         }
         __syncthreads();   // previous tile fully consumed
         if (!TA) {
@@ -133,6 +137,20 @@ __global__ void __launch_bounds__(NT) gemm_f32_kernel(int M, int N, int K, Mat A
         }
     }
 
+    if (partial) {
+        float* pz = partial + (long)blockIdx.z * M * N;
+#pragma unroll
+        for (int i = 0; i < TM; ++i) {
+            const int m = m0 + ty * TM + i;
+            if (m >= M) continue;
+#pragma unroll
+            for (int j = 0; j < TN; ++j) {
+                const int n = n0 + tx * TN + j;
+                if (n < N) pz[(long)m * N + n] = acc[i][j];
+            }
+        }
+        return;
+    }
     float* Cp = const_cast<float*>(C.p);
 #pragma unroll
     for (int i = 0; i < TM; ++i) {
@@ -159,15 +177,43 @@ __global__ void __launch_bounds__(NT) gemm_f32_kernel(int M, int N, int K, Mat A
     }
 }
 
-int launch(int ta, int tb, int M, int N, int K, Mat A, Mat B, Mat C, Epi e, cudaStream_t st) {
+// C = alpha * sum_z partial[z] (+ C when accumulating), fixed summation order => deterministic
+__global__ void splitk_reduce_kernel(const float* __restrict__ partial, int splits, int M, int N, Mat C, float alpha, int accum) {
+    const long total = (long)M * N;
+    float* Cp = const_cast<float*>(C.p);
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int z = 0; z < splits; ++z) s += partial[(long)z * total + i];
+        const int m = (int)(i / N), n = (int)(i - (long)m * N);
+        const long off = row_off(C, m) + n;
+        s *= alpha;
+        Cp[off] = accum ? Cp[off] + s : s;
+    }
+}
+
+int launch(int ta, int tb, int M, int N, int K, Mat A, Mat B, Mat C, Epi e, cudaStream_t st, int splits = 1,
+           float* partial = nullptr) {
     if (M <= 0 || N <= 0) return PCTTS_OK;
     if (K < 0) return PCTTS_EINVAL;
-    dim3 grid(pctts_div_up(N, BN), pctts_div_up(M, BM));
-    if (!ta && !tb) gemm_f32_kernel<false, false><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e);
-    else if (!ta && tb) gemm_f32_kernel<false, true><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e);
-    else if (ta && !tb) gemm_f32_kernel<true, false><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e);
-    else gemm_f32_kernel<true, true><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e);
+    int kchunk = K;
+    if (splits > 1) {
+        kchunk = ((K + splits - 1) / splits + BK - 1) / BK * BK;
+        splits = (K + kchunk - 1) / kchunk;
+    }
+    if (splits <= 1) partial = nullptr;
+    dim3 grid(pctts_div_up(N, BN), pctts_div_up(M, BM), partial ? splits : 1);
+    if (!ta && !tb) gemm_f32_kernel<false, false><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e, kchunk, partial);
+    else if (!ta && tb) gemm_f32_kernel<false, true><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e, kchunk, partial);
+    else if (ta && !tb) gemm_f32_kernel<true, false><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e, kchunk, partial);
+    else gemm_f32_kernel<true, true><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e, kchunk, partial);
     PCTTS_LAUNCH_CHECK();
+    if (partial) {
+        const long total = (long)M * N;
+        int blocks = pctts_div_up(total, 256);
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        splitk_reduce_kernel<<<blocks, 256, 0, st>>>(partial, splits, M, N, C, e.alpha, (e.flags & PCTTS_EPI_ACCUM) ? 1 : 0);
+        PCTTS_LAUNCH_CHECK();
+    }
     return PCTTS_OK;
 }
 
@@ -186,4 +232,19 @@ extern "C" int pctts_gemm_f32(int transA, int transB, int M, int N, int K, float
     Mat a{A, lda, segA, segstrideA}, b{B, ldb, segB, segstrideB}, c{C, ldc, segC, segstrideC};
     Epi e{bias, aux, addmod, addrows, flags, alpha};
     return launch(transA, transB, M, N, K, a, b, c, e, (cudaStream_t)stream);
+}
+
+
+// Split-K variant for long reductions with few output tiles (weight gradients: M,N ~ 256, K = B*T rows).
+// workspace holds splits*M*N floats; only alpha and PCTTS_EPI_ACCUM are applied (by the deterministic reduce pass).
+extern "C" int pctts_gemm_splitk_f32(int transA, int transB, int M, int N, int K, float alpha,
+                                     const float* A, long lda, int segA, long segstrideA,
+                                     const float* B, long ldb, int segB, long segstrideB,
+                                     float* C, long ldc, int segC, long segstrideC,
+                                     int flags, int splits, float* workspace, void* stream) {
+    if (!A || !B || !C || !workspace || splits < 1) return PCTTS_EINVAL;
+    if (flags & ~PCTTS_EPI_ACCUM) return PCTTS_EUNSUPPORTED;
+    Mat a{A, lda, segA, segstrideA}, b{B, ldb, segB, segstrideB}, c{C, ldc, segC, segstrideC};
+    Epi e{nullptr, nullptr, nullptr, 0, flags, alpha};
+    return launch(transA, transB, M, N, K, a, b, c, e, (cudaStream_t)stream, splits, workspace);
 }

@@ -264,6 +264,7 @@ int launch(bool bwd, const LstmArgs& a, int ndir, cudaStream_t st) {
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     PCTTS_CUDA(cudaLaunchKernelEx(&cfg, kern, a));
+    pctts_note_launch();
     return PCTTS_OK;
 }
 

@@ -45,12 +45,10 @@ __device__ __forceinline__ void red_terms(const RedArgs& a, long r, int c, doubl
     }
 }
 
-// sums[0][c], sums[1][c] (double) <- column reductions.  partial: [gridDim.x][2][C] doubles, counter: 1 uint (zeroed).
+// Stage 1: CTA b reduces its contiguous slab of rows and writes partial[b][2][C] (doubles).
 template <int MODE>
-__global__ void __launch_bounds__(RT) colreduce_kernel(RedArgs a, double* __restrict__ partial, double* __restrict__ sums,
-                                                       unsigned int* __restrict__ counter) {
+__global__ void __launch_bounds__(RT) colreduce_kernel(RedArgs a, double* __restrict__ partial) {
     __shared__ double s1[RT], s2[RT];
-    __shared__ bool is_last;
     const int C = a.C, tid = threadIdx.x;
     const int rpb = C >= RT ? 1 : RT / C;          // rows handled concurrently by one CTA
     const int cpt = C > RT ? (C + RT - 1) / RT : 1; // channels per thread (C > 256)
@@ -61,8 +59,18 @@ __global__ void __launch_bounds__(RT) colreduce_kernel(RedArgs a, double* __rest
         double q1 = 0.0, q2 = 0.0;
         const int c = (C >= RT) ? tid + cc * RT : tid % C;
         const int rl = (C >= RT) ? 0 : tid / C;
-        if (c < C && rl < rpb)
-            for (long r = r_begin + rl; r < r_end; r += rpb) red_terms<MODE>(a, r, c, q1, q2);
+        if (c < C && rl < rpb) {
+            // two independent chains for a little more memory-level parallelism
+            double p1 = 0.0, p2 = 0.0;
+            long r = r_begin + rl;
+            for (; r + rpb < r_end; r += 2 * rpb) {
+                red_terms<MODE>(a, r, c, q1, q2);
+                red_terms<MODE>(a, r + rpb, c, p1, p2);
+            }
+            if (r < r_end) red_terms<MODE>(a, r, c, q1, q2);
+            q1 += p1;
+            q2 += p2;
+        }
         s1[tid] = q1;
         s2[tid] = q2;
         __syncthreads();
@@ -80,24 +88,18 @@ __global__ void __launch_bounds__(RT) colreduce_kernel(RedArgs a, double* __rest
         }
         __syncthreads();
     }
-    __threadfence();
-    if (tid == 0) {
-        const unsigned int ticket = atomicAdd(counter, 1u);
-        is_last = (ticket == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    for (int c = tid; c < C; c += RT) {
-        double q1 = 0.0, q2 = 0.0;
-        for (unsigned int b = 0; b < gridDim.x; ++b) {
-            q1 += partial[((long)b * 2 + 0) * C + c];
-            q2 += partial[((long)b * 2 + 1) * C + c];
-        }
-        sums[c] = q1;
-        sums[C + c] = q2;
-    }
-    if (tid == 0) *counter = 0u;   // ready for the next launch / graph replay
+}
+
+// Stage 2: one warp per output element e in [0, 2C): lanes stride over the CTA partials, butterfly sum (fixed order).
+__global__ void __launch_bounds__(RT) colreduce_final_kernel(const double* __restrict__ partial, double* __restrict__ sums,
+                                                             int nblk, int C) {
+    const int e = blockIdx.x * (RT / 32) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (e >= 2 * C) return;
+    double q = 0.0;
+    for (int b = lane; b < nblk; b += 32) q += partial[(long)b * 2 * C + e];
+    q = warp_sum_d(q);
+    if (lane == 0) sums[e] = q;
 }
 
 // STATS finalize: mean / invstd from (possibly all-reduced) sums; optional moving-average update.
@@ -159,7 +161,7 @@ int reduce_grid(long rows, int C) {
     const int rpb = C >= RT ? 1 : RT / C;
     long want = (rows + (long)rpb * 8 - 1) / ((long)rpb * 8);   // >= 8 row-iterations per CTA
     if (want < 1) want = 1;
-    if (want > 148 * 4) want = 148 * 4;
+    if (want > 148 * 2) want = 148 * 2;
     return (int)want;
 }
 
@@ -183,6 +185,21 @@ Ws carve(void* workspace, long rows, int C) {
     w.counter = (unsigned int*)(w.sums + 2 * C);
     return w;
 }
+#define PCTTS_CUDA_RC(call)            \
+    do {                               \
+        int rc__ = (call);             \
+        if (rc__ != PCTTS_OK) return rc__; \
+    } while (0)
+
+template <int MODE>
+int run_colreduce(const RedArgs& a, const Ws& w, cudaStream_t st) {
+    const int grid = reduce_grid(a.rows, a.C);
+    colreduce_kernel<MODE><<<grid, RT, 0, st>>>(a, w.partial);
+    PCTTS_LAUNCH_CHECK();
+    colreduce_final_kernel<<<pctts_div_up(2 * a.C, RT / 32), RT, 0, st>>>(w.partial, w.sums, grid, a.C);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
 }  // namespace
 
 // Column sums of x and x^2 -> workspace sums (double [2][C]); the counter inside the workspace must start at 0
@@ -191,8 +208,7 @@ extern "C" int pctts_bn_stats(const float* x, long rows, int C, void* workspace,
     if (!x || !workspace || rows <= 0 || C <= 0) return PCTTS_EINVAL;
     Ws w = carve(workspace, rows, C);
     RedArgs a{x, nullptr, nullptr, nullptr, nullptr, nullptr, rows, C, 0};
-    colreduce_kernel<MODE_STATS><<<reduce_grid(rows, C), RT, 0, (cudaStream_t)stream>>>(a, w.partial, w.sums, w.counter);
-    PCTTS_LAUNCH_CHECK();
+    PCTTS_CUDA_RC(run_colreduce<MODE_STATS>(a, w, (cudaStream_t)stream));
     return PCTTS_OK;
 }
 
@@ -226,8 +242,7 @@ extern "C" int pctts_bn_bwd_reduce(const float* x, const float* dy, const float*
     if (!x || !dy || !mean || !invstd || !gamma || !beta || !workspace || rows <= 0) return PCTTS_EINVAL;
     Ws w = carve(workspace, rows, C);
     RedArgs a{x, dy, mean, invstd, gamma, beta, rows, C, lrelu};
-    colreduce_kernel<MODE_BNBWD><<<reduce_grid(rows, C), RT, 0, (cudaStream_t)stream>>>(a, w.partial, w.sums, w.counter);
-    PCTTS_LAUNCH_CHECK();
+    PCTTS_CUDA_RC(run_colreduce<MODE_BNBWD>(a, w, (cudaStream_t)stream));
     return PCTTS_OK;
 }
 
@@ -257,8 +272,7 @@ extern "C" int pctts_colsum(const float* x, long rows, int C, float* out, int ac
     Ws w = carve(workspace, rows, C);
     cudaStream_t st = (cudaStream_t)stream;
     RedArgs a{x, nullptr, nullptr, nullptr, nullptr, nullptr, rows, C, 0};
-    colreduce_kernel<MODE_COLSUM><<<reduce_grid(rows, C), RT, 0, st>>>(a, w.partial, w.sums, w.counter);
-    PCTTS_LAUNCH_CHECK();
+    PCTTS_CUDA_RC(run_colreduce<MODE_COLSUM>(a, w, st));
     sums_to_grads_kernel<<<pctts_div_up(C, 128), 128, 0, st>>>(w.sums, C, out, nullptr, accumulate, 1.0);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;

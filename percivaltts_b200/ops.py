@@ -69,6 +69,8 @@ class CudaOps(object):
         self._red = {}
         self._wg = {}
         self._lse_ws = None
+        self._splitk_ws = None
+        self._ws_keep = []
         self.launches = 0          # number of C-ABI kernel-launching calls (reset by the caller)
 
     # -- helpers ---------------------------------------------------------------------------------------------
@@ -113,6 +115,19 @@ class CudaOps(object):
             flags |= EPI_ADDMOD
             assert addmod.dim() == 2 and addmod.shape[1] == N and addmod.is_contiguous()
             addrows = addmod.shape[0]
+        if (flags & ~EPI_ACCUM) == 0 and K >= 1024:
+            # long reduction, few output tiles (weight gradients): split K over the idle SMs, deterministic two-stage sum
+            tiles = ((M + 127) // 128) * ((N + 63) // 64)
+            splits = min((2 * 148) // tiles, K // 256, 64)
+            if splits > 1:
+                need = splits * M * N
+                if self._splitk_ws is None or self._splitk_ws.numel() < need:
+                    self._ws_keep.append(self._splitk_ws)      # captured graphs may still point at the old one
+                    self._splitk_ws = self.empty(need)
+                self._ck(self.lib.pctts_gemm_splitk_f32(int(transA), int(transB), M, N, K, float(alpha), pa, lda, sa, ssa, pb, ldb,
+                                                        sb, ssb, pc, ldc, sc, ssc, flags, splits, self._splitk_ws.data_ptr(),
+                                                        self._stream()), 'pctts_gemm_splitk_f32')
+                return
         self._ck(self.lib.pctts_gemm_f32(int(transA), int(transB), M, N, K, float(alpha), pa, lda, sa, ssa, pb, ldb, sb, ssb,
                                          pc, ldc, sc, ssc, _ptr(bias), _ptr(aux), _ptr(addmod), addrows, flags,
                                          self._stream()), 'pctts_gemm_f32')
