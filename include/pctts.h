@@ -55,6 +55,29 @@ int pctts_gemm_splitk_f32(int transA, int transB, int M, int N, int K, float alp
                           float* C, long ldc, int segC, long segstrideC,
                           int flags, int splits, float* workspace, void* stream);
 
+/* ---- the same contractions on the 5th-generation tensor cores (tcgen05.mma, TMEM accumulators, TMA-fed) ----------------------
+ * fp32 operands are carried as bf16 planes [hi | lo] with x = hi + lo + O(2^-17 |x|) (pctts_split_bf16); nterms = 3 forms
+ * Ahi.Bhi + Ahi.Blo + Alo.Bhi in one fp32 accumulator (fp32-grade products), nterms = 1 is plain bf16 (hi planes only).
+ * A shadow is `parts` planes of [rows, ld_dst] bf16 (ld_dst % 8 == 0, plane pitch part_stride elements, 16-byte aligned). */
+int pctts_split_bf16(const float* src, long ld, int seg, long segstride, long rows, int cols, void* dst, long ld_dst,
+                     long part_stride, int parts, void* stream);
+int pctts_gemm_tc_splits(int M, int N, int K);                 /* host call: recommended split-K factor (1 = none) */
+long pctts_gemm_tc_workspace(int M, int N, int splits);        /* host call: floats of split-K workspace */
+/* C[M,N] = epilogue(alpha * op(A) op(B)) from the shadows of the STORED matrices (A: [M,K], or [K,M] when transA; B: [K,N], or
+ * [N,K] when transB); C / aux fp32 with row pitch ldc; flags as for pctts_gemm_f32 except ATOMIC; splits > 1 needs the workspace
+ * and allows only PCTTS_EPI_ACCUM (deterministic two-stage sum). */
+int pctts_gemm_tc(int transA, int transB, int M, int N, int K, float alpha, const void* Ash, long lda, long a_part_stride,
+                  const void* Bsh, long ldb, long b_part_stride, float* C, long ldc, const float* bias, const float* aux,
+                  const float* addmod, int addrows, int flags, int nterms, int splits, float* workspace, void* stream);
+/* Conv1D 'same' (networktts.py:116-120) without materialising im2col: xsh = shadow of the time-padded input [B*(T+W-1), CIN],
+ * wsh = shadow of the keras kernel [W*CIN, COUT]; y [B*T, COUT] (row pitch ldy) = epilogue(conv); aux uses y's addressing. */
+int pctts_conv1d_tc_fwd(const void* xsh, long ldx, long x_part_stride, const void* wsh, long ldw, long w_part_stride, float* y,
+                        long ldy, int B, int T, int W, int CIN, int COUT, const float* bias, const float* aux, int flags, int nterms,
+                        void* stream);
+/* dw[W*CIN, COUT] (+)= sum_{b,t} xpad[b,t+w,c] dz[b,t,n];  dzsh = shadow of dz [B*T, COUT] */
+int pctts_conv1d_tc_wgrad(const void* xsh, long ldx, long x_part_stride, const void* dzsh, long lddz, long dz_part_stride, float* dw,
+                          int B, int T, int W, int CIN, int COUT, int accumulate, int nterms, void* stream);
+
 /* ---- Conv2D 'same', stride 1, NHWC, HWIO (networktts.py:122-126; modeltts_common.py:98,100; networks_critic.py:67) ------ */
 /* y[n,t,f,:] = epilogue(sum_{kt,kf,ci} x[n,t+kt-pad_t,f+kf-pad_f,ci] w[kt,kf,ci,:]).  xpitch/ypitch/auxpitch = floats between
  * consecutive t rows, *batch = floats between consecutive n (lets the first / last layer read / write the spectral columns

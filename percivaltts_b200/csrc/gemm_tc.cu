@@ -1,0 +1,504 @@
+// tcgen05 / TMEM / TMA GEMM family for the dense contractions of the WGAN-GP step.
+//
+// What it replaces in the reference: the cuBLAS / cuDNN calls behind keras Dense (networktts.py:59-63,196-197), Conv1D k=21
+// (networktts.py:116-120; the dominant contraction, 18.3 GFLOP forward at the demo shape) and the LSTM input projections
+// (networktts.py:90-94), forward, data gradient and weight gradient.
+//
+// Numerics.  The reference computes in fp32.  The 5th-generation tensor cores take bf16 (or tf32) inputs, so every fp32
+// operand x is carried as a two-term bf16 expansion  x = hi + lo + O(2^-17 |x|)  (pctts_split_bf16) and a product is formed as
+//     A.B  ~=  Ahi.Bhi + Ahi.Blo + Alo.Bhi          (three tcgen05.mma per k-slice, one fp32 accumulator in TMEM)
+// which drops only the lo.lo term: relative error ~2^-16 per product, fp32 accumulation -- two orders of magnitude inside the
+// 1e-3 parity budget of the fp32 configuration.  nterms = 1 (hi.hi only) is the bf16 configuration of BASELINE config #3.
+//
+// Structure (one 128 x BN output tile per CTA, 128 threads):
+//   warp 0 / lane 0 : TMA producer.  Per 64-deep k-block one cp.async.bulk.tensor per operand plane into a 128B-swizzled
+//                     stage (K-major operands: one [ROWS x 64] box; MN-major operands: ROWS/64 boxes of [64 k x 64 mn]).
+//   warp 1 / lane 0 : MMA issuer.  4 k-slices (K=16) x nterms tcgen05.mma.cta_group::1.kind::f16 per stage, tcgen05.commit
+//                     releases the stage back to the producer; a final commit signals the epilogue.
+//   warp 2          : TMEM allocation (BN fp32 columns) / deallocation.
+//   all 4 warps     : epilogue. tcgen05.ld 32x32b.x32 (thread = accumulator row), fused alpha / bias / per-row-block addend /
+//                     LeakyReLU / sigmoid / LeakyReLU' mask / accumulate, fp32 stores; or raw split-K partials.
+//
+// Operand addressing is an affine map (tile index, k-block) -> TMA coordinates, which lets the same kernel run
+//   * plain GEMMs in all four transpose combinations from row-major storage (K-major or MN-major UMMA descriptors),
+//   * the 'same' Conv1D forward as a *virtual* im2col GEMM (k-block = (tap w, 64 channels); the A box is the activation
+//     matrix shifted down by w rows; out-of-range channels / rows are zero-filled by TMA),
+//   * the Conv1D weight gradient (M-tile = (tap w, 128 channels); k-block = (utterance b, 64 frames); 3-D tensor maps).
+#include "common.cuh"
+#include "pctts.h"
+#include "tc_common.cuh"
+#include <cuda_bf16.h>
+
+namespace {
+
+using namespace tcx;
+
+constexpr int BM = 128, BK = 64;
+constexpr int MAX_STAGES = 8;
+constexpr uint32_t A_PLANE_BYTES = BM * BK * 2;   // 16 KB
+
+struct Geom {
+    int mn_major;   // 0: K-major (TMA inner dim = k), 1: MN-major (TMA inner dim = m / n)
+    int t_div;      // tile index t -> (t % t_div, t / t_div)
+    int t_lo[3], t_hi[3], k_lo[3], k_hi[3];
+};
+
+struct Params {
+    Geom a, b;
+    int kb_div;     // k-block index kb -> (kb % kb_div, kb / kb_div)
+    int num_kb, kb_per_split;
+    int nterms, stages;
+    // output
+    float* C;
+    long ldc;
+    int N;
+    int seg_len, seg_valid, nseg;   // accumulator row r -> (seg = r / seg_len, t = r % seg_len); stored iff t < seg_valid,
+                                    // at C row seg * seg_valid + t
+    float alpha;
+    const float* bias;
+    const float* aux;
+    const float* addmod;
+    int addrows;
+    int flags;
+    float* partial;   // split-K: raw sums, plane z at partial + z * crows * N (dense rows of N floats)
+    long crows;
+};
+
+__device__ __forceinline__ void coords(const Geom& g, int t, int kb_lo, int kb_hi, int (&c)[3]) {
+    const int tl = t % g.t_div, th = t / g.t_div;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) c[d] = tl * g.t_lo[d] + th * g.t_hi[d] + kb_lo * g.k_lo[d] + kb_hi * g.k_hi[d];
+}
+
+template <int BN>
+__global__ void __launch_bounds__(128, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const Params p) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
+    __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
+    __shared__ __align__(8) uint64_t accum_bar;
+    __shared__ uint32_t tmem_slot;
+
+    constexpr uint32_t B_PLANE_BYTES = BN * BK * 2;
+    const int parts = p.nterms > 1 ? 2 : 1;
+    const uint32_t stage_bytes = parts * (A_PLANE_BYTES + B_PLANE_BYTES);
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B atoms need 1024-byte alignment
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nt = blockIdx.x, mt = blockIdx.y;
+    const int kb_begin = blockIdx.z * p.kb_per_split;
+    const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
+    const int nkb = kb_end - kb_begin;
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&mapA);
+        tma_prefetch_desc(&mapB);
+        for (int s = 0; s < p.stages; ++s) {
+            mbar_init(smem_u32(&full_bar[s]), 1);
+            mbar_init(smem_u32(&empty_bar[s]), 1);
+        }
+        mbar_init(smem_u32(&accum_bar), 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<BN>(smem_u32(&tmem_slot));
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_acc = tmem_slot;
+
+    if (warp == 0 && lane == 0) {
+        // ---------------- TMA producer ----------------
+        for (int i = 0; i < nkb; ++i) {
+            const int s = i % p.stages;
+            const uint32_t ph = (uint32_t)(i / p.stages) & 1u;
+            mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1u);
+            const uint32_t fb = smem_u32(&full_bar[s]);
+            mbar_arrive_expect_tx(fb, stage_bytes);
+            const int kb = kb_begin + i;
+            const int kb_lo = kb % p.kb_div, kb_hi = kb / p.kb_div;
+            int ca[3], cb[3];
+            coords(p.a, mt, kb_lo, kb_hi, ca);
+            coords(p.b, nt, kb_lo, kb_hi, cb);
+            const uint32_t sa = smem_base + s * stage_bytes;
+            const uint32_t sb = sa + parts * A_PLANE_BYTES;
+            for (int part = 0; part < parts; ++part) {
+                if (!p.a.mn_major) {
+                    tma_load_4d(sa + part * A_PLANE_BYTES, &mapA, fb, ca[0], ca[1], ca[2], part);
+                } else {
+#pragma unroll
+                    for (int h = 0; h < BM / 64; ++h)
+                        tma_load_4d(sa + part * A_PLANE_BYTES + h * 8192, &mapA, fb, ca[0] + 64 * h, ca[1], ca[2], part);
+                }
+                if (!p.b.mn_major) {
+                    tma_load_4d(sb + part * B_PLANE_BYTES, &mapB, fb, cb[0], cb[1], cb[2], part);
+                } else {
+#pragma unroll
+                    for (int h = 0; h < BN / 64; ++h)
+                        tma_load_4d(sb + part * B_PLANE_BYTES + h * 8192, &mapB, fb, cb[0] + 64 * h, cb[1], cb[2], part);
+                }
+            }
+        }
+    } else if (warp == 1 && lane == 0) {
+        // ---------------- MMA issuer ----------------
+        const uint32_t idesc = umma_idesc_bf16(BM, BN, p.a.mn_major, p.b.mn_major);
+        // K-major SW128 tile: rows of 128 B, 8-row groups 1024 B apart (SBO); a K=16 slice is 32 B further along the row.
+        // MN-major SW128 tile: [k][64 mn] rows of 128 B; 8-k groups 1024 B apart (SBO); next 64 mn 8192 B apart (LBO);
+        //                      a K=16 slice is 16 rows = 2048 B further.
+        const uint32_t a_lbo = p.a.mn_major ? 8192u : 16u, a_step = p.a.mn_major ? 2048u : 32u;
+        const uint32_t b_lbo = p.b.mn_major ? 8192u : 16u, b_step = p.b.mn_major ? 2048u : 32u;
+        for (int i = 0; i < nkb; ++i) {
+            const int s = i % p.stages;
+            const uint32_t ph = (uint32_t)(i / p.stages) & 1u;
+            mbar_wait(smem_u32(&full_bar[s]), ph);
+            tc_fence_after();
+            const uint32_t sa = smem_base + s * stage_bytes;
+            const uint32_t sb = sa + parts * A_PLANE_BYTES;
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) {
+                const uint64_t ah = umma_smem_desc(sa + k * a_step, a_lbo, 1024u);
+                const uint64_t bh = umma_smem_desc(sb + k * b_step, b_lbo, 1024u);
+                umma_bf16(tmem_acc, ah, bh, idesc, (i | k) != 0);
+                if (parts == 2) {
+                    const uint64_t al = umma_smem_desc(sa + A_PLANE_BYTES + k * a_step, a_lbo, 1024u);
+                    const uint64_t bl = umma_smem_desc(sb + B_PLANE_BYTES + k * b_step, b_lbo, 1024u);
+                    umma_bf16(tmem_acc, ah, bl, idesc, 1u);
+                    umma_bf16(tmem_acc, al, bh, idesc, 1u);
+                }
+            }
+            umma_commit(smem_u32(&empty_bar[s]));   // stage reusable once these MMAs have read it
+        }
+        umma_commit(smem_u32(&accum_bar));          // accumulator complete
+    }
+    __syncwarp();
+
+    // ---------------- epilogue (all warps; warp w owns TMEM lanes 32w..32w+31 = tile rows) ----------------
+    mbar_wait(smem_u32(&accum_bar), 0);
+    tc_fence_after();
+    const int r = mt * BM + warp * 32 + lane;
+    const int seg = r / p.seg_len, tt = r - seg * p.seg_len;
+    const bool row_ok = tt < p.seg_valid && seg < p.nseg;
+    const long crow = (long)seg * p.seg_valid + tt;
+    const int n0 = nt * BN;
+    const int flags = p.flags;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+        const int nb = n0 + c * 32;
+        if (nb >= p.N) break;
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_acc + ((uint32_t)(warp * 32) << 16) + (uint32_t)(c * 32), v);
+        tmem_ld_wait();
+        if (!row_ok) continue;
+        if (p.partial) {
+            float* dst = p.partial + ((long)blockIdx.z * p.crows + crow) * p.N + nb;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (nb + j < p.N) dst[j] = __uint_as_float(v[j]);
+            continue;
+        }
+        float* dst = p.C + crow * p.ldc + nb;
+        const float* auxp = p.aux ? p.aux + crow * p.ldc + nb : nullptr;
+        const float* addp = (flags & PCTTS_EPI_ADDMOD) ? p.addmod + (crow % p.addrows) * (long)p.N + nb : nullptr;
+        float o[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            float x = __uint_as_float(v[j]) * p.alpha;
+            if (nb + j < p.N) {
+                if (flags & PCTTS_EPI_BIAS) x += __ldg(p.bias + nb + j);
+                if (flags & PCTTS_EPI_ADDMOD) x += __ldg(addp + j);
+                if (flags & PCTTS_EPI_LRELU) x = lrelu_f(x);
+                if (flags & PCTTS_EPI_SIGMOID) x = sigmoid_f(x);
+                if (flags & PCTTS_EPI_DLRELU_AUX) x *= dlrelu_from_out(auxp[j]);
+                if (flags & PCTTS_EPI_ACCUM) x += dst[j];
+            }
+            o[j] = x;
+        }
+        const bool vec = (nb + 32 <= p.N) && ((((uintptr_t)dst) & 15) == 0);
+        if (vec) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (nb + j < p.N) dst[j] = o[j];
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc<BN>(tmem_acc);
+}
+
+// C (+)= alpha * sum_z partial[z], fixed order (deterministic)
+__global__ void tc_splitk_reduce_kernel(const float* __restrict__ partial, int splits, long rows, int N, float* __restrict__ C,
+                                        long ldc, float alpha, int accum) {
+    const long total = rows * N;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int z = 0; z < splits; ++z) s += partial[(long)z * total + i];
+        const long m = i / N;
+        const int n = (int)(i - m * N);
+        float* c = C + m * ldc + n;
+        s *= alpha;
+        *c = accum ? *c + s : s;
+    }
+}
+
+// x -> bf16 hi (+ lo) planes; one thread per pair of columns
+__global__ void split_bf16_kernel(const float* __restrict__ src, long ld, int seg, long segstride, long rows, int cols,
+                                  __nv_bfloat16* __restrict__ dst, long ld_dst, long part_stride, int parts) {
+    const long pairs_per_row = ld_dst / 2;
+    const long total = rows * pairs_per_row;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const long r = i / pairs_per_row;
+        const int c = (int)(i - r * pairs_per_row) * 2;
+        long off;
+        if (seg > 0) {
+            const long s = r / seg;
+            off = s * segstride + (r - s * seg) * ld;
+        } else {
+            off = r * ld;
+        }
+        const float x0 = c < cols ? src[off + c] : 0.f;
+        const float x1 = c + 1 < cols ? src[off + c + 1] : 0.f;
+        const __nv_bfloat16 h0 = __float2bfloat16_rn(x0), h1 = __float2bfloat16_rn(x1);
+        __nv_bfloat162 hv;
+        hv.x = h0;
+        hv.y = h1;
+        *reinterpret_cast<__nv_bfloat162*>(dst + r * ld_dst + c) = hv;
+        if (parts > 1) {
+            __nv_bfloat162 lv;
+            lv.x = __float2bfloat16_rn(x0 - __bfloat162float(h0));
+            lv.y = __float2bfloat16_rn(x1 - __bfloat162float(h1));
+            *reinterpret_cast<__nv_bfloat162*>(dst + part_stride + r * ld_dst + c) = lv;
+        }
+    }
+}
+
+struct Launch {
+    const void* a_base;
+    uint64_t a_dims[4];
+    uint64_t a_strides[3];
+    const void* b_base;
+    uint64_t b_dims[4];
+    uint64_t b_strides[3];
+    int m_tiles, n_tiles_hint;   // n tiles derive from N and BN
+    int splits;
+};
+
+int pick_bn(int m_tiles, int N) {
+    if (N <= 64) return 64;
+    const int t128 = m_tiles * ((N + 127) / 128);
+    return t128 >= 100 ? 128 : 64;
+}
+
+template <int BN>
+int launch_bn(const Launch& L, Params p, cudaStream_t st) {
+    CUtensorMap mapA, mapB;
+    const uint32_t boxA[4] = {64u, p.a.mn_major ? 64u : (uint32_t)BM, 1u, 1u};
+    const uint32_t boxB[4] = {64u, p.b.mn_major ? 64u : (uint32_t)BN, 1u, 1u};
+    int rc = make_map_bf16_4d(&mapA, L.a_base, L.a_dims, L.a_strides, boxA);
+    if (rc) return rc < 0 ? rc : PCTTS_EINVAL;
+    rc = make_map_bf16_4d(&mapB, L.b_base, L.b_dims, L.b_strides, boxB);
+    if (rc) return rc < 0 ? rc : PCTTS_EINVAL;
+    const int parts = p.nterms > 1 ? 2 : 1;
+    const uint32_t stage_bytes = parts * (A_PLANE_BYTES + BN * BK * 2);
+    int stages = (int)((200u * 1024u) / stage_bytes);
+    if (stages > MAX_STAGES) stages = MAX_STAGES;
+    if (stages > p.kb_per_split) stages = p.kb_per_split < 2 ? 2 : p.kb_per_split;
+    p.stages = stages;
+    const size_t smem = (size_t)stages * stage_bytes + 1024;
+    static bool attr_done = false;
+    if (!attr_done) {
+        PCTTS_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        attr_done = true;
+    }
+    dim3 grid((p.N + BN - 1) / BN, L.m_tiles, L.splits);
+    gemm_tc_kernel<BN><<<grid, 128, smem, st>>>(mapA, mapB, p);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
+int launch_tc(const Launch& L, Params p, int bn, float* C, long ldc, float alpha, int accum, cudaStream_t st) {
+    int rc = bn == 128 ? launch_bn<128>(L, p, st) : launch_bn<64>(L, p, st);
+    if (rc) return rc;
+    if (p.partial) {
+        const long total = p.crows * p.N;
+        int blocks = pctts_div_up(total, 256);
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        tc_splitk_reduce_kernel<<<blocks, 256, 0, st>>>(p.partial, L.splits, p.crows, p.N, C, ldc, alpha, accum);
+        PCTTS_LAUNCH_CHECK();
+    }
+    return PCTTS_OK;
+}
+
+void zero3(int (&v)[3]) { v[0] = v[1] = v[2] = 0; }
+
+// geometry of a plain row-major stored matrix used as the A (tile = 128 rows) or B (tile = bn cols) operand
+//   K-major  (stored [mn, k]): coords (k, mn)      MN-major (stored [k, mn]): coords (mn, k)
+void plain_geom(Geom& g, int mn_major, int tile) {
+    g.mn_major = mn_major;
+    g.t_div = 1 << 30;
+    zero3(g.t_lo), zero3(g.t_hi), zero3(g.k_lo), zero3(g.k_hi);
+    if (!mn_major) {
+        g.k_lo[0] = BK;
+        g.t_lo[1] = tile;
+    } else {
+        g.t_lo[0] = tile;
+        g.k_lo[1] = BK;
+    }
+}
+
+}  // namespace
+
+extern "C" int pctts_split_bf16(const float* src, long ld, int seg, long segstride, long rows, int cols, void* dst, long ld_dst,
+                                long part_stride, int parts, void* stream) {
+    if (!src || !dst || rows < 0 || cols <= 0 || ld_dst < cols || (ld_dst & 7) || parts < 1 || parts > 2) return PCTTS_EINVAL;
+    if (rows == 0) return PCTTS_OK;
+    const long total = rows * (ld_dst / 2);
+    int blocks = pctts_div_up(total, 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    split_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(src, ld, seg, segstride, rows, cols, (__nv_bfloat16*)dst, ld_dst,
+                                                                part_stride, parts);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
+extern "C" long pctts_gemm_tc_workspace(int M, int N, int splits) { return splits > 1 ? (long)splits * M * N : 0; }
+
+extern "C" int pctts_gemm_tc_splits(int M, int N, int K) {
+    const int m_tiles = (M + BM - 1) / BM;
+    const int bn = pick_bn(m_tiles, N);
+    const int tiles = m_tiles * ((N + bn - 1) / bn);
+    const int num_kb = (K + BK - 1) / BK;
+    if (tiles >= 74 || num_kb < 8) return 1;
+    int splits = 148 / tiles;
+    if (splits > num_kb / 2) splits = num_kb / 2;
+    if (splits > 32) splits = 32;
+    return splits < 1 ? 1 : splits;
+}
+
+extern "C" int pctts_gemm_tc(int transA, int transB, int M, int N, int K, float alpha, const void* Ash, long lda, long a_part_stride,
+                             const void* Bsh, long ldb, long b_part_stride, float* C, long ldc, const float* bias, const float* aux,
+                             const float* addmod, int addrows, int flags, int nterms, int splits, float* workspace, void* stream) {
+    if (!Ash || !Bsh || !C || M <= 0 || N <= 0 || K <= 0) return PCTTS_EINVAL;
+    if (nterms != 1 && nterms != 3) return PCTTS_EINVAL;
+    if (flags & PCTTS_EPI_ATOMIC) return PCTTS_EUNSUPPORTED;
+    if ((flags & PCTTS_EPI_BIAS) && !bias) return PCTTS_EINVAL;
+    if ((flags & PCTTS_EPI_DLRELU_AUX) && !aux) return PCTTS_EINVAL;
+    if ((flags & PCTTS_EPI_ADDMOD) && (!addmod || addrows <= 0)) return PCTTS_EINVAL;
+    if (splits > 1 && (!workspace || (flags & ~PCTTS_EPI_ACCUM))) return PCTTS_EINVAL;
+    const int parts = nterms > 1 ? 2 : 1;
+    Launch L;
+    Params p;
+    L.m_tiles = (M + BM - 1) / BM;
+    const int bn = pick_bn(L.m_tiles, N);
+    // A: stored [M,K] (K-major) or, transposed, [K,M] (MN-major);  B: stored [K,N] (MN-major) or, transposed, [N,K] (K-major)
+    plain_geom(p.a, transA ? 1 : 0, BM);
+    plain_geom(p.b, transB ? 0 : 1, bn);
+    L.a_base = Ash;
+    L.a_dims[0] = transA ? M : K, L.a_dims[1] = transA ? K : M, L.a_dims[2] = 1, L.a_dims[3] = parts;
+    L.a_strides[0] = lda * 2, L.a_strides[1] = L.a_dims[1] * lda * 2, L.a_strides[2] = a_part_stride * 2;
+    L.b_base = Bsh;
+    L.b_dims[0] = transB ? K : N, L.b_dims[1] = transB ? N : K, L.b_dims[2] = 1, L.b_dims[3] = parts;
+    L.b_strides[0] = ldb * 2, L.b_strides[1] = L.b_dims[1] * ldb * 2, L.b_strides[2] = b_part_stride * 2;
+    p.kb_div = 1 << 30;
+    p.num_kb = (K + BK - 1) / BK;
+    if (splits < 1) splits = 1;
+    if (splits > p.num_kb) splits = p.num_kb;
+    p.kb_per_split = (p.num_kb + splits - 1) / splits;
+    L.splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
+    p.nterms = nterms;
+    p.C = C, p.ldc = ldc, p.N = N;
+    p.seg_len = 1 << 30, p.seg_valid = M, p.nseg = 1;
+    p.alpha = alpha, p.bias = bias, p.aux = aux, p.addmod = addmod, p.addrows = addrows, p.flags = flags;
+    p.partial = L.splits > 1 ? workspace : nullptr;
+    p.crows = M;
+    return launch_tc(L, p, bn, C, ldc, alpha, (flags & PCTTS_EPI_ACCUM) ? 1 : 0, (cudaStream_t)stream);
+}
+
+// 'same' Conv1D forward as a virtual-im2col GEMM.  xsh: bf16 planes of the time-padded input [B, T+W-1, CIN] (row pitch ldx);
+// wsh: bf16 planes of the keras kernel [W*CIN, COUT] (row pitch ldw);  y [B*T, COUT] fp32 = epilogue(im2col(x) . w).
+// Accumulator rows run over the flat padded row space r = b*(T+W-1) + t'; rows with t' >= T are computed and dropped.
+extern "C" int pctts_conv1d_tc_fwd(const void* xsh, long ldx, long x_part_stride, const void* wsh, long ldw, long w_part_stride,
+                                   float* y, long ldy, int B, int T, int W, int CIN, int COUT, const float* bias, const float* aux,
+                                   int flags, int nterms, void* stream) {
+    if (!xsh || !wsh || !y || B <= 0 || T <= 0 || W <= 0 || CIN <= 0 || COUT <= 0) return PCTTS_EINVAL;
+    if (nterms != 1 && nterms != 3) return PCTTS_EINVAL;
+    if (flags & (PCTTS_EPI_ATOMIC | PCTTS_EPI_ADDMOD)) return PCTTS_EUNSUPPORTED;
+    if ((flags & PCTTS_EPI_BIAS) && !bias) return PCTTS_EINVAL;
+    if ((flags & PCTTS_EPI_DLRELU_AUX) && !aux) return PCTTS_EINVAL;
+    const int parts = nterms > 1 ? 2 : 1;
+    const int Tp = T + W - 1;
+    const long rows = (long)B * Tp;
+    Launch L;
+    Params p;
+    L.m_tiles = (int)((rows + BM - 1) / BM);
+    const int bn = pick_bn(L.m_tiles, COUT);
+    const int kb_seg = (CIN + BK - 1) / BK;
+    // A: K-major over the flat padded activation matrix; k-block (w, j): 64 channels from j*64, rows shifted down by w
+    p.a.mn_major = 0, p.a.t_div = 1 << 30;
+    zero3(p.a.t_lo), zero3(p.a.t_hi), zero3(p.a.k_lo), zero3(p.a.k_hi);
+    p.a.t_lo[1] = BM, p.a.k_lo[0] = BK, p.a.k_hi[1] = 1;
+    L.a_base = xsh;
+    L.a_dims[0] = CIN, L.a_dims[1] = rows, L.a_dims[2] = 1, L.a_dims[3] = parts;
+    L.a_strides[0] = ldx * 2, L.a_strides[1] = rows * ldx * 2, L.a_strides[2] = x_part_stride * 2;
+    // B: MN-major kernel matrix [W*CIN, COUT]; k-block (w, j) starts at row w*CIN + j*64 (rows past the tap meet zero A columns)
+    p.b.mn_major = 1, p.b.t_div = 1 << 30;
+    zero3(p.b.t_lo), zero3(p.b.t_hi), zero3(p.b.k_lo), zero3(p.b.k_hi);
+    p.b.t_lo[0] = bn, p.b.k_lo[1] = BK, p.b.k_hi[1] = CIN;
+    L.b_base = wsh;
+    L.b_dims[0] = COUT, L.b_dims[1] = (uint64_t)W * CIN, L.b_dims[2] = 1, L.b_dims[3] = parts;
+    L.b_strides[0] = ldw * 2, L.b_strides[1] = L.b_dims[1] * ldw * 2, L.b_strides[2] = w_part_stride * 2;
+    p.kb_div = kb_seg;
+    p.num_kb = kb_seg * W;
+    p.kb_per_split = p.num_kb;
+    L.splits = 1;
+    p.nterms = nterms;
+    p.C = y, p.ldc = ldy, p.N = COUT;
+    p.seg_len = Tp, p.seg_valid = T, p.nseg = B;
+    p.alpha = 1.f, p.bias = bias, p.aux = aux, p.addmod = nullptr, p.addrows = 0, p.flags = flags;
+    p.partial = nullptr;
+    p.crows = (long)B * T;
+    return launch_tc(L, p, bn, y, ldy, 1.f, 0, (cudaStream_t)stream);
+}
+
+// Conv1D weight gradient dw[w*CIN + c, n] (+)= sum_{b,t} xpad[b, t+w, c] dz[b, t, n].
+// xsh as above; dzsh: bf16 planes of dz [B*T, COUT] (row pitch lddz).  M-tile = (tap w, 128 channels), k-block = (b, 64 frames).
+extern "C" int pctts_conv1d_tc_wgrad(const void* xsh, long ldx, long x_part_stride, const void* dzsh, long lddz, long dz_part_stride,
+                                     float* dw, int B, int T, int W, int CIN, int COUT, int accumulate, int nterms, void* stream) {
+    if (!xsh || !dzsh || !dw || B <= 0 || T <= 0 || W <= 0 || CIN <= 0 || COUT <= 0) return PCTTS_EINVAL;
+    if (nterms != 1 && nterms != 3) return PCTTS_EINVAL;
+    const int parts = nterms > 1 ? 2 : 1;
+    const int Tp = T + W - 1;
+    Launch L;
+    Params p;
+    const int ct = (CIN + BM - 1) / BM;          // channel tiles per tap
+    L.m_tiles = ct * W;
+    const int bn = pick_bn(L.m_tiles, COUT);
+    const int kb_seg = (T + BK - 1) / BK;        // k-blocks per utterance
+    // A: MN-major view of xpad as (c, t', b); tile (w, ci): channels ci*128.., frames shifted by w
+    p.a.mn_major = 1, p.a.t_div = ct;
+    zero3(p.a.t_lo), zero3(p.a.t_hi), zero3(p.a.k_lo), zero3(p.a.k_hi);
+    p.a.t_lo[0] = BM, p.a.t_hi[1] = 1, p.a.k_lo[1] = BK, p.a.k_hi[2] = 1;
+    L.a_base = xsh;
+    L.a_dims[0] = CIN, L.a_dims[1] = Tp, L.a_dims[2] = B, L.a_dims[3] = parts;
+    L.a_strides[0] = ldx * 2, L.a_strides[1] = (uint64_t)Tp * ldx * 2, L.a_strides[2] = x_part_stride * 2;
+    // B: MN-major view of dz as (n, t, b); frames >= T are zero-filled by TMA, which also cancels the A rows read past them
+    p.b.mn_major = 1, p.b.t_div = 1 << 30;
+    zero3(p.b.t_lo), zero3(p.b.t_hi), zero3(p.b.k_lo), zero3(p.b.k_hi);
+    p.b.t_lo[0] = bn, p.b.k_lo[1] = BK, p.b.k_hi[2] = 1;
+    L.b_base = dzsh;
+    L.b_dims[0] = COUT, L.b_dims[1] = T, L.b_dims[2] = B, L.b_dims[3] = parts;
+    L.b_strides[0] = lddz * 2, L.b_strides[1] = (uint64_t)T * lddz * 2, L.b_strides[2] = dz_part_stride * 2;
+    p.kb_div = kb_seg;
+    p.num_kb = kb_seg * B;
+    p.kb_per_split = p.num_kb;
+    L.splits = 1;
+    p.nterms = nterms;
+    p.C = dw, p.ldc = COUT, p.N = COUT;
+    p.seg_len = ct * BM, p.seg_valid = CIN, p.nseg = W;
+    p.alpha = 1.f, p.bias = nullptr, p.aux = nullptr, p.addmod = nullptr, p.addrows = 0;
+    p.flags = accumulate ? PCTTS_EPI_ACCUM : 0;
+    p.partial = nullptr;
+    p.crows = (long)W * CIN;
+    return launch_tc(L, p, bn, dw, COUT, 1.f, accumulate, (cudaStream_t)stream);
+}

@@ -42,6 +42,7 @@ class ParamStore(object):
         self.state = ops.zeros(max(nstate, 1))
         self.step = ops.zeros(1, dtype=torch.int32)
         self.ntrain, self.nstate = ntrain, nstate
+        ops.register_persistent(self.flat)      # GEMM operand shadows of the weights follow load() / adam()
         self.p, self.g = OrderedDict(), OrderedDict()
         ot = os_ = 0
         for name, shape, trainable in self.shapes:
@@ -62,6 +63,7 @@ class ParamStore(object):
         for name, shape, _ in self.shapes:
             w = torch.as_tensor(np.asarray(weights[name])).to(self.flat.dtype).reshape(*shape)
             self.p[name].copy_(w)
+        self.ops.refresh_persistent(self.flat)
 
     def export(self):
         return OrderedDict((name, self.p[name].detach().cpu().numpy().copy()) for name, _, _ in self.shapes)
@@ -73,6 +75,7 @@ class ParamStore(object):
         if self.ntrain:
             self.ops.adam(self.flat[:self.ntrain], self.grad[:self.ntrain], self.m[:self.ntrain], self.v[:self.ntrain],
                           lr, beta1, beta2, eps, self.step)
+            self.ops.refresh_persistent(self.flat)
 
 
 def _im2col_view(xp, T, W):
@@ -182,8 +185,7 @@ class Generator(object):
         for i in range(a.ctx_nbcnnlayers):                                   # pCNN1D (networktts.py:116-120)
             xp = pl['ctx_xp'][i]
             o.pad_time(xp, x, left, W - 1 - left)
-            k = p['g.ctx.cnn%d.kernel' % i]
-            o.gemm(_im2col_view(xp, T, W), k.view(-1, H), pl['ctx_z'][i])
+            o.conv1d(xp, p['g.ctx.cnn%d.kernel' % i], pl['ctx_z'][i], T)
             self._bn_fwd(pl['ctx_z'][i], pl['ctx_y'][i], pl['ctx_bn'][i], training, update_stats, sync)
             x = pl['ctx_y'][i].view(B, T, H)
         x2 = x.reshape(M, -1)
@@ -314,7 +316,7 @@ class Generator(object):
             dz = pl['dB'] if dcur is not pl['dB'] else pl['dA']
             self._bn_bwd(pl['ctx_z'][i], dcur, dz, pl['ctx_bn'][i], sync)
             k = p['g.ctx.cnn%d.kernel' % i]
-            o.gemm(_im2col_view(pl['ctx_xp'][i], T, W), dz, g['g.ctx.cnn%d.kernel' % i].view(-1, H), transA=True)
+            o.conv1d_wgrad(pl['ctx_xp'][i], dz, g['g.ctx.cnn%d.kernel' % i], T)
             if i > 0:
                 # data gradient = 'same' correlation of dz with the time-flipped, in/out-transposed kernel
                 o.pad_time(pl['ctx_dzp'], dz.view(B, T, H), W - 1 - left, left)
@@ -387,8 +389,7 @@ class Critic(object):
         for i in range(a.ctx_nbcnnlayers):
             xp = pl['ctx_xp'][i]
             o.pad_time(xp, x, left, W - 1 - left)
-            o.gemm(_im2col_view(xp, T, W), p['c.ctx.cnn%d.kernel' % i].view(-1, H), pl['ctx_y'][i],
-                   bias=p['c.ctx.cnn%d.bias' % i], flags=EPI_LRELU)
+            o.conv1d(xp, p['c.ctx.cnn%d.kernel' % i], pl['ctx_y'][i], T, bias=p['c.ctx.cnn%d.bias' % i], flags=EPI_LRELU)
             x = pl['ctx_y'][i].view(B, T, H)
         x2 = x.reshape(M, -1)
         for i in range(2):
@@ -493,7 +494,7 @@ class Critic(object):
                 dcur = dnext
         left = (W - 1) // 2
         for i in range(a.ctx_nbcnnlayers - 1, -1, -1):
-            o.gemm(_im2col_view(pl['ctx_xp'][i], T, W), dcur, g['c.ctx.cnn%d.kernel' % i].view(-1, H), transA=True)
+            o.conv1d_wgrad(pl['ctx_xp'][i], dcur, g['c.ctx.cnn%d.kernel' % i], T)
             o.colsum(dcur, g['c.ctx.cnn%d.bias' % i])
             if i > 0:
                 o.pad_time(pl['ctx_dzp'], dcur.view(B, T, H), W - 1 - left, left)

@@ -8,6 +8,9 @@ PyTorch or CPU fallback: constructing `CudaOps` without a B200 and a built libpc
 The engine (percivaltts_b200/engine.py) is written against this interface; tests/cpu_ops_double.py implements the
 same interface with plain torch on the CPU *for testing the host logic only* (it is not importable from the package).
 """
+import contextlib
+import os
+
 import torch
 
 from . import _lib
@@ -57,15 +60,56 @@ class ReduceWorkspace(object):
         return self.buf.data_ptr()
 
 
+def _extent(t):
+    """[lo, hi) byte range touched by the view t."""
+    lo = t.data_ptr()
+    n = 1
+    for size, stride in zip(t.shape, t.stride()):
+        if size == 0:
+            return lo, lo
+        n += (size - 1) * stride
+    return lo, lo + n * t.element_size()
+
+
+class Shadow(object):
+    """bf16 [hi | lo] planes of an fp32 matrix view, the operand format of the tcgen05 GEMMs (pctts_split_bf16):
+    `parts` planes of [rows, ld] bf16, ld = cols rounded up to 8 elements (16-byte TMA row pitch)."""
+
+    def __init__(self, device, rows, cols, parts):
+        self.rows, self.cols, self.parts = int(rows), int(cols), int(parts)
+        self.ld = (self.cols + 7) // 8 * 8
+        self.part_stride = self.rows * self.ld
+        self.buf = torch.empty(self.parts * self.part_stride, dtype=torch.bfloat16, device=device)
+
+    @property
+    def ptr(self):
+        return self.buf.data_ptr()
+
+
+PRECISIONS = {'fp32x3': 3, 'bf16': 1, 'simt': 0}
+
+
 class CudaOps(object):
     name = 'cuda'
 
-    def __init__(self, device=None):
+    def __init__(self, device=None, precision=None):
+        """precision: 'fp32x3' (default; tcgen05 GEMMs on bf16 hi/lo splits, three products per k-slice, fp32-grade),
+        'bf16' (tcgen05 GEMMs on single bf16 operands, fp32 accumulate) or 'simt' (exact fp32 CUDA-core GEMMs)."""
         if not torch.cuda.is_available():
             raise _lib.PcttsError('percivaltts_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback')
         self.lib = _lib.load()
         self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
         _lib.check(self.lib.pctts_device_check(self.device.index or 0), 'pctts_device_check')
+        precision = precision or os.environ.get('PCTTS_PRECISION', 'fp32x3')
+        if precision not in PRECISIONS:
+            raise ValueError('unknown precision %r (one of %s)' % (precision, sorted(PRECISIONS)))
+        self.precision = precision
+        self.nterms = PRECISIONS[precision]
+        self._shadows = {}         # view key -> Shadow
+        self._fresh = {}           # view key -> (lo, hi): activation shadows valid inside the current step scope
+        self._persist_ranges = []  # [lo, hi) of parameter buffers: their shadows are refreshed by refresh_persistent()
+        self._persist = {}         # view key -> (Shadow, view)
+        self._tracking = False
         self._red = {}
         self._wg = {}
         self._lse_ws = None
@@ -94,6 +138,66 @@ class CudaOps(object):
     def zeros(self, *shape, dtype=torch.float32):
         return torch.zeros(*shape, dtype=dtype, device=self.device)
 
+    # -- bf16 operand shadows of the tensor-core GEMMs ----------------------------------------------------------
+    @contextlib.contextmanager
+    def step_scope(self):
+        """Inside the scope an activation is split once and its shadow reused until a kernel of this object overwrites the
+        memory it came from (every writer reports through _wrote).  Outside a scope every GEMM re-splits its operands."""
+        outer = self._tracking
+        if not outer:
+            self._fresh.clear()
+        self._tracking = True
+        try:
+            yield self
+        finally:
+            self._tracking = outer
+            if not outer:
+                self._fresh.clear()
+
+    def register_persistent(self, flat):
+        """Declare a parameter buffer: shadows of views into it stay valid until refresh_persistent(flat)."""
+        self._persist_ranges.append(_extent(flat))
+
+    def refresh_persistent(self, flat):
+        """Re-split every shadow taken from views of `flat` (after Adam or a weight load)."""
+        lo, hi = _extent(flat)
+        for key, (sh, view) in self._persist.items():
+            if lo <= key[0] < hi:
+                self._split(view, sh)
+
+    def _wrote(self, t):
+        if self._fresh and t is not None:
+            lo, hi = _extent(t)
+            for key in [k for k, (a, b) in self._fresh.items() if a < hi and lo < b]:
+                del self._fresh[key]
+
+    def _split(self, t, sh):
+        p, ld, seg, ss, rows, cols = _mat(t)
+        self._ck(self.lib.pctts_split_bf16(p, ld, seg, ss, rows, cols, sh.ptr, sh.ld, sh.part_stride, sh.parts, self._stream()),
+                 'pctts_split_bf16')
+
+    def shadow(self, t):
+        """Up-to-date bf16 shadow of the 2-D / segmented 3-D fp32 view t."""
+        key = (t.data_ptr(), tuple(t.shape), tuple(t.stride()))
+        sh = self._shadows.get(key)
+        if sh is None:
+            _, _, _, _, rows, cols = _mat(t)
+            sh = self._shadows[key] = Shadow(self.device, rows, cols, 2 if self.nterms == 3 else 1)
+        ptr = key[0]
+        if any(lo <= ptr < hi for lo, hi in self._persist_ranges):
+            if key not in self._persist:
+                self._persist[key] = (sh, t)
+                self._split(t, sh)
+            return sh
+        if key not in self._fresh:
+            self._split(t, sh)
+            if self._tracking:
+                self._fresh[key] = _extent(t)
+        return sh
+
+    def _tc_ok(self, M, N, K, C, flags):
+        return (self.nterms > 0 and C.dim() == 2 and M >= 32 and N >= 8 and K >= 16 and not (flags & EPI_ATOMIC))
+
     # -- dense contractions ----------------------------------------------------------------------------------
     def gemm(self, A, B, C, transA=False, transB=False, alpha=1.0, bias=None, aux=None, addmod=None, flags=0):
         """C = epilogue(alpha * op(A) op(B)); A/B/C are 2-D or segmented 3-D views (see _mat)."""
@@ -115,22 +219,74 @@ class CudaOps(object):
             flags |= EPI_ADDMOD
             assert addmod.dim() == 2 and addmod.shape[1] == N and addmod.is_contiguous()
             addrows = addmod.shape[0]
+        if self._tc_ok(M, N, K, C, flags):
+            sha, shb = self.shadow(A), self.shadow(B)
+            self._wrote(C)
+            splits, ws = 1, None
+            if (flags & ~EPI_ACCUM) == 0:
+                splits = self.lib.pctts_gemm_tc_splits(M, N, K)
+                if splits > 1:
+                    ws = self._splitk(self.lib.pctts_gemm_tc_workspace(M, N, splits))
+            self._ck(self.lib.pctts_gemm_tc(int(transA), int(transB), M, N, K, float(alpha), sha.ptr, sha.ld, sha.part_stride,
+                                            shb.ptr, shb.ld, shb.part_stride, pc, ldc, _ptr(bias), _ptr(aux), _ptr(addmod),
+                                            addrows, flags, self.nterms, splits, _ptr(ws), self._stream()), 'pctts_gemm_tc')
+            return
+        self._wrote(C)
         if (flags & ~EPI_ACCUM) == 0 and K >= 1024:
             # long reduction, few output tiles (weight gradients): split K over the idle SMs, deterministic two-stage sum
             tiles = ((M + 127) // 128) * ((N + 63) // 64)
             splits = min((2 * 148) // tiles, K // 256, 64)
             if splits > 1:
-                need = splits * M * N
-                if self._splitk_ws is None or self._splitk_ws.numel() < need:
-                    self._ws_keep.append(self._splitk_ws)      # captured graphs may still point at the old one
-                    self._splitk_ws = self.empty(need)
+                ws = self._splitk(splits * M * N)
                 self._ck(self.lib.pctts_gemm_splitk_f32(int(transA), int(transB), M, N, K, float(alpha), pa, lda, sa, ssa, pb, ldb,
-                                                        sb, ssb, pc, ldc, sc, ssc, flags, splits, self._splitk_ws.data_ptr(),
+                                                        sb, ssb, pc, ldc, sc, ssc, flags, splits, ws.data_ptr(),
                                                         self._stream()), 'pctts_gemm_splitk_f32')
                 return
         self._ck(self.lib.pctts_gemm_f32(int(transA), int(transB), M, N, K, float(alpha), pa, lda, sa, ssa, pb, ldb, sb, ssb,
                                          pc, ldc, sc, ssc, _ptr(bias), _ptr(aux), _ptr(addmod), addrows, flags,
                                          self._stream()), 'pctts_gemm_f32')
+
+    def _splitk(self, need):
+        if self._splitk_ws is None or self._splitk_ws.numel() < need:
+            self._ws_keep.append(self._splitk_ws)      # captured graphs may still point at the old one
+            self._splitk_ws = self.empty(max(int(need), 1))
+        return self._splitk_ws
+
+    # -- 1-D convolutions (pCNN1D, networktts.py:116-120) --------------------------------------------------------
+    def conv1d(self, xp, kernel, y, T, bias=None, aux=None, flags=0):
+        """'same' Conv1D of the time-padded input xp [B, T+W-1, CIN] with the keras kernel [W, CIN, COUT] -> y [B*T, COUT]
+        (virtual im2col: no patch matrix is ever written)."""
+        B, Tp, CIN = xp.shape
+        W, ci, COUT = kernel.shape
+        assert ci == CIN and Tp == T + W - 1 and xp.is_contiguous() and kernel.is_contiguous()
+        assert tuple(y.shape) == (B * T, COUT) and y.stride(1) == 1
+        if self.nterms > 0 and COUT >= 8:
+            if bias is not None:
+                flags |= EPI_BIAS
+            if aux is not None:
+                flags |= EPI_DLRELU_AUX
+                assert tuple(aux.shape) == tuple(y.shape) and aux.stride() == y.stride()
+            shx, shw = self.shadow(xp.view(B * Tp, CIN)), self.shadow(kernel.view(W * CIN, COUT))
+            self._wrote(y)
+            self._ck(self.lib.pctts_conv1d_tc_fwd(shx.ptr, shx.ld, shx.part_stride, shw.ptr, shw.ld, shw.part_stride, y.data_ptr(),
+                                                  y.stride(0), B, T, W, CIN, COUT, _ptr(bias), _ptr(aux), flags, self.nterms,
+                                                  self._stream()), 'pctts_conv1d_tc_fwd')
+            return
+        self.gemm(xp.as_strided((B, T, W * CIN), (Tp * CIN, CIN, 1)), kernel.view(W * CIN, COUT), y, bias=bias, aux=aux, flags=flags)
+
+    def conv1d_wgrad(self, xp, dz, dw, T):
+        """dw [W, CIN, COUT] = sum_{b,t} xp[b, t+w, :]^T dz[b*T+t, :]"""
+        B, Tp, CIN = xp.shape
+        W, ci, COUT = dw.shape
+        assert ci == CIN and Tp == T + W - 1 and xp.is_contiguous() and dw.is_contiguous()
+        assert tuple(dz.shape) == (B * T, COUT) and dz.is_contiguous()
+        if self.nterms > 0 and COUT >= 8:
+            shx, shz = self.shadow(xp.view(B * Tp, CIN)), self.shadow(dz)
+            self._ck(self.lib.pctts_conv1d_tc_wgrad(shx.ptr, shx.ld, shx.part_stride, shz.ptr, shz.ld, shz.part_stride,
+                                                    dw.data_ptr(), B, T, W, CIN, COUT, 0, self.nterms, self._stream()),
+                     'pctts_conv1d_tc_wgrad')
+            return
+        self.gemm(xp.as_strided((B, T, W * CIN), (Tp * CIN, CIN, 1)), dz, dw.view(W * CIN, COUT), transA=True)
 
     # -- 2-D convolutions ------------------------------------------------------------------------------------
     def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0):
@@ -148,6 +304,7 @@ class CudaOps(object):
             flags |= EPI_DLRELU_AUX
             assert tuple(aux.shape) == tuple(y.shape)
             pa, ab, ap = _map4(aux)
+        self._wrote(y)
         self._ck(self.lib.pctts_conv2d_fwd(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
                                            xp, yp, ap, xb, yb, ab, flags, self._stream()), 'pctts_conv2d_fwd')
 
@@ -189,6 +346,7 @@ class CudaOps(object):
     def bn_apply(self, x, y, mean, invstd_or_var, gamma, beta, eps, use_var, lrelu):
         rows, C = x.shape
         assert x.is_contiguous() and y.is_contiguous()
+        self._wrote(y)
         self._ck(self.lib.pctts_bn_apply(x.data_ptr(), y.data_ptr(), mean.data_ptr(), invstd_or_var.data_ptr(),
                                          gamma.data_ptr(), beta.data_ptr(), rows, C, float(eps), int(use_var), int(lrelu),
                                          self._stream()), 'pctts_bn_apply')
@@ -206,6 +364,7 @@ class CudaOps(object):
                      accumulate=False):
         rows, C = x.shape
         assert dx.is_contiguous()
+        self._wrote(dx)
         self._ck(self.lib.pctts_bn_bwd_apply(x.data_ptr(), dy.data_ptr(), dx.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
                                              gamma.data_ptr(), beta.data_ptr(), rows, C, float(count), int(lrelu),
                                              _ptr(dgamma), _ptr(dbeta), float(grad_scale), int(accumulate), ws.ptr,
@@ -231,6 +390,7 @@ class CudaOps(object):
         for t in list(zx) + list(U):
             assert t.is_contiguous()
         assert hout.is_contiguous() and hout.shape[2] == ndir * H
+        self._wrote(hout)
         self._ck(self.lib.pctts_lstm_fwd(zx[0].data_ptr(), _ptr(z1), U[0].data_ptr(), _ptr(u1), hout.data_ptr(), _ptr(g[0]),
                                          _ptr(g1), _ptr(c[0]), _ptr(c1), B, T, H, ndir, hout.shape[2], cluster_size,
                                          batch_chunk, self._stream()), 'pctts_lstm_fwd')
@@ -241,6 +401,8 @@ class CudaOps(object):
         H = H4 // 4
         u1, g1, c1, d1 = (U[1], gates[1], cstate[1], dz[1]) if ndir == 2 else (None, None, None, None)
         assert dhout.is_contiguous()
+        for t_ in dz:
+            self._wrote(t_)
         self._ck(self.lib.pctts_lstm_bwd(dhout.data_ptr(), U[0].data_ptr(), _ptr(u1), gates[0].data_ptr(), _ptr(g1),
                                          cstate[0].data_ptr(), _ptr(c1), dz[0].data_ptr(), _ptr(d1), B, T, H, ndir,
                                          dhout.shape[2], cluster_size, batch_chunk, self._stream()), 'pctts_lstm_bwd')
@@ -249,11 +411,13 @@ class CudaOps(object):
     def critic_pack_inputs(self, real, fake, alpha, s0, S, off):
         B, T, O = real.shape
         assert real.is_contiguous() and fake.is_contiguous() and s0.is_contiguous() and tuple(s0.shape) == (3 * B, T, S)
+        self._wrote(s0)
         self._ck(self.lib.pctts_critic_pack_inputs(real.data_ptr(), fake.data_ptr(), alpha.data_ptr(), s0.data_ptr(), B, T, O, S,
                                                    off, self._stream()), 'pctts_critic_pack_inputs')
 
     def fill_segments(self, p, n0, v0, n1=0, v1=0.0, n2=0, v2=0.0):
         assert p.is_contiguous() and p.numel() == n0 + n1 + n2
+        self._wrote(p)
         self._ck(self.lib.pctts_fill_segments(p.data_ptr(), n0, float(v0), n1, float(v1), n2, float(v2), self._stream()),
                  'pctts_fill_segments')
 
@@ -270,6 +434,7 @@ class CudaOps(object):
     def gp_scale(self, g, ss, r0, lam, Bglobal, losses, slot):
         B = g.shape[0]
         assert g.is_contiguous() and r0.is_contiguous()
+        self._wrote(r0)
         self._ck(self.lib.pctts_gp_scale(g.data_ptr(), ss.data_ptr(), r0.data_ptr(), B, g.numel() // B, float(lam), int(Bglobal),
                                          losses.data_ptr(), slot, self._stream()), 'pctts_gp_scale')
 
@@ -283,34 +448,40 @@ class CudaOps(object):
         assert pred.is_contiguous() and real.is_contiguous() and (dpred is None or dpred.is_contiguous())
         if self._lse_ws is None:
             self._lse_ws = torch.zeros(self.lib.pctts_lse_workspace_bytes(), dtype=torch.uint8, device=self.device)
+        self._wrote(dpred)
         self._ck(self.lib.pctts_lse_loss_grad(pred.data_ptr(), real.data_ptr(), _ptr(w), _ptr(dpred), rows, O, float(scale_loss),
                                               float(scale_grad), losses.data_ptr(), slot, self._lse_ws.data_ptr(),
                                               self._stream()), 'pctts_lse_loss_grad')
 
     def adam(self, p, g, m, v, lr, beta1, beta2, eps, step):
         assert p.is_contiguous() and g.is_contiguous() and step.dtype == torch.int32
+        self._wrote(p)
         self._ck(self.lib.pctts_adam(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), float(lr), float(beta1),
                                      float(beta2), float(eps), step.data_ptr(), self._stream()), 'pctts_adam')
 
     # -- small movers ----------------------------------------------------------------------------------------
     def add(self, out, a, b):
         assert out.is_contiguous() and a.is_contiguous() and b.is_contiguous()
+        self._wrote(out)
         self._ck(self.lib.pctts_add(out.data_ptr(), a.data_ptr(), b.data_ptr(), out.numel(), self._stream()), 'pctts_add')
 
     def sigmoid_bwd(self, dy, y, dz):
         rows, cols = dy.shape
+        self._wrote(dz)
         self._ck(self.lib.pctts_sigmoid_bwd(dy.data_ptr(), dy.stride(0), y.data_ptr(), y.stride(0), dz.data_ptr(), dz.stride(0),
                                             rows, cols, self._stream()), 'pctts_sigmoid_bwd')
 
     def copy2d(self, dst, src, accumulate=False):
         rows, cols = dst.shape
         assert tuple(src.shape) == (rows, cols)
+        self._wrote(dst)
         self._ck(self.lib.pctts_copy2d(dst.data_ptr(), dst.stride(0), src.data_ptr(), src.stride(0), rows, cols, int(accumulate),
                                        self._stream()), 'pctts_copy2d')
 
     def pad_time(self, dst, src, left, right):
         B, T, C = src.shape
         assert dst.is_contiguous() and src.is_contiguous() and tuple(dst.shape) == (B, T + left + right, C)
+        self._wrote(dst)
         self._ck(self.lib.pctts_pad_time(dst.data_ptr(), src.data_ptr(), B, T, C, left, right, self._stream()), 'pctts_pad_time')
 
     def uniform(self, out, seed, counter):

@@ -63,7 +63,11 @@ class WGANStepper(object):
         return b
 
     # ------------------------------------------------------------------------------------------------------------
-    def critic_step(self, X, Y, alpha=None, apply=True):
+    def critic_step(self, *args, **kw):
+        with self.ops.step_scope():
+            return self._critic_step(*args, **kw)
+
+    def _critic_step(self, X, Y, alpha=None, apply=True):
         """One critic update on device tensors X [B,T,ctx], Y [B,T,O].  alpha [B] overrides the random
         interpolation weights (RandomWeightedAverage, optimizertts_wgan.py:44-51)."""
         o, a, sync = self.ops, self.a, self.sync
@@ -100,7 +104,11 @@ class WGANStepper(object):
             sync.allreduce(self.C.params.grad)
             self.C.params.adam(*self.copt, eps=self.adam_eps)
 
-    def generator_step(self, X, Y, apply=True):
+    def generator_step(self, *args, **kw):
+        with self.ops.step_scope():
+            return self._generator_step(*args, **kw)
+
+    def _generator_step(self, X, Y, apply=True):
         """One generator update (BN moving statistics move here, like in the reference's generator_model)."""
         o, a, sync = self.ops, self.a, self.sync
         B, T, _ = X.shape
@@ -132,7 +140,11 @@ class WGANStepper(object):
             sync.allreduce(self.G.params.grad)
             self.G.params.adam(*self.gopt, eps=self.adam_eps)
 
-    def evaluate_losses(self, X, Y, alpha=None):
+    def evaluate_losses(self, *args, **kw):
+        with self.ops.step_scope():
+            return self._evaluate_losses(*args, **kw)
+
+    def _evaluate_losses(self, X, Y, alpha=None):
         """Critic and generator objectives on one batch in inference mode (BN moving statistics), no update:
         what critic_model.evaluate / generator_model.evaluate return in update_validation_cost (:244-262)."""
         o, a = self.ops, self.a
@@ -164,7 +176,11 @@ class WGANStepper(object):
         else:
             o.loss_combine(self.losses, L_GEN, L_GW, 1.0)
 
-    def predict(self, X, out=None):
+    def predict(self, *args, **kw):
+        with self.ops.step_scope():
+            return self._predict(*args, **kw)
+
+    def _predict(self, X, out=None):
         """Generator inference forward (BN moving statistics): ModelTTS.predict (modeltts.py:68-69)."""
         B, T, _ = X.shape
         gpl = self.G.plan(B, T, with_backward=False)

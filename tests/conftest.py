@@ -19,3 +19,13 @@ def cuda_ops():
         pytest.skip('no CUDA device')
     from percivaltts_b200.ops import CudaOps
     return CudaOps()
+
+
+@pytest.fixture(scope='session')
+def cuda_ops_simt():
+    """Exact-fp32 CUDA-core GEMMs (the tensor-core path has its own tests and tolerances)."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip('no CUDA device')
+    from percivaltts_b200.ops import CudaOps
+    return CudaOps(precision='simt')

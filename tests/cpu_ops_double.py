@@ -51,6 +51,29 @@ class CpuOpsDouble(object):
             self._red[key] = _Ws(C, self.dtype)
         return self._red[key]
 
+    # ---- operand-shadow bookkeeping of the CUDA path: nothing to do here -----------------------------------------
+    def step_scope(self):
+        import contextlib
+        return contextlib.nullcontext(self)
+
+    def register_persistent(self, flat):
+        pass
+
+    def refresh_persistent(self, flat):
+        pass
+
+    # ---- conv1d (virtual im2col) ---------------------------------------------------------------------------------
+    def conv1d(self, xp, kernel, y, T, bias=None, aux=None, flags=0):
+        B, Tp, CIN = xp.shape
+        W, _, COUT = kernel.shape
+        self.gemm(xp.as_strided((B, T, W * CIN), (Tp * CIN, CIN, 1)), kernel.reshape(W * CIN, COUT), y, bias=bias, aux=aux,
+                  flags=flags)
+
+    def conv1d_wgrad(self, xp, dz, dw, T):
+        B, Tp, CIN = xp.shape
+        W, _, COUT = dw.shape
+        self.gemm(xp.as_strided((B, T, W * CIN), (Tp * CIN, CIN, 1)), dz, dw.view(W * CIN, COUT), transA=True)
+
     # ---- gemm ------------------------------------------------------------------------------------------------
     def gemm(self, A, B, C, transA=False, transB=False, alpha=1.0, bias=None, aux=None, addmod=None, flags=0):
         self.launches += 1

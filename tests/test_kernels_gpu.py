@@ -40,7 +40,7 @@ GEMM_CASES = [
 
 
 @pytest.mark.parametrize('M,N,K,ta,tb', GEMM_CASES)
-def test_gemm_plain_and_epilogues(cuda_ops, M, N, K, ta, tb):
+def test_gemm_plain_and_epilogues(cuda_ops_simt, M, N, K, ta, tb):
     A = rnd(K, M) if ta else rnd(M, K)
     B = rnd(N, K, seed=1) if tb else rnd(K, N, seed=1)
     bias, aux, addmod = rnd(N, seed=2), rnd(M, N, seed=3), rnd(max(M // 3, 1), N, seed=4)
@@ -50,12 +50,12 @@ def test_gemm_plain_and_epilogues(cuda_ops, M, N, K, ta, tb):
         want = C0.clone()
         REF.gemm(A, B, want, transA=ta, transB=tb, alpha=0.7, flags=flags, **kw)
         got = dev(C0)
-        cuda_ops.gemm(dev(A), dev(B), got, transA=ta, transB=tb, alpha=0.7, flags=flags,
+        cuda_ops_simt.gemm(dev(A), dev(B), got, transA=ta, transB=tb, alpha=0.7, flags=flags,
                       **dict((k, dev(v)) for k, v in kw.items()))
         close(got, want, 3e-5, ('gemm', flags, list(kw)))
 
 
-def test_gemm_segmented_views_conv1d_im2col(cuda_ops):
+def test_gemm_segmented_views_conv1d_im2col(cuda_ops_simt):
     """Conv1D 'same' as a GEMM over the virtual im2col view of a zero-padded buffer, forward and weight gradient."""
     Bn, T, C, W, H = 3, 29, 11, 5, 13
     xp = torch.zeros(Bn, T + W - 1, C, dtype=torch.float64)
@@ -66,13 +66,13 @@ def test_gemm_segmented_views_conv1d_im2col(cuda_ops):
     REF.gemm(view(xp), k, want)
     got = torch.zeros(Bn * T, H, device='cuda')
     xpd = dev(xp)
-    cuda_ops.gemm(view(xpd), dev(k), got)
+    cuda_ops_simt.gemm(view(xpd), dev(k), got)
     close(got, want, 2e-5, 'conv1d fwd')
     dz = rnd(Bn * T, H, seed=2)
     wantw = torch.zeros(W * C, H, dtype=torch.float64)
     REF.gemm(view(xp), dz, wantw, transA=True)
     gotw = torch.zeros(W * C, H, device='cuda')
-    cuda_ops.gemm(view(xpd), dev(dz), gotw, transA=True)
+    cuda_ops_simt.gemm(view(xpd), dev(dz), gotw, transA=True)
     close(gotw, wantw, 2e-5, 'conv1d wgrad')
     # strided C / sliced 3-D operands (LSTM recurrent-kernel gradient pattern)
     h = rnd(Bn, T, 2 * H, seed=3)
@@ -80,13 +80,13 @@ def test_gemm_segmented_views_conv1d_im2col(cuda_ops):
     wantu = torch.zeros(H, 4 * H, dtype=torch.float64)
     REF.gemm(h[:, 0:T - 1, H:], dzl[:, 1:T], wantu, transA=True)
     gotu = torch.zeros(H, 4 * H, device='cuda')
-    cuda_ops.gemm(dev(h)[:, 0:T - 1, H:], dev(dzl)[:, 1:T], gotu, transA=True)
+    cuda_ops_simt.gemm(dev(h)[:, 0:T - 1, H:], dev(dzl)[:, 1:T], gotu, transA=True)
     close(gotu, wantu, 2e-5, 'lstm dU')
     out = rnd(Bn * T, 7, seed=5)
     wanto = out.clone()
     REF.gemm(h.view(Bn * T, 2 * H), rnd(2 * H, 1, seed=6), wanto[:, 2:3], bias=rnd(1, seed=7))
     goto = dev(out)
-    cuda_ops.gemm(dev(h).view(Bn * T, 2 * H), dev(rnd(2 * H, 1, seed=6)), goto[:, 2:3], bias=dev(rnd(1, seed=7)))
+    cuda_ops_simt.gemm(dev(h).view(Bn * T, 2 * H), dev(rnd(2 * H, 1, seed=6)), goto[:, 2:3], bias=dev(rnd(1, seed=7)))
     close(goto, wanto, 2e-5, 'strided C')
 
 
