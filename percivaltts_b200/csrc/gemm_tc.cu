@@ -48,6 +48,7 @@ struct Params {
     int kb_div;     // k-block index kb -> (kb % kb_div, kb / kb_div)
     int num_kb, kb_per_split;
     int nterms, stages;
+    int chunk_kb;   // k-blocks accumulated in TMEM before the sum is promoted to fp32 registers (round-to-nearest adds)
     // output
     float* C;
     long ldc;
@@ -70,17 +71,21 @@ __device__ __forceinline__ void coords(const Geom& g, int t, int kb_lo, int kb_h
     for (int d = 0; d < 3; ++d) c[d] = tl * g.t_lo[d] + th * g.t_hi[d] + kb_lo * g.k_lo[d] + kb_hi * g.k_hi[d];
 }
 
+constexpr int NUM_THREADS = 192;   // warp 0: TMA producer, warp 1: MMA issuer, warps 2..5: accumulator drain + epilogue
+
 template <int BN>
-__global__ void __launch_bounds__(128, 1)
+__global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const Params p) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
     __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
-    __shared__ __align__(8) uint64_t accum_bar;
+    __shared__ __align__(8) uint64_t acc_full[2];
+    __shared__ __align__(8) uint64_t acc_empty[2];
     __shared__ uint32_t tmem_slot;
 
     constexpr uint32_t B_PLANE_BYTES = BN * BK * 2;
-    const int parts = p.nterms > 1 ? 2 : 1;
+    constexpr int TMEM_COLS = BN == 128 ? 512 : 256;   // main accumulator x2 (ping-pong) + correction accumulator
+    const int parts = p.nterms == 6 ? 3 : (p.nterms == 3 ? 2 : 1);
     const uint32_t stage_bytes = parts * (A_PLANE_BYTES + B_PLANE_BYTES);
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B atoms need 1024-byte alignment
 
@@ -89,6 +94,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     const int kb_begin = blockIdx.z * p.kb_per_split;
     const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
     const int nkb = kb_end - kb_begin;
+    const int CH = p.chunk_kb;
+    const int nchunks = (nkb + CH - 1) / CH;
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&mapA);
@@ -97,134 +104,179 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             mbar_init(smem_u32(&full_bar[s]), 1);
             mbar_init(smem_u32(&empty_bar[s]), 1);
         }
-        mbar_init(smem_u32(&accum_bar), 1);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(smem_u32(&acc_full[b]), 1);
+            mbar_init(smem_u32(&acc_empty[b]), 4);   // one arrival per drain warp
+        }
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc<BN>(smem_u32(&tmem_slot));
+    if (warp == 2) tmem_alloc<TMEM_COLS>(smem_u32(&tmem_slot));
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_acc = tmem_slot;
+    const uint32_t tmem_base = tmem_slot;
+    const uint32_t tmem_corr = tmem_base + 2 * BN;
 
-    if (warp == 0 && lane == 0) {
-        // ---------------- TMA producer ----------------
-        for (int i = 0; i < nkb; ++i) {
-            const int s = i % p.stages;
-            const uint32_t ph = (uint32_t)(i / p.stages) & 1u;
-            mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1u);
-            const uint32_t fb = smem_u32(&full_bar[s]);
-            mbar_arrive_expect_tx(fb, stage_bytes);
-            const int kb = kb_begin + i;
-            const int kb_lo = kb % p.kb_div, kb_hi = kb / p.kb_div;
-            int ca[3], cb[3];
-            coords(p.a, mt, kb_lo, kb_hi, ca);
-            coords(p.b, nt, kb_lo, kb_hi, cb);
-            const uint32_t sa = smem_base + s * stage_bytes;
-            const uint32_t sb = sa + parts * A_PLANE_BYTES;
-            for (int part = 0; part < parts; ++part) {
-                if (!p.a.mn_major) {
-                    tma_load_4d(sa + part * A_PLANE_BYTES, &mapA, fb, ca[0], ca[1], ca[2], part);
-                } else {
+    if (warp == 0) {
+        if (lane == 0) {
+            // ---------------- TMA producer ----------------
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % p.stages;
+                const uint32_t ph = (uint32_t)(i / p.stages) & 1u;
+                mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1u);
+                const uint32_t fb = smem_u32(&full_bar[s]);
+                mbar_arrive_expect_tx(fb, stage_bytes);
+                const int kb = kb_begin + i;
+                const int kb_lo = kb % p.kb_div, kb_hi = kb / p.kb_div;
+                int ca[3], cb[3];
+                coords(p.a, mt, kb_lo, kb_hi, ca);
+                coords(p.b, nt, kb_lo, kb_hi, cb);
+                const uint32_t sa = smem_base + s * stage_bytes;
+                const uint32_t sb = sa + parts * A_PLANE_BYTES;
+                for (int part = 0; part < parts; ++part) {
+                    if (!p.a.mn_major) {
+                        tma_load_4d(sa + part * A_PLANE_BYTES, &mapA, fb, ca[0], ca[1], ca[2], part);
+                    } else {
 #pragma unroll
-                    for (int h = 0; h < BM / 64; ++h)
-                        tma_load_4d(sa + part * A_PLANE_BYTES + h * 8192, &mapA, fb, ca[0] + 64 * h, ca[1], ca[2], part);
-                }
-                if (!p.b.mn_major) {
-                    tma_load_4d(sb + part * B_PLANE_BYTES, &mapB, fb, cb[0], cb[1], cb[2], part);
-                } else {
+                        for (int h = 0; h < BM / 64; ++h)
+                            tma_load_4d(sa + part * A_PLANE_BYTES + h * 8192, &mapA, fb, ca[0] + 64 * h, ca[1], ca[2], part);
+                    }
+                    if (!p.b.mn_major) {
+                        tma_load_4d(sb + part * B_PLANE_BYTES, &mapB, fb, cb[0], cb[1], cb[2], part);
+                    } else {
 #pragma unroll
-                    for (int h = 0; h < BN / 64; ++h)
-                        tma_load_4d(sb + part * B_PLANE_BYTES + h * 8192, &mapB, fb, cb[0] + 64 * h, cb[1], cb[2], part);
+                        for (int h = 0; h < BN / 64; ++h)
+                            tma_load_4d(sb + part * B_PLANE_BYTES + h * 8192, &mapB, fb, cb[0] + 64 * h, cb[1], cb[2], part);
+                    }
                 }
             }
         }
-    } else if (warp == 1 && lane == 0) {
-        // ---------------- MMA issuer ----------------
-        const uint32_t idesc = umma_idesc_bf16(BM, BN, p.a.mn_major, p.b.mn_major);
-        // K-major SW128 tile: rows of 128 B, 8-row groups 1024 B apart (SBO); a K=16 slice is 32 B further along the row.
-        // MN-major SW128 tile: [k][64 mn] rows of 128 B; 8-k groups 1024 B apart (SBO); next 64 mn 8192 B apart (LBO);
-        //                      a K=16 slice is 16 rows = 2048 B further.
-        const uint32_t a_lbo = p.a.mn_major ? 8192u : 16u, a_step = p.a.mn_major ? 2048u : 32u;
-        const uint32_t b_lbo = p.b.mn_major ? 8192u : 16u, b_step = p.b.mn_major ? 2048u : 32u;
-        for (int i = 0; i < nkb; ++i) {
-            const int s = i % p.stages;
-            const uint32_t ph = (uint32_t)(i / p.stages) & 1u;
-            mbar_wait(smem_u32(&full_bar[s]), ph);
-            tc_fence_after();
-            const uint32_t sa = smem_base + s * stage_bytes;
-            const uint32_t sb = sa + parts * A_PLANE_BYTES;
-#pragma unroll
-            for (int k = 0; k < BK / 16; ++k) {
-                const uint64_t ah = umma_smem_desc(sa + k * a_step, a_lbo, 1024u);
-                const uint64_t bh = umma_smem_desc(sb + k * b_step, b_lbo, 1024u);
-                umma_bf16(tmem_acc, ah, bh, idesc, (i | k) != 0);
-                if (parts == 2) {
-                    const uint64_t al = umma_smem_desc(sa + A_PLANE_BYTES + k * a_step, a_lbo, 1024u);
-                    const uint64_t bl = umma_smem_desc(sb + B_PLANE_BYTES + k * b_step, b_lbo, 1024u);
-                    umma_bf16(tmem_acc, ah, bl, idesc, 1u);
-                    umma_bf16(tmem_acc, al, bh, idesc, 1u);
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ---------------- MMA issuer ----------------
+            const uint32_t idesc = umma_idesc_bf16(BM, BN, p.a.mn_major, p.b.mn_major);
+            // K-major SW128 tile: rows of 128 B, 8-row groups 1024 B apart (SBO); a K=16 slice is 32 B further along the row.
+            // MN-major SW128 tile: [k][64 mn] rows of 128 B; 8-k groups 1024 B apart (SBO); next 64 mn 8192 B apart (LBO);
+            //                      a K=16 slice is 16 rows = 2048 B further.
+            const uint32_t a_lbo = p.a.mn_major ? 8192u : 16u, a_step = p.a.mn_major ? 2048u : 32u;
+            const uint32_t b_lbo = p.b.mn_major ? 8192u : 16u, b_step = p.b.mn_major ? 2048u : 32u;
+            uint32_t corr_started = 0;
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % p.stages;
+                const uint32_t ph = (uint32_t)(i / p.stages) & 1u;
+                const int c = i / CH, buf = c & 1;
+                const bool chunk_first = (i - c * CH) == 0;
+                if (chunk_first) {      // the drain warps must have emptied this ping-pong buffer
+                    mbar_wait(smem_u32(&acc_empty[buf]), (((uint32_t)c >> 1) & 1u) ^ 1u);
+                    tc_fence_after();
                 }
-            }
-            umma_commit(smem_u32(&empty_bar[s]));   // stage reusable once these MMAs have read it
-        }
-        umma_commit(smem_u32(&accum_bar));          // accumulator complete
-    }
-    __syncwarp();
-
-    // ---------------- epilogue (all warps; warp w owns TMEM lanes 32w..32w+31 = tile rows) ----------------
-    mbar_wait(smem_u32(&accum_bar), 0);
-    tc_fence_after();
-    const int r = mt * BM + warp * 32 + lane;
-    const int seg = r / p.seg_len, tt = r - seg * p.seg_len;
-    const bool row_ok = tt < p.seg_valid && seg < p.nseg;
-    const long crow = (long)seg * p.seg_valid + tt;
-    const int n0 = nt * BN;
-    const int flags = p.flags;
+                mbar_wait(smem_u32(&full_bar[s]), ph);
+                tc_fence_after();
+                const uint32_t sa = smem_base + s * stage_bytes;
+                const uint32_t sb = sa + parts * A_PLANE_BYTES;
+                const uint32_t tmem_main = tmem_base + buf * BN;
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
-        const int nb = n0 + c * 32;
-        if (nb >= p.N) break;
-        uint32_t v[32];
-        tmem_ld_32x32(tmem_acc + ((uint32_t)(warp * 32) << 16) + (uint32_t)(c * 32), v);
-        tmem_ld_wait();
-        if (!row_ok) continue;
-        if (p.partial) {
-            float* dst = p.partial + ((long)blockIdx.z * p.crows + crow) * p.N + nb;
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-                if (nb + j < p.N) dst[j] = __uint_as_float(v[j]);
-            continue;
-        }
-        float* dst = p.C + crow * p.ldc + nb;
-        const float* auxp = p.aux ? p.aux + crow * p.ldc + nb : nullptr;
-        const float* addp = (flags & PCTTS_EPI_ADDMOD) ? p.addmod + (crow % p.addrows) * (long)p.N + nb : nullptr;
-        float o[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            float x = __uint_as_float(v[j]) * p.alpha;
-            if (nb + j < p.N) {
-                if (flags & PCTTS_EPI_BIAS) x += __ldg(p.bias + nb + j);
-                if (flags & PCTTS_EPI_ADDMOD) x += __ldg(addp + j);
-                if (flags & PCTTS_EPI_LRELU) x = lrelu_f(x);
-                if (flags & PCTTS_EPI_SIGMOID) x = sigmoid_f(x);
-                if (flags & PCTTS_EPI_DLRELU_AUX) x *= dlrelu_from_out(auxp[j]);
-                if (flags & PCTTS_EPI_ACCUM) x += dst[j];
+                for (int k = 0; k < BK / 16; ++k) {
+                    // planes 0 (hi), 1, 2 (lo): every product A_i . B_j with i + j < parts (1, 3 or 6 tcgen05.mma per k-slice).
+                    // hi.hi goes to the chunk accumulator; the corrections (2^-8 and smaller) to their own accumulator, so that
+                    // the tensor core's truncating accumulate costs them nothing.
+                    for (int ia = 0; ia < parts; ++ia) {
+                        const uint64_t ad = umma_smem_desc(sa + ia * A_PLANE_BYTES + k * a_step, a_lbo, 1024u);
+                        for (int ib = 0; ib < parts - ia; ++ib) {
+                            const uint64_t bd = umma_smem_desc(sb + ib * B_PLANE_BYTES + k * b_step, b_lbo, 1024u);
+                            if ((ia | ib) == 0) {
+                                umma_bf16(tmem_main, ad, bd, idesc, (chunk_first && k == 0) ? 0u : 1u);
+                            } else {
+                                umma_bf16(tmem_corr, ad, bd, idesc, corr_started);
+                                corr_started = 1u;
+                            }
+                        }
+                    }
+                }
+                umma_commit(smem_u32(&empty_bar[s]));   // stage reusable once these MMAs have read it
+                if ((i - c * CH) == CH - 1 || i == nkb - 1) umma_commit(smem_u32(&acc_full[buf]));
             }
-            o[j] = x;
         }
-        const bool vec = (nb + 32 <= p.N) && ((((uintptr_t)dst) & 15) == 0);
-        if (vec) {
+    } else {
+        // ---------------- accumulator drain + epilogue: warps 2..5, TMEM lane quarter (warp & 3) ----------------
+        const int q = warp & 3;
+        const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+        float tot[BN];
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
-        } else {
+        for (int j = 0; j < BN; ++j) tot[j] = 0.f;
+        // promote every finished chunk (chunk_kb k-blocks of hi.hi products) into fp32 registers with round-to-nearest adds
+        for (int c = 0; c < nchunks; ++c) {
+            const int buf = c & 1;
+            mbar_wait(smem_u32(&acc_full[buf]), ((uint32_t)c >> 1) & 1u);
+            tc_fence_after();
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-                if (nb + j < p.N) dst[j] = o[j];
+            for (int g = 0; g < BN / 32; ++g) {
+                uint32_t v[32];
+                tmem_ld_32x32(tmem_base + lane_addr + (uint32_t)(buf * BN + g * 32), v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) tot[g * 32 + j] += __uint_as_float(v[j]);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&acc_empty[buf]));
+        }
+        const int r = mt * BM + q * 32 + lane;
+        const int seg = r / p.seg_len, tt = r - seg * p.seg_len;
+        const bool row_ok = tt < p.seg_valid && seg < p.nseg;
+        const long crow = (long)seg * p.seg_valid + tt;
+        const int n0 = nt * BN;
+        const int flags = p.flags;
+#pragma unroll
+        for (int g = 0; g < BN / 32; ++g) {
+            const int nb = n0 + g * 32;
+            if (parts > 1) {
+                uint32_t v[32];
+                tmem_ld_32x32(tmem_corr + lane_addr + (uint32_t)(g * 32), v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) tot[g * 32 + j] += __uint_as_float(v[j]);
+            }
+            if (!row_ok || nb >= p.N) continue;
+            if (p.partial) {
+                float* dst = p.partial + ((long)blockIdx.z * p.crows + crow) * p.N + nb;
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (nb + j < p.N) dst[j] = tot[g * 32 + j];
+                continue;
+            }
+            float* dst = p.C + crow * p.ldc + nb;
+            const float* auxp = p.aux ? p.aux + crow * p.ldc + nb : nullptr;
+            const float* addp = (flags & PCTTS_EPI_ADDMOD) ? p.addmod + (crow % p.addrows) * (long)p.N + nb : nullptr;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                float x = tot[g * 32 + j] * p.alpha;
+                if (nb + j < p.N) {
+                    if (flags & PCTTS_EPI_BIAS) x += __ldg(p.bias + nb + j);
+                    if (flags & PCTTS_EPI_ADDMOD) x += __ldg(addp + j);
+                    if (flags & PCTTS_EPI_LRELU) x = lrelu_f(x);
+                    if (flags & PCTTS_EPI_SIGMOID) x = sigmoid_f(x);
+                    if (flags & PCTTS_EPI_DLRELU_AUX) x *= dlrelu_from_out(auxp[j]);
+                    if (flags & PCTTS_EPI_ACCUM) x += dst[j];
+                }
+                tot[g * 32 + j] = x;
+            }
+            const bool vec = (nb + 32 <= p.N) && ((((uintptr_t)dst) & 15) == 0);
+            if (vec) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4)
+                    *reinterpret_cast<float4*>(dst + j) =
+                        make_float4(tot[g * 32 + j], tot[g * 32 + j + 1], tot[g * 32 + j + 2], tot[g * 32 + j + 3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (nb + j < p.N) dst[j] = tot[g * 32 + j];
+            }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 2) tmem_dealloc<BN>(tmem_acc);
+    if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
 // C (+)= alpha * sum_z partial[z], fixed order (deterministic)
@@ -265,10 +317,17 @@ __global__ void split_bf16_kernel(const float* __restrict__ src, long ld, int se
         hv.y = h1;
         *reinterpret_cast<__nv_bfloat162*>(dst + r * ld_dst + c) = hv;
         if (parts > 1) {
-            __nv_bfloat162 lv;
-            lv.x = __float2bfloat16_rn(x0 - __bfloat162float(h0));
-            lv.y = __float2bfloat16_rn(x1 - __bfloat162float(h1));
-            *reinterpret_cast<__nv_bfloat162*>(dst + part_stride + r * ld_dst + c) = lv;
+            const float r0 = x0 - __bfloat162float(h0), r1 = x1 - __bfloat162float(h1);
+            __nv_bfloat162 mv;
+            mv.x = __float2bfloat16_rn(r0);
+            mv.y = __float2bfloat16_rn(r1);
+            *reinterpret_cast<__nv_bfloat162*>(dst + part_stride + r * ld_dst + c) = mv;
+            if (parts > 2) {
+                __nv_bfloat162 lv;
+                lv.x = __float2bfloat16_rn(r0 - __bfloat162float(mv.x));
+                lv.y = __float2bfloat16_rn(r1 - __bfloat162float(mv.y));
+                *reinterpret_cast<__nv_bfloat162*>(dst + 2 * part_stride + r * ld_dst + c) = lv;
+            }
         }
     }
 }
@@ -299,12 +358,13 @@ int launch_bn(const Launch& L, Params p, cudaStream_t st) {
     if (rc) return rc < 0 ? rc : PCTTS_EINVAL;
     rc = make_map_bf16_4d(&mapB, L.b_base, L.b_dims, L.b_strides, boxB);
     if (rc) return rc < 0 ? rc : PCTTS_EINVAL;
-    const int parts = p.nterms > 1 ? 2 : 1;
+    const int parts = p.nterms == 6 ? 3 : (p.nterms == 3 ? 2 : 1);
     const uint32_t stage_bytes = parts * (A_PLANE_BYTES + BN * BK * 2);
-    int stages = (int)((200u * 1024u) / stage_bytes);
+    int stages = (int)((219u * 1024u) / stage_bytes);
     if (stages > MAX_STAGES) stages = MAX_STAGES;
     if (stages > p.kb_per_split) stages = p.kb_per_split < 2 ? 2 : p.kb_per_split;
     p.stages = stages;
+    p.chunk_kb = p.nterms == 1 ? (1 << 20) : 4;
     const size_t smem = (size_t)stages * stage_bytes + 1024;
     static bool attr_done = false;
     if (!attr_done) {
@@ -312,7 +372,7 @@ int launch_bn(const Launch& L, Params p, cudaStream_t st) {
         attr_done = true;
     }
     dim3 grid((p.N + BN - 1) / BN, L.m_tiles, L.splits);
-    gemm_tc_kernel<BN><<<grid, 128, smem, st>>>(mapA, mapB, p);
+    gemm_tc_kernel<BN><<<grid, NUM_THREADS, smem, st>>>(mapA, mapB, p);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -351,7 +411,7 @@ void plain_geom(Geom& g, int mn_major, int tile) {
 
 extern "C" int pctts_split_bf16(const float* src, long ld, int seg, long segstride, long rows, int cols, void* dst, long ld_dst,
                                 long part_stride, int parts, void* stream) {
-    if (!src || !dst || rows < 0 || cols <= 0 || ld_dst < cols || (ld_dst & 7) || parts < 1 || parts > 2) return PCTTS_EINVAL;
+    if (!src || !dst || rows < 0 || cols <= 0 || ld_dst < cols || (ld_dst & 7) || parts < 1 || parts > 3) return PCTTS_EINVAL;
     if (rows == 0) return PCTTS_OK;
     const long total = rows * (ld_dst / 2);
     int blocks = pctts_div_up(total, 256);
@@ -380,13 +440,13 @@ extern "C" int pctts_gemm_tc(int transA, int transB, int M, int N, int K, float 
                              const void* Bsh, long ldb, long b_part_stride, float* C, long ldc, const float* bias, const float* aux,
                              const float* addmod, int addrows, int flags, int nterms, int splits, float* workspace, void* stream) {
     if (!Ash || !Bsh || !C || M <= 0 || N <= 0 || K <= 0) return PCTTS_EINVAL;
-    if (nterms != 1 && nterms != 3) return PCTTS_EINVAL;
+    if (nterms != 1 && nterms != 3 && nterms != 6) return PCTTS_EINVAL;
     if (flags & PCTTS_EPI_ATOMIC) return PCTTS_EUNSUPPORTED;
     if ((flags & PCTTS_EPI_BIAS) && !bias) return PCTTS_EINVAL;
     if ((flags & PCTTS_EPI_DLRELU_AUX) && !aux) return PCTTS_EINVAL;
     if ((flags & PCTTS_EPI_ADDMOD) && (!addmod || addrows <= 0)) return PCTTS_EINVAL;
     if (splits > 1 && (!workspace || (flags & ~PCTTS_EPI_ACCUM))) return PCTTS_EINVAL;
-    const int parts = nterms > 1 ? 2 : 1;
+    const int parts = nterms == 6 ? 3 : (nterms == 3 ? 2 : 1);
     Launch L;
     Params p;
     L.m_tiles = (M + BM - 1) / BM;
@@ -422,11 +482,11 @@ extern "C" int pctts_conv1d_tc_fwd(const void* xsh, long ldx, long x_part_stride
                                    float* y, long ldy, int B, int T, int W, int CIN, int COUT, const float* bias, const float* aux,
                                    int flags, int nterms, void* stream) {
     if (!xsh || !wsh || !y || B <= 0 || T <= 0 || W <= 0 || CIN <= 0 || COUT <= 0) return PCTTS_EINVAL;
-    if (nterms != 1 && nterms != 3) return PCTTS_EINVAL;
+    if (nterms != 1 && nterms != 3 && nterms != 6) return PCTTS_EINVAL;
     if (flags & (PCTTS_EPI_ATOMIC | PCTTS_EPI_ADDMOD)) return PCTTS_EUNSUPPORTED;
     if ((flags & PCTTS_EPI_BIAS) && !bias) return PCTTS_EINVAL;
     if ((flags & PCTTS_EPI_DLRELU_AUX) && !aux) return PCTTS_EINVAL;
-    const int parts = nterms > 1 ? 2 : 1;
+    const int parts = nterms == 6 ? 3 : (nterms == 3 ? 2 : 1);
     const int Tp = T + W - 1;
     const long rows = (long)B * Tp;
     Launch L;
@@ -466,8 +526,8 @@ extern "C" int pctts_conv1d_tc_fwd(const void* xsh, long ldx, long x_part_stride
 extern "C" int pctts_conv1d_tc_wgrad(const void* xsh, long ldx, long x_part_stride, const void* dzsh, long lddz, long dz_part_stride,
                                      float* dw, int B, int T, int W, int CIN, int COUT, int accumulate, int nterms, void* stream) {
     if (!xsh || !dzsh || !dw || B <= 0 || T <= 0 || W <= 0 || CIN <= 0 || COUT <= 0) return PCTTS_EINVAL;
-    if (nterms != 1 && nterms != 3) return PCTTS_EINVAL;
-    const int parts = nterms > 1 ? 2 : 1;
+    if (nterms != 1 && nterms != 3 && nterms != 6) return PCTTS_EINVAL;
+    const int parts = nterms == 6 ? 3 : (nterms == 3 ? 2 : 1);
     const int Tp = T + W - 1;
     Launch L;
     Params p;

@@ -86,21 +86,27 @@ class Shadow(object):
         return self.buf.data_ptr()
 
 
-PRECISIONS = {'fp32x3': 3, 'bf16': 1, 'simt': 0}
+PRECISIONS = {'fp32': 6, 'fp32x3': 3, 'bf16': 1, 'simt': 0}      # -> tcgen05.mma products per k-slice
+PLANES = {6: 3, 3: 2, 1: 1, 0: 0}
 
 
 class CudaOps(object):
     name = 'cuda'
 
     def __init__(self, device=None, precision=None):
-        """precision: 'fp32x3' (default; tcgen05 GEMMs on bf16 hi/lo splits, three products per k-slice, fp32-grade),
-        'bf16' (tcgen05 GEMMs on single bf16 operands, fp32 accumulate) or 'simt' (exact fp32 CUDA-core GEMMs)."""
+        """precision of the dense contractions (everything else is fp32 CUDA-core arithmetic):
+        'fp32'   (default) tcgen05 GEMMs on three-plane bf16 expansions (24 significand bits), the six products of order
+                 <= 2 per k-slice, fp32 accumulation in TMEM: fp32-grade results (products exact to ~2^-23);
+        'fp32x3' two planes / three products: products exact to ~2^-16 -- faster, inside 1e-3 on outputs and losses but
+                 not on every gradient of an ill-conditioned (tiny batch-norm batch) step;
+        'bf16'   one plane / one product (BASELINE config #3; tolerance stated separately);
+        'simt'   exact fp32 CUDA-core GEMMs (no tensor cores)."""
         if not torch.cuda.is_available():
             raise _lib.PcttsError('percivaltts_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback')
         self.lib = _lib.load()
         self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
         _lib.check(self.lib.pctts_device_check(self.device.index or 0), 'pctts_device_check')
-        precision = precision or os.environ.get('PCTTS_PRECISION', 'fp32x3')
+        precision = precision or os.environ.get('PCTTS_PRECISION', 'fp32')
         if precision not in PRECISIONS:
             raise ValueError('unknown precision %r (one of %s)' % (precision, sorted(PRECISIONS)))
         self.precision = precision
@@ -182,7 +188,7 @@ class CudaOps(object):
         sh = self._shadows.get(key)
         if sh is None:
             _, _, _, _, rows, cols = _mat(t)
-            sh = self._shadows[key] = Shadow(self.device, rows, cols, 2 if self.nterms == 3 else 1)
+            sh = self._shadows[key] = Shadow(self.device, rows, cols, PLANES[self.nterms])
         ptr = key[0]
         if any(lo <= ptr < hi for lo, hi in self._persist_ranges):
             if key not in self._persist:
