@@ -63,6 +63,7 @@ int pctts_split_bf16(const float* src, long ld, int seg, long segstride, long ro
                      long part_stride, int parts, void* stream);
 int pctts_gemm_tc_splits(int M, int N, int K);                 /* host call: recommended split-K factor (1 = none) */
 long pctts_gemm_tc_workspace(int M, int N, int splits);        /* host call: floats of split-K workspace */
+int pctts_gemm_tc_set_trace(void* buf);  /* developer probe: 64*8 int64 clock stamps of CTA (0,0,0) of the next launches; NULL = off */
 /* C[M,N] = epilogue(alpha * op(A) op(B)) from the shadows of the STORED matrices (A: [M,K], or [K,M] when transA; B: [K,N], or
  * [N,K] when transB); C / aux fp32 with row pitch ldc; flags as for pctts_gemm_f32 except ATOMIC; splits > 1 needs the workspace
  * and allows only PCTTS_EPI_ACCUM (deterministic two-stage sum). */

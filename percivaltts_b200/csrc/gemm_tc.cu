@@ -28,6 +28,7 @@
 #include "pctts.h"
 #include "tc_common.cuh"
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -48,6 +49,8 @@ struct Params {
     int kb_div;     // k-block index kb -> (kb % kb_div, kb / kb_div)
     int num_kb, kb_per_split;
     int nterms, stages;
+    long long* trace;   // developer probe: clock64() stamps of CTA (0,0,0), 8 per k-block (pctts_gemm_tc_set_trace)
+    int debug;      // developer probe (PCTTS_TC_DEBUG): 1 = skip the TMA loads, 2 = skip the MMAs
     int chunk_kb;   // k-blocks accumulated in TMEM before the sum is promoted to fp32 registers (round-to-nearest adds)
     // output
     float* C;
@@ -90,6 +93,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B atoms need 1024-byte alignment
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool tr0 = p.trace && (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
+    if (tr0 && threadIdx.x == 0) p.trace[3] = clock64();
     const int nt = blockIdx.x, mt = blockIdx.y;
     const int kb_begin = blockIdx.z * p.kb_per_split;
     const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
@@ -115,68 +120,87 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
+    if (tr0 && threadIdx.x == 0) p.trace[7] = clock64();
     const uint32_t tmem_corr = tmem_base + 2 * BN;
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ---------------- TMA producer ----------------
-            for (int i = 0; i < nkb; ++i) {
-                const int s = i % p.stages;
-                const uint32_t ph = (uint32_t)(i / p.stages) & 1u;
-                mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1u);
-                const uint32_t fb = smem_u32(&full_bar[s]);
-                mbar_arrive_expect_tx(fb, stage_bytes);
-                const int kb = kb_begin + i;
-                const int kb_lo = kb % p.kb_div, kb_hi = kb / p.kb_div;
-                int ca[3], cb[3];
-                coords(p.a, mt, kb_lo, kb_hi, ca);
-                coords(p.b, nt, kb_lo, kb_hi, cb);
-                const uint32_t sa = smem_base + s * stage_bytes;
-                const uint32_t sb = sa + parts * A_PLANE_BYTES;
-                for (int part = 0; part < parts; ++part) {
-                    if (!p.a.mn_major) {
-                        tma_load_4d(sa + part * A_PLANE_BYTES, &mapA, fb, ca[0], ca[1], ca[2], part);
-                    } else {
+        // ---------------- TMA producer (whole warp walks the loop, one elected lane issues) ----------------
+        int s = 0;
+        uint32_t ph = 0;
+        int kb_lo = kb_begin % p.kb_div, kb_hi = kb_begin / p.kb_div;
+        int a0[3], b0[3];
+        coords(p.a, mt, 0, 0, a0);      // tile part of the affine coordinate map; the k-block part is added per iteration
+        coords(p.b, nt, 0, 0, b0);
+        for (int i = 0; i < nkb; ++i) {
+            const bool tr = p.trace && (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && i < 64;
+            if (tr && lane == 0) p.trace[i * 8 + 0] = clock64();
+            mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1u);
+            if (tr && lane == 0) p.trace[i * 8 + 1] = clock64();
+            const uint32_t fb = smem_u32(&full_bar[s]);
+            int ca[3], cb[3];
 #pragma unroll
-                        for (int h = 0; h < BM / 64; ++h)
-                            tma_load_4d(sa + part * A_PLANE_BYTES + h * 8192, &mapA, fb, ca[0] + 64 * h, ca[1], ca[2], part);
-                    }
-                    if (!p.b.mn_major) {
-                        tma_load_4d(sb + part * B_PLANE_BYTES, &mapB, fb, cb[0], cb[1], cb[2], part);
-                    } else {
+            for (int d = 0; d < 3; ++d) {
+                ca[d] = a0[d] + kb_lo * p.a.k_lo[d] + kb_hi * p.a.k_hi[d];
+                cb[d] = b0[d] + kb_lo * p.b.k_lo[d] + kb_hi * p.b.k_hi[d];
+            }
+            const uint32_t sa = smem_base + s * stage_bytes;
+            const uint32_t sb = sa + parts * A_PLANE_BYTES;
+            if (elect_one()) {
+                if (p.debug & 1) {
+                    mbar_arrive(fb);
+                } else {
+                    mbar_arrive_expect_tx(fb, stage_bytes);
+                    for (int part = 0; part < parts; ++part) {
+                        if (!p.a.mn_major) {
+                            tma_load_4d(sa + part * A_PLANE_BYTES, &mapA, fb, ca[0], ca[1], ca[2], part);
+                        } else {
 #pragma unroll
-                        for (int h = 0; h < BN / 64; ++h)
-                            tma_load_4d(sb + part * B_PLANE_BYTES + h * 8192, &mapB, fb, cb[0] + 64 * h, cb[1], cb[2], part);
+                            for (int h = 0; h < BM / 64; ++h)
+                                tma_load_4d(sa + part * A_PLANE_BYTES + h * 8192, &mapA, fb, ca[0] + 64 * h, ca[1], ca[2], part);
+                        }
+                        if (!p.b.mn_major) {
+                            tma_load_4d(sb + part * B_PLANE_BYTES, &mapB, fb, cb[0], cb[1], cb[2], part);
+                        } else {
+#pragma unroll
+                            for (int h = 0; h < BN / 64; ++h)
+                                tma_load_4d(sb + part * B_PLANE_BYTES + h * 8192, &mapB, fb, cb[0] + 64 * h, cb[1], cb[2], part);
+                        }
                     }
                 }
             }
+            __syncwarp();
+            if (tr && lane == 0) p.trace[i * 8 + 2] = clock64();
+            if (++s == p.stages) s = 0, ph ^= 1u;
+            if (++kb_lo == p.kb_div) kb_lo = 0, ++kb_hi;
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ---------------- MMA issuer ----------------
-            const uint32_t idesc = umma_idesc_bf16(BM, BN, p.a.mn_major, p.b.mn_major);
-            // K-major SW128 tile: rows of 128 B, 8-row groups 1024 B apart (SBO); a K=16 slice is 32 B further along the row.
-            // MN-major SW128 tile: [k][64 mn] rows of 128 B; 8-k groups 1024 B apart (SBO); next 64 mn 8192 B apart (LBO);
-            //                      a K=16 slice is 16 rows = 2048 B further.
-            const uint32_t a_lbo = p.a.mn_major ? 8192u : 16u, a_step = p.a.mn_major ? 2048u : 32u;
-            const uint32_t b_lbo = p.b.mn_major ? 8192u : 16u, b_step = p.b.mn_major ? 2048u : 32u;
-            uint32_t corr_started = 0;
-            for (int i = 0; i < nkb; ++i) {
-                const int s = i % p.stages;
-                const uint32_t ph = (uint32_t)(i / p.stages) & 1u;
-                const int c = i / CH, buf = c & 1;
-                const bool chunk_first = (i - c * CH) == 0;
-                if (chunk_first) {      // the drain warps must have emptied this ping-pong buffer
-                    mbar_wait(smem_u32(&acc_empty[buf]), (((uint32_t)c >> 1) & 1u) ^ 1u);
-                    tc_fence_after();
-                }
-                mbar_wait(smem_u32(&full_bar[s]), ph);
-                tc_fence_after();
-                const uint32_t sa = smem_base + s * stage_bytes;
-                const uint32_t sb = sa + parts * A_PLANE_BYTES;
-                const uint32_t tmem_main = tmem_base + buf * BN;
+        // ---------------- MMA issuer (whole warp walks the loop, one elected lane issues) ----------------
+        const uint32_t idesc = umma_idesc_bf16(BM, BN, p.a.mn_major, p.b.mn_major);
+        // K-major SW128 tile: rows of 128 B, 8-row groups 1024 B apart (SBO); a K=16 slice is 32 B further along the row.
+        // MN-major SW128 tile: [k][64 mn] rows of 128 B; 8-k groups 1024 B apart (SBO); next 64 mn 8192 B apart (LBO);
+        //                      a K=16 slice is 16 rows = 2048 B further.
+        const uint32_t a_lbo = p.a.mn_major ? 8192u : 16u, a_step = p.a.mn_major ? 2048u : 32u;
+        const uint32_t b_lbo = p.b.mn_major ? 8192u : 16u, b_step = p.b.mn_major ? 2048u : 32u;
+        const int nk = (p.debug & 2) ? 0 : BK / 16;
+        int s = 0, c = 0, cpos = 0;
+        uint32_t ph = 0;
+        for (int i = 0; i < nkb; ++i) {
+            const int buf = c & 1;
+            const bool chunk_first = cpos == 0;
+            if (chunk_first) {      // the drain warps must have emptied this ping-pong buffer
+                mbar_wait(smem_u32(&acc_empty[buf]), (((uint32_t)c >> 1) & 1u) ^ 1u);
+            }
+            const bool tr = p.trace && (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && i < 64;
+            if (tr && lane == 0) p.trace[i * 8 + 4] = clock64();
+            mbar_wait(smem_u32(&full_bar[s]), ph);
+            tc_fence_after();
+            if (tr && lane == 0) p.trace[i * 8 + 5] = clock64();
+            const uint32_t sa = smem_base + s * stage_bytes;
+            const uint32_t sb = sa + parts * A_PLANE_BYTES;
+            const uint32_t tmem_main = tmem_base + buf * BN;
+            if (elect_one()) {
 #pragma unroll 1
-                for (int k = 0; k < BK / 16; ++k) {
+                for (int k = 0; k < nk; ++k) {
                     // planes 0 (hi), 1, 2 (lo): every product A_i . B_j with i + j < parts (1, 3 or 6 tcgen05.mma per k-slice).
                     // hi.hi goes to the chunk accumulator; the corrections (2^-8 and smaller) to their own accumulator, so that
                     // the tensor core's truncating accumulate costs them nothing.
@@ -184,18 +208,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                         const uint64_t ad = umma_smem_desc(sa + ia * A_PLANE_BYTES + k * a_step, a_lbo, 1024u);
                         for (int ib = 0; ib < parts - ia; ++ib) {
                             const uint64_t bd = umma_smem_desc(sb + ib * B_PLANE_BYTES + k * b_step, b_lbo, 1024u);
-                            if ((ia | ib) == 0) {
+                            if ((ia | ib) == 0)
                                 umma_bf16(tmem_main, ad, bd, idesc, (chunk_first && k == 0) ? 0u : 1u);
-                            } else {
-                                umma_bf16(tmem_corr, ad, bd, idesc, corr_started);
-                                corr_started = 1u;
-                            }
+                            else
+                                umma_bf16(tmem_corr, ad, bd, idesc, (i == 0 && k == 0 && ia == 0 && ib == 1) ? 0u : 1u);
                         }
                     }
                 }
                 umma_commit(smem_u32(&empty_bar[s]));   // stage reusable once these MMAs have read it
-                if ((i - c * CH) == CH - 1 || i == nkb - 1) umma_commit(smem_u32(&acc_full[buf]));
+                if (cpos == CH - 1 || i == nkb - 1) umma_commit(smem_u32(&acc_full[buf]));
             }
+            __syncwarp();
+            if (tr && lane == 0) p.trace[i * 8 + 6] = clock64();
+            if (++s == p.stages) s = 0, ph ^= 1u;
+            if (++cpos == CH) cpos = 0, ++c;
         }
     } else {
         // ---------------- accumulator drain + epilogue: warps 2..5, TMEM lane quarter (warp & 3) ----------------
@@ -221,15 +247,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             __syncwarp();
             if (lane == 0) mbar_arrive(smem_u32(&acc_empty[buf]));
         }
-        const int r = mt * BM + q * 32 + lane;
-        const int seg = r / p.seg_len, tt = r - seg * p.seg_len;
-        const bool row_ok = tt < p.seg_valid && seg < p.nseg;
-        const long crow = (long)seg * p.seg_valid + tt;
-        const int n0 = nt * BN;
-        const int flags = p.flags;
+        if (tr0 && threadIdx.x == 64) p.trace[8 + 3] = clock64();
+        // ---- epilogue, phase 1: add the correction accumulator and park the raw tile in (now idle) pipeline smem, row per thread
+        constexpr int LDS = BN + 4;                     // floats per smem row: 16-byte phases of 8 lanes hit 8 distinct bank groups
+        float* tile = reinterpret_cast<float*>(smem_raw + (smem_base - smem_u32(smem_raw)));
+        long* crow_s = reinterpret_cast<long*>(tile + BM * LDS);
+        const int rl = q * 32 + lane;                   // row inside the tile
+        {
+            const int r = mt * BM + rl;
+            const int seg = r / p.seg_len, tt = r - seg * p.seg_len;
+            crow_s[rl] = (tt < p.seg_valid && seg < p.nseg) ? (long)seg * p.seg_valid + tt : -1;
+        }
 #pragma unroll
         for (int g = 0; g < BN / 32; ++g) {
-            const int nb = n0 + g * 32;
             if (parts > 1) {
                 uint32_t v[32];
                 tmem_ld_32x32(tmem_corr + lane_addr + (uint32_t)(g * 32), v);
@@ -237,46 +267,78 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 #pragma unroll
                 for (int j = 0; j < 32; ++j) tot[g * 32 + j] += __uint_as_float(v[j]);
             }
-            if (!row_ok || nb >= p.N) continue;
-            if (p.partial) {
-                float* dst = p.partial + ((long)blockIdx.z * p.crows + crow) * p.N + nb;
 #pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (nb + j < p.N) dst[j] = tot[g * 32 + j];
-                continue;
+            for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<float4*>(tile + rl * LDS + g * 32 + j) =
+                    make_float4(tot[g * 32 + j], tot[g * 32 + j + 1], tot[g * 32 + j + 2], tot[g * 32 + j + 3]);
+        }
+        if (tr0 && threadIdx.x == 64) p.trace[16 + 7] = clock64();
+        asm volatile("bar.sync 1, 128;" ::: "memory");   // the four epilogue warps only
+        if (tr0 && threadIdx.x == 64) p.trace[24 + 3] = clock64();
+        // ---- phase 2: coalesced pass over the tile.  A thread keeps one group of 4 columns and walks down the rows, so that the
+        //      column-only terms (bias, bounds) are hoisted; the body is kept short on purpose: with one epilogue warp per
+        //      scheduler it runs at dependent-issue latency, and straight-line unrolled code ran at instruction-fetch speed.
+        const int n0 = nt * BN;
+        const int flags = p.flags;
+        const int et = threadIdx.x - 64;                // 0..127
+        constexpr int V = BN / 4;                       // float4 per row
+        constexpr int RSTEP = 128 / V;                  // rows covered by the 128 threads per pass
+        const int c4 = (et % V) * 4, nb = n0 + c4;
+        const int nval = p.N - nb;                      // valid columns of this thread's group (<= 0: nothing to do)
+        if (nval > 0) {
+            const bool full4 = nval >= 4;
+            float bias4[4] = {0.f, 0.f, 0.f, 0.f};
+            if (flags & PCTTS_EPI_BIAS) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (j < nval) bias4[j] = __ldg(p.bias + nb + j);
             }
-            float* dst = p.C + crow * p.ldc + nb;
-            const float* auxp = p.aux ? p.aux + crow * p.ldc + nb : nullptr;
-            const float* addp = (flags & PCTTS_EPI_ADDMOD) ? p.addmod + (crow % p.addrows) * (long)p.N + nb : nullptr;
+            const float alpha = p.alpha;
+            const long ldo = p.partial ? (long)p.N : p.ldc;
+            float* const obase = p.partial ? p.partial + (long)blockIdx.z * p.crows * p.N + nb : p.C + nb;
+            const int eflags = p.partial ? 0 : flags;
+            const bool ovec = full4 && ((ldo & 3) == 0) && ((((uintptr_t)obase) & 15) == 0);
+#pragma unroll 1
+            for (int row = et / V; row < BM; row += RSTEP) {
+                const long crow = crow_s[row];
+                if (crow < 0) continue;
+                const float4 t4 = *reinterpret_cast<const float4*>(tile + row * LDS + c4);
+                float x[4] = {t4.x, t4.y, t4.z, t4.w};
+                float* dst = obase + crow * ldo;
+                if (eflags | (alpha != 1.f)) {
+                    const float* auxp = (eflags & PCTTS_EPI_DLRELU_AUX) ? p.aux + crow * p.ldc + nb : nullptr;
+                    const float* addp = (eflags & PCTTS_EPI_ADDMOD) ? p.addmod + (long)((int)crow % p.addrows) * p.N + nb : nullptr;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                float x = tot[g * 32 + j] * p.alpha;
-                if (nb + j < p.N) {
-                    if (flags & PCTTS_EPI_BIAS) x += __ldg(p.bias + nb + j);
-                    if (flags & PCTTS_EPI_ADDMOD) x += __ldg(addp + j);
-                    if (flags & PCTTS_EPI_LRELU) x = lrelu_f(x);
-                    if (flags & PCTTS_EPI_SIGMOID) x = sigmoid_f(x);
-                    if (flags & PCTTS_EPI_DLRELU_AUX) x *= dlrelu_from_out(auxp[j]);
-                    if (flags & PCTTS_EPI_ACCUM) x += dst[j];
+                    for (int j = 0; j < 4; ++j) {
+                        if (j < nval) {
+                            float y = x[j];
+                            if (!p.partial) y *= alpha;
+                            y += bias4[j];
+                            if (eflags & PCTTS_EPI_ADDMOD) y += __ldg(addp + j);
+                            if (eflags & PCTTS_EPI_LRELU) y = lrelu_f(y);
+                            if (eflags & PCTTS_EPI_SIGMOID) y = sigmoid_f(y);
+                            if (eflags & PCTTS_EPI_DLRELU_AUX) y *= dlrelu_from_out(auxp[j]);
+                            if (eflags & PCTTS_EPI_ACCUM) y += dst[j];
+                            x[j] = y;
+                        }
+                    }
                 }
-                tot[g * 32 + j] = x;
-            }
-            const bool vec = (nb + 32 <= p.N) && ((((uintptr_t)dst) & 15) == 0);
-            if (vec) {
+                if (p.debug & 8) continue;
+                if (ovec) {
+                    *reinterpret_cast<float4*>(dst) = make_float4(x[0], x[1], x[2], x[3]);
+                } else {
 #pragma unroll
-                for (int j = 0; j < 32; j += 4)
-                    *reinterpret_cast<float4*>(dst + j) =
-                        make_float4(tot[g * 32 + j], tot[g * 32 + j + 1], tot[g * 32 + j + 2], tot[g * 32 + j + 3]);
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (nb + j < p.N) dst[j] = tot[g * 32 + j];
+                    for (int j = 0; j < 4; ++j)
+                        if (j < nval) dst[j] = x[j];
+                }
             }
         }
     }
+    if (tr0 && threadIdx.x == 64) p.trace[8 + 7] = clock64();
     tc_fence_before();
     __syncthreads();
     if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
+    if (tr0 && threadIdx.x == 64) p.trace[16 + 3] = clock64();
 }
 
 // C (+)= alpha * sum_z partial[z], fixed order (deterministic)
@@ -332,6 +394,8 @@ __global__ void split_bf16_kernel(const float* __restrict__ src, long ld, int se
     }
 }
 
+long long* g_trace = nullptr;
+
 struct Launch {
     const void* a_base;
     uint64_t a_dims[4];
@@ -365,7 +429,13 @@ int launch_bn(const Launch& L, Params p, cudaStream_t st) {
     if (stages > p.kb_per_split) stages = p.kb_per_split < 2 ? 2 : p.kb_per_split;
     p.stages = stages;
     p.chunk_kb = p.nterms == 1 ? (1 << 20) : 4;
-    const size_t smem = (size_t)stages * stage_bytes + 1024;
+    static const int dbg = getenv("PCTTS_TC_DEBUG") ? atoi(getenv("PCTTS_TC_DEBUG")) : 0;
+    p.debug = dbg;
+    p.trace = g_trace;
+    size_t smem = (size_t)stages * stage_bytes;
+    const size_t epi = (size_t)BM * (BN + 4) * 4 + BM * 8;      // the epilogue parks the output tile in the pipeline smem
+    if (smem < epi) smem = epi;
+    smem += 1024;
     static bool attr_done = false;
     if (!attr_done) {
         PCTTS_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
@@ -419,6 +489,12 @@ extern "C" int pctts_split_bf16(const float* src, long ld, int seg, long segstri
     split_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(src, ld, seg, segstride, rows, cols, (__nv_bfloat16*)dst, ld_dst,
                                                                 part_stride, parts);
     PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
+/* developer probe: device buffer of 64*8 int64 receiving clock64() stamps of CTA (0,0,0); NULL switches it off */
+extern "C" int pctts_gemm_tc_set_trace(void* buf) {
+    g_trace = (long long*)buf;
     return PCTTS_OK;
 }
 
