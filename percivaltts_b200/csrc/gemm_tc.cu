@@ -76,7 +76,7 @@ __device__ __forceinline__ void coords(const Geom& g, int t, int kb_lo, int kb_h
 
 constexpr int NUM_THREADS = 192;   // warp 0: TMA producer, warp 1: MMA issuer, warps 2..5: accumulator drain + epilogue
 
-template <int BN>
+template <int BN, int PARTS>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const Params p) {
     extern __shared__ uint8_t smem_raw[];
@@ -88,8 +88,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 
     constexpr uint32_t B_PLANE_BYTES = BN * BK * 2;
     constexpr int TMEM_COLS = BN == 128 ? 512 : 256;   // main accumulator x2 (ping-pong) + correction accumulator
-    const int parts = p.nterms == 6 ? 3 : (p.nterms == 3 ? 2 : 1);
-    const uint32_t stage_bytes = parts * (A_PLANE_BYTES + B_PLANE_BYTES);
+    constexpr int parts = PARTS;                       // bf16 planes per operand: 1 (bf16), 2 (fp32x3), 3 (fp32)
+    constexpr uint32_t stage_bytes = parts * (A_PLANE_BYTES + B_PLANE_BYTES);
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B atoms need 1024-byte alignment
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -179,9 +179,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         // K-major SW128 tile: rows of 128 B, 8-row groups 1024 B apart (SBO); a K=16 slice is 32 B further along the row.
         // MN-major SW128 tile: [k][64 mn] rows of 128 B; 8-k groups 1024 B apart (SBO); next 64 mn 8192 B apart (LBO);
         //                      a K=16 slice is 16 rows = 2048 B further.
-        const uint32_t a_lbo = p.a.mn_major ? 8192u : 16u, a_step = p.a.mn_major ? 2048u : 32u;
-        const uint32_t b_lbo = p.b.mn_major ? 8192u : 16u, b_step = p.b.mn_major ? 2048u : 32u;
-        const int nk = (p.debug & 2) ? 0 : BK / 16;
+        const uint32_t a_lbo = p.a.mn_major ? 8192u : 16u, a_step16 = p.a.mn_major ? 128u : 2u;
+        const uint32_t b_lbo = p.b.mn_major ? 8192u : 16u, b_step16 = p.b.mn_major ? 128u : 2u;
+        // descriptor of plane 0 / stage 0 / k-slice 0; the others differ only in the 14-bit start-address field (no carry out)
+        const uint64_t adesc0 = umma_smem_desc(smem_base, a_lbo, 1024u);
+        const uint64_t bdesc0 = umma_smem_desc(smem_base + parts * A_PLANE_BYTES, b_lbo, 1024u);
         int s = 0, c = 0, cpos = 0;
         uint32_t ph = 0;
         for (int i = 0; i < nkb; ++i) {
@@ -195,23 +197,26 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             mbar_wait(smem_u32(&full_bar[s]), ph);
             tc_fence_after();
             if (tr && lane == 0) p.trace[i * 8 + 5] = clock64();
-            const uint32_t sa = smem_base + s * stage_bytes;
-            const uint32_t sb = sa + parts * A_PLANE_BYTES;
+            const uint32_t soff = (uint32_t)s * (stage_bytes >> 4);     // descriptors address smem in 16-byte units
             const uint32_t tmem_main = tmem_base + buf * BN;
             if (elect_one()) {
-#pragma unroll 1
-                for (int k = 0; k < nk; ++k) {
-                    // planes 0 (hi), 1, 2 (lo): every product A_i . B_j with i + j < parts (1, 3 or 6 tcgen05.mma per k-slice).
-                    // hi.hi goes to the chunk accumulator; the corrections (2^-8 and smaller) to their own accumulator, so that
-                    // the tensor core's truncating accumulate costs them nothing.
-                    for (int ia = 0; ia < parts; ++ia) {
-                        const uint64_t ad = umma_smem_desc(sa + ia * A_PLANE_BYTES + k * a_step, a_lbo, 1024u);
-                        for (int ib = 0; ib < parts - ia; ++ib) {
-                            const uint64_t bd = umma_smem_desc(sb + ib * B_PLANE_BYTES + k * b_step, b_lbo, 1024u);
-                            if ((ia | ib) == 0)
-                                umma_bf16(tmem_main, ad, bd, idesc, (chunk_first && k == 0) ? 0u : 1u);
-                            else
-                                umma_bf16(tmem_corr, ad, bd, idesc, (i == 0 && k == 0 && ia == 0 && ib == 1) ? 0u : 1u);
+                if (!(p.debug & 2)) {
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {
+                        // planes 0 (hi), 1, 2 (lo): every product A_i . B_j with i + j < parts (1, 3 or 6 tcgen05.mma per
+                        // k-slice).  hi.hi goes to the chunk accumulator; the corrections (2^-8 and smaller) to their own
+                        // accumulator, so that the tensor core's truncating accumulate costs them nothing.
+#pragma unroll
+                        for (int ia = 0; ia < parts; ++ia) {
+                            const uint64_t ad = adesc0 + soff + (uint32_t)(ia * (A_PLANE_BYTES >> 4)) + (uint32_t)k * a_step16;
+#pragma unroll
+                            for (int ib = 0; ib < parts - ia; ++ib) {
+                                const uint64_t bd = bdesc0 + soff + (uint32_t)(ib * (B_PLANE_BYTES >> 4)) + (uint32_t)k * b_step16;
+                                if ((ia | ib) == 0)
+                                    umma_bf16(tmem_main, ad, bd, idesc, (chunk_first && k == 0) ? 0u : 1u);
+                                else
+                                    umma_bf16(tmem_corr, ad, bd, idesc, (i == 0 && k == 0 && ia == 0 && ib == 1) ? 0u : 1u);
+                            }
                         }
                     }
                 }
@@ -413,7 +418,7 @@ int pick_bn(int m_tiles, int N) {
     return t128 >= 100 ? 128 : 64;
 }
 
-template <int BN>
+template <int BN, int PARTS>
 int launch_bn(const Launch& L, Params p, cudaStream_t st) {
     CUtensorMap mapA, mapB;
     const uint32_t boxA[4] = {64u, p.a.mn_major ? 64u : (uint32_t)BM, 1u, 1u};
@@ -422,7 +427,7 @@ int launch_bn(const Launch& L, Params p, cudaStream_t st) {
     if (rc) return rc < 0 ? rc : PCTTS_EINVAL;
     rc = make_map_bf16_4d(&mapB, L.b_base, L.b_dims, L.b_strides, boxB);
     if (rc) return rc < 0 ? rc : PCTTS_EINVAL;
-    const int parts = p.nterms == 6 ? 3 : (p.nterms == 3 ? 2 : 1);
+    constexpr int parts = PARTS;
     const uint32_t stage_bytes = parts * (A_PLANE_BYTES + BN * BK * 2);
     int stages = (int)((219u * 1024u) / stage_bytes);
     if (stages > MAX_STAGES) stages = MAX_STAGES;
@@ -438,17 +443,20 @@ int launch_bn(const Launch& L, Params p, cudaStream_t st) {
     smem += 1024;
     static bool attr_done = false;
     if (!attr_done) {
-        PCTTS_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        PCTTS_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, PARTS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         attr_done = true;
     }
     dim3 grid((p.N + BN - 1) / BN, L.m_tiles, L.splits);
-    gemm_tc_kernel<BN><<<grid, NUM_THREADS, smem, st>>>(mapA, mapB, p);
+    gemm_tc_kernel<BN, PARTS><<<grid, NUM_THREADS, smem, st>>>(mapA, mapB, p);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
 
 int launch_tc(const Launch& L, Params p, int bn, float* C, long ldc, float alpha, int accum, cudaStream_t st) {
-    int rc = bn == 128 ? launch_bn<128>(L, p, st) : launch_bn<64>(L, p, st);
+    int rc;
+    if (p.nterms == 6) rc = bn == 128 ? launch_bn<128, 3>(L, p, st) : launch_bn<64, 3>(L, p, st);
+    else if (p.nterms == 3) rc = bn == 128 ? launch_bn<128, 2>(L, p, st) : launch_bn<64, 2>(L, p, st);
+    else rc = bn == 128 ? launch_bn<128, 1>(L, p, st) : launch_bn<64, 1>(L, p, st);
     if (rc) return rc;
     if (p.partial) {
         const long total = p.crows * p.N;

@@ -102,8 +102,8 @@ def test_critic_and_generator_step_vs_oracle(cuda_ops, kw, B, T):
 def test_training_trajectory_vs_oracle(cuda_ops):
     """Six batches of the train_on_batch policy with Adam updates: weights stay within fp32 tolerance of the fp64
     oracle trainer (optimizertts_wgan.py:216-241).  Adam's first updates are ~lr*sign(g): an element whose gradient is at
-    round-off level moves by +-lr per step in ANY fp32 evaluation, so the per-tensor criterion is the relative L2 distance
-    (2e-3); single elements may differ by a few lr (max-norm bound 1e-2)."""
+    round-off level moves by +-lr per step in ANY fp32 evaluation, so the criterion is the relative L2 distance over all
+    the weights of a network (2e-3); single elements may differ by a few lr (per-tensor max-norm bound 1e-2)."""
     ao, wg, wc, wgt, wct, X, Y, alpha, st = setup(cuda_ops, MID, 2, 40)
     tr = O.OracleTrainer(ao, wg, wc, dtype=torch.float64)
     gu = 0
@@ -117,13 +117,14 @@ def test_training_trajectory_vs_oracle(cuda_ops):
             st.generator_step(Xd, Yd)
             gu += 1
     assert gu == tr.generator_updates
-    def l2err(got, want):
-        got, want = got.detach().cpu().double(), want.detach().double()
-        return float(((got - want) ** 2).sum() ** 0.5 / ((want ** 2).sum() ** 0.5 + 1e-30))
     for store, ref in ((st.C.params, tr.wc), (st.G.params, tr.wg)):
+        num = den = 0.0
         for k, v in ref.items():
-            assert l2err(store.p[k], v) < 2e-3, (k, l2err(store.p[k], v))
-            assert relerr(store.p[k], v) < 1e-2, (k, relerr(store.p[k], v))
+            got, want = store.p[k].detach().cpu().double(), v.detach().double()
+            num += float(((got - want) ** 2).sum())
+            den += float((want ** 2).sum())
+            assert relerr(got, want) < 1e-2, (k, relerr(got, want))
+        assert (num / den) ** 0.5 < 2e-3, (num / den) ** 0.5
 
 
 def test_inference_predict_and_validation_losses(cuda_ops):
