@@ -14,3 +14,8 @@ if [ "$1" == "ncu" ]; then
   ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/launches.csv python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/ncu.log 2>&1
   echo "ncu rc=$?"; tail -3 gpurun_out/ncu.log; wc -l gpurun_out/launches.csv
 fi
+if [ "$2" == "full" ]; then
+  # one --set full capture of the top kernels (after the plain run above exited 0)
+  ncu --set full --clock-control none --import-source on -k regex:"${3:-gemm_tc}" -s 40 -c 3 -o gpurun_out/prof_full python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
+  echo "ncu full rc=$?"; tail -3 gpurun_out/ncu_full.log
+fi
