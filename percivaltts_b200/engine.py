@@ -173,9 +173,12 @@ class Generator(object):
         else:
             o.bn_apply(z2, y2, mm, mv, g, b, A.BN_EPS, 1, 1)
 
-    def forward(self, pl, ctx, out, training=True, update_stats=False, sync=None):
+    def forward(self, pl, ctx, out, training=True, update_stats=False, sync=None, spec_only=False):
         """ctx [B,T,ctxsize] -> out [B,T,O] (both contiguous device tensors).  training: BN uses batch statistics
-        (all-reduced through `sync`); update_stats: also move the BN moving averages (generator step only)."""
+        (all-reduced through `sync`); update_stats: also move the BN moving averages (generator step only).
+        spec_only: evaluate the ctx trunk and the spectral branch only and leave the F0 / noise-mask columns of `out`
+        untouched -- the critic reads nothing but out[:,:,1:1+S] (networks_critic.py:58), so in the critic step the two
+        other branches cannot influence any returned loss or updated weight."""
         o, a, p = self.ops, self.a, self.params.p
         sync = sync or LocalSync()
         B, T, M = pl['B'], pl['T'], pl['M']
@@ -196,11 +199,12 @@ class Generator(object):
         lctx = x2
         out2 = out.view(M, O)
         # F0: Bidirectional LSTM + Dense(1)   (modeltts_common.py:82-84, networktts.py:85-96)
-        for d, dn in enumerate(('fw', 'bw')):
-            o.gemm(lctx, p['g.f0.blstm.%s.kernel' % dn], pl['zx'][d].view(M, 4 * H), bias=p['g.f0.blstm.%s.bias' % dn])
-        o.lstm_fwd(pl['zx'], [p['g.f0.blstm.fw.recurrent'], p['g.f0.blstm.bw.recurrent']], pl['hout'], pl['gates'],
-                   pl['cstate'])
-        o.gemm(pl['hout'].view(M, 2 * H), p['g.f0.out.kernel'], out2[:, 0:1], bias=p['g.f0.out.bias'])
+        if not spec_only:
+            for d, dn in enumerate(('fw', 'bw')):
+                o.gemm(lctx, p['g.f0.blstm.%s.kernel' % dn], pl['zx'][d].view(M, 4 * H), bias=p['g.f0.blstm.%s.bias' % dn])
+            o.lstm_fwd(pl['zx'], [p['g.f0.blstm.fw.recurrent'], p['g.f0.blstm.bw.recurrent']], pl['hout'], pl['gates'],
+                       pl['cstate'])
+            o.gemm(pl['hout'].view(M, 2 * H), p['g.f0.out.kernel'], out2[:, 0:1], bias=p['g.f0.out.bias'])
         # Spec: Dense projection, [B,T,S,1] map, pCNN2D stack, Conv2D(1)   (modeltts_common.py:95-101)
         o.gemm(lctx, p['g.spec.proj.kernel'], pl['s'], bias=p['g.spec.proj.bias'])
         amap = pl['s'].view(B, T, S, 1)
@@ -212,11 +216,12 @@ class Generator(object):
         o.conv2d(amap, p['g.spec.out.kernel'], out[:, :, 1:1 + S].unsqueeze(-1), bias=p['g.spec.out.bias'])
         # NM: pFC x (L//2), Dense(sigmoid)   (modeltts_common.py:117-121)
         n2 = lctx
-        for i in range(a.gen_nbcnnlayers // 2):
+        for i in range(0 if spec_only else a.gen_nbcnnlayers // 2):
             o.gemm(n2, p['g.nm.fc%d.kernel' % i], pl['nm_z'][i])
             self._bn_fwd(pl['nm_z'][i], pl['nm_y'][i], pl['nm_bn'][i], training, update_stats, sync)
             n2 = pl['nm_y'][i]
-        o.gemm(n2, p['g.nm.out.kernel'], out2[:, 1 + S:], bias=p['g.nm.out.bias'], flags=EPI_SIGMOID)
+        if not spec_only:
+            o.gemm(n2, p['g.nm.out.kernel'], out2[:, 1 + S:], bias=p['g.nm.out.bias'], flags=EPI_SIGMOID)
         pl['lctx'], pl['ctx_in'] = lctx, ctx
         return out
 

@@ -29,7 +29,8 @@ def critic_runs(generator_updates):
 class WGANStepper(object):
     def __init__(self, ops, arch, generator=None, critic=None, errtype='WLSWGAN', sync=None,
                  critic_lr=1e-4, critic_beta1=0.5, critic_beta2=0.9, gen_lr=1e-3, gen_beta1=0.5, gen_beta2=0.9,
-                 gp_lambda=10.0, w_ls=None, w_wgan_mean=1.0, adam_eps=1e-7, seed=123):
+                 gp_lambda=10.0, w_ls=None, w_wgan_mean=1.0, adam_eps=1e-7, seed=123,
+                 critic_step_full_generator=False):
         if errtype not in ('WGAN', 'WLSWGAN'):
             raise ValueError('unknown errtype ' + str(errtype))
         self.ops, self.a, self.errtype = ops, arch, errtype
@@ -40,6 +41,8 @@ class WGANStepper(object):
         self.gopt = (gen_lr, gen_beta1, gen_beta2)
         self.adam_eps = adam_eps
         self.lam = float(gp_lambda)
+        # False: the frozen generator of the critic step evaluates only what the critic reads (the spectral branch)
+        self.critic_step_full_generator = bool(critic_step_full_generator)
         self.wbar = float(w_wgan_mean)
         self.w_ls = None
         if errtype == 'WLSWGAN':
@@ -76,7 +79,8 @@ class WGANStepper(object):
         bf = self.buffers(B, T)
         gpl = self.G.plan(B, T)
         # frozen generator, learning phase 1: batch statistics, no moving-average update (:121-128)
-        self.G.forward(gpl, X, bf['fake'], training=True, update_stats=False, sync=sync)
+        self.G.forward(gpl, X, bf['fake'], training=True, update_stats=False, sync=sync,
+                       spec_only=not self.critic_step_full_generator)
         if alpha is None:
             o.uniform(bf['alpha'], self.seed, self.counter)
             alpha = bf['alpha']
