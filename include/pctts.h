@@ -87,6 +87,13 @@ int pctts_conv1d_tc_wgrad(const void* xsh, long ldx, long x_part_stride, const v
 int pctts_conv2d_fwd(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T, int F,
                      int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch, long auxpitch,
                      long xbatch, long ybatch, long auxbatch, int flags, void* stream);
+/* The same convolution for CIN = COUT = 4, 5x5, pad 2 as an implicit GEMM on the tensor cores (tcgen05.mma + TMEM; the input tile
+ * is staged once in shared memory as bf16 planes and read in place as the im2col operand).  nterms as for pctts_gemm_tc.
+ * Bases must be 16-byte aligned and pitches multiples of 4 floats; pctts_conv2d_tc_supported() is a host call. */
+int pctts_conv2d_tc_supported(int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f);
+int pctts_conv2d_tc_fwd(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T, int F,
+                        int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch, long auxpitch,
+                        long xbatch, long ybatch, long auxbatch, int flags, int nterms, void* stream);
 int pctts_conv2d_flip_weights(const float* w, float* wt, int KH, int KW, int CIN, int COUT, void* stream);
 long pctts_conv2d_wgrad_workspace(int NB, int T, int CIN, int COUT, int KH, int KW); /* floats; host call */
 /* dw[kt,kf,ci,co] (+)= scale * sum_{n,t,f} x[n,t+kt-pad_t,f+kf-pad_f,ci] dy[n,t,f,co]   (deterministic two-stage) */

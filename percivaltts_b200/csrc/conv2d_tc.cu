@@ -1,0 +1,403 @@
+// Conv2D 5x5 'same', 4 -> 4 channels, NHWC, as an implicit GEMM on the 5th-generation tensor cores (tcgen05.mma, TMEM).
+//
+// Reference ops: the pCNN2D stack of the generator (networktts.py:122-126, modeltts_common.py:98) and the Conv2D stack of the
+// critic (networks_critic.py:66-68), forward; with flipped kernels the data gradient; with a LeakyReLU' mask the
+// forward-mode (tangent) sweep of the gradient penalty.
+//
+// Formulation.  One accumulator row = 4 consecutive output pixels of a frame row; its 16 columns are (pixel jo, channel co) --
+// exactly the NHWC order of the 64 output bytes.  For one kernel row kt the 4 outputs read a window of 8 input pixels x 4
+// channels = 32 values, so K = 5 x 32 = 160 and the weight operand is the block-Toeplitz matrix
+//     Bmat[(kt, u, ci), (jo, co)] = w[kt, u - jo, ci, co]   (0 <= u - jo < 5, else 0),      u = 0..7.
+// The activation operand is never expanded: the input tile lives in shared memory as bf16 NHWC pixel PAIRS (16 bytes =
+// one UMMA core-matrix row), de-interleaved by pair parity into two arrays.  Accumulator rows r, r+1, .. are 4 pixels = 2 pairs
+// apart, i.e. consecutive entries of one parity array: a K-major no-swizzle core matrix (8 rows x 16 B) is 8 consecutive
+// entries, and the 4 chunks of a window alternate between the arrays.  The UMMA shared-memory descriptor expresses this with
+// SBO = 128 B (next 8 rows) and LBO = (even array - odd array) + 16 B (next chunk): an im2col matrix that is 10x larger than
+// the tile is read in place.
+//
+// Numerics (see gemm_tc.cu): fp32 operands are expanded into `PARTS` bf16 planes; the weight planes are concatenated along N
+// ([B0 | B1 | B2], 48 columns), so one MMA per activation plane forms the products with every weight plane it needs
+// (orders i + j <= PARTS-1).  hi.hi lands in its own 16 accumulator columns; the corrections share the two other blocks.
+//
+// Structure (persistent CTAs, one per SM; a tile = TT output frame rows of one sample):
+//   warps 0-3  producers   fp32 global -> bf16 planes, pair arrays of a 2-stage ring, fence.proxy.async, mbarrier arrive
+//   warp  4    MMA issuer  per 128-row block: 5 kt x 2 halves x PARTS tcgen05.mma; tcgen05.commit frees the stage / signals
+//   warps 5-8  epilogue    tcgen05.ld (TMEM lane quarter = warp % 4), sum of the column blocks, bias / LeakyReLU / LeakyReLU'
+//                          mask / accumulate, 64-byte stores; TMEM accumulators are double-buffered across tiles
+#include "common.cuh"
+#include "pctts.h"
+#include "tc_common.cuh"
+#include <cuda_bf16.h>
+
+namespace {
+
+using namespace tcx;
+
+constexpr int C2_THREADS = 288;          // 9 warps
+constexpr int C2_PROD = 128;             // producer threads
+constexpr int C2_MAXBLK = 5;             // 128-row blocks per tile (48 TMEM columns each, two buffers: 480 of 512 columns)
+constexpr int C2_TMEM_COLS = 512;
+constexpr int KT = 5, KW5 = 5;
+constexpr int NMMA = KT * 2;             // (kt, half) k-steps of 16
+
+struct C2Params {
+    const float* x;
+    const float* w;      // [5][5][4][4]
+    const float* bias;
+    const float* aux;
+    float* y;
+    int NB, T, F;
+    int G;               // 4-pixel groups per padded row (Fp = 4G >= F + 2)
+    int TT;              // output rows per tile
+    int tiles_per_sample, ntiles;
+    int nblk;            // 128-row blocks per tile
+    int entries;         // 16-byte entries per parity array
+    long xpitch, ypitch, auxpitch, xbatch, ybatch, auxbatch;
+    int flags;
+};
+
+// shared-memory matrix descriptor, no swizzle (INTERLEAVE), K-major: core matrix = 8 rows x 16 bytes, contiguous
+__device__ __forceinline__ uint64_t umma_desc_noswz(uint32_t addr, uint32_t lbo, uint32_t sbo) {
+    uint64_t d = 0;
+    d |= (uint64_t)((addr >> 4) & 0x3FFF);
+    d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;
+    return d;
+}
+
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(__nv_bfloat16 a, __nv_bfloat16 b) {
+    return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);
+}
+
+// 8 floats (2 pixels x 4 channels) -> PARTS 16-byte bf16 entries
+template <int PARTS>
+__device__ __forceinline__ void split8(const float (&v)[8], uint4 (&out)[PARTS]) {
+    uint32_t w[PARTS][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float a = v[2 * i], b = v[2 * i + 1];
+#pragma unroll
+        for (int p = 0; p < PARTS; ++p) {
+            const __nv_bfloat16 ha = __float2bfloat16_rn(a), hb = __float2bfloat16_rn(b);
+            w[p][i] = pack_bf16(ha, hb);
+            a -= __bfloat162float(ha);
+            b -= __bfloat162float(hb);
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < PARTS; ++p) out[p] = make_uint4(w[p][0], w[p][1], w[p][2], w[p][3]);
+}
+
+// shared-memory carve-up (bytes, 16-byte aligned):
+//   Bmat   NMMA x [2 chunks][16*PARTS rows][16 B]
+//   stage s, plane p: odd array [entries][16 B] | even array [entries][16 B]
+template <int PARTS>
+struct C2Smem {
+    static constexpr uint32_t b_rows = 16 * PARTS;
+    static constexpr uint32_t b_chunk = b_rows * 16;         // LBO of the weight operand
+    static constexpr uint32_t b_mma = 2 * b_chunk;
+    static constexpr uint32_t b_bytes = NMMA * b_mma;
+    __host__ __device__ static uint32_t plane_bytes(int entries) { return 2u * (uint32_t)entries * 16u; }
+    __host__ __device__ static uint32_t stage_bytes(int entries) { return PARTS * plane_bytes(entries); }
+    __host__ __device__ static uint32_t total(int entries) { return b_bytes + 2 * stage_bytes(entries) + 16; }
+};
+
+template <int PARTS>
+__global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params p) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t full_bar[2], empty_bar[2], acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_slot;
+    using L = C2Smem<PARTS>;
+    constexpr int BLKCOLS = 16 * PARTS;
+    constexpr int BUFCOLS = C2_MAXBLK * BLKCOLS;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t smem_base = (smem_u32(smem_raw) + 15u) & ~15u;
+    uint8_t* const smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
+    const int G = p.G, TT = p.TT, entries = p.entries;
+    const uint32_t plane_bytes = L::plane_bytes(entries), stage_bytes = L::stage_bytes(entries);
+    const uint32_t even_off = (uint32_t)entries * 16u;
+
+    if (tid == 0) {
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(smem_u32(&full_bar[s]), C2_PROD);
+            mbar_init(smem_u32(&empty_bar[s]), 1);
+            mbar_init(smem_u32(&acc_full[s]), 1);
+            mbar_init(smem_u32(&acc_empty[s]), 128);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 4) tmem_alloc<C2_TMEM_COLS>(smem_u32(&tmem_slot));
+
+    // ---- block-Toeplitz weight operand, all planes: Bmat[mma j = (kt,h)][chunk c][row n = 16*plane + 4*jo + co][8 k]
+    {
+        __nv_bfloat16* B = reinterpret_cast<__nv_bfloat16*>(smem_al);
+        const int total = NMMA * 2 * 16 * 8;          // (j, c, n16, kk)
+        for (int i = tid; i < total; i += C2_THREADS) {
+            const int kk = i & 7, n16 = (i >> 3) & 15, c = (i >> 7) & 1, j = i >> 8;
+            const int kt = j >> 1, h = j & 1;
+            const int k16 = c * 8 + kk, u = 4 * h + (k16 >> 2), ci = k16 & 3;
+            const int jo = n16 >> 2, co = n16 & 3, kf = u - jo;
+            float v = (kf >= 0 && kf < KW5) ? __ldg(p.w + ((kt * KW5 + kf) * 4 + ci) * 4 + co) : 0.f;
+#pragma unroll
+            for (int pl = 0; pl < PARTS; ++pl) {
+                const __nv_bfloat16 hv = __float2bfloat16_rn(v);
+                B[(size_t)j * (L::b_mma / 2) + (size_t)c * (L::b_chunk / 2) + (size_t)(16 * pl + n16) * 8 + kk] = hv;
+                v -= __bfloat162float(hv);
+            }
+        }
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp < 4) {
+        // ------------------------------------------------ producers ------------------------------------------------
+        const int row_pairs = 2 * G;
+        const int npairs = (TT + 4) * row_pairs;
+        int it = 0;
+        for (int ti = blockIdx.x; ti < p.ntiles; ti += gridDim.x, ++it) {
+            const int s = it & 1;
+            const uint32_t ph = (uint32_t)(it >> 1) & 1u;
+            const int n = ti / p.tiles_per_sample;
+            const int t0 = (ti - n * p.tiles_per_sample) * TT;
+            const float* xb = p.x + (long)n * p.xbatch;
+            uint8_t* const st = smem_al + L::b_bytes + (size_t)s * stage_bytes;
+            mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1u);
+            // pairs 0,1 (the zero prefix) and the two pairs after the last row
+            if (tid < 4) {
+                const int m = tid < 2 ? tid : 2 + npairs + (tid - 2);
+                uint8_t* dst = st + ((m & 1) ? 0u : even_off) + (size_t)(m >> 1) * 16;
+#pragma unroll
+                for (int pl = 0; pl < PARTS; ++pl) *reinterpret_cast<uint4*>(dst + (size_t)pl * plane_bytes) = make_uint4(0, 0, 0, 0);
+            }
+            for (int idx = tid; idx < npairs; idx += C2_PROD) {
+                const int tt = idx / row_pairs, j = idx - tt * row_pairs;
+                const int t = t0 - 2 + tt, f = 2 * j;
+                float v[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = 0.f;
+                if (t >= 0 && t < p.T && f < p.F) {
+                    const float* src = xb + (long)t * p.xpitch + (long)f * 4;
+                    const float4 a = *reinterpret_cast<const float4*>(src);
+                    v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w;
+                    if (f + 1 < p.F) {
+                        const float4 b = *reinterpret_cast<const float4*>(src + 4);
+                        v[4] = b.x, v[5] = b.y, v[6] = b.z, v[7] = b.w;
+                    }
+                }
+                uint4 e[PARTS];
+                split8<PARTS>(v, e);
+                const int m = 2 + idx;
+                uint8_t* dst = st + ((m & 1) ? 0u : even_off) + (size_t)(m >> 1) * 16;
+#pragma unroll
+                for (int pl = 0; pl < PARTS; ++pl) *reinterpret_cast<uint4*>(dst + (size_t)pl * plane_bytes) = e[pl];
+            }
+            fence_proxy_async();
+            mbar_arrive(smem_u32(&full_bar[s]));
+        }
+    } else if (warp == 4) {
+        // ------------------------------------------------ MMA issuer ------------------------------------------------
+        uint32_t idesc[PARTS];
+#pragma unroll
+        for (int pa = 0; pa < PARTS; ++pa) idesc[pa] = umma_idesc_bf16(128, 16 * (PARTS - pa), 0, 0);
+        const uint32_t a_lbo = even_off + 16u;
+        const uint64_t bdesc0 = umma_desc_noswz(smem_base, L::b_chunk, 128u);
+        int it = 0;
+        for (int ti = blockIdx.x; ti < p.ntiles; ti += gridDim.x, ++it) {
+            const int s = it & 1;
+            const uint32_t ph = (uint32_t)(it >> 1) & 1u;
+            mbar_wait(smem_u32(&acc_empty[s]), ph ^ 1u);
+            mbar_wait(smem_u32(&full_bar[s]), ph);
+            tc_fence_after();
+            const uint32_t st = smem_base + L::b_bytes + (uint32_t)s * stage_bytes;
+            const uint64_t adesc0 = umma_desc_noswz(st, a_lbo, 128u);
+            if (elect_one()) {
+                for (int blk = 0; blk < p.nblk; ++blk) {
+                    const uint32_t dcol = tmem_base + (uint32_t)(s * BUFCOLS + blk * BLKCOLS);
+#pragma unroll
+                    for (int kt = 0; kt < KT; ++kt) {
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            const uint32_t aoff = (uint32_t)(blk * 128 + kt * G + h);              // 16-byte units
+                            const uint64_t bd = bdesc0 + (uint64_t)((kt * 2 + h) * (L::b_mma >> 4));
+#pragma unroll
+                            for (int pa = 0; pa < PARTS; ++pa) {
+                                const uint64_t ad = adesc0 + (uint64_t)(aoff + (uint32_t)pa * (plane_bytes >> 4));
+                                umma_bf16(dcol + 16u * pa, ad, bd, idesc[pa], (kt | h | pa) == 0 ? 0u : 1u);
+                            }
+                        }
+                    }
+                }
+                umma_commit(smem_u32(&empty_bar[s]));
+                umma_commit(smem_u32(&acc_full[s]));
+            }
+            __syncwarp();
+        }
+    } else {
+        // ------------------------------------------------ epilogue ------------------------------------------------
+        const int q = warp & 3;
+        const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+        const int flags = p.flags;
+        float bias4[4] = {0.f, 0.f, 0.f, 0.f};
+        if (flags & PCTTS_EPI_BIAS) {
+#pragma unroll
+            for (int co = 0; co < 4; ++co) bias4[co] = __ldg(p.bias + co);
+        }
+        const int rows_valid = TT * G;
+        int it = 0;
+        for (int ti = blockIdx.x; ti < p.ntiles; ti += gridDim.x, ++it) {
+            const int s = it & 1;
+            const uint32_t ph = (uint32_t)(it >> 1) & 1u;
+            const int n = ti / p.tiles_per_sample;
+            const int t0 = (ti - n * p.tiles_per_sample) * TT;
+            mbar_wait(smem_u32(&acc_full[s]), ph);
+            tc_fence_after();
+            for (int blk = 0; blk < p.nblk; ++blk) {
+                const uint32_t col = tmem_base + lane_addr + (uint32_t)(s * BUFCOLS + blk * BLKCOLS);
+                uint32_t c0[16];
+                float acc[16];
+                tmem_ld_32x16(col, c0);
+                if (PARTS > 1) {
+                    uint32_t c1[16];
+                    tmem_ld_32x16(col + 16, c1);
+                    if (PARTS > 2) {
+                        uint32_t c2[16];
+                        tmem_ld_32x16(col + 32, c2);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            acc[i] = __uint_as_float(c0[i]) + (__uint_as_float(c1[i]) + __uint_as_float(c2[i]));
+                    } else {
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) acc[i] = __uint_as_float(c0[i]) + __uint_as_float(c1[i]);
+                    }
+                } else {
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) acc[i] = __uint_as_float(c0[i]);
+                }
+                const int r = blk * 128 + q * 32 + lane;
+                if (r < rows_valid) {
+                    const int to = r / G, g = r - to * G;
+                    const int t = t0 + to;
+                    if (t < p.T) {
+                        float* dst = p.y + (long)n * p.ybatch + (long)t * p.ypitch + (long)g * 16;
+                        const float* ax = (flags & PCTTS_EPI_DLRELU_AUX)
+                                              ? p.aux + (long)n * p.auxbatch + (long)t * p.auxpitch + (long)g * 16 : nullptr;
+#pragma unroll
+                        for (int jo = 0; jo < 4; ++jo) {
+                            if (4 * g + jo < p.F) {
+                                float o[4];
+#pragma unroll
+                                for (int co = 0; co < 4; ++co) {
+                                    float v = acc[4 * jo + co] + bias4[co];
+                                    if (flags & PCTTS_EPI_LRELU) v = lrelu_f(v);
+                                    o[co] = v;
+                                }
+                                if (flags & PCTTS_EPI_DLRELU_AUX) {
+                                    const float4 a4 = *reinterpret_cast<const float4*>(ax + 4 * jo);
+                                    o[0] *= dlrelu_from_out(a4.x), o[1] *= dlrelu_from_out(a4.y);
+                                    o[2] *= dlrelu_from_out(a4.z), o[3] *= dlrelu_from_out(a4.w);
+                                }
+                                if (flags & PCTTS_EPI_ACCUM) {
+                                    const float4 d4 = *reinterpret_cast<const float4*>(dst + 4 * jo);
+                                    o[0] += d4.x, o[1] += d4.y, o[2] += d4.z, o[3] += d4.w;
+                                }
+                                *reinterpret_cast<float4*>(dst + 4 * jo) = make_float4(o[0], o[1], o[2], o[3]);
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(smem_u32(&acc_empty[s]));
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) tmem_dealloc<C2_TMEM_COLS>(tmem_base);
+}
+
+// rows per tile: fewest waves of the persistent grid, then fewest 128-row blocks per wave
+int pick_tt(int NB, int T, int G, int* nblk_out) {
+    int best_tt = 0, best_blk = 0;
+    double best = 1e30;
+    for (int tt = 1; tt <= T && tt <= 64; ++tt) {
+        const int nblk = (tt * G + 127) / 128;
+        if (nblk > C2_MAXBLK) break;
+        const long tiles = (long)NB * ((T + tt - 1) / tt);
+        const long waves = (tiles + 147) / 148;
+        const double cost = (double)waves * (nblk + 0.3 + 0.02 * (tt + 4));
+        if (cost <= best) best = cost, best_tt = tt, best_blk = nblk;
+    }
+    *nblk_out = best_blk;
+    return best_tt;
+}
+
+template <int PARTS>
+int launch_c2(C2Params& p, cudaStream_t st) {
+    const size_t smem = C2Smem<PARTS>::total(p.entries);
+    if (smem > 226 * 1024) return PCTTS_EUNSUPPORTED;      // + the static barriers stays under the 227 KB opt-in limit
+    static size_t attr_smem = 0;
+    if (smem > attr_smem) {
+        PCTTS_CUDA(cudaFuncSetAttribute(conv2d_tc_kernel<PARTS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_smem = smem;
+    }
+    const int grid = p.ntiles < 148 ? p.ntiles : 148;
+    conv2d_tc_kernel<PARTS><<<grid, C2_THREADS, smem, st>>>(p);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
+}  // namespace
+
+extern "C" int pctts_conv2d_tc_supported(int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f) {
+    const int G = (F + 2 + 3) / 4;
+    return (CIN == 4 && COUT == 4 && KH == 5 && KW == 5 && pad_t == 2 && pad_f == 2 && F >= 1 && G <= 128) ? 1 : 0;
+}
+
+extern "C" int pctts_conv2d_tc_fwd(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T,
+                                   int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch,
+                                   long auxpitch, long xbatch, long ybatch, long auxbatch, int flags, int nterms, void* stream) {
+    if (!x || !w || !y || NB < 0 || T < 0 || F <= 0) return PCTTS_EINVAL;
+    if (!pctts_conv2d_tc_supported(F, CIN, COUT, KH, KW, pad_t, pad_f)) return PCTTS_EUNSUPPORTED;
+    if (nterms != 1 && nterms != 3 && nterms != 6) return PCTTS_EINVAL;
+    if ((flags & PCTTS_EPI_BIAS) && !bias) return PCTTS_EINVAL;
+    if ((flags & PCTTS_EPI_DLRELU_AUX) && !aux) return PCTTS_EINVAL;
+    if (flags & ~(PCTTS_EPI_BIAS | PCTTS_EPI_LRELU | PCTTS_EPI_DLRELU_AUX | PCTTS_EPI_ACCUM)) return PCTTS_EUNSUPPORTED;
+    // float4 accesses: 16-byte aligned bases and row / sample pitches
+    if ((((uintptr_t)x | (uintptr_t)y | (uintptr_t)aux) & 15) || ((xpitch | ypitch | xbatch | ybatch) & 3) ||
+        (aux && ((auxpitch | auxbatch) & 3)))
+        return PCTTS_EUNSUPPORTED;
+    if (NB == 0 || T == 0) return PCTTS_OK;
+    C2Params p;
+    p.x = x, p.w = w, p.bias = bias, p.aux = aux, p.y = y;
+    p.NB = NB, p.T = T, p.F = F;
+    p.G = (F + 2 + 3) / 4;
+    p.TT = pick_tt(NB, T, p.G, &p.nblk);
+    if (p.TT < 1) return PCTTS_EUNSUPPORTED;
+    p.tiles_per_sample = (T + p.TT - 1) / p.TT;
+    p.ntiles = NB * p.tiles_per_sample;
+    p.entries = p.nblk * 128 + 4 * p.G + 8;
+    p.xpitch = xpitch, p.ypitch = ypitch, p.auxpitch = auxpitch, p.xbatch = xbatch, p.ybatch = ybatch, p.auxbatch = auxbatch;
+    p.flags = flags;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (nterms == 6) return launch_c2<3>(p, st);
+    if (nterms == 3) return launch_c2<2>(p, st);
+    return launch_c2<1>(p, st);
+}

@@ -111,6 +111,7 @@ class CudaOps(object):
             raise ValueError('unknown precision %r (one of %s)' % (precision, sorted(PRECISIONS)))
         self.precision = precision
         self.nterms = PRECISIONS[precision]
+        self.conv2d_tc = os.environ.get('PCTTS_CONV2D_TC', '1') != '0'   # tcgen05 implicit-GEMM Conv2D (4->4, 5x5)
         self._shadows = {}         # view key -> Shadow
         self._fresh = {}           # view key -> (lo, hi): activation shadows valid inside the current step scope
         self._persist_ranges = []  # [lo, hi) of parameter buffers: their shadows are refreshed by refresh_persistent()
@@ -311,6 +312,13 @@ class CudaOps(object):
             assert tuple(aux.shape) == tuple(y.shape)
             pa, ab, ap = _map4(aux)
         self._wrote(y)
+        if (self.nterms > 0 and self.conv2d_tc and self.lib.pctts_conv2d_tc_supported(F, CIN, COUT, KH, KW, pad_t, pad_f)
+                and not ((px | py | (pa or 0)) & 15) and not ((xp | yp | ap | xb | yb | ab) & 3)):
+            # implicit GEMM on the tensor cores (4 -> 4 channels, 5x5): forward, data gradient (flipped kernels), GP tangent sweep
+            self._ck(self.lib.pctts_conv2d_tc_fwd(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
+                                                  xp, yp, ap, xb, yb, ab, flags, self.nterms, self._stream()),
+                     'pctts_conv2d_tc_fwd')
+            return
         self._ck(self.lib.pctts_conv2d_fwd(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
                                            xp, yp, ap, xb, yb, ab, flags, self._stream()), 'pctts_conv2d_fwd')
 
