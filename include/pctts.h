@@ -90,6 +90,7 @@ int pctts_conv2d_fwd(const float* x, const float* w, const float* bias, const fl
 /* The same convolution for CIN = COUT = 4, 5x5, pad 2 as an implicit GEMM on the tensor cores (tcgen05.mma + TMEM; the input tile
  * is staged once in shared memory as bf16 planes and read in place as the im2col operand).  nterms as for pctts_gemm_tc.
  * Bases must be 16-byte aligned and pitches multiples of 4 floats; pctts_conv2d_tc_supported() is a host call. */
+int pctts_conv2d_tc_set_trace(void* buf);   /* developer probe: 32*8 int64 clock stamps of CTA 0 of the next launches; NULL = off */
 int pctts_conv2d_tc_supported(int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f);
 int pctts_conv2d_tc_fwd(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T, int F,
                         int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch, long auxpitch,
@@ -120,7 +121,9 @@ int pctts_colsum(const float* x, long rows, int C, float* out, int accumulate, v
 
 /* ---- LSTM / Bidirectional(LSTM) recurrence (networktts.py:72-96): persistent cluster kernel, U resident in smem -------- */
 /* zx* = x.W + b  [B,T,4H] (gate order i,f,c,o); U* [H,4H]; hout [B,T,ldh] (direction d -> columns d*H..); the gates and c buffers are
- * written when non-NULL (needed by the backward).  ndir = 1 (LSTM) or 2 (Bidirectional: direction 1 runs time-reversed). */
+ * written when non-NULL (needed by the backward).  ndir = 1 (LSTM) or 2 (Bidirectional: direction 1 runs time-reversed).
+ * H in {32,64,128,256}: register-resident weights, clusters of H/32 CTAs synchronised by DSMEM st.async + mbarrier transaction counts
+ * (cluster_size / batch_chunk ignored); other H, or cluster_size = -n: shared-memory-resident weights, clusters of n, cluster barriers. */
 int pctts_lstm_fwd(const float* zx0, const float* zx1, const float* U0, const float* U1, float* hout, float* gates0,
                    float* gates1, float* c0, float* c1, int B, int T, int H, int ndir, int ldh, int cluster_size,
                    int batch_chunk, void* stream);

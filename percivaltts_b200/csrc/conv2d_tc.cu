@@ -20,9 +20,9 @@
 // (orders i + j <= PARTS-1).  hi.hi lands in its own 16 accumulator columns; the corrections share the two other blocks.
 //
 // Structure (persistent CTAs, one per SM; a tile = TT output frame rows of one sample):
-//   warps 0-3  producers   fp32 global -> bf16 planes, pair arrays of a 2-stage ring, fence.proxy.async, mbarrier arrive
-//   warp  4    MMA issuer  per 128-row block: 5 kt x 2 halves x PARTS tcgen05.mma; tcgen05.commit frees the stage / signals
-//   warps 5-8  epilogue    tcgen05.ld (TMEM lane quarter = warp % 4), sum of the column blocks, bias / LeakyReLU / LeakyReLU'
+//   warps 0-7  producers   fp32 global -> bf16 planes, pair arrays of a 2-stage ring, fence.proxy.async, mbarrier arrive
+//   warp  8    MMA issuer  per 128-row block: 5 kt x 2 halves x PARTS tcgen05.mma; tcgen05.commit frees the stage / signals
+//   warps 9-12 epilogue    tcgen05.ld (TMEM lane quarter = warp % 4), sum of the column blocks, bias / LeakyReLU / LeakyReLU'
 //                          mask / accumulate, 64-byte stores; TMEM accumulators are double-buffered across tiles
 #include "common.cuh"
 #include "pctts.h"
@@ -33,8 +33,10 @@ namespace {
 
 using namespace tcx;
 
-constexpr int C2_THREADS = 288;          // 9 warps
-constexpr int C2_PROD = 128;             // producer threads
+constexpr int C2_PROD = 256;             // producer threads (warps 0-7)
+constexpr int C2_PW = C2_PROD / 32;      // index of the MMA warp; epilogue warps follow
+constexpr int C2_THREADS = C2_PROD + 32 + 128;
+constexpr int C2_UNR = 6;                // pixel pairs in flight per producer thread
 constexpr int C2_MAXBLK = 5;             // 128-row blocks per tile (48 TMEM columns each, two buffers: 480 of 512 columns)
 constexpr int C2_TMEM_COLS = 512;
 constexpr int KT = 5, KW5 = 5;
@@ -54,6 +56,7 @@ struct C2Params {
     int entries;         // 16-byte entries per parity array
     long xpitch, ypitch, auxpitch, xbatch, ybatch, auxbatch;
     int flags;
+    long long* trace;    // developer probe (pctts_conv2d_tc_set_trace): clock64() stamps of CTA 0, 8 per tile
 };
 
 // shared-memory matrix descriptor, no swizzle (INTERLEAVE), K-major: core matrix = 8 rows x 16 bytes, contiguous
@@ -80,7 +83,8 @@ __device__ __forceinline__ uint32_t pack_bf16(__nv_bfloat16 a, __nv_bfloat16 b) 
     return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);
 }
 
-// 8 floats (2 pixels x 4 channels) -> PARTS 16-byte bf16 entries
+// 8 floats (2 pixels x 4 channels) -> PARTS 16-byte bf16 entries.  Every plane but the last takes the top 16 bits of the running
+// remainder (truncation: the remainder stays exact and three planes carry all 24 significand bits); the last plane rounds.
 template <int PARTS>
 __device__ __forceinline__ void split8(const float (&v)[8], uint4 (&out)[PARTS]) {
     uint32_t w[PARTS][4];
@@ -89,10 +93,14 @@ __device__ __forceinline__ void split8(const float (&v)[8], uint4 (&out)[PARTS])
         float a = v[2 * i], b = v[2 * i + 1];
 #pragma unroll
         for (int p = 0; p < PARTS; ++p) {
-            const __nv_bfloat16 ha = __float2bfloat16_rn(a), hb = __float2bfloat16_rn(b);
-            w[p][i] = pack_bf16(ha, hb);
-            a -= __bfloat162float(ha);
-            b -= __bfloat162float(hb);
+            if (p + 1 < PARTS) {
+                const uint32_t ua = __float_as_uint(a) & 0xFFFF0000u, ub = __float_as_uint(b) & 0xFFFF0000u;
+                w[p][i] = __byte_perm(ua, ub, 0x7632);
+                a -= __uint_as_float(ua);
+                b -= __uint_as_float(ub);
+            } else {
+                w[p][i] = pack_bf16(__float2bfloat16_rn(a), __float2bfloat16_rn(b));
+            }
         }
     }
 #pragma unroll
@@ -123,6 +131,7 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
     constexpr int BUFCOLS = C2_MAXBLK * BLKCOLS;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (p.trace && blockIdx.x == 0 && tid == 0) p.trace[31 * 8 + 0] = clock64();
     const uint32_t smem_base = (smem_u32(smem_raw) + 15u) & ~15u;
     uint8_t* const smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
     const int G = p.G, TT = p.TT, entries = p.entries;
@@ -138,7 +147,39 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
         }
         fence_barrier_init();
     }
-    if (warp == 4) tmem_alloc<C2_TMEM_COLS>(smem_u32(&tmem_slot));
+    if (warp == C2_PW) tmem_alloc<C2_TMEM_COLS>(smem_u32(&tmem_slot));
+
+    // ---- producer set-up (all threads compute it; only the producer warps issue loads)
+    const int row_pairs = 2 * G;
+    const int npairs = (TT + 4) * row_pairs;
+    constexpr int PASS = C2_UNR * C2_PROD;
+    const int npass = (npairs + PASS - 1) / PASS;
+    const int my_tiles = (p.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int nitems = my_tiles * npass;
+    // item k = (tile it = k / npass, pass k % npass): the loads of item k+1 are in flight while item k is converted
+    auto issue = [&](int k, float4 (&va)[C2_UNR], float4 (&vb)[C2_UNR]) {
+        const int it = k / npass, pass = k - it * npass;
+        const int ti = blockIdx.x + it * gridDim.x;
+        const int n = ti / p.tiles_per_sample;
+        const int t0 = (ti - n * p.tiles_per_sample) * TT;
+        const float* xb = p.x + (long)n * p.xbatch;
+#pragma unroll
+        for (int u = 0; u < C2_UNR; ++u) {
+            const int idx = pass * PASS + u * C2_PROD + tid;
+            va[u] = vb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (idx < npairs) {
+                const int tt = idx / row_pairs, j = idx - tt * row_pairs;
+                const int t = t0 - 2 + tt, f = 2 * j;
+                if (t >= 0 && t < p.T && f < p.F) {
+                    const float* src = xb + (long)t * p.xpitch + (long)f * 4;
+                    va[u] = *reinterpret_cast<const float4*>(src);
+                    if (f + 1 < p.F) vb[u] = *reinterpret_cast<const float4*>(src + 4);
+                }
+            }
+        }
+    };
+    float4 ca[C2_UNR], cb[C2_UNR], na[C2_UNR], nb[C2_UNR];
+    if (warp < C2_PW && nitems > 0) issue(0, ca, cb);   // first tile's loads fly while the weight operand is built
 
     // ---- block-Toeplitz weight operand, all planes: Bmat[mma j = (kt,h)][chunk c][row n = 16*plane + 4*jo + co][8 k]
     {
@@ -163,53 +204,51 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
+    if (p.trace && blockIdx.x == 0 && tid == 0) p.trace[31 * 8 + 1] = clock64();
 
-    if (warp < 4) {
+    if (warp < C2_PW) {
         // ------------------------------------------------ producers ------------------------------------------------
-        const int row_pairs = 2 * G;
-        const int npairs = (TT + 4) * row_pairs;
-        int it = 0;
-        for (int ti = blockIdx.x; ti < p.ntiles; ti += gridDim.x, ++it) {
+        for (int k = 0; k < nitems; ++k) {
+            const int it = k / npass, pass = k - it * npass;
             const int s = it & 1;
             const uint32_t ph = (uint32_t)(it >> 1) & 1u;
-            const int n = ti / p.tiles_per_sample;
-            const int t0 = (ti - n * p.tiles_per_sample) * TT;
-            const float* xb = p.x + (long)n * p.xbatch;
             uint8_t* const st = smem_al + L::b_bytes + (size_t)s * stage_bytes;
-            mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1u);
-            // pairs 0,1 (the zero prefix) and the two pairs after the last row
-            if (tid < 4) {
-                const int m = tid < 2 ? tid : 2 + npairs + (tid - 2);
-                uint8_t* dst = st + ((m & 1) ? 0u : even_off) + (size_t)(m >> 1) * 16;
+            if (k + 1 < nitems) issue(k + 1, na, nb);
+            const bool tr = p.trace && blockIdx.x == 0 && tid == 0 && it < 32;
+            if (pass == 0) {
+                if (tr) p.trace[it * 8 + 0] = clock64();
+                mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1u);
+                if (tr) p.trace[it * 8 + 1] = clock64();
+                // pairs 0,1 (the zero prefix) and the two pairs after the last row
+                if (tid < 4) {
+                    const int m = tid < 2 ? tid : 2 + npairs + (tid - 2);
+                    uint8_t* dst = st + ((m & 1) ? 0u : even_off) + (size_t)(m >> 1) * 16;
 #pragma unroll
-                for (int pl = 0; pl < PARTS; ++pl) *reinterpret_cast<uint4*>(dst + (size_t)pl * plane_bytes) = make_uint4(0, 0, 0, 0);
-            }
-            for (int idx = tid; idx < npairs; idx += C2_PROD) {
-                const int tt = idx / row_pairs, j = idx - tt * row_pairs;
-                const int t = t0 - 2 + tt, f = 2 * j;
-                float v[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = 0.f;
-                if (t >= 0 && t < p.T && f < p.F) {
-                    const float* src = xb + (long)t * p.xpitch + (long)f * 4;
-                    const float4 a = *reinterpret_cast<const float4*>(src);
-                    v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w;
-                    if (f + 1 < p.F) {
-                        const float4 b = *reinterpret_cast<const float4*>(src + 4);
-                        v[4] = b.x, v[5] = b.y, v[6] = b.z, v[7] = b.w;
-                    }
+                    for (int pl = 0; pl < PARTS; ++pl) *reinterpret_cast<uint4*>(dst + (size_t)pl * plane_bytes) = make_uint4(0, 0, 0, 0);
                 }
-                uint4 e[PARTS];
-                split8<PARTS>(v, e);
-                const int m = 2 + idx;
-                uint8_t* dst = st + ((m & 1) ? 0u : even_off) + (size_t)(m >> 1) * 16;
-#pragma unroll
-                for (int pl = 0; pl < PARTS; ++pl) *reinterpret_cast<uint4*>(dst + (size_t)pl * plane_bytes) = e[pl];
             }
-            fence_proxy_async();
-            mbar_arrive(smem_u32(&full_bar[s]));
+#pragma unroll
+            for (int u = 0; u < C2_UNR; ++u) {
+                const int idx = pass * PASS + u * C2_PROD + tid;
+                if (idx < npairs) {
+                    const float v[8] = {ca[u].x, ca[u].y, ca[u].z, ca[u].w, cb[u].x, cb[u].y, cb[u].z, cb[u].w};
+                    uint4 e[PARTS];
+                    split8<PARTS>(v, e);
+                    const int m = 2 + idx;
+                    uint8_t* dst = st + ((m & 1) ? 0u : even_off) + (size_t)(m >> 1) * 16;
+#pragma unroll
+                    for (int pl = 0; pl < PARTS; ++pl) *reinterpret_cast<uint4*>(dst + (size_t)pl * plane_bytes) = e[pl];
+                }
+            }
+            if (pass == npass - 1) {
+                fence_proxy_async();
+                mbar_arrive(smem_u32(&full_bar[s]));
+                if (tr) p.trace[it * 8 + 2] = clock64();
+            }
+#pragma unroll
+            for (int u = 0; u < C2_UNR; ++u) ca[u] = na[u], cb[u] = nb[u];
         }
-    } else if (warp == 4) {
+    } else if (warp == C2_PW) {
         // ------------------------------------------------ MMA issuer ------------------------------------------------
         uint32_t idesc[PARTS];
 #pragma unroll
@@ -223,6 +262,8 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
             mbar_wait(smem_u32(&acc_empty[s]), ph ^ 1u);
             mbar_wait(smem_u32(&full_bar[s]), ph);
             tc_fence_after();
+            const bool tr = p.trace && blockIdx.x == 0 && lane == 0 && it < 32;
+            if (tr) p.trace[it * 8 + 3] = clock64();
             const uint32_t st = smem_base + L::b_bytes + (uint32_t)s * stage_bytes;
             const uint64_t adesc0 = umma_desc_noswz(st, a_lbo, 128u);
             if (elect_one()) {
@@ -246,6 +287,7 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
                 umma_commit(smem_u32(&acc_full[s]));
             }
             __syncwarp();
+            if (tr) p.trace[it * 8 + 4] = clock64();
         }
     } else {
         // ------------------------------------------------ epilogue ------------------------------------------------
@@ -264,8 +306,11 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
             const uint32_t ph = (uint32_t)(it >> 1) & 1u;
             const int n = ti / p.tiles_per_sample;
             const int t0 = (ti - n * p.tiles_per_sample) * TT;
+            const bool tr = p.trace && blockIdx.x == 0 && tid == C2_PROD + 32 && it < 32;
+            if (tr) p.trace[it * 8 + 5] = clock64();
             mbar_wait(smem_u32(&acc_full[s]), ph);
             tc_fence_after();
+            if (tr) p.trace[it * 8 + 6] = clock64();
             for (int blk = 0; blk < p.nblk; ++blk) {
                 const uint32_t col = tmem_base + lane_addr + (uint32_t)(s * BUFCOLS + blk * BLKCOLS);
                 uint32_t c0[16];
@@ -326,12 +371,16 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
             }
             tc_fence_before();
             mbar_arrive(smem_u32(&acc_empty[s]));
+            if (tr) p.trace[it * 8 + 7] = clock64();
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) tmem_dealloc<C2_TMEM_COLS>(tmem_base);
+    if (warp == C2_PW) tmem_dealloc<C2_TMEM_COLS>(tmem_base);
+    if (p.trace && blockIdx.x == 0 && tid == 0) p.trace[31 * 8 + 2] = clock64();
 }
+
+long long* g_c2_trace = nullptr;
 
 // rows per tile: fewest waves of the persistent grid, then fewest 128-row blocks per wave
 int pick_tt(int NB, int T, int G, int* nblk_out) {
@@ -366,6 +415,13 @@ int launch_c2(C2Params& p, cudaStream_t st) {
 
 }  // namespace
 
+/* developer probe: device buffer of 32*8 int64 receiving clock64() stamps of CTA 0 (per tile: producer start / stage free /
+ * stage filled, MMA operands ready / issued, epilogue start / accumulator ready / stored); NULL switches it off */
+extern "C" int pctts_conv2d_tc_set_trace(void* buf) {
+    g_c2_trace = (long long*)buf;
+    return PCTTS_OK;
+}
+
 extern "C" int pctts_conv2d_tc_supported(int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f) {
     const int G = (F + 2 + 3) / 4;
     return (CIN == 4 && COUT == 4 && KH == 5 && KW == 5 && pad_t == 2 && pad_f == 2 && F >= 1 && G <= 128) ? 1 : 0;
@@ -396,6 +452,7 @@ extern "C" int pctts_conv2d_tc_fwd(const float* x, const float* w, const float* 
     p.entries = p.nblk * 128 + 4 * p.G + 8;
     p.xpitch = xpitch, p.ypitch = ypitch, p.auxpitch = auxpitch, p.xbatch = xbatch, p.ybatch = ybatch, p.auxbatch = auxbatch;
     p.flags = flags;
+    p.trace = g_c2_trace;
     cudaStream_t st = (cudaStream_t)stream;
     if (nterms == 6) return launch_c2<3>(p, st);
     if (nterms == 3) return launch_c2<2>(p, st);

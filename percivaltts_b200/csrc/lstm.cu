@@ -6,10 +6,16 @@
 // for all T steps; h_t slices are exchanged through distributed shared memory with one cluster barrier per step.
 // The input projection x.W + b is hoisted out (one GEMM over all time steps) and read here as zx.
 #include <cooperative_groups.h>
+#include <stdlib.h>
 #include "common.cuh"
 #include "pctts.h"
 
 namespace cg = cooperative_groups;
+
+// lstm_fast.cu: register-resident, dataflow-synchronised kernels for H in {32, 64, 128, 256}
+int pctts_lstm_fast_supported(int H);
+int pctts_lstm_fast(bool bwd, const float* const* zx, const float* const* U, float* hout, float* const* gates, float* const* cstate,
+                    const float* dhout, float* const* dz, int B, int T, int H, int ndir, int ldh, cudaStream_t st);
 
 namespace {
 
@@ -286,6 +292,12 @@ int dispatch(bool bwd, LstmArgs& a, int ndir, int cluster_size, int batch_chunk,
     return launch<8>(bwd, a, ndir, st);
 }
 
+// PCTTS_LSTM_FAST=0 (environment) or a negative cluster_size argument (-n = generic kernels with clusters of n) selects the shared-memory-resident generic kernels
+bool use_fast(int H) {
+    static const bool on = !(getenv("PCTTS_LSTM_FAST") && atoi(getenv("PCTTS_LSTM_FAST")) == 0);
+    return on && pctts_lstm_fast_supported(H);
+}
+
 }  // namespace
 
 extern "C" int pctts_lstm_fwd(const float* zx0, const float* zx1, const float* U0, const float* U1, float* hout, float* gates0,
@@ -296,7 +308,9 @@ extern "C" int pctts_lstm_fwd(const float* zx0, const float* zx1, const float* U
     a.zx[0] = zx0; a.zx[1] = zx1; a.U[0] = U0; a.U[1] = U1; a.hout = hout;
     a.gates[0] = gates0; a.gates[1] = gates1; a.cstate[0] = c0; a.cstate[1] = c1;
     a.B = B; a.T = T; a.H = H; a.ldh = ldh;
-    return dispatch(false, a, ndir, cluster_size, batch_chunk, (cudaStream_t)stream);
+    if (B > 0 && T > 0 && cluster_size >= 0 && use_fast(H))
+        return pctts_lstm_fast(false, a.zx, a.U, hout, a.gates, a.cstate, nullptr, nullptr, B, T, H, ndir, ldh, (cudaStream_t)stream);
+    return dispatch(false, a, ndir, cluster_size < 0 ? -cluster_size : cluster_size, batch_chunk, (cudaStream_t)stream);
 }
 
 extern "C" int pctts_lstm_bwd(const float* dhout, const float* U0, const float* U1, const float* gates0, const float* gates1,
@@ -309,5 +323,7 @@ extern "C" int pctts_lstm_bwd(const float* dhout, const float* U0, const float* 
     a.cstate[0] = const_cast<float*>(c0); a.cstate[1] = const_cast<float*>(c1);
     a.dz[0] = dz0; a.dz[1] = dz1;
     a.B = B; a.T = T; a.H = H; a.ldh = ldh;
-    return dispatch(true, a, ndir, cluster_size, batch_chunk, (cudaStream_t)stream);
+    if (B > 0 && T > 0 && cluster_size >= 0 && use_fast(H))
+        return pctts_lstm_fast(true, nullptr, a.U, nullptr, a.gates, a.cstate, dhout, a.dz, B, T, H, ndir, ldh, (cudaStream_t)stream);
+    return dispatch(true, a, ndir, cluster_size < 0 ? -cluster_size : cluster_size, batch_chunk, (cudaStream_t)stream);
 }

@@ -182,7 +182,9 @@ def test_batchnorm_forward_backward(cuda_ops, rows, C):
     close(csd, cs, 1e-5, 'colsum')
 
 
-@pytest.mark.parametrize('B,T,H', [(10, 50, 256), (3, 17, 8), (2, 9, 2), (1, 1, 4), (5, 33, 24)])
+# H in {32,64,128,256}: register-resident dataflow kernels (lstm_fast.cu); other H: generic shared-memory kernels (lstm.cu)
+@pytest.mark.parametrize('B,T,H', [(10, 50, 256), (3, 17, 8), (2, 9, 2), (1, 1, 4), (5, 33, 24), (3, 400, 256), (1, 1, 256), (1, 2, 32),
+                                   (5, 21, 32), (4, 30, 64), (7, 13, 128)])
 def test_lstm_forward_and_bptt(cuda_ops, B, T, H):
     zx = [rnd(B, T, 4 * H, seed=d) for d in range(2)]
     U = [rnd(H, 4 * H, seed=2 + d) * (1.0 / np.sqrt(H)) for d in range(2)]
@@ -206,6 +208,13 @@ def test_lstm_forward_and_bptt(cuda_ops, B, T, H):
     cuda_ops.lstm_bwd(dev(dh), Ud, [dev(t) for t in gates], [dev(t) for t in cst], dzd)
     for d in range(2):
         close(dzd[d], dz[d], 2e-4, 'lstm dz')
+    # both kernel families agree (a negative cluster_size forces the generic kernels) and one direction alone works
+    hg = torch.zeros(B, T, 2 * H, device='cuda')
+    cuda_ops.lstm_fwd(zxd, Ud, hg, None, None, cluster_size=-8)
+    close(hg, hout, 1e-4, 'lstm h generic')
+    h1 = torch.zeros(B, T, H, device='cuda')
+    cuda_ops.lstm_fwd(zxd[:1], Ud[:1], h1)
+    close(h1, hout[:, :, :H], 1e-4, 'lstm single direction')
 
 
 def test_wgan_gp_pieces(cuda_ops):

@@ -81,7 +81,9 @@ def test_critic_and_generator_step_vs_oracle(cuda_ops, kw, B, T):
     st.critic_step(Xd, Yd, alpha=torch.tensor(alpha).cuda(), apply=False)
     torch.cuda.synchronize()
     losses = st.losses.cpu()
-    assert relerr(st.buffers(B, T)['fake'], rc['fake']) < TOL
+    # the critic step evaluates the frozen generator's spectral branch only (all the critic reads, networks_critic.py:58)
+    S = ao.spec_size
+    assert relerr(st.buffers(B, T)['fake'][:, :, 1:1 + S], rc['fake'][:, :, 1:1 + S]) < TOL
     cpl = st.C.plan(3, B, T)
     for slot, key in ((W.L_REAL, 'l_real'), (W.L_FAKE, 'l_fake'), (W.L_GP, 'gp'), (W.L_CRITIC, 'loss')):
         assert abs(float(losses[slot]) - float(rc[key])) < TOL * max(abs(float(rc[key])), 1e-2), (key, losses, rc[key])
@@ -167,3 +169,21 @@ def test_gp_properties_at_demo_size(cuda_ops):
     assert torch.isfinite(grads1).all() and float(grads1.abs().max()) > 0
     st.critic_step(Xd, Yd, alpha=ad, apply=False)
     assert torch.equal(st.C.params.grad, grads1) and torch.equal(st.losses, losses1)
+
+
+def test_critic_step_spectral_only_generator_is_result_preserving(cuda_ops):
+    """The critic step skips the frozen generator's F0 / noise-mask branches (the critic reads out[:,:,1:1+S] only):
+    losses and critic gradients are bit-identical to the step that evaluates the whole generator, whose full output
+    matches the oracle's `fake`."""
+    ao, wg, wc, wgt, wct, X, Y, alpha, st = setup(cuda_ops, MID, 3, 57)
+    Xd, Yd, ad = torch.tensor(X).cuda(), torch.tensor(Y).cuda(), torch.tensor(alpha).cuda()
+    st.critic_step(Xd, Yd, alpha=ad, apply=False)
+    grads, losses = st.C.params.grad.clone(), st.losses.clone()
+    st.critic_step_full_generator = True
+    st.buffers(3, 57)['fake'].zero_()
+    st.critic_step(Xd, Yd, alpha=ad, apply=False)
+    assert torch.equal(st.C.params.grad, grads) and torch.equal(st.losses, losses)
+    dt = torch.float64
+    rc = O.critic_step(ao, wgt, wct, torch.tensor(X, dtype=dt), torch.tensor(Y, dtype=dt),
+                       torch.tensor(alpha, dtype=dt).reshape(-1, 1, 1))
+    assert relerr(st.buffers(3, 57)['fake'], rc['fake']) < TOL
