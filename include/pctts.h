@@ -102,6 +102,12 @@ int pctts_conv2d_wgrad(const float* x, const float* dy, float* dw, float* worksp
                        int KH, int KW, int pad_t, int pad_f, long xpitch, long dypitch, long xbatch, long dybatch, float scale,
                        int accumulate, void* stream);
 
+/* dw as above and, in the same pass, dbias[co] = sum_{n < nb_bias, t, f} dy[n,t,f,co] (dbias may be NULL).  4 -> 4 channels, 5x5,
+ * pad 2, 16-byte aligned bases and pitches that are multiples of 4 floats only; otherwise PCTTS_EUNSUPPORTED. */
+int pctts_conv2d_wgrad_bias(const float* x, const float* dy, float* dw, float* dbias, int nb_bias, float* workspace, int NB, int T,
+                            int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long dypitch, long xbatch,
+                            long dybatch, float scale, int accumulate, void* stream);
+
 /* ---- BatchNormalization(axis=-1) + LeakyReLU (networktts.py:61-62,118-119,124-125), data [rows, C] ------------------- */
 long pctts_colreduce_workspace_bytes(long rows, int C);            /* host call; zero the workspace once after allocation */
 void* pctts_colreduce_sums_ptr(void* workspace, long rows, int C); /* host call; double sums[2][C] inside the workspace

@@ -330,7 +330,29 @@ extern "C" int pctts_conv2d_flip_weights(const float* w, float* wt, int KH, int 
 }
 
 extern "C" long pctts_conv2d_wgrad_workspace(int NB, int T, int CIN, int COUT, int KH, int KW) {
-    return (long)NB * pctts_div_up(T, WG_TT) * KH * KW * CIN * COUT;
+    return (long)NB * pctts_div_up(T, WG_TT) * (KH * KW * CIN * COUT + COUT);     // per-CTA partials of dW and of the bias gradient
+}
+
+// conv2d_wgrad44.cu
+int pctts_conv2d_wgrad44_supported(int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, const void* x, const void* dy,
+                                   long xpitch, long dypitch, long xbatch, long dybatch);
+int pctts_conv2d_wgrad44(const float* x, const float* dy, float* dw, float* dbias, int nb_bias, float* workspace, int NB, int T,
+                         int F, long xpitch, long dypitch, long xbatch, long dybatch, float scale, int accumulate, cudaStream_t st);
+
+int pctts_reduce_partials(const float* partial, float* out, int nblk, int NW, float scale, int accumulate, cudaStream_t st) {
+    reduce_partials_kernel<<<pctts_div_up(NW, 8), 256, 0, st>>>(partial, out, nblk, NW, scale, accumulate);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
+extern "C" int pctts_conv2d_wgrad_bias(const float* x, const float* dy, float* dw, float* dbias, int nb_bias, float* workspace, int NB,
+                                       int T, int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long dypitch,
+                                       long xbatch, long dybatch, float scale, int accumulate, void* stream) {
+    if (!x || !dy || !dw || !workspace || NB <= 0 || T <= 0 || F <= 0 || nb_bias < 0 || nb_bias > NB) return PCTTS_EINVAL;
+    if (!pctts_conv2d_wgrad44_supported(F, CIN, COUT, KH, KW, pad_t, pad_f, x, dy, xpitch, dypitch, xbatch, dybatch))
+        return PCTTS_EUNSUPPORTED;
+    return pctts_conv2d_wgrad44(x, dy, dw, dbias, nb_bias, workspace, NB, T, F, xpitch, dypitch, xbatch, dybatch, scale, accumulate,
+                                (cudaStream_t)stream);
 }
 
 extern "C" int pctts_conv2d_wgrad(const float* x, const float* dy, float* dw, float* workspace, int NB, int T, int F, int CIN,
@@ -338,6 +360,8 @@ extern "C" int pctts_conv2d_wgrad(const float* x, const float* dy, float* dw, fl
                                   long dybatch, float scale, int accumulate, void* stream) {
     if (!x || !dy || !dw || !workspace || NB <= 0 || T <= 0 || F <= 0) return PCTTS_EINVAL;
     cudaStream_t st = (cudaStream_t)stream;
+    if (pctts_conv2d_wgrad44_supported(F, CIN, COUT, KH, KW, pad_t, pad_f, x, dy, xpitch, dypitch, xbatch, dybatch))
+        return pctts_conv2d_wgrad44(x, dy, dw, nullptr, 0, workspace, NB, T, F, xpitch, dypitch, xbatch, dybatch, scale, accumulate, st);
     const int NW = KH * KW * CIN * COUT;
     const int nblk = NB * pctts_div_up(T, WG_TT);
     int rc = PCTTS_EUNSUPPORTED;

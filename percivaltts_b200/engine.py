@@ -466,8 +466,8 @@ class Critic(object):
         fM = first_order_apps * M
         for i in range(L):
             ain = pl['a'][i - 1] if i > 0 else pl['s0']
-            o.conv2d_wgrad(ain, pl['da'][i], g['c.spec.cnn%d.kernel' % i])
-            o.colsum(pl['da'][i].view(nM * S, Fl)[:fM * S], g['c.spec.cnn%d.bias' % i])
+            o.conv2d_wgrad(ain, pl['da'][i], g['c.spec.cnn%d.kernel' % i], dbias=g['c.spec.cnn%d.bias' % i],
+                           bias_samples=first_order_apps * B)
         o.gemm(pl['a'][L - 1].view(nM, SF), pl['dp'][0], g['c.post.fc0.kernel'][:SF], transA=True)
         for i in (1, 2):
             o.gemm(pl['p'][i - 1], pl['dp'][i], g['c.post.fc%d.kernel' % i], transA=True)

@@ -328,7 +328,9 @@ class CudaOps(object):
         self._ck(self.lib.pctts_conv2d_flip_weights(w.data_ptr(), wt.data_ptr(), KH, KW, CIN, COUT, self._stream()),
                  'pctts_conv2d_flip_weights')
 
-    def conv2d_wgrad(self, x, dy, dw, scale=1.0, accumulate=False, pad=None):
+    def conv2d_wgrad(self, x, dy, dw, scale=1.0, accumulate=False, pad=None, dbias=None, bias_samples=None):
+        """dw = scale * sum x (*) dy; with `dbias` also the bias gradient sum_{n < bias_samples} dy (same pass for the
+        4 -> 4 channel 5x5 layers, a separate column sum otherwise)."""
         N, T, F, CIN = x.shape
         KH, KW, ci, COUT = dw.shape
         assert ci == CIN and tuple(dy.shape) == (N, T, F, COUT) and dw.is_contiguous()
@@ -336,9 +338,19 @@ class CudaOps(object):
         key = (N, T, CIN, COUT, KH, KW)
         ws = self._wg.get(key)
         if ws is None:
-            ws = self._wg[key] = self.empty(self.lib.pctts_conv2d_wgrad_workspace(*key))
+            ws = self._wg[key] = self.empty(max(self.lib.pctts_conv2d_wgrad_workspace(*key), 148 * (KH * KW * CIN * COUT + COUT)))
         px, xb, xp = _map4(x)
         pd, db, dp = _map4(dy)
+        nb = N if bias_samples is None else int(bias_samples)
+        if dbias is not None:
+            assert dbias.numel() == COUT and dbias.is_contiguous()
+            rc = self.lib.pctts_conv2d_wgrad_bias(px, pd, dw.data_ptr(), dbias.data_ptr(), nb, ws.data_ptr(), N, T, F, CIN, COUT, KH, KW,
+                                                  pad_t, pad_f, xp, dp, xb, db, float(scale), int(accumulate), self._stream())
+            if rc != -2:
+                self._ck(rc, 'pctts_conv2d_wgrad_bias')
+                return
+            assert dy.is_contiguous()
+            self.colsum(dy.view(N * T * F, COUT)[:nb * T * F], dbias)
         self._ck(self.lib.pctts_conv2d_wgrad(px, pd, dw.data_ptr(), ws.data_ptr(), N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
                                              xp, dp, xb, db, float(scale), int(accumulate), self._stream()),
                  'pctts_conv2d_wgrad')

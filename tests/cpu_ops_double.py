@@ -129,8 +129,11 @@ class CpuOpsDouble(object):
         self.launches += 1
         wt.copy_(torch.flip(w, dims=(0, 1)).permute(0, 1, 3, 2))
 
-    def conv2d_wgrad(self, x, dy, dw, scale=1.0, accumulate=False, pad=None):
+    def conv2d_wgrad(self, x, dy, dw, scale=1.0, accumulate=False, pad=None, dbias=None, bias_samples=None):
         self.launches += 1
+        if dbias is not None:
+            nb = x.shape[0] if bias_samples is None else bias_samples
+            dbias.copy_(dy[:nb].sum(dim=(0, 1, 2)))
         KH, KW, CIN, COUT = dw.shape
         pad_t, pad_f = ((KH - 1) // 2, (KW - 1) // 2) if pad is None else pad
         T, Fq = x.shape[1], x.shape[2]

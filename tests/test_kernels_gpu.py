@@ -94,7 +94,7 @@ CONV_CASES = [(1, 4, 5, 5), (4, 4, 5, 5), (4, 1, 5, 5), (1, 2, 3, 3), (2, 2, 3, 
 
 
 @pytest.mark.parametrize('CIN,COUT,KH,KW', CONV_CASES)
-@pytest.mark.parametrize('N,T,F', [(2, 37, 129), (1, 5, 17), (3, 16, 65)])
+@pytest.mark.parametrize('N,T,F', [(2, 37, 129), (1, 5, 17), (3, 16, 65), (4, 100, 130)])
 def test_conv2d_fwd_flip_wgrad(cuda_ops, CIN, COUT, KH, KW, N, T, F):
     x, w, b = rnd(N, T, F, CIN), rnd(KH, KW, CIN, COUT, seed=1), rnd(COUT, seed=2)
     aux = rnd(N, T, F, COUT, seed=3)
@@ -122,6 +122,15 @@ def test_conv2d_fwd_flip_wgrad(cuda_ops, CIN, COUT, KH, KW, N, T, F):
     dw = torch.zeros(KH, KW, CIN, COUT, device='cuda')
     cuda_ops.conv2d_wgrad(dev(x), dev(dy), dw, scale=0.5)
     close(dw, dw_want, 3e-5, 'wgrad')
+    # fused bias gradient over the first samples only (critic: the GP rows carry no bias gradient), accumulate form
+    db_want, dw_acc = torch.zeros(COUT, dtype=torch.float64), rnd(KH, KW, CIN, COUT, seed=6)
+    dw_want2 = dw_acc.clone()
+    nb = max(N - 1, 1)
+    REF.conv2d_wgrad(x, dy, dw_want2, accumulate=True, dbias=db_want, bias_samples=nb)
+    dw2, db = dev(dw_acc), torch.zeros(COUT, device='cuda')
+    cuda_ops.conv2d_wgrad(dev(x), dev(dy), dw2, accumulate=True, dbias=db, bias_samples=nb)
+    close(dw2, dw_want2, 3e-5, 'wgrad accumulate')
+    close(db, db_want, 3e-5, 'fused bias gradient')
 
 
 def test_conv2d_strided_feature_views(cuda_ops):

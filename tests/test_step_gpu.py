@@ -102,37 +102,41 @@ def test_critic_and_generator_step_vs_oracle(cuda_ops, kw, B, T):
 
 
 def test_training_trajectory_vs_oracle(cuda_ops):
-    """Six batches of the train_on_batch policy with Adam updates: weights stay within fp32 tolerance of the fp64
-    oracle trainer (optimizertts_wgan.py:216-241).  Adam's first updates are ~lr*sign(g): an element whose gradient is at
-    round-off level moves by +-lr per update in ANY fp32 evaluation, so the criteria are (i) the relative L2 distance over
-    all the weights of a network < 2e-3 and (ii) no single element further than 2*lr*updates (every sign flipped) from
-    the oracle's."""
+    """Six batches of the train_on_batch policy with Adam updates against the fp64 oracle trainer (optimizertts_wgan.py:216-241).
+    Adam's first updates are ~lr*sign(g): an element whose gradient is at round-off level moves by +-lr per update in ANY fp32
+    evaluation, the oracle's own fp32 run included.  Criteria: (i) no element further than 2*lr*updates (every sign flipped)
+    from the fp64 trajectory, (ii) per network, the L2 distance to the fp64 trajectory is within 3x the distance of the oracle's
+    own fp32 trajectory (or 1e-3 relative, whichever is larger): as good as a plain fp32 evaluation of the reference graph."""
     ao, wg, wc, wgt, wct, X, Y, alpha, st = setup(cuda_ops, MID, 2, 40)
     tr = O.OracleTrainer(ao, wg, wc, dtype=torch.float64)
+    tr32 = O.OracleTrainer(ao, wg, wc, dtype=torch.float32)
     gu = 0
     nb = 6
     for batchid in range(nb):
         X, Y, al = O.synthetic_batch(ao, 2, 40, seed=100 + batchid)
         bid = batchid * 5
         tr.train_on_batch(bid, X, Y, al)
+        tr32.train_on_batch(bid, X, Y, al)
         Xd, Yd = torch.tensor(X).cuda(), torch.tensor(Y).cuda()
         st.critic_step(Xd, Yd, alpha=torch.tensor(al).cuda())
         if bid % W.critic_runs(gu) == 0:
             st.generator_step(Xd, Yd)
             gu += 1
     assert gu == tr.generator_updates
-    for store, ref, lr, nupd in ((st.C.params, tr.wc, st.copt[0], nb), (st.G.params, tr.wg, st.gopt[0], gu)):
-        num = den = 0.0
+    for store, ref, ref32, lr, nupd in ((st.C.params, tr.wc, tr32.wc, st.copt[0], nb), (st.G.params, tr.wg, tr32.wg, st.gopt[0], gu)):
+        num = num32 = den = 0.0
         trainable = set(store.g.keys())
         for k, v in ref.items():
             got, want = store.p[k].detach().cpu().double(), v.detach().double()
             num += float(((got - want) ** 2).sum())
+            num32 += float(((ref32[k].detach().double() - want) ** 2).sum())
             den += float((want ** 2).sum())
             if k in trainable:
                 assert float((got - want).abs().max()) <= 2.0 * lr * nupd * 1.001, (k, float((got - want).abs().max()))
             else:
                 assert relerr(got, want) < 1e-2, (k, relerr(got, want))
-        assert (num / den) ** 0.5 < 2e-3, (num / den) ** 0.5
+        d, d32 = (num / den) ** 0.5, (num32 / den) ** 0.5
+        assert d < max(3.0 * d32, 1e-3), (d, d32)
 
 
 def test_inference_predict_and_validation_losses(cuda_ops):

@@ -82,7 +82,8 @@ def main():
                note='%.2f GFLOP' % (fl / 1e9))
         report('conv2d_simt_fwd 4->4 %s' % tag, lambda: simt.conv2d(x, w, y, bias=bias, flags=EPI_LRELU), nbytes=2 * mapb)
         dw = torch.empty(5, 5, 4, 4, device=dev)
-        report('conv2d_wgrad 4->4 %s' % tag, lambda: ops.conv2d_wgrad(x, y, dw), nbytes=2 * mapb)
+        dbias = torch.empty(4, device=dev)
+        report("conv2d_wgrad 4->4 %s (+bias)" % tag, lambda: ops.conv2d_wgrad(x, y, dw, dbias=dbias), nbytes=2 * mapb, note="%.2f GFLOP, CUDA cores" % (fl / 1e9))
     x1, y4, w14 = rnd(3 * B, T, S, 1), torch.empty(3 * B, T, S, 4, device=dev), rnd(5, 5, 1, 4)
     report('conv2d_simt_fwd 1->4 3B', lambda: ops.conv2d(x1, w14, y4), nbytes=3 * B * T * S * 4 * 5)
     w41 = rnd(5, 5, 4, 1)
