@@ -1,0 +1,81 @@
+"""
+Data-parallel parity on real GPUs (launch: torchrun --nproc-per-node N tools/dp_gpu_check.py): N ranks, each with B/N utterances
+of one global batch, sync-BN + NCCL all-reduce of the flat gradients, against the CPU oracle's single-device step on the whole
+batch.  Also runs the CUDA-graph trainer path for a few steps to check that replicas stay bit-identical.
+"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+import torch.distributed as dist
+from oracle import percival_oracle as O
+from percivaltts_b200 import arch as A, parallel, wgan as W
+from percivaltts_b200.ops import CudaOps
+from percivaltts_b200.trainer import DeviceTrainer
+from percivaltts_b200.wgan import WGANStepper
+
+KW = dict(ctxsize=60, spec_size=33, nm_size=9, hiddenwidth=32, ctx_nbcnnlayers=1, ctx_winlen=21, gen_nbcnnlayers=4,
+          gen_nbfilters=4, gen_winlen=5, spec_freqlen=5)
+
+
+def main():
+    import faulthandler
+    faulthandler.dump_traceback_later(90, exit=True)
+    sync, device = parallel.init_from_env()
+    rank, world = sync.rank, sync.world
+    ops = CudaOps()
+    ao, a = O.Arch(**KW), A.Arch(**KW)
+    wg = O.perturb_params(O.init_params(O.generator_param_shapes(ao), seed=1))
+    wc = O.perturb_params(O.init_params(O.critic_param_shapes(ao), seed=2))
+    _, wls, wbar = O.wlswgan_weights(ao)
+    st = WGANStepper(ops, a, w_ls=wls, w_wgan_mean=wbar, sync=sync)
+    st.G.params.load(wg)
+    st.C.params.load(wc)
+    Bg, T = 2 * world, 48
+    X, Y, alpha = O.synthetic_batch(ao, Bg, T, seed=11)
+    Xl, Yl, al = (torch.tensor(parallel.shard_batch(v, rank, world)).to(device) for v in (X, Y, alpha))
+    st.critic_step(Xl, Yl, alpha=al, apply=False)
+    sync.allreduce(st.C.params.grad)
+    lc = float(st.losses[W.L_CRITIC])
+    gc = st.C.params.export_grads()
+    st.generator_step(Xl, Yl, apply=False)
+    sync.allreduce(st.G.params.grad)
+    lg = float(st.losses[W.L_GEN])
+    gg = st.G.params.export_grads()
+    ok = True
+    if rank == 0:
+        dt = torch.float64
+        wgt, wct = O.to_torch(wg, dt, True), O.to_torch(wc, dt, True)
+        Xt, Yt = torch.tensor(X, dtype=dt), torch.tensor(Y, dtype=dt)
+        rc = O.critic_step(ao, wgt, wct, Xt, Yt, torch.tensor(alpha, dtype=dt).reshape(-1, 1, 1))
+        rg = O.generator_step(ao, wgt, wct, Xt, Yt)
+        def rel(got, want):
+            want = want.detach().double().numpy()
+            return float(np.abs(got - want).max() / (np.abs(want).max() + 1e-30))
+        worst = max([rel(gc[k], v) for k, v in rc['grads'].items() if float(v.abs().max()) > 1e-10] +
+                    [rel(gg[k], v) for k, v in rg['grads'].items() if float(v.abs().max()) > 1e-10])
+        print('dp%d: critic loss %.6f (oracle %.6f)  generator loss %.6f (oracle %.6f)  worst grad rel err %.2e'
+              % (world, lc, float(rc['loss']), lg, float(rg['loss']), worst))
+        ok = abs(lc - float(rc['loss'])) < 1e-3 * max(abs(float(rc['loss'])), 1e-2) and abs(lg - float(rg['loss'])) < 1e-3 * abs(float(rg['loss'])) and worst < 1e-3
+    # graph path: replicas must stay bit-identical after updates
+    tr = DeviceTrainer(st)
+    for i in range(6):
+        Xb, Yb, _ = O.synthetic_batch(ao, Bg, T, seed=20 + i)
+        tr.train_on_batch(i * 5, parallel.shard_batch(Xb, rank, world), parallel.shard_batch(Yb, rank, world))
+    flat = torch.cat([st.C.params.flat, st.G.params.flat, st.G.params.state])
+    ref = flat.clone()
+    if world > 1:
+        dist.broadcast(ref, 0)
+    same = bool(torch.equal(ref, flat))
+    t = torch.tensor([int(ok and same)], device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print('replicas identical after 6 graph steps:', same, ' ALL OK' if int(t) else ' FAILED')
+    # destroy_process_group() blocks while captured CUDA graphs still hold NCCL work: leave through os._exit
+    sys.stdout.flush()
+    os._exit(0 if int(t) else 1)
+
+
+if __name__ == '__main__':
+    main()
