@@ -10,6 +10,7 @@ same interface with plain torch on the CPU *for testing the host logic only* (it
 """
 import contextlib
 import os
+import weakref
 
 import torch
 
@@ -114,7 +115,8 @@ class CudaOps(object):
         self.conv2d_tc = os.environ.get('PCTTS_CONV2D_TC', '1') != '0'   # tcgen05 implicit-GEMM Conv2D (4->4, 5x5)
         self._shadows = {}         # view key -> Shadow
         self._fresh = {}           # view key -> (lo, hi): activation shadows valid inside the current step scope
-        self._persist_ranges = []  # [lo, hi) of parameter buffers: their shadows are refreshed by refresh_persistent()
+        self._persist_ranges = []  # (weakref of the parameter buffer, lo, hi): shadows of views into it are refreshed by
+                                   # refresh_persistent(); a range dies with its buffer (the addresses may be reused)
         self._persist = {}         # view key -> (Shadow, view)
         self._tracking = False
         self._red = {}
@@ -163,7 +165,20 @@ class CudaOps(object):
 
     def register_persistent(self, flat):
         """Declare a parameter buffer: shadows of views into it stay valid until refresh_persistent(flat)."""
-        self._persist_ranges.append(_extent(flat))
+        lo, hi = _extent(flat)
+        self._persist_ranges.append((weakref.ref(flat), lo, hi))
+
+    def _is_persistent(self, ptr):
+        """ptr lies in a LIVE registered parameter buffer.  Ranges of buffers that no longer exist are dropped together with the
+        shadows taken from them: their memory goes back to the allocator and may come back as an activation."""
+        dead = [r for r in self._persist_ranges if r[0]() is None]
+        if dead:
+            self._persist_ranges = [r for r in self._persist_ranges if r[0]() is not None]
+            for _, lo, hi in dead:
+                for key in [k for k in self._persist if lo <= k[0] < hi]:
+                    del self._persist[key]
+                    self._shadows.pop(key, None)
+        return any(lo <= ptr < hi for _, lo, hi in self._persist_ranges)
 
     def refresh_persistent(self, flat):
         """Re-split every shadow taken from views of `flat` (after Adam or a weight load)."""
@@ -191,7 +206,7 @@ class CudaOps(object):
             _, _, _, _, rows, cols = _mat(t)
             sh = self._shadows[key] = Shadow(self.device, rows, cols, PLANES[self.nterms])
         ptr = key[0]
-        if any(lo <= ptr < hi for lo, hi in self._persist_ranges):
+        if self._is_persistent(ptr):
             if key not in self._persist:
                 self._persist[key] = (sh, t)
                 self._split(t, sh)

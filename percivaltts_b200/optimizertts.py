@@ -67,6 +67,8 @@ class OptimizerTTS(object):
     def default_options(self, cfg):
         return cfg
 
+    supports_prefetch = False      # train_on_batch() takes next_batch=(X, Y) (B200 addition; the reference loads synchronously)
+
     def prepare(self):
         raise NotImplementedError('prepare() has to be provided by the loss-specific sub-class')
 
@@ -158,17 +160,27 @@ class OptimizerTTS(object):
             np.random.shuffle(rndidx)
             rndidxb = np.split(rndidx, nbbatches)
             costs_tra_batches, load_times, train_times = [], [], []
+            def load_batch(bid):
+                fid_lst_trab = [fid_lst_tra[bidx] for bidx in rndidxb[bid]]
+                return data.load_inoutset(indir, outdir, wdir, fid_lst_trab, length=cfg.train_batch_length,
+                                          lengthmax=cfg.train_batch_lengthmax,
+                                          maskpadtype=cfg.train_batch_padtype, cropmode=cfg.train_batch_cropmode)
+            # one batch of look-ahead: batch i+1 is read (same order of numpy RNG draws as the reference, which loads batch by
+            # batch, optimizertts.py:231-232) before batch i trains, so that its host->device copy overlaps the kernels of batch i
+            t0 = time.time()
+            nxt = load_batch(0) if nbbatches > 0 else None
             for batchid in range(nbbatches):
-                t0 = time.time()
                 print_tty('\r    Training batch {}/{}'.format(1 + batchid, nbbatches))
-                fid_lst_trab = [fid_lst_tra[bidx] for bidx in rndidxb[batchid]]
-                X_trab, Y_trab, W_trab = data.load_inoutset(indir, outdir, wdir, fid_lst_trab, length=cfg.train_batch_length,
-                                                            lengthmax=cfg.train_batch_lengthmax,
-                                                            maskpadtype=cfg.train_batch_padtype, cropmode=cfg.train_batch_cropmode)
+                X_trab, Y_trab, W_trab = nxt
+                nxt = load_batch(batchid + 1) if batchid + 1 < nbbatches else None
                 load_times.append(time.time() - t0)
                 t1 = time.time()
-                cost_tra = self.train_on_batch(batchid, X_trab, Y_trab)
-                train_times.append(time.time() - t1)
+                if self.supports_prefetch and nxt is not None:
+                    cost_tra = self.train_on_batch(batchid, X_trab, Y_trab, next_batch=(nxt[0], nxt[1]))
+                else:
+                    cost_tra = self.train_on_batch(batchid, X_trab, Y_trab)
+                t0 = time.time()
+                train_times.append(t0 - t1)
                 if cost_tra is not None:
                     if np.isnan(cost_tra):
                         print_log('    E{} Batch {}/{} train cost = {}'.format(epoch, 1 + batchid, nbbatches, cost_tra))

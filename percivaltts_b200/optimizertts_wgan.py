@@ -22,6 +22,7 @@ from .wgan import WGANStepper, NLOSS, L_CRITIC, L_GEN
 
 
 class OptimizerTTSWGAN(optimizertts.OptimizerTTS):
+    supports_prefetch = True
 
     def __init__(self, cfgtomerge, model, errtype='WGAN', critic=None, **kwargs):
         optimizertts.OptimizerTTS.__init__(self, cfgtomerge, model, errtype, **kwargs)
@@ -111,11 +112,13 @@ class OptimizerTTSWGAN(optimizertts.OptimizerTTS):
         self.trainer.generator_updates = self.generator_updates
 
     # ---- the hot path -----------------------------------------------------------------------------------------------
-    def train_on_batch(self, batchid, X_trab, Y_trab, alpha=None):
+    def train_on_batch(self, batchid, X_trab, Y_trab, alpha=None, next_batch=None):
         """One critic update, plus one generator update when batchid % critic_runs == 0 (optimizertts_wgan.py:216-241).
         X_trab [B,T,ctxsize], Y_trab [B,T,out] host float32 arrays (not retained).  Returns the generator cost or None.
-        `alpha` [B] fixes the interpolation weights of the gradient penalty (tests); default: device RNG."""
-        critic_cost, cost_tra = self.trainer.train_on_batch(batchid, X_trab, Y_trab, alpha=alpha)
+        `alpha` [B] fixes the interpolation weights of the gradient penalty (tests); default: device RNG.
+        `next_batch` = (X, Y) of the following call when the caller already holds it (the base loop does): its host->device
+        copy then overlaps this batch's kernels."""
+        critic_cost, cost_tra = self.trainer.train_on_batch(batchid, X_trab, Y_trab, alpha=alpha, next_batch=next_batch)
         self.costs_tra_critic_batches.append(critic_cost)
         self.generator_updates = self.trainer.generator_updates
         return cost_tra

@@ -36,6 +36,11 @@ class DeviceTrainer(object):
         self.generator_updates = 0
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        # double-buffered prefetch of the NEXT batch (train_on_batch(..., next_batch=)): pinned + device staging, own copy stream
+        self._pf = None
+        self._pf_slot = 0
+        self._pf_bufs = [None, None]
+        self._copy_stream = None
 
     # ---- shape state / graph capture ---------------------------------------------------------------------------
     def shape_state(self, B, T):
@@ -101,12 +106,50 @@ class DeviceTrainer(object):
         if alpha is not None:
             s.alpha.copy_(torch.as_tensor(np.asarray(alpha, dtype=np.float32)), non_blocking=False)
 
-    def train_on_batch(self, batchid, X, Y, alpha=None):
+    def _prefetch(self, X, Y):
+        """Stage the next batch while the GPU runs the current one: numpy -> pinned (host memcpy) -> device staging buffer on
+        the copy stream.  The batch is recognised by object identity at the next train_on_batch() call."""
+        if self.ops.device.type != 'cuda':
+            return
+        X = np.ascontiguousarray(X, dtype=np.float32)
+        Y = np.ascontiguousarray(Y, dtype=np.float32)
+        j = self._pf_slot ^ 1
+        need = (X.size, Y.size)
+        b = self._pf_bufs[j]
+        if b is None or b['cap'][0] < need[0] or b['cap'][1] < need[1]:
+            b = self._pf_bufs[j] = dict(
+                cap=need, Xh=torch.empty(need[0], dtype=torch.float32, pin_memory=True),
+                Yh=torch.empty(need[1], dtype=torch.float32, pin_memory=True),
+                Xd=torch.empty(need[0], dtype=torch.float32, device=self.ops.device),
+                Yd=torch.empty(need[1], dtype=torch.float32, device=self.ops.device), ev=torch.cuda.Event())
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.ops.device)
+        b['Xh'][:X.size].copy_(torch.from_numpy(X.reshape(-1)))
+        b['Yh'][:Y.size].copy_(torch.from_numpy(Y.reshape(-1)))
+        with torch.cuda.stream(self._copy_stream):
+            b['Xd'][:X.size].copy_(b['Xh'][:X.size], non_blocking=True)
+            b['Yd'][:Y.size].copy_(b['Yh'][:Y.size], non_blocking=True)
+            b['ev'].record(self._copy_stream)
+        self.h2d_bytes += (X.size + Y.size) * 4
+        self._pf_slot = j
+        self._pf = (X, Y, tuple(X.shape), tuple(Y.shape))
+
+    def train_on_batch(self, batchid, X, Y, alpha=None, next_batch=None):
         """-> (critic_cost, generator_cost or None), python floats (one blocking read of the loss vector per batch,
-        like the reference's float(critic_returns), optimizertts_wgan.py:220-221)."""
+        like the reference's float(critic_returns), optimizertts_wgan.py:220-221).
+        next_batch = (X, Y) of the following call, if known: it is staged to the device while this batch computes."""
         B, T = int(X.shape[0]), int(X.shape[1])
         s = self.shape_state(B, T)
-        self.stage(s, X, Y, alpha)
+        pf = self._pf
+        if pf is not None and alpha is None and (pf[0] is X or (pf[2] == tuple(X.shape) and np.shares_memory(pf[0], X))) \
+                and (pf[1] is Y or (pf[3] == tuple(Y.shape) and np.shares_memory(pf[1], Y))):
+            b = self._pf_bufs[self._pf_slot]
+            torch.cuda.current_stream(self.ops.device).wait_event(b['ev'])
+            s.X.view(-1).copy_(b['Xd'][:s.X.numel()], non_blocking=True)
+            s.Y.view(-1).copy_(b['Yd'][:s.Y.numel()], non_blocking=True)
+        else:
+            self.stage(s, X, Y, alpha)
+        self._pf = None
         self.critic_step_device(s, explicit_alpha=alpha is not None)
         trained_gen = False
         if batchid % W.critic_runs(self.generator_updates) == 0:
@@ -114,6 +157,8 @@ class DeviceTrainer(object):
             trained_gen = True
         s.lossh.copy_(self.st.losses, non_blocking=True)
         self.d2h_bytes += W.NLOSS * 4
+        if next_batch is not None:
+            self._prefetch(next_batch[0], next_batch[1])
         if self.ops.device.type == 'cuda':
             torch.cuda.current_stream(self.ops.device).synchronize()
         critic_cost = float(s.lossh[W.L_CRITIC])

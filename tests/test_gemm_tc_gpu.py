@@ -174,3 +174,24 @@ def test_shadow_freshness_inside_step_scope(cuda_ops):
         assert cuda_ops.launches - n0 == first - 1
         want = torch.ones(M, K, dtype=torch.float64) @ B.cpu().double()
         assert err(C, want) < TOL6
+
+
+def test_parameter_ranges_die_with_their_buffer():
+    """A registered parameter buffer that has been freed must not make later tensors at the same address 'persistent'
+    (their bf16 operand shadows would never be refreshed): regression test for a stale-range aliasing bug."""
+    from percivaltts_b200.ops import CudaOps
+    ops = CudaOps()
+    flat = ops.zeros(64 * 64)
+    ops.register_persistent(flat)
+    ptr = flat.data_ptr()
+    del flat
+    a = ops.empty(64, 64)
+    if a.data_ptr() != ptr:
+        pytest.skip('allocator did not hand the freed block back')
+    b = torch.randn(64, 64, device='cuda')
+    c = ops.empty(64, 64)
+    for _ in range(2):
+        a.normal_()
+        ops.gemm(a, b, c)
+        want = a.double() @ b.double()
+        assert float((c.double() - want).abs().max()) < 1e-4 * float(want.abs().max())

@@ -191,3 +191,23 @@ def test_critic_step_spectral_only_generator_is_result_preserving(cuda_ops):
     rc = O.critic_step(ao, wgt, wct, torch.tensor(X, dtype=dt), torch.tensor(Y, dtype=dt),
                        torch.tensor(alpha, dtype=dt).reshape(-1, 1, 1))
     assert relerr(st.buffers(3, 57)['fake'], rc['fake']) < TOL
+
+
+def test_next_batch_prefetch_is_bit_identical(cuda_ops):
+    """DeviceTrainer.train_on_batch(..., next_batch=) stages the following host batch while the current one computes; the
+    trajectory (CUDA graphs, device RNG for alpha) is bit-identical to the synchronous staging of every batch."""
+    from percivaltts_b200.trainer import DeviceTrainer
+    batches = [O.synthetic_batch(O.Arch(**MID), 2, 40, seed=300 + i)[:2] for i in range(5)]
+    finals = []
+    for prefetch in (False, True):
+        ao, wg, wc, wgt, wct, X, Y, alpha, st = setup(cuda_ops, MID, 2, 40)
+        tr = DeviceTrainer(st)
+        costs = []
+        for i, (Xb, Yb) in enumerate(batches):
+            nxt = batches[i + 1] if prefetch and i + 1 < len(batches) else None
+            costs.append(tr.train_on_batch(i * 5, Xb, Yb, next_batch=nxt))
+        finals.append((costs, st.C.params.flat.clone(), st.G.params.flat.clone(), st.G.params.state.clone()))
+    assert finals[0][0] == finals[1][0]
+    for a_, b_ in zip(finals[0][1:], finals[1][1:]):
+        assert torch.equal(a_, b_)
+    assert all(np.isfinite(c[0]) for c in finals[0][0])

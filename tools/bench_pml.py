@@ -1,0 +1,66 @@
+"""
+BASELINE config #5: PML vocoder feature compress / decompress throughput over 1 M synthetic frames:
+SPEC = exp(N(-6,2)) [1e6, 2049] -> fwlspec [1e6,129] (log|.| + mel-band interpolation) and back (Catmull-Rom + exp);
+NM ~ U(0,1) [1e6, 2049] -> fwnm [1e6,33] and back.  Processed in chunks of 250 k frames (2 GB in) through the public API
+(sigproc.linbnd2fwbnd_device / fwbnd2linbnd_device); CUDA events around the kernels, data resident in HBM.
+CPU baseline: the numpy oracle (oracle/pml_oracle.py) on 10 k frames, one core.
+"""
+import json, os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+from percivaltts_b200 import sigproc as sp
+from percivaltts_b200.ops import CudaOps
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def main():
+    ops = CudaOps()
+    peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json'))) if os.path.exists(os.path.join(ROOT, 'MEASURED_PEAKS.json')) else {}
+    hbm = float(peaks.get('hbm_gbs', 6650.0))
+    fs, dftlen, NB = 16000, 4096, 2049
+    total, chunk = 1000000, 250000
+    g = torch.Generator(device='cuda').manual_seed(3)
+    spec = torch.exp(torch.randn(chunk, NB, device='cuda', generator=g) * 2 - 6)
+    nm = torch.rand(chunk, NB, device='cuda', generator=g)
+    out = {}
+    for name, x, K, log_abs in (('spec', spec, 129, True), ('nm', nm, 33, False)):
+        y = torch.empty(chunk, K, device='cuda')
+        back = torch.empty(chunk, NB, device='cuda')
+        for _ in range(2):
+            sp.linbnd2fwbnd_device(x, fs, dftlen, K, log_abs=log_abs, out=y, ops=ops)
+            sp.fwbnd2linbnd_device(y, fs, dftlen, smooth=log_abs, do_exp=log_abs, out=back, ops=ops)
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        torch.cuda.synchronize()
+        e[0].record()
+        for _ in range(total // chunk):
+            sp.linbnd2fwbnd_device(x, fs, dftlen, K, log_abs=log_abs, out=y, ops=ops)
+        e[1].record()
+        for _ in range(total // chunk):
+            sp.fwbnd2linbnd_device(y, fs, dftlen, smooth=log_abs, do_exp=log_abs, out=back, ops=ops)
+        e[2].record()
+        torch.cuda.synchronize()
+        tc, td = e[0].elapsed_time(e[1]), e[1].elapsed_time(e[2])
+        nbytes = total * (NB + K) * 4.0
+        out[name] = {'bands': K, 'compress_ms': round(tc, 3), 'compress_frames_per_s': round(total / tc * 1e3),
+                     'compress_GBps': round(nbytes / tc / 1e6, 1), 'compress_frac_of_measured_hbm': round(nbytes / tc / 1e6 / hbm, 3),
+                     'decompress_ms': round(td, 3), 'decompress_frames_per_s': round(total / td * 1e3),
+                     'decompress_GBps': round(nbytes / td / 1e6, 1), 'decompress_frac_of_measured_hbm': round(nbytes / td / 1e6 / hbm, 3)}
+        if name == 'nm':   # the operator is convex: the noise mask stays inside [0,1] (pulsemodel/synthesis.py:82,376)
+            out[name]['decompressed_range'] = [float(back.min()), float(back.max())]
+    # CPU baseline: numpy oracle, 10 k frames, single thread
+    from oracle import pml_oracle as PO
+    xs = np.exp(np.random.RandomState(0).normal(-6, 2, size=(10000, NB)))
+    t0 = time.perf_counter()
+    c = PO.linbnd2fwbnd(np.log(np.abs(xs)), fs, dftlen, 129)
+    t1 = time.perf_counter()
+    PO.fwbnd2linbnd(c, fs, dftlen, smooth=True)
+    t2 = time.perf_counter()
+    out['cpu_oracle'] = {'frames': 10000, 'cores': 1, 'compress_frames_per_s': round(10000 / (t1 - t0)), 'decompress_frames_per_s': round(10000 / (t2 - t1))}
+    out.update(config='pml_1M_frames', hbm_peak_GBps=hbm, bytes_per_frame={'compress_spec': (NB + 129) * 4, 'compress_nm': (NB + 33) * 4})
+    print(json.dumps(out))
+
+
+if __name__ == '__main__':
+    main()
