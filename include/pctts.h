@@ -35,6 +35,8 @@ int pctts_abi_version(void);
 int pctts_device_check(int dev);
 /* number of kernels this library has launched (or recorded into a CUDA graph under capture) so far. Host call. */
 long pctts_launch_count(void);
+/* programmatic dependent launch between the library's kernels (default off; env PCTTS_PDL=1 turns it on). Host call. */
+int pctts_set_pdl(int on);
 
 /* ---- dense contractions: keras Dense (networktts.py:59-63,196-197), Conv1D as virtual-im2col GEMM (networktts.py:116-120),
  *      LSTM input projections (networktts.py:90-94), and all their data / weight gradients ------------------------------- */

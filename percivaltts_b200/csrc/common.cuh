@@ -26,6 +26,36 @@ void pctts_note_launch();
         if (e__ != cudaSuccess) return (int)e__;      \
     } while (0)
 
+// Programmatic dependent launch: every kernel of the library can be launched with the programmatic-stream-serialization
+// attribute and opens with pdl_entry(): `launch_dependents` lets the next kernel of the stream be scheduled (its CTAs become
+// resident and run their prologue) while this one is still running; `wait` then blocks until the previous kernel has completed
+// and flushed its writes.  No global memory is touched before the wait, so stream order semantics are unchanged; what
+// would disappear is the launch latency + prologue between the ~200 dependent kernels of a step.  Opt-in (PCTTS_PDL=1):
+// inside the captured step graphs the measured gain on B200 is nil (see api.cu).
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_entry() {
+    pdl_trigger();
+    pdl_wait();
+}
+
+int pctts_pdl_enabled();
+
+template <typename... KA, typename... A>
+static inline void pctts_launch(void (*kern)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pctts_pdl_enabled() ? 1 : 0;
+    (void)cudaLaunchKernelEx(&cfg, kern, static_cast<KA>(args)...);   // the error, if any, is read by PCTTS_LAUNCH_CHECK
+}
+
 __device__ __forceinline__ float lrelu_f(float x) { return x > 0.f ? x : PCTTS_LRELU_ALPHA * x; }
 // derivative of LeakyReLU written in terms of the *output* (sign-preserving, so y>0 <=> x>0)
 __device__ __forceinline__ float dlrelu_from_out(float y) { return y > 0.f ? 1.f : PCTTS_LRELU_ALPHA; }

@@ -19,6 +19,7 @@ __global__ void __launch_bounds__(NTHREADS)
 conv2d_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                   const float* aux, float* y, int T, int F, int pad_t, int pad_f,
                   long xpitch, long ypitch, long auxpitch, long xbatch, long ybatch, long auxbatch, int flags) {
+    pdl_entry();
     extern __shared__ __align__(16) float smem[];
     constexpr int NW = KH * KW * CIN * COUT;
     float* ws = smem;                                   // [KH][KW][CIN][COUT]
@@ -98,6 +99,7 @@ __global__ void conv2d_fwd_generic(const float* __restrict__ x, const float* __r
                                    float* y, int NB, int T, int F, int CIN, int COUT, int KH, int KW,
                                    int pad_t, int pad_f, long xpitch, long ypitch, long auxpitch, long xbatch,
                                    long ybatch, long auxbatch, int flags) {
+    pdl_entry();
     const long total = (long)NB * T * F * COUT;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
         const int co = (int)(i % COUT);
@@ -127,6 +129,7 @@ __global__ void conv2d_fwd_generic(const float* __restrict__ x, const float* __r
 }
 
 __global__ void conv2d_flip_kernel(const float* __restrict__ w, float* __restrict__ wt, int KH, int KW, int CIN, int COUT) {
+    pdl_entry();
     const int total = KH * KW * CIN * COUT;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         // i indexes wt[kt][kf][co][ci]
@@ -147,6 +150,7 @@ template <int CIN, int COUT, int KH, int KW>
 __global__ void __launch_bounds__(KH * WG_PS * 32)
 conv2d_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ partial, int T, int F,
                     int pad_t, int pad_f, long xpitch, long dypitch, long xbatch, long dybatch) {
+    pdl_entry();
     extern __shared__ __align__(16) float smem[];
     constexpr int NW = KH * KW * CIN * COUT;
     constexpr int NTH = KH * WG_PS * 32;
@@ -219,6 +223,7 @@ conv2d_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy, f
 __global__ void conv2d_wgrad_generic(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ partial,
                                      int T, int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch,
                                      long dypitch, long xbatch, long dybatch) {
+    pdl_entry();
     // one CTA per (time-slab, n); thread loops over weight elements; slow, exact, for unusual shapes only
     const int NW = KH * KW * CIN * COUT;
     const int t0 = blockIdx.x * WG_TT, n = blockIdx.y;
@@ -247,6 +252,7 @@ __global__ void conv2d_wgrad_generic(const float* __restrict__ x, const float* _
 // one warp per weight element: lanes stride over the per-CTA partials, butterfly sum in a fixed order
 __global__ void reduce_partials_kernel(const float* __restrict__ partial, float* __restrict__ out, int nblk, int NW,
                                        float scale, int accumulate) {
+    pdl_entry();
     const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (i >= NW) return;
@@ -270,8 +276,7 @@ int launch_fwd(const float* x, const float* w, const float* bias, const float* a
     auto kern = conv2d_fwd_kernel<CIN, COUT, KH, KW>;
     if (smem > 48 * 1024) PCTTS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(pctts_div_up(T, TT), NB, pctts_div_up(F, FT_MAX));
-    kern<<<grid, NTHREADS, smem, st>>>(x, w, bias, aux, y, T, F, pad_t, pad_f, xpitch, ypitch, auxpitch, xbatch, ybatch,
-                                       auxbatch, flags);
+    pctts_launch(kern, grid, NTHREADS, smem, st, x, w, bias, aux, y, T, F, pad_t, pad_f, xpitch, ypitch, auxpitch, xbatch, ybatch, auxbatch, flags);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -286,7 +291,7 @@ int launch_wgrad(const float* x, const float* dy, float* partial, int NB, int T,
     if (smem > 200 * 1024) return PCTTS_EUNSUPPORTED;
     if (smem > 48 * 1024) PCTTS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(pctts_div_up(T, WG_TT), NB);
-    kern<<<grid, KH * WG_PS * 32, smem, st>>>(x, dy, partial, T, F, pad_t, pad_f, xpitch, dypitch, xbatch, dybatch);
+    pctts_launch(kern, grid, KH * WG_PS * 32, smem, st, x, dy, partial, T, F, pad_t, pad_f, xpitch, dypitch, xbatch, dybatch);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -315,8 +320,7 @@ extern "C" int pctts_conv2d_fwd(const float* x, const float* w, const float* bia
     const long total = (long)NB * T * F * COUT;
     int blocks = pctts_div_up(total, 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
-    conv2d_fwd_generic<<<blocks, 256, 0, st>>>(x, w, bias, aux, y, NB, T, F, CIN, COUT, KH, KW, pad_t, pad_f, xpitch, ypitch,
-                                               auxpitch, xbatch, ybatch, auxbatch, flags);
+    pctts_launch(conv2d_fwd_generic, blocks, 256, 0, st, x, w, bias, aux, y, NB, T, F, CIN, COUT, KH, KW, pad_t, pad_f, xpitch, ypitch, auxpitch, xbatch, ybatch, auxbatch, flags);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -324,7 +328,7 @@ extern "C" int pctts_conv2d_fwd(const float* x, const float* w, const float* bia
 extern "C" int pctts_conv2d_flip_weights(const float* w, float* wt, int KH, int KW, int CIN, int COUT, void* stream) {
     if (!w || !wt) return PCTTS_EINVAL;
     const int total = KH * KW * CIN * COUT;
-    conv2d_flip_kernel<<<pctts_div_up(total, 128), 128, 0, (cudaStream_t)stream>>>(w, wt, KH, KW, CIN, COUT);
+    pctts_launch(conv2d_flip_kernel, pctts_div_up(total, 128), 128, 0, (cudaStream_t)stream, w, wt, KH, KW, CIN, COUT);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -340,7 +344,7 @@ int pctts_conv2d_wgrad44(const float* x, const float* dy, float* dw, float* dbia
                          int F, long xpitch, long dypitch, long xbatch, long dybatch, float scale, int accumulate, cudaStream_t st);
 
 int pctts_reduce_partials(const float* partial, float* out, int nblk, int NW, float scale, int accumulate, cudaStream_t st) {
-    reduce_partials_kernel<<<pctts_div_up(NW, 8), 256, 0, st>>>(partial, out, nblk, NW, scale, accumulate);
+    pctts_launch(reduce_partials_kernel, pctts_div_up(NW, 8), 256, 0, st, partial, out, nblk, NW, scale, accumulate);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -375,13 +379,12 @@ extern "C" int pctts_conv2d_wgrad(const float* x, const float* dy, float* dw, fl
 #undef WG_ARGS
     if (rc == PCTTS_EUNSUPPORTED) {
         dim3 grid(pctts_div_up(T, WG_TT), NB);
-        conv2d_wgrad_generic<<<grid, 128, 0, st>>>(x, dy, workspace, T, F, CIN, COUT, KH, KW, pad_t, pad_f, xpitch, dypitch,
-                                                   xbatch, dybatch);
+        pctts_launch(conv2d_wgrad_generic, grid, 128, 0, st, x, dy, workspace, T, F, CIN, COUT, KH, KW, pad_t, pad_f, xpitch, dypitch, xbatch, dybatch);
         PCTTS_LAUNCH_CHECK();
         rc = PCTTS_OK;
     }
     if (rc != PCTTS_OK) return rc;
-    reduce_partials_kernel<<<pctts_div_up(NW, 8), 256, 0, st>>>(workspace, dw, nblk, NW, scale, accumulate);
+    pctts_launch(reduce_partials_kernel, pctts_div_up(NW, 8), 256, 0, st, workspace, dw, nblk, NW, scale, accumulate);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

@@ -123,6 +123,7 @@ struct C2Smem {
 
 template <int PARTS>
 __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params p) {
+    pdl_trigger();   // the wait follows the barrier / TMEM set-up (nothing before it touches global memory)
     extern __shared__ __align__(16) uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[2], empty_bar[2], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_slot;
@@ -178,6 +179,7 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
             }
         }
     };
+    pdl_wait();
     float4 ca[C2_UNR], cb[C2_UNR], na[C2_UNR], nb[C2_UNR];
     if (warp < C2_PW && nitems > 0) issue(0, ca, cb);   // first tile's loads fly while the weight operand is built
 
@@ -408,7 +410,7 @@ int launch_c2(C2Params& p, cudaStream_t st) {
         attr_smem = smem;
     }
     const int grid = p.ntiles < 148 ? p.ntiles : 148;
-    conv2d_tc_kernel<PARTS><<<grid, C2_THREADS, smem, st>>>(p);
+    pctts_launch(conv2d_tc_kernel<PARTS>, grid, C2_THREADS, smem, st, p);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

@@ -54,6 +54,7 @@ __device__ __forceinline__ void fma_px(float (&acc)[5][4][4], const float4& w0, 
 }
 
 __global__ void __launch_bounds__(W4_THREADS, 1) conv2d_wgrad44_kernel(const W4Params p) {
+    pdl_entry();
     extern __shared__ __align__(16) float4 smem4[];
     const int F = p.F, FW = F + 4;
     const int xs_n = (W4_TT + 4) * FW, dys_n = W4_TT * F;       // float4 (pixel) counts
@@ -206,7 +207,7 @@ int pctts_conv2d_wgrad44(const float* x, const float* dy, float* dw, float* dbia
         attr_smem = smem;
     }
     const int grid = p.ntiles < 148 ? p.ntiles : 148;
-    conv2d_wgrad44_kernel<<<grid, W4_THREADS, smem, st>>>(p);
+    pctts_launch(conv2d_wgrad44_kernel, grid, W4_THREADS, smem, st, p);
     PCTTS_LAUNCH_CHECK();
     int rc = pctts_reduce_partials(workspace, dw, grid, W4_NW, scale, accumulate, st);
     if (rc) return rc;

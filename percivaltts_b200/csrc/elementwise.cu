@@ -20,6 +20,7 @@ inline int ew_blocks(long n, int per_thread = 4) {
 // the critic reads nothing else from its feature input, networks_critic.py:58)
 __global__ void critic_pack_kernel(const float* __restrict__ real, const float* __restrict__ fake,
                                    const float* __restrict__ alpha, float* __restrict__ s0, int B, int T, int O, int S, int off) {
+    pdl_entry();
     const long per = (long)B * T * S;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < per; i += (long)gridDim.x * blockDim.x) {
         const int f = (int)(i % S);
@@ -34,6 +35,7 @@ __global__ void critic_pack_kernel(const float* __restrict__ real, const float* 
 }
 
 __global__ void fill_segments_kernel(float* __restrict__ p, long n0, float v0, long n1, float v1, long n2, float v2) {
+    pdl_entry();
     const long n = n0 + n1 + n2;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
         p[i] = i < n0 ? v0 : (i < n0 + n1 ? v1 : v2);
@@ -41,6 +43,7 @@ __global__ void fill_segments_kernel(float* __restrict__ p, long n0, float v0, l
 
 // losses[slot] = scale * sum(x[0:n])        (single CTA; n is at most a few thousand on this path)
 __global__ void sum_scaled_kernel(const float* __restrict__ x, long n, double scale, float* __restrict__ losses, int slot) {
+    pdl_entry();
     __shared__ double scratch[32];
     double s = 0.0;
     for (long i = threadIdx.x; i < n; i += blockDim.x) s += x[i];
@@ -50,6 +53,7 @@ __global__ void sum_scaled_kernel(const float* __restrict__ x, long n, double sc
 
 // ss[b] = sum over the sample of g^2   (one CTA per sample, deterministic)
 __global__ void gp_norm_kernel(const float* __restrict__ g, long per_sample, float* __restrict__ ss) {
+    pdl_entry();
     __shared__ double scratch[32];
     const float* p = g + (long)blockIdx.x * per_sample;
     double s = 0.0;
@@ -64,6 +68,7 @@ __global__ void gp_norm_kernel(const float* __restrict__ g, long per_sample, flo
 // r0[b,:] = lambda * 2 (n_b - 1) / (n_b * Bglobal) * g[b,:];  losses[gp_slot] = sum_b (1-n_b)^2 / Bglobal  (local share)
 __global__ void gp_scale_kernel(const float* __restrict__ g, const float* __restrict__ ss, float* __restrict__ r0, int B,
                                 long per_sample, float lambda, float inv_bglobal, float* __restrict__ losses, int gp_slot) {
+    pdl_entry();
     const long n = (long)B * per_sample;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
         const int b = (int)(i / per_sample);
@@ -81,6 +86,7 @@ __global__ void gp_scale_kernel(const float* __restrict__ g, const float* __rest
 }
 
 __global__ void loss_combine_kernel(float* __restrict__ losses, int out, int a, float ca, int b, float cb, int c, float cc) {
+    pdl_entry();
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         float v = ca * losses[a];
         if (b >= 0) v += cb * losses[b];
@@ -93,6 +99,7 @@ __global__ void loss_combine_kernel(float* __restrict__ losses, int out, int a, 
 __global__ void lse_kernel(const float* __restrict__ pred, const float* __restrict__ real, const float* __restrict__ w,
                            float* __restrict__ dpred, long rows, int O, double scale_loss, float scale_grad,
                            double* __restrict__ partial, unsigned int* __restrict__ counter, float* __restrict__ losses, int slot) {
+    pdl_entry();
     __shared__ double scratch[32];
     __shared__ bool is_last;
     const long n = rows * O;
@@ -123,6 +130,7 @@ __global__ void lse_kernel(const float* __restrict__ pred, const float* __restri
 // Keras-2.2 Adam: t = step+1; lr_t = lr*sqrt(1-b2^t)/(1-b1^t); m,v updated; p -= lr_t*m/(sqrt(v)+eps)
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                             long n, float lr, float b1, float b2, float eps, const int* __restrict__ step) {
+    pdl_entry();
     __shared__ float lr_t_s;
     if (threadIdx.x == 0) {
         const double t = (double)(*step + 1);
@@ -139,15 +147,18 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
         p[i] -= lr_t * mi / (sqrtf(vi) + eps);
     }
 }
-__global__ void incr_kernel(int* step) { if (threadIdx.x == 0 && blockIdx.x == 0) *step += 1; }
+__global__ void incr_kernel(int* step) {
+    pdl_entry(); if (threadIdx.x == 0 && blockIdx.x == 0) *step += 1; }
 
 __global__ void add_kernel(float* __restrict__ out, const float* __restrict__ a, const float* __restrict__ b, long n) {
+    pdl_entry();
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) out[i] = a[i] + b[i];
 }
 
 // dz = dy * y * (1-y) on a [rows, cols] window with independent leading dimensions
 __global__ void sigmoid_bwd_kernel(const float* __restrict__ dy, long lddy, const float* __restrict__ y, long ldy,
                                    float* __restrict__ dz, long lddz, long rows, int cols) {
+    pdl_entry();
     const long n = rows * cols;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
         const long r = i / cols;
@@ -159,6 +170,7 @@ __global__ void sigmoid_bwd_kernel(const float* __restrict__ dy, long lddy, cons
 
 __global__ void copy2d_kernel(float* __restrict__ dst, long ldd, const float* __restrict__ src, long lds, long rows, int cols,
                               int accumulate) {
+    pdl_entry();
     const long n = rows * cols;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
         const long r = i / cols;
@@ -171,6 +183,7 @@ __global__ void copy2d_kernel(float* __restrict__ dst, long ldd, const float* __
 
 // dst [B, T+left+right, C] <- zero halo + src [B, T, C]
 __global__ void pad_time_kernel(float* __restrict__ dst, const float* __restrict__ src, int B, int T, int C, int left, int right) {
+    pdl_entry();
     const int Tp = T + left + right;
     const long n = (long)B * Tp * C;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
@@ -192,6 +205,7 @@ __device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {
     return x ^ (x >> 31);
 }
 __global__ void uniform_kernel(float* __restrict__ out, int n, unsigned long long seed, unsigned long long* __restrict__ counter) {
+    pdl_entry();
     const unsigned long long ctr = *counter;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
@@ -199,7 +213,8 @@ __global__ void uniform_kernel(float* __restrict__ out, int n, unsigned long lon
         out[i] = (float)(r >> 40) * (1.0f / 16777216.0f);
     }
 }
-__global__ void incr64_kernel(unsigned long long* c) { if (threadIdx.x == 0 && blockIdx.x == 0) *c += 1ull; }
+__global__ void incr64_kernel(unsigned long long* c) {
+    pdl_entry(); if (threadIdx.x == 0 && blockIdx.x == 0) *c += 1ull; }
 
 }  // namespace
 
@@ -208,7 +223,7 @@ extern "C" int pctts_critic_pack_inputs(const float* real, const float* fake, co
     if (!real || !fake || !alpha || !s0 || off < 0 || off + S > O) return PCTTS_EINVAL;
     const long per = (long)B * T * S;
     if (per == 0) return PCTTS_OK;
-    critic_pack_kernel<<<ew_blocks(per), ET, 0, (cudaStream_t)stream>>>(real, fake, alpha, s0, B, T, O, S, off);
+    pctts_launch(critic_pack_kernel, ew_blocks(per), ET, 0, (cudaStream_t)stream, real, fake, alpha, s0, B, T, O, S, off);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -216,21 +231,21 @@ extern "C" int pctts_critic_pack_inputs(const float* real, const float* fake, co
 extern "C" int pctts_fill_segments(float* p, long n0, float v0, long n1, float v1, long n2, float v2, void* stream) {
     if (!p || n0 < 0 || n1 < 0 || n2 < 0) return PCTTS_EINVAL;
     if (n0 + n1 + n2 == 0) return PCTTS_OK;
-    fill_segments_kernel<<<ew_blocks(n0 + n1 + n2), ET, 0, (cudaStream_t)stream>>>(p, n0, v0, n1, v1, n2, v2);
+    pctts_launch(fill_segments_kernel, ew_blocks(n0 + n1 + n2), ET, 0, (cudaStream_t)stream, p, n0, v0, n1, v1, n2, v2);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
 
 extern "C" int pctts_sum_scaled(const float* x, long n, double scale, float* losses, int slot, void* stream) {
     if (!x || !losses || n < 0) return PCTTS_EINVAL;
-    sum_scaled_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(x, n, scale, losses, slot);
+    pctts_launch(sum_scaled_kernel, 1, 1024, 0, (cudaStream_t)stream, x, n, scale, losses, slot);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
 
 extern "C" int pctts_gp_norms(const float* g, int B, long per_sample, float* ss, void* stream) {
     if (!g || !ss || B <= 0) return PCTTS_EINVAL;
-    gp_norm_kernel<<<B, 1024, 0, (cudaStream_t)stream>>>(g, per_sample, ss);
+    pctts_launch(gp_norm_kernel, B, 1024, 0, (cudaStream_t)stream, g, per_sample, ss);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -238,15 +253,14 @@ extern "C" int pctts_gp_norms(const float* g, int B, long per_sample, float* ss,
 extern "C" int pctts_gp_scale(const float* g, const float* ss, float* r0, int B, long per_sample, float lambda, int Bglobal,
                               float* losses, int gp_slot, void* stream) {
     if (!g || !ss || !r0 || !losses || B <= 0 || Bglobal <= 0) return PCTTS_EINVAL;
-    gp_scale_kernel<<<ew_blocks((long)B * per_sample), ET, 0, (cudaStream_t)stream>>>(g, ss, r0, B, per_sample, lambda,
-                                                                                     1.f / (float)Bglobal, losses, gp_slot);
+    pctts_launch(gp_scale_kernel, ew_blocks((long)B * per_sample), ET, 0, (cudaStream_t)stream, g, ss, r0, B, per_sample, lambda, 1.f / (float)Bglobal, losses, gp_slot);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
 
 extern "C" int pctts_loss_combine(float* losses, int out, int a, float ca, int b, float cb, int c, float cc, void* stream) {
     if (!losses) return PCTTS_EINVAL;
-    loss_combine_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(losses, out, a, ca, b, cb, c, cc);
+    pctts_launch(loss_combine_kernel, 1, 32, 0, (cudaStream_t)stream, losses, out, a, ca, b, cb, c, cc);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -258,8 +272,7 @@ extern "C" int pctts_lse_loss_grad(const float* pred, const float* real, const f
     if (!pred || !real || !losses || !workspace || rows <= 0 || O <= 0) return PCTTS_EINVAL;
     double* partial = (double*)workspace;
     unsigned int* counter = (unsigned int*)(partial + 148 * 8);
-    lse_kernel<<<ew_blocks(rows * O), ET, 0, (cudaStream_t)stream>>>(pred, real, w, dpred, rows, O, scale_loss, scale_grad, partial,
-                                                                     counter, losses, slot);
+    pctts_launch(lse_kernel, ew_blocks(rows * O), ET, 0, (cudaStream_t)stream, pred, real, w, dpred, rows, O, scale_loss, scale_grad, partial, counter, losses, slot);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -269,10 +282,10 @@ extern "C" int pctts_adam(float* p, const float* g, float* m, float* v, long n, 
     if (!p || !g || !m || !v || !step || n < 0) return PCTTS_EINVAL;
     cudaStream_t st = (cudaStream_t)stream;
     if (n > 0) {
-        adam_kernel<<<ew_blocks(n), ET, 0, st>>>(p, g, m, v, n, lr, beta1, beta2, eps, step);
+        pctts_launch(adam_kernel, ew_blocks(n), ET, 0, st, p, g, m, v, n, lr, beta1, beta2, eps, step);
         PCTTS_LAUNCH_CHECK();
     }
-    incr_kernel<<<1, 32, 0, st>>>(step);
+    pctts_launch(incr_kernel, 1, 32, 0, st, step);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -280,7 +293,7 @@ extern "C" int pctts_adam(float* p, const float* g, float* m, float* v, long n, 
 extern "C" int pctts_add(float* out, const float* a, const float* b, long n, void* stream) {
     if (!out || !a || !b || n < 0) return PCTTS_EINVAL;
     if (n == 0) return PCTTS_OK;
-    add_kernel<<<ew_blocks(n), ET, 0, (cudaStream_t)stream>>>(out, a, b, n);
+    pctts_launch(add_kernel, ew_blocks(n), ET, 0, (cudaStream_t)stream, out, a, b, n);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -289,7 +302,7 @@ extern "C" int pctts_sigmoid_bwd(const float* dy, long lddy, const float* y, lon
                                  void* stream) {
     if (!dy || !y || !dz || rows < 0 || cols < 0) return PCTTS_EINVAL;
     if (rows * cols == 0) return PCTTS_OK;
-    sigmoid_bwd_kernel<<<ew_blocks(rows * cols), ET, 0, (cudaStream_t)stream>>>(dy, lddy, y, ldy, dz, lddz, rows, cols);
+    pctts_launch(sigmoid_bwd_kernel, ew_blocks(rows * cols), ET, 0, (cudaStream_t)stream, dy, lddy, y, ldy, dz, lddz, rows, cols);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -297,7 +310,7 @@ extern "C" int pctts_sigmoid_bwd(const float* dy, long lddy, const float* y, lon
 extern "C" int pctts_copy2d(float* dst, long ldd, const float* src, long lds, long rows, int cols, int accumulate, void* stream) {
     if (!dst || !src || rows < 0 || cols < 0) return PCTTS_EINVAL;
     if (rows * cols == 0) return PCTTS_OK;
-    copy2d_kernel<<<ew_blocks(rows * cols), ET, 0, (cudaStream_t)stream>>>(dst, ldd, src, lds, rows, cols, accumulate);
+    pctts_launch(copy2d_kernel, ew_blocks(rows * cols), ET, 0, (cudaStream_t)stream, dst, ldd, src, lds, rows, cols, accumulate);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -306,7 +319,7 @@ extern "C" int pctts_pad_time(float* dst, const float* src, int B, int T, int C,
     if (!dst || !src || B < 0 || T < 0 || C <= 0 || left < 0 || right < 0) return PCTTS_EINVAL;
     const long n = (long)B * (T + left + right) * C;
     if (n == 0) return PCTTS_OK;
-    pad_time_kernel<<<ew_blocks(n), ET, 0, (cudaStream_t)stream>>>(dst, src, B, T, C, left, right);
+    pctts_launch(pad_time_kernel, ew_blocks(n), ET, 0, (cudaStream_t)stream, dst, src, B, T, C, left, right);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -315,10 +328,10 @@ extern "C" int pctts_uniform(float* out, int n, unsigned long long seed, unsigne
     if (!out || !counter || n < 0) return PCTTS_EINVAL;
     cudaStream_t st = (cudaStream_t)stream;
     if (n > 0) {
-        uniform_kernel<<<pctts_div_up(n, 128), 128, 0, st>>>(out, n, seed, counter);
+        pctts_launch(uniform_kernel, pctts_div_up(n, 128), 128, 0, st, out, n, seed, counter);
         PCTTS_LAUNCH_CHECK();
     }
-    incr64_kernel<<<1, 32, 0, st>>>(counter);
+    pctts_launch(incr64_kernel, 1, 32, 0, st, counter);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

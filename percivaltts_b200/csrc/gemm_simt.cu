@@ -44,6 +44,7 @@ struct Epi {
 template <bool TA, bool TB>
 __global__ void __launch_bounds__(NT) gemm_f32_kernel(int M, int N, int K, Mat A, Mat B, Mat C, Epi e, int kchunk,
                                                        float* __restrict__ partial) {
+    pdl_entry();
     __shared__ __align__(16) float As[BK][BM + 4];
     __shared__ __align__(16) float Bs[BK][BN + 4];
     const int tid = threadIdx.x;
@@ -179,6 +180,7 @@ __global__ void __launch_bounds__(NT) gemm_f32_kernel(int M, int N, int K, Mat A
 
 // C = alpha * sum_z partial[z] (+ C when accumulating), fixed summation order => deterministic
 __global__ void splitk_reduce_kernel(const float* __restrict__ partial, int splits, int M, int N, Mat C, float alpha, int accum) {
+    pdl_entry();
     const long total = (long)M * N;
     float* Cp = const_cast<float*>(C.p);
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -202,16 +204,16 @@ int launch(int ta, int tb, int M, int N, int K, Mat A, Mat B, Mat C, Epi e, cuda
     }
     if (splits <= 1) partial = nullptr;
     dim3 grid(pctts_div_up(N, BN), pctts_div_up(M, BM), partial ? splits : 1);
-    if (!ta && !tb) gemm_f32_kernel<false, false><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e, kchunk, partial);
-    else if (!ta && tb) gemm_f32_kernel<false, true><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e, kchunk, partial);
-    else if (ta && !tb) gemm_f32_kernel<true, false><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e, kchunk, partial);
-    else gemm_f32_kernel<true, true><<<grid, NT, 0, st>>>(M, N, K, A, B, C, e, kchunk, partial);
+    if (!ta && !tb) pctts_launch(gemm_f32_kernel<false, false>, grid, NT, 0, st, M, N, K, A, B, C, e, kchunk, partial);
+    else if (!ta && tb) pctts_launch(gemm_f32_kernel<false, true>, grid, NT, 0, st, M, N, K, A, B, C, e, kchunk, partial);
+    else if (ta && !tb) pctts_launch(gemm_f32_kernel<true, false>, grid, NT, 0, st, M, N, K, A, B, C, e, kchunk, partial);
+    else pctts_launch(gemm_f32_kernel<true, true>, grid, NT, 0, st, M, N, K, A, B, C, e, kchunk, partial);
     PCTTS_LAUNCH_CHECK();
     if (partial) {
         const long total = (long)M * N;
         int blocks = pctts_div_up(total, 256);
         if (blocks > 148 * 8) blocks = 148 * 8;
-        splitk_reduce_kernel<<<blocks, 256, 0, st>>>(partial, splits, M, N, C, e.alpha, (e.flags & PCTTS_EPI_ACCUM) ? 1 : 0);
+        pctts_launch(splitk_reduce_kernel, blocks, 256, 0, st, partial, splits, M, N, C, e.alpha, (e.flags & PCTTS_EPI_ACCUM) ? 1 : 0);
         PCTTS_LAUNCH_CHECK();
     }
     return PCTTS_OK;

@@ -79,6 +79,7 @@ constexpr int NUM_THREADS = 192;   // warp 0: TMA producer, warp 1: MMA issuer, 
 template <int BN, int PARTS>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const Params p) {
+    pdl_trigger();   // the wait follows the barrier / TMEM set-up (nothing before it touches global memory)
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
     __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
@@ -119,6 +120,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    pdl_wait();
     const uint32_t tmem_base = tmem_slot;
     if (tr0 && threadIdx.x == 0) p.trace[7] = clock64();
     const uint32_t tmem_corr = tmem_base + 2 * BN;
@@ -349,6 +351,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 // C (+)= alpha * sum_z partial[z], fixed order (deterministic)
 __global__ void tc_splitk_reduce_kernel(const float* __restrict__ partial, int splits, long rows, int N, float* __restrict__ C,
                                         long ldc, float alpha, int accum) {
+    pdl_entry();
     const long total = rows * N;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
         float s = 0.f;
@@ -364,6 +367,7 @@ __global__ void tc_splitk_reduce_kernel(const float* __restrict__ partial, int s
 // x -> bf16 hi (+ lo) planes; one thread per pair of columns
 __global__ void split_bf16_kernel(const float* __restrict__ src, long ld, int seg, long segstride, long rows, int cols,
                                   __nv_bfloat16* __restrict__ dst, long ld_dst, long part_stride, int parts) {
+    pdl_entry();
     const long pairs_per_row = ld_dst / 2;
     const long total = rows * pairs_per_row;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -447,7 +451,7 @@ int launch_bn(const Launch& L, Params p, cudaStream_t st) {
         attr_done = true;
     }
     dim3 grid((p.N + BN - 1) / BN, L.m_tiles, L.splits);
-    gemm_tc_kernel<BN, PARTS><<<grid, NUM_THREADS, smem, st>>>(mapA, mapB, p);
+    pctts_launch(gemm_tc_kernel<BN, PARTS>, grid, NUM_THREADS, smem, st, mapA, mapB, p);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -462,7 +466,7 @@ int launch_tc(const Launch& L, Params p, int bn, float* C, long ldc, float alpha
         const long total = p.crows * p.N;
         int blocks = pctts_div_up(total, 256);
         if (blocks > 148 * 8) blocks = 148 * 8;
-        tc_splitk_reduce_kernel<<<blocks, 256, 0, st>>>(p.partial, L.splits, p.crows, p.N, C, ldc, alpha, accum);
+        pctts_launch(tc_splitk_reduce_kernel, blocks, 256, 0, st, p.partial, L.splits, p.crows, p.N, C, ldc, alpha, accum);
         PCTTS_LAUNCH_CHECK();
     }
     return PCTTS_OK;
@@ -494,8 +498,7 @@ extern "C" int pctts_split_bf16(const float* src, long ld, int seg, long segstri
     const long total = rows * (ld_dst / 2);
     int blocks = pctts_div_up(total, 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
-    split_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(src, ld, seg, segstride, rows, cols, (__nv_bfloat16*)dst, ld_dst,
-                                                                part_stride, parts);
+    pctts_launch(split_bf16_kernel, blocks, 256, 0, (cudaStream_t)stream, src, ld, seg, segstride, rows, cols, (__nv_bfloat16*)dst, ld_dst, part_stride, parts);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

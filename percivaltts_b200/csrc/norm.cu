@@ -48,6 +48,7 @@ __device__ __forceinline__ void red_terms(const RedArgs& a, long r, int c, doubl
 // Stage 1: CTA b reduces its contiguous slab of rows and writes partial[b][2][C] (doubles).
 template <int MODE>
 __global__ void __launch_bounds__(RT) colreduce_kernel(RedArgs a, double* __restrict__ partial) {
+    pdl_entry();
     __shared__ double s1[RT], s2[RT];
     const int C = a.C, tid = threadIdx.x;
     const int rpb = C >= RT ? 1 : RT / C;          // rows handled concurrently by one CTA
@@ -93,6 +94,7 @@ __global__ void __launch_bounds__(RT) colreduce_kernel(RedArgs a, double* __rest
 // Stage 2: one warp per output element e in [0, 2C): lanes stride over the CTA partials, butterfly sum (fixed order).
 __global__ void __launch_bounds__(RT) colreduce_final_kernel(const double* __restrict__ partial, double* __restrict__ sums,
                                                              int nblk, int C) {
+    pdl_entry();
     const int e = blockIdx.x * (RT / 32) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (e >= 2 * C) return;
@@ -106,6 +108,7 @@ __global__ void __launch_bounds__(RT) colreduce_final_kernel(const double* __res
 __global__ void bn_finalize_kernel(const double* __restrict__ sums, double count, int C, float eps, float momentum,
                                    float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ moving_mean,
                                    float* __restrict__ moving_var) {
+    pdl_entry();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const double m = sums[c] / count;
@@ -122,6 +125,7 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sums, double count
 __global__ void bn_apply_kernel(const float* __restrict__ x, float* __restrict__ y, const float* __restrict__ mean,
                                 const float* __restrict__ invstd_or_var, const float* __restrict__ gamma,
                                 const float* __restrict__ beta, long total, int C, float eps, int use_var, int lrelu) {
+    pdl_entry();
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
         const int c = (int)(i % C);
         const float is = use_var ? rsqrtf(invstd_or_var[c] + eps) : invstd_or_var[c];
@@ -136,6 +140,7 @@ __global__ void bn_bwd_apply_kernel(const float* __restrict__ x, const float* __
                                     const float* __restrict__ mean, const float* __restrict__ invstd,
                                     const float* __restrict__ gamma, const float* __restrict__ beta,
                                     const double* __restrict__ sums, double count, long total, int C, int lrelu) {
+    pdl_entry();
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
         const int c = (int)(i % C);
         const float xh = (x[i] - mean[c]) * invstd[c];
@@ -151,6 +156,7 @@ __global__ void bn_bwd_apply_kernel(const float* __restrict__ x, const float* __
 
 __global__ void sums_to_grads_kernel(const double* __restrict__ sums, int C, float* __restrict__ g1, float* __restrict__ g2,
                                      int accumulate, double scale) {
+    pdl_entry();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     if (g1) g1[c] = (accumulate ? g1[c] : 0.f) + (float)(sums[c] * scale);
@@ -194,9 +200,9 @@ Ws carve(void* workspace, long rows, int C) {
 template <int MODE>
 int run_colreduce(const RedArgs& a, const Ws& w, cudaStream_t st) {
     const int grid = reduce_grid(a.rows, a.C);
-    colreduce_kernel<MODE><<<grid, RT, 0, st>>>(a, w.partial);
+    pctts_launch(colreduce_kernel<MODE>, grid, RT, 0, st, a, w.partial);
     PCTTS_LAUNCH_CHECK();
-    colreduce_final_kernel<<<pctts_div_up(2 * a.C, RT / 32), RT, 0, st>>>(w.partial, w.sums, grid, a.C);
+    pctts_launch(colreduce_final_kernel, pctts_div_up(2 * a.C, RT / 32), RT, 0, st, w.partial, w.sums, grid, a.C);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -218,8 +224,7 @@ extern "C" int pctts_bn_finalize(void* workspace, long rows, int C, double count
                                  float* invstd, float* moving_mean, float* moving_var, void* stream) {
     if (!workspace || !mean || !invstd || count <= 0) return PCTTS_EINVAL;
     Ws w = carve(workspace, rows, C);
-    bn_finalize_kernel<<<pctts_div_up(C, 128), 128, 0, (cudaStream_t)stream>>>(w.sums, count, C, eps, momentum, mean, invstd,
-                                                                             moving_mean, moving_var);
+    pctts_launch(bn_finalize_kernel, pctts_div_up(C, 128), 128, 0, (cudaStream_t)stream, w.sums, count, C, eps, momentum, mean, invstd, moving_mean, moving_var);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -231,7 +236,7 @@ extern "C" int pctts_bn_apply(const float* x, float* y, const float* mean, const
     if (total == 0) return PCTTS_OK;
     int blocks = pctts_div_up(total, 256 * 4);
     if (blocks > 148 * 8) blocks = 148 * 8;
-    bn_apply_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, y, mean, invstd_or_var, gamma, beta, total, C, eps, use_var, lrelu);
+    pctts_launch(bn_apply_kernel, blocks, 256, 0, (cudaStream_t)stream, x, y, mean, invstd_or_var, gamma, beta, total, C, eps, use_var, lrelu);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -257,10 +262,10 @@ extern "C" int pctts_bn_bwd_apply(const float* x, const float* dy, float* dx, co
     const long total = rows * C;
     int blocks = pctts_div_up(total, 256 * 4);
     if (blocks > 148 * 8) blocks = 148 * 8;
-    bn_bwd_apply_kernel<<<blocks, 256, 0, st>>>(x, dy, dx, mean, invstd, gamma, beta, w.sums, count, total, C, lrelu);
+    pctts_launch(bn_bwd_apply_kernel, blocks, 256, 0, st, x, dy, dx, mean, invstd, gamma, beta, w.sums, count, total, C, lrelu);
     PCTTS_LAUNCH_CHECK();
     if (dgamma || dbeta) {
-        sums_to_grads_kernel<<<pctts_div_up(C, 128), 128, 0, st>>>(w.sums, C, dbeta, dgamma, accumulate, (double)grad_scale);
+        pctts_launch(sums_to_grads_kernel, pctts_div_up(C, 128), 128, 0, st, w.sums, C, dbeta, dgamma, accumulate, (double)grad_scale);
         PCTTS_LAUNCH_CHECK();
     }
     return PCTTS_OK;
@@ -273,7 +278,7 @@ extern "C" int pctts_colsum(const float* x, long rows, int C, float* out, int ac
     cudaStream_t st = (cudaStream_t)stream;
     RedArgs a{x, nullptr, nullptr, nullptr, nullptr, nullptr, rows, C, 0};
     PCTTS_CUDA_RC(run_colreduce<MODE_COLSUM>(a, w, st));
-    sums_to_grads_kernel<<<pctts_div_up(C, 128), 128, 0, st>>>(w.sums, C, out, nullptr, accumulate, 1.0);
+    pctts_launch(sums_to_grads_kernel, pctts_div_up(C, 128), 128, 0, st, w.sums, C, out, nullptr, accumulate, 1.0);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

@@ -14,6 +14,7 @@ constexpr int WARPS = 8;
 __global__ void __launch_bounds__(WARPS * 32)
 pml_compress_kernel(const float* __restrict__ in, const int* __restrict__ idx, const float* __restrict__ wgt,
                     float* __restrict__ out, long T, int nbins, int K, int log_abs) {
+    pdl_entry();
     extern __shared__ float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* row = smem + (long)warp * nbins;
@@ -47,6 +48,7 @@ pml_compress_kernel(const float* __restrict__ in, const int* __restrict__ idx, c
 __global__ void __launch_bounds__(WARPS * 32)
 pml_decompress_kernel(const float* __restrict__ in, const int* __restrict__ idx, const float* __restrict__ wgt,
                       float* __restrict__ out, long T, int K, int nbins, int smooth, int do_exp) {
+    pdl_entry();
     extern __shared__ float smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float* row = smem + (long)warp * K;
@@ -86,7 +88,7 @@ extern "C" int pctts_pml_linbnd2fwbnd(const float* in, const int* idx, const flo
     PCTTS_CUDA(cudaFuncSetAttribute(pml_compress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     long blocks = (T + WARPS - 1) / WARPS;
     if (blocks > 148 * 3) blocks = 148 * 3;
-    pml_compress_kernel<<<(int)blocks, WARPS * 32, smem, (cudaStream_t)stream>>>(in, idx, wgt, out, T, nbins, K, log_abs);
+    pctts_launch(pml_compress_kernel, (int)blocks, WARPS * 32, smem, (cudaStream_t)stream, in, idx, wgt, out, T, nbins, K, log_abs);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -101,7 +103,7 @@ extern "C" int pctts_pml_fwbnd2linbnd(const float* in, const int* idx, const flo
         PCTTS_CUDA(cudaFuncSetAttribute(pml_decompress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     long blocks = (T + WARPS - 1) / WARPS;
     if (blocks > 148 * 8) blocks = 148 * 8;
-    pml_decompress_kernel<<<(int)blocks, WARPS * 32, smem, (cudaStream_t)stream>>>(in, idx, wgt, out, T, K, nbins, smooth, do_exp);
+    pctts_launch(pml_decompress_kernel, (int)blocks, WARPS * 32, smem, (cudaStream_t)stream, in, idx, wgt, out, T, K, nbins, smooth, do_exp);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
