@@ -6,6 +6,8 @@
 #include "common.cuh"
 #include "pctts.h"
 #include <stdint.h>
+#include <stdlib.h>
+#include "tc_common.cuh"
 
 namespace {
 
@@ -260,12 +262,87 @@ pml_decompress_tma_kernel(const float* __restrict__ in, const int* __restrict__ 
     if (tid == 0) bulk_wait_read<0>();                    // shared memory must outlive the reads of the last stores
 }
 
+// ---- compress fast path: full-line bulk loads ---------------------------------------------------------------------------------
+// Same alignment argument as for the decompress stores: four consecutive [nbins] fp32 rows are one contiguous 16*nbins-byte
+// span with a 16-byte-aligned start, which the TMA engine brings into shared memory as a single bulk copy
+// (cp.async.bulk.shared::cluster.global, completion on an mbarrier) with no register staging and no split cache lines.
+// A block owns a ring of CSTAGES such spans; warp w gathers the K bands of frame w of the current span.
+constexpr int CSTAGES = 3;
+constexpr int CG = 4;          // frames per span = warps per block
+
+__device__ __forceinline__ void bulk_load(uint32_t sdst, const float* gsrc, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(sdst), "l"(gsrc),
+                 "r"(bytes), "r"(bar)
+                 : "memory");
+}
+
+__global__ void __launch_bounds__(CG * 32)
+pml_compress_tma_kernel(const float* __restrict__ in, const int* __restrict__ idx, const float* __restrict__ wgt,
+                        float* __restrict__ out, long ngroups, int nbins, int K, int log_abs) {
+    pdl_entry();
+    extern __shared__ float4 smem4[];
+    __shared__ __align__(8) uint64_t full_bar[CSTAGES];
+    float* stage = reinterpret_cast<float*>(smem4);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t span_bytes = (uint32_t)CG * nbins * 4u;
+    const long span_floats = (long)CG * nbins;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < CSTAGES; ++s) tcx::mbar_init(tcx::smem_u32(&full_bar[s]), 1);
+        tcx::fence_barrier_init();
+    }
+    __syncthreads();
+    const long g0 = blockIdx.x, gstep = gridDim.x;
+    auto issue = [&](long g, int s) {
+        const uint32_t bar = tcx::smem_u32(&full_bar[s]);
+        tcx::mbar_arrive_expect_tx(bar, span_bytes);
+        bulk_load(tcx::smem_u32(stage + s * span_floats), in + g * span_floats, span_bytes, bar);
+    };
+    if (threadIdx.x == 0)
+        for (int s = 0; s < CSTAGES; ++s)
+            if (g0 + s * gstep < ngroups) issue(g0 + s * gstep, s);
+    int s = 0;
+    uint32_t ph = 0;
+    for (long g = g0; g < ngroups; g += gstep) {
+        tcx::mbar_wait(tcx::smem_u32(&full_bar[s]), ph);
+        const float* row = stage + s * span_floats + (long)warp * nbins;
+        float* dst = out + (g * CG + warp) * K;
+        for (int k = lane; k < K; k += 32) {
+            const int j = __ldg(idx + k);
+            const float w = __ldg(wgt + k);
+            float a = row[j], b = row[min(j + 1, nbins - 1)];
+            if (log_abs) {
+                a = logf(fabsf(a));
+                b = logf(fabsf(b));
+            }
+            dst[k] = (w == 0.f) ? a : fmaf(w, b - a, a);
+        }
+        __syncthreads();                                   // every warp is done with stage s
+        if (threadIdx.x == 0 && g + CSTAGES * gstep < ngroups) issue(g + CSTAGES * gstep, s);
+        if (++s == CSTAGES) s = 0, ph ^= 1u;
+    }
+}
+
 }  // namespace
 
 extern "C" int pctts_pml_linbnd2fwbnd(const float* in, const int* idx, const float* wgt, float* out, long T, int nbins, int K,
                                       int log_abs, void* stream) {
     if (T == 0) return PCTTS_OK;
     if (!in || !idx || !wgt || !out || T < 0 || nbins <= 1 || K <= 0) return PCTTS_EINVAL;
+    static const int no_tma = getenv("PCTTS_PML_NO_TMA") ? atoi(getenv("PCTTS_PML_NO_TMA")) : 0;
+    const size_t span = (size_t)CG * nbins * sizeof(float);
+    if (!no_tma && T >= CG && (((uintptr_t)in) & 15) == 0 && CSTAGES * span <= 220 * 1024) {
+        // whole 4-frame spans through the bulk-load kernel, the (< 4 frames) tail through the generic one
+        const long ngroups = T / CG;
+        const size_t sm = CSTAGES * span;
+        PCTTS_CUDA(cudaFuncSetAttribute(pml_compress_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        const int per = (int)((227 * 1024) / (sm + 1024));
+        long nb = ngroups < 148L * per ? ngroups : 148L * per;
+        pctts_launch(pml_compress_tma_kernel, (int)nb, CG * 32, sm, (cudaStream_t)stream, in, idx, wgt, out, ngroups, nbins, K, log_abs);
+        PCTTS_LAUNCH_CHECK();
+        const long done = ngroups * CG;
+        if (done == T) return PCTTS_OK;
+        in += done * nbins, out += done * K, T -= done;
+    }
     const size_t smem = (size_t)CWARPS * nbins * sizeof(float);
     if (smem > 227 * 1024) return PCTTS_EUNSUPPORTED;
     PCTTS_CUDA(cudaFuncSetAttribute(pml_compress_kernel<CUNR, CWARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
