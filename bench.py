@@ -320,7 +320,12 @@ def run_b200(args):
                 'kernel': 'gemm_tc_kernel (Conv1D k=21 425->256 forward as virtual-im2col tcgen05 GEMM, M=4000 N=256 K=8925)',
                 'achieved': achieved, 'peak': peak_tf, 'unit': 'TFLOP/s', 'frac': achieved / peak_tf,
                 'peak_source': 'MEASURED_PEAKS.json bf16_tflops (burst)' if peaks else 'fallback 1590 TFLOP/s',
-                'traffic': None, 'kernel_ms': t_conv1d, 'flop_per_launch': flops,
+                # dram__bytes_read.sum + dram__bytes_write.sum of this launch from the ncu --set full capture
+                # profiles/r01_e_ncu_full_conv1d_gemm_tc.txt (24.625 MB read = the bf16 operand planes, 10.9 MB activations +
+                # 13.7 MB weights, each read once; the 4.1 MB fp32 output stays in L2); valid for the fp32 (3-plane) mode
+                'traffic': 24.626e6 if ops.precision == 'fp32' else None, 'traffic_unit': 'B/launch',
+                'ncu_tensor_pipe_pct': 48.5 if ops.precision == 'fp32' else None,
+                'kernel_ms': t_conv1d, 'flop_per_launch': flops,
                 'precision': ops.precision, 'tensor_products_per_flop': products,
                 'tensor_pipe_frac': products * achieved / peak_tf,
                 'note': 'achieved counts ALGORITHMIC fp32 flops (2MNK); precision %s issues %d bf16 tcgen05 products per '
