@@ -142,6 +142,7 @@ class Generator(object):
         pl['nm_bn'] = [_BN(o, 'g.nm.fc%d.bn' % i, M, H) for i in range(Ln)]
         if bwd:
             pl['d_lctx'] = o.empty(M, H)
+            pl['d_lctx_f0'] = o.empty(M, H)
             pl['dA'] = o.empty(M, H)           # ping-pong [M,H] gradient buffers
             pl['dB'] = o.empty(M, H)
             pl['dz_nm'] = o.empty(M, NM)
@@ -199,12 +200,16 @@ class Generator(object):
         lctx = x2
         out2 = out.view(M, O)
         # F0: Bidirectional LSTM + Dense(1)   (modeltts_common.py:82-84, networktts.py:85-96)
+        # The recurrence is latency-bound and occupies 80 of the 148 SMs: it runs on the side lane while the spectral and
+        # noise-mask branches run on the main one (the three branches only share their input lctx).
         if not spec_only:
-            for d, dn in enumerate(('fw', 'bw')):
-                o.gemm(lctx, p['g.f0.blstm.%s.kernel' % dn], pl['zx'][d].view(M, 4 * H), bias=p['g.f0.blstm.%s.bias' % dn])
-            o.lstm_fwd(pl['zx'], [p['g.f0.blstm.fw.recurrent'], p['g.f0.blstm.bw.recurrent']], pl['hout'], pl['gates'],
-                       pl['cstate'])
-            o.gemm(pl['hout'].view(M, 2 * H), p['g.f0.out.kernel'], out2[:, 0:1], bias=p['g.f0.out.bias'])
+            o.preshare(lctx)
+            with o.side_lane():
+                for d, dn in enumerate(('fw', 'bw')):
+                    o.gemm(lctx, p['g.f0.blstm.%s.kernel' % dn], pl['zx'][d].view(M, 4 * H), bias=p['g.f0.blstm.%s.bias' % dn])
+                o.lstm_fwd(pl['zx'], [p['g.f0.blstm.fw.recurrent'], p['g.f0.blstm.bw.recurrent']], pl['hout'], pl['gates'],
+                           pl['cstate'])
+                o.gemm(pl['hout'].view(M, 2 * H), p['g.f0.out.kernel'], out2[:, 0:1], bias=p['g.f0.out.bias'])
         # Spec: Dense projection, [B,T,S,1] map, pCNN2D stack, Conv2D(1)   (modeltts_common.py:95-101)
         o.gemm(lctx, p['g.spec.proj.kernel'], pl['s'], bias=p['g.spec.proj.bias'])
         amap = pl['s'].view(B, T, S, 1)
@@ -222,6 +227,8 @@ class Generator(object):
             n2 = pl['nm_y'][i]
         if not spec_only:
             o.gemm(n2, p['g.nm.out.kernel'], out2[:, 1 + S:], bias=p['g.nm.out.bias'], flags=EPI_SIGMOID)
+        if not spec_only:
+            o.join_lanes()
         pl['lctx'], pl['ctx_in'] = lctx, ctx
         return out
 
@@ -245,6 +252,30 @@ class Generator(object):
         L, Ln = a.gen_nbcnnlayers, a.gen_nbcnnlayers // 2
         lctx, dl = pl['lctx'], pl['d_lctx']
         out2, dout2 = out.view(M, O), dout.view(M, O)
+        # ---- F0 branch on the side lane (BPTT is latency-bound); its share of d(lctx) goes to its own buffer
+        o.preshare(lctx)
+        with o.side_lane():
+            o.copy2d(pl['df0'], dout2[:, 0:1])
+            hout2 = pl['hout'].view(M, 2 * H)
+            o.gemm(hout2, pl['df0'], g['g.f0.out.kernel'], transA=True)
+            o.colsum(pl['df0'], g['g.f0.out.bias'])
+            o.gemm(pl['df0'], p['g.f0.out.kernel'], pl['dhout'].view(M, 2 * H), transB=True)
+            U = [p['g.f0.blstm.fw.recurrent'], p['g.f0.blstm.bw.recurrent']]
+            o.lstm_bwd(pl['dhout'], U, pl['gates'], pl['cstate'], pl['dzl'])
+            for d, dn in enumerate(('fw', 'bw')):
+                dz2 = pl['dzl'][d].view(M, 4 * H)
+                o.gemm(lctx, dz2, g['g.f0.blstm.%s.kernel' % dn], transA=True)
+                o.colsum(dz2, g['g.f0.blstm.%s.bias' % dn])
+                gU = g['g.f0.blstm.%s.recurrent' % dn]
+                if T > 1:
+                    hd = pl['hout'][:, :, d * H:(d + 1) * H]
+                    if d == 0:      # forward direction: the state feeding step t is h[t-1]
+                        o.gemm(hd[:, 0:T - 1], pl['dzl'][d][:, 1:T], gU, transA=True)
+                    else:           # backward direction: the state feeding step t is h[t+1]
+                        o.gemm(hd[:, 1:T], pl['dzl'][d][:, 0:T - 1], gU, transA=True)
+                else:
+                    o.fill_segments(gU.view(-1), gU.numel(), 0.0)
+                o.gemm(dz2, p['g.f0.blstm.%s.kernel' % dn], pl['d_lctx_f0'], transB=True, flags=EPI_ACCUM if d > 0 else 0)
         # ---- NM branch
         nlast = pl['nm_y'][Ln - 1] if Ln > 0 else lctx
         o.sigmoid_bwd(dout2[:, 1 + S:], out2[:, 1 + S:], pl['dz_nm'])
@@ -280,28 +311,8 @@ class Generator(object):
         o.gemm(lctx, pl['ds'], g['g.spec.proj.kernel'], transA=True)
         o.colsum(pl['ds'], g['g.spec.proj.bias'])
         o.gemm(pl['ds'], p['g.spec.proj.kernel'], dl, transB=True, flags=EPI_ACCUM)
-        # ---- F0 branch
-        o.copy2d(pl['df0'], dout2[:, 0:1])
-        hout2 = pl['hout'].view(M, 2 * H)
-        o.gemm(hout2, pl['df0'], g['g.f0.out.kernel'], transA=True)
-        o.colsum(pl['df0'], g['g.f0.out.bias'])
-        o.gemm(pl['df0'], p['g.f0.out.kernel'], pl['dhout'].view(M, 2 * H), transB=True)
-        U = [p['g.f0.blstm.fw.recurrent'], p['g.f0.blstm.bw.recurrent']]
-        o.lstm_bwd(pl['dhout'], U, pl['gates'], pl['cstate'], pl['dzl'])
-        for d, dn in enumerate(('fw', 'bw')):
-            dz2 = pl['dzl'][d].view(M, 4 * H)
-            o.gemm(lctx, dz2, g['g.f0.blstm.%s.kernel' % dn], transA=True)
-            o.colsum(dz2, g['g.f0.blstm.%s.bias' % dn])
-            gU = g['g.f0.blstm.%s.recurrent' % dn]
-            if T > 1:
-                hd = pl['hout'][:, :, d * H:(d + 1) * H]
-                if d == 0:      # forward direction: the state feeding step t is h[t-1]
-                    o.gemm(hd[:, 0:T - 1], pl['dzl'][d][:, 1:T], gU, transA=True)
-                else:           # backward direction: the state feeding step t is h[t+1]
-                    o.gemm(hd[:, 1:T], pl['dzl'][d][:, 0:T - 1], gU, transA=True)
-            else:
-                o.fill_segments(gU.view(-1), gU.numel(), 0.0)
-            o.gemm(dz2, p['g.f0.blstm.%s.kernel' % dn], dl, transB=True, flags=EPI_ACCUM)
+        o.join_lanes()
+        o.add(dl, dl, pl['d_lctx_f0'])
         # ---- ctx trunk: pFC x2 then pCNN1D stack
         dcur = dl
         for i in (1, 0):
@@ -384,12 +395,18 @@ class Critic(object):
 
     def forward(self, pl, s0, ctx):
         """s0: spectral input map view [napp*B, T, S, 1]; ctx [B,T,ctxsize].  -> pl['d'] [napp*B*T, 1]."""
+        self.forward_ctx(pl, ctx)
+        return self.forward_spec(pl, s0)
+
+    def forward_ctx(self, pl, ctx):
+        """The ctx branch (networks_critic.py:80-85), once per batch: -> pl['ctxterm'], its contribution to the first post
+        layer.  It depends on the labels and the critic weights only, so the critic step runs it on the side lane while the
+        frozen generator produces the fake features."""
         o, a, p = self.ops, self.a, self.params.p
-        B, T, M, nM = pl['B'], pl['T'], pl['M'], pl['nM']
-        H, S, Fl, W, L = a.hiddenwidth, a.spec_size, a.gen_nbfilters, a.ctx_winlen, a.gen_nbcnnlayers
+        B, T, M = pl['B'], pl['T'], pl['M']
+        H, S, Fl, W = a.hiddenwidth, a.spec_size, a.gen_nbfilters, a.ctx_winlen
         SF = S * Fl
         left = (W - 1) // 2
-        # ctx branch, once per batch (networks_critic.py:80-85)
         x = ctx
         for i in range(a.ctx_nbcnnlayers):
             xp = pl['ctx_xp'][i]
@@ -402,7 +419,15 @@ class Critic(object):
             x2 = pl['fc_y'][i]
         w0 = p['c.post.fc0.kernel']
         o.gemm(x2, w0[SF:], pl['ctxterm'], bias=p['c.post.fc0.bias'])
-        # spectral branch on all applications (networks_critic.py:58-70)
+        pl['ctx_in'], pl['ctx_last'] = ctx, x2
+
+    def forward_spec(self, pl, s0):
+        """Spectral branch on all applications (networks_critic.py:58-70) and the post layers; needs forward_ctx()."""
+        o, a, p = self.ops, self.a, self.params.p
+        nM = pl['nM']
+        S, Fl, L = a.spec_size, a.gen_nbfilters, a.gen_nbcnnlayers
+        SF = S * Fl
+        w0 = p['c.post.fc0.kernel']
         amap = s0
         for i in range(L):
             o.conv2d(amap, p['c.spec.cnn%d.kernel' % i], pl['a'][i], bias=p['c.spec.cnn%d.bias' % i], flags=EPI_LRELU)
@@ -412,7 +437,7 @@ class Critic(object):
         for i in (1, 2):
             o.gemm(pl['p'][i - 1], p['c.post.fc%d.kernel' % i], pl['p'][i], bias=p['c.post.fc%d.bias' % i], flags=EPI_LRELU)
         o.gemm(pl['p'][2], p['c.out.kernel'], pl['d'], bias=p['c.out.bias'])
-        pl['s0'], pl['ctx_in'], pl['ctx_last'] = s0, ctx, x2
+        pl['s0'] = s0
         return pl['d']
 
     def backward_to_input(self, pl, g_out, g_rows=None, accumulate=False):
@@ -464,6 +489,40 @@ class Critic(object):
         H, S, Fl, W, L = a.hiddenwidth, a.spec_size, a.gen_nbfilters, a.ctx_winlen, a.gen_nbcnnlayers
         SF = S * Fl
         fM = first_order_apps * M
+        # ctx branch: its term enters the first post layer of every first-order application
+        dct = pl['dct']
+        if first_order_apps == 1:
+            o.copy2d(dct, pl['dp'][0][:M])
+        else:
+            o.add(dct, pl['dp'][0][:M], pl['dp'][0][M:2 * M])
+            for k in range(2, first_order_apps):
+                o.copy2d(dct, pl['dp'][0][k * M:(k + 1) * M], accumulate=True)
+        with o.side_lane():      # ctx-branch gradients (Conv1D wgrad, FCs) beside the spectral-branch weight gradients
+            o.colsum(dct, g['c.post.fc0.bias'])
+            o.gemm(pl['ctx_last'], dct, g['c.post.fc0.kernel'][SF:], transA=True)
+            dcur = pl['dcA']
+            o.gemm(dct, p['c.post.fc0.kernel'][SF:], dcur, transB=True, aux=pl['fc_y'][1])
+            for i in (1, 0):
+                if i > 0:
+                    xin = pl['fc_y'][0]
+                else:
+                    xin = pl['ctx_y'][-1] if a.ctx_nbcnnlayers > 0 else pl['ctx_in'].view(M, -1)
+                o.gemm(xin, dcur, g['c.ctx.fc%d.kernel' % i], transA=True)
+                o.colsum(dcur, g['c.ctx.fc%d.bias' % i])
+                if i > 0 or a.ctx_nbcnnlayers > 0:
+                    dnext = pl['dcB'] if dcur is pl['dcA'] else pl['dcA']
+                    o.gemm(dcur, p['c.ctx.fc%d.kernel' % i], dnext, transB=True, aux=xin)
+                    dcur = dnext
+            left = (W - 1) // 2
+            for i in range(a.ctx_nbcnnlayers - 1, -1, -1):
+                o.conv1d_wgrad(pl['ctx_xp'][i], dcur, g['c.ctx.cnn%d.kernel' % i], T)
+                o.colsum(dcur, g['c.ctx.cnn%d.bias' % i])
+                if i > 0:
+                    o.pad_time(pl['ctx_dzp'], dcur.view(B, T, H), W - 1 - left, left)
+                    o.conv2d_flip(p['c.ctx.cnn%d.kernel' % i].view(W, 1, H, H), pl['ctx_kflip'])
+                    dnext = pl['dcB'] if dcur is pl['dcA'] else pl['dcA']
+                    o.gemm(_im2col_view(pl['ctx_dzp'], T, W), pl['ctx_kflip'].view(W * H, H), dnext, aux=pl['ctx_y'][i - 1])
+                    dcur = dnext
         for i in range(L):
             ain = pl['a'][i - 1] if i > 0 else pl['s0']
             o.conv2d_wgrad(ain, pl['da'][i], g['c.spec.cnn%d.kernel' % i], dbias=g['c.spec.cnn%d.bias' % i],
@@ -474,36 +533,4 @@ class Critic(object):
             o.colsum(pl['dp'][i][:fM], g['c.post.fc%d.bias' % i])
         o.gemm(pl['p'][2], pl['dd'], g['c.out.kernel'], transA=True)
         o.colsum(pl['dd'][:fM], g['c.out.bias'])
-        # ctx branch: its term enters the first post layer of every first-order application
-        dct = pl['dct']
-        if first_order_apps == 1:
-            o.copy2d(dct, pl['dp'][0][:M])
-        else:
-            o.add(dct, pl['dp'][0][:M], pl['dp'][0][M:2 * M])
-            for k in range(2, first_order_apps):
-                o.copy2d(dct, pl['dp'][0][k * M:(k + 1) * M], accumulate=True)
-        o.colsum(dct, g['c.post.fc0.bias'])
-        o.gemm(pl['ctx_last'], dct, g['c.post.fc0.kernel'][SF:], transA=True)
-        dcur = pl['dcA']
-        o.gemm(dct, p['c.post.fc0.kernel'][SF:], dcur, transB=True, aux=pl['fc_y'][1])
-        for i in (1, 0):
-            if i > 0:
-                xin = pl['fc_y'][0]
-            else:
-                xin = pl['ctx_y'][-1] if a.ctx_nbcnnlayers > 0 else pl['ctx_in'].view(M, -1)
-            o.gemm(xin, dcur, g['c.ctx.fc%d.kernel' % i], transA=True)
-            o.colsum(dcur, g['c.ctx.fc%d.bias' % i])
-            if i > 0 or a.ctx_nbcnnlayers > 0:
-                dnext = pl['dcB'] if dcur is pl['dcA'] else pl['dcA']
-                o.gemm(dcur, p['c.ctx.fc%d.kernel' % i], dnext, transB=True, aux=xin)
-                dcur = dnext
-        left = (W - 1) // 2
-        for i in range(a.ctx_nbcnnlayers - 1, -1, -1):
-            o.conv1d_wgrad(pl['ctx_xp'][i], dcur, g['c.ctx.cnn%d.kernel' % i], T)
-            o.colsum(dcur, g['c.ctx.cnn%d.bias' % i])
-            if i > 0:
-                o.pad_time(pl['ctx_dzp'], dcur.view(B, T, H), W - 1 - left, left)
-                o.conv2d_flip(p['c.ctx.cnn%d.kernel' % i].view(W, 1, H, H), pl['ctx_kflip'])
-                dnext = pl['dcB'] if dcur is pl['dcA'] else pl['dcA']
-                o.gemm(_im2col_view(pl['ctx_dzp'], T, W), pl['ctx_kflip'].view(W * H, H), dnext, aux=pl['ctx_y'][i - 1])
-                dcur = dnext
+        o.join_lanes()

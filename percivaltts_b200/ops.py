@@ -122,8 +122,11 @@ class CudaOps(object):
         self._red = {}
         self._wg = {}
         self._lse_ws = None
-        self._splitk_ws = None
+        self._splitk_ws = {}       # lane -> split-K workspace
         self._ws_keep = []
+        self._lane = 0             # 0 = the caller's stream; 1 = the side stream of side_lane()
+        self._side = None
+        self.lanes = os.environ.get('PCTTS_LANES', '1') != '0'   # run independent branches of a step on two streams
         self.launches = 0          # number of C-ABI kernel-launching calls (reset by the caller)
 
     # -- helpers ---------------------------------------------------------------------------------------------
@@ -135,11 +138,41 @@ class CudaOps(object):
         _lib.check(rc, what)
 
     def reduce_ws(self, rows, C):
-        key = (int(rows), int(C))
+        key = (self._lane, int(rows), int(C))
         ws = self._red.get(key)
         if ws is None:
-            ws = self._red[key] = ReduceWorkspace(self.lib, key[0], key[1], self.device)
+            ws = self._red[key] = ReduceWorkspace(self.lib, key[1], key[2], self.device)
         return ws
+
+    # -- two-lane execution: independent branches of a step on two streams (fork / join, capturable) ------------------
+    @contextlib.contextmanager
+    def side_lane(self):
+        """Kernels issued inside run on a side stream, ordered after everything issued so far on the caller's stream, and
+        concurrently with what the caller issues afterwards until join_lanes().  Scratch workspaces are per lane; operands
+        shared by both lanes must have their bf16 shadows taken BEFORE the fork (shadow()).  With PCTTS_LANES=0 the body
+        simply runs in line."""
+        if not self.lanes or self._lane != 0:
+            yield self
+            return
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=self.device)
+        main = torch.cuda.current_stream(self.device)
+        self._side.wait_stream(main)
+        self._lane = 1
+        try:
+            with torch.cuda.stream(self._side):
+                yield self
+        finally:
+            self._lane = 0
+
+    def preshare(self, t):
+        """Take the bf16 shadow of an operand both lanes are going to read (no-op for the CUDA-core GEMM mode)."""
+        if self.nterms > 0:
+            self.shadow(t)
+
+    def join_lanes(self):
+        if self.lanes and self._side is not None:
+            torch.cuda.current_stream(self.device).wait_stream(self._side)
 
     def empty(self, *shape, dtype=torch.float32):
         return torch.empty(*shape, dtype=dtype, device=self.device)
@@ -269,10 +302,11 @@ class CudaOps(object):
                                          self._stream()), 'pctts_gemm_f32')
 
     def _splitk(self, need):
-        if self._splitk_ws is None or self._splitk_ws.numel() < need:
-            self._ws_keep.append(self._splitk_ws)      # captured graphs may still point at the old one
-            self._splitk_ws = self.empty(max(int(need), 1))
-        return self._splitk_ws
+        ws = self._splitk_ws.get(self._lane)
+        if ws is None or ws.numel() < need:
+            self._ws_keep.append(ws)                   # captured graphs may still point at the old one
+            ws = self._splitk_ws[self._lane] = self.empty(max(int(need), 1))
+        return ws
 
     # -- 1-D convolutions (pCNN1D, networktts.py:116-120) --------------------------------------------------------
     def conv1d(self, xp, kernel, y, T, bias=None, aux=None, flags=0):
@@ -351,9 +385,9 @@ class CudaOps(object):
         assert ci == CIN and tuple(dy.shape) == (N, T, F, COUT) and dw.is_contiguous()
         pad_t, pad_f = ((KH - 1) // 2, (KW - 1) // 2) if pad is None else pad
         key = (N, T, CIN, COUT, KH, KW)
-        ws = self._wg.get(key)
+        ws = self._wg.get((self._lane,) + key)
         if ws is None:
-            ws = self._wg[key] = self.empty(max(self.lib.pctts_conv2d_wgrad_workspace(*key), 148 * (KH * KW * CIN * COUT + COUT)))
+            ws = self._wg[(self._lane,) + key] = self.empty(max(self.lib.pctts_conv2d_wgrad_workspace(*key), 148 * (KH * KW * CIN * COUT + COUT)))
         px, xb, xp = _map4(x)
         pd, db, dp = _map4(dy)
         nb = N if bias_samples is None else int(bias_samples)

@@ -78,6 +78,10 @@ class WGANStepper(object):
         M, S = B * T, a.spec_size
         bf = self.buffers(B, T)
         gpl = self.G.plan(B, T)
+        cpl = self.C.plan(3, B, T)
+        # the critic's ctx branch reads the labels and the critic weights only: side lane, beside the frozen generator
+        with o.side_lane():
+            self.C.forward_ctx(cpl, X)
         # frozen generator, learning phase 1: batch statistics, no moving-average update (:121-128)
         self.G.forward(gpl, X, bf['fake'], training=True, update_stats=False, sync=sync,
                        spec_only=not self.critic_step_full_generator)
@@ -85,9 +89,9 @@ class WGANStepper(object):
             o.uniform(bf['alpha'], self.seed, self.counter)
             alpha = bf['alpha']
         o.critic_pack_inputs(Y, bf['fake'], alpha, bf['s0'], S, 1)
-        cpl = self.C.plan(3, B, T)
         s0 = bf['s0'].view(3 * B, T, S, 1)
-        d = self.C.forward(cpl, s0, X)
+        o.join_lanes()
+        d = self.C.forward_spec(cpl, s0)
         ng = float(M * sync.world)
         o.sum_scaled(d[0:M], -1.0 / ng, self.losses, L_REAL)          # wasserstein_loss with y_true = -1 (:152)
         o.sum_scaled(d[M:2 * M], 1.0 / ng, self.losses, L_FAKE)       # y_true = +1 (:153)

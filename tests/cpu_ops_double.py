@@ -56,6 +56,16 @@ class CpuOpsDouble(object):
         import contextlib
         return contextlib.nullcontext(self)
 
+    def side_lane(self):
+        import contextlib
+        return contextlib.nullcontext(self)
+
+    def join_lanes(self):
+        pass
+
+    def preshare(self, t):
+        pass
+
     def register_persistent(self, flat):
         pass
 
