@@ -440,7 +440,7 @@ class Critic(object):
         pl['s0'] = s0
         return pl['d']
 
-    def backward_to_input(self, pl, g_out, g_rows=None, accumulate=False):
+    def backward_to_input(self, pl, g_out, g_rows=None, accumulate=False, ctx_grads_apps=0):
         """Back-propagate pl['dd'] (d objective / d critic output, [nM,1]) to the spectral input.  The per-layer
         pre-activation gradients stay in pl['dp'] / pl['da'] for param_grads().  g_out: [n,T,S,1] view receiving the
         input gradient of the applications `g_rows` (slice over the napp*B sample axis; default all)."""
@@ -451,6 +451,9 @@ class Critic(object):
         o.gemm(pl['dd'], p['c.out.kernel'], pl['dp'][2], transB=True, aux=pl['p'][2])
         o.gemm(pl['dp'][2], p['c.post.fc2.kernel'], pl['dp'][1], transB=True, aux=pl['p'][1])
         o.gemm(pl['dp'][1], p['c.post.fc1.kernel'], pl['dp'][0], transB=True, aux=pl['p'][0])
+        if ctx_grads_apps:
+            o.preshare(pl['dp'][0])      # both lanes read it: the main one as a GEMM operand
+            self.param_grads_ctx(pl, ctx_grads_apps)
         o.gemm(pl['dp'][0], p['c.post.fc0.kernel'][:SF], pl['da'][L - 1].view(nM, SF), transB=True,
                aux=pl['a'][L - 1].view(nM, SF))
         for i in range(L - 1, -1, -1):
@@ -479,16 +482,14 @@ class Critic(object):
         for i in (1, 2):
             o.gemm(pl['p'][i - 1][r2], p['c.post.fc%d.kernel' % i], pl['p'][i][r2], aux=pl['p'][i][r2])
 
-    def param_grads(self, pl, first_order_apps=2):
-        """Gradients of every critic parameter from the stored layer inputs (activations, or tangents on the GP rows)
-        and pre-activation gradients.  Kernels use all napp applications; biases and the ctx branch only the first
-        `first_order_apps` (the gradient penalty reaches neither: optimizertts_wgan.py:57-68 differentiates through
-        piecewise-constant masks)."""
+    def param_grads_ctx(self, pl, first_order_apps=2):
+        """Gradients of the ctx branch and of its rows of the first post layer, on the side lane.  They depend on pl['dp'][0]
+        only, so the critic step forks them as soon as backward_to_input() has produced it (ctx_grads_apps), long before the
+        gradient-penalty sweep that the spectral weight gradients wait for; param_grads() joins."""
         o, a, p, g = self.ops, self.a, self.params.p, self.params.g
-        B, T, M, nM = pl['B'], pl['T'], pl['M'], pl['nM']
-        H, S, Fl, W, L = a.hiddenwidth, a.spec_size, a.gen_nbfilters, a.ctx_winlen, a.gen_nbcnnlayers
+        B, T, M = pl['B'], pl['T'], pl['M']
+        H, S, Fl, W = a.hiddenwidth, a.spec_size, a.gen_nbfilters, a.ctx_winlen
         SF = S * Fl
-        fM = first_order_apps * M
         # ctx branch: its term enters the first post layer of every first-order application
         dct = pl['dct']
         if first_order_apps == 1:
@@ -523,6 +524,21 @@ class Critic(object):
                     dnext = pl['dcB'] if dcur is pl['dcA'] else pl['dcA']
                     o.gemm(_im2col_view(pl['ctx_dzp'], T, W), pl['ctx_kflip'].view(W * H, H), dnext, aux=pl['ctx_y'][i - 1])
                     dcur = dnext
+        pl['ctx_grads_done'] = True
+
+    def param_grads(self, pl, first_order_apps=2):
+        """Gradients of every critic parameter from the stored layer inputs (activations, or tangents on the GP rows)
+        and pre-activation gradients.  Kernels use all napp applications; biases and the ctx branch only the first
+        `first_order_apps` (the gradient penalty reaches neither: optimizertts_wgan.py:57-68 differentiates through
+        piecewise-constant masks)."""
+        o, a, p, g = self.ops, self.a, self.params.p, self.params.g
+        B, T, M, nM = pl['B'], pl['T'], pl['M'], pl['nM']
+        H, S, Fl, W, L = a.hiddenwidth, a.spec_size, a.gen_nbfilters, a.ctx_winlen, a.gen_nbcnnlayers
+        SF = S * Fl
+        fM = first_order_apps * M
+        if not pl.get('ctx_grads_done'):
+            self.param_grads_ctx(pl, first_order_apps)
+        pl['ctx_grads_done'] = False
         for i in range(L):
             ain = pl['a'][i - 1] if i > 0 else pl['s0']
             o.conv2d_wgrad(ain, pl['da'][i], g['c.spec.cnn%d.kernel' % i], dbias=g['c.spec.cnn%d.bias' % i],

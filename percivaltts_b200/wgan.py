@@ -99,7 +99,7 @@ class WGANStepper(object):
         # all-ones seed of sum(D(xhat)) (:57)
         o.fill_segments(cpl['dd'].view(-1), M, -1.0 / ng, M, 1.0 / ng, M, 1.0)
         rows = slice(2 * B, 3 * B)
-        self.C.backward_to_input(cpl, bf['g'], g_rows=rows)
+        self.C.backward_to_input(cpl, bf['g'], g_rows=rows, ctx_grads_apps=2)
         o.gp_norms(bf['g'].view(B, T * S), bf['ss'])                   # ||g_b||^2 (:59-64)
         # tangent seed = lambda * d(mean_b (1-||g_b||)^2)/dg, written over the (no longer needed) xhat rows of s0
         o.gp_scale(bf['g'].view(B, T * S), bf['ss'], bf['s0'][rows].view(B, T * S), self.lam, B * sync.world, self.losses, L_GP)
@@ -124,9 +124,12 @@ class WGANStepper(object):
         bf = self.buffers(B, T)
         gpl = self.G.plan(B, T)
         pred = bf['fake']
-        self.G.forward(gpl, X, pred, training=True, update_stats=True, sync=sync)
         cpl = self.C.plan(1, B, T)
-        d = self.C.forward(cpl, pred[:, :, 1:1 + S].unsqueeze(-1), X)
+        with o.side_lane():
+            self.C.forward_ctx(cpl, X)
+        self.G.forward(gpl, X, pred, training=True, update_stats=True, sync=sync)      # joins the lanes
+        o.join_lanes()
+        d = self.C.forward_spec(cpl, pred[:, :, 1:1 + S].unsqueeze(-1))
         ng = float(M * sync.world)
         o.sum_scaled(d, -1.0 / ng, self.losses, L_GW)
         dpred = bf['dpred']
@@ -174,7 +177,7 @@ class WGANStepper(object):
         o.sum_scaled(d[M:2 * M], -1.0 / ng, self.losses, L_GW)
         o.fill_segments(cpl['dd'].view(-1), M, 0.0, M, 0.0, M, 1.0)
         rows = slice(2 * B, 3 * B)
-        self.C.backward_to_input(cpl, bf['g'], g_rows=rows)
+        self.C.backward_to_input(cpl, bf['g'], g_rows=rows, ctx_grads_apps=2)
         o.gp_norms(bf['g'].view(B, T * S), bf['ss'])
         o.gp_scale(bf['g'].view(B, T * S), bf['ss'], bf['s0'][rows].view(B, T * S), self.lam, B, self.losses, L_GP)
         o.loss_combine(self.losses, L_CRITIC, L_REAL, 1.0, L_FAKE, 1.0, L_GP, self.lam)
