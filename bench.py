@@ -337,7 +337,8 @@ def run_b200(args):
     launches = args.steps * n_critic + ((args.steps + 4) // 5) * n_gen
     out = {
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
-        'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'dtype': 'bf16' if ops.precision == 'bf16' else 'f32',
         'data': 'synthetic',
         'config': {'workload': WORKLOAD, 'global_batch_utterances': B * world, 'frames_per_step': B * T * world,
                    'schedule': '1 critic update per step + 1 generator update every 5th step (generator_updates>=25)',
