@@ -448,20 +448,43 @@ class Critic(object):
         nM = pl['nM']
         S, Fl, L = a.spec_size, a.gen_nbfilters, a.gen_nbcnnlayers
         SF = S * Fl
-        o.gemm(pl['dd'], p['c.out.kernel'], pl['dp'][2], transB=True, aux=pl['p'][2])
-        o.gemm(pl['dp'][2], p['c.post.fc2.kernel'], pl['dp'][1], transB=True, aux=pl['p'][1])
-        o.gemm(pl['dp'][1], p['c.post.fc1.kernel'], pl['dp'][0], transB=True, aux=pl['p'][0])
-        if ctx_grads_apps:
-            o.preshare(pl['dp'][0])      # both lanes read it: the main one as a GEMM operand
-            self.param_grads_ctx(pl, ctx_grads_apps)
-        o.gemm(pl['dp'][0], p['c.post.fc0.kernel'][:SF], pl['da'][L - 1].view(nM, SF), transB=True,
-               aux=pl['a'][L - 1].view(nM, SF))
         for i in range(L - 1, -1, -1):
             o.conv2d_flip(p['c.spec.cnn%d.kernel' % i], pl['wflip'][i])
-        for i in range(L - 1, 0, -1):
-            o.conv2d(pl['da'][i], pl['wflip'][i], pl['da'][i - 1], aux=pl['a'][i - 1])
+        if g_rows is not None and ctx_grads_apps and getattr(o, 'lanes', False) and g_rows.start > 0 \
+                and g_rows.stop == pl['nB']:
+            # critic step.  Only the interpolated applications' input gradient is on the critical path (norm -> penalty ->
+            # tangent sweep); the other applications' pre-activation gradients are needed by the weight gradients only:
+            # side lane, followed there by everything else that hangs off them (ctx branch, bias sums).
+            with o.side_lane():
+                self._dgrad_chain(pl, slice(0, g_rows.start))
+                pl['side_event'] = o.lane_event()
+                self.param_grads_ctx(pl, ctx_grads_apps)
+            self._dgrad_chain(pl, g_rows)
+        else:
+            self._dgrad_chain(pl, slice(0, pl['nB']))
+            if ctx_grads_apps:
+                self.param_grads_ctx(pl, ctx_grads_apps)
         src = pl['da'][0] if g_rows is None else pl['da'][0][g_rows]
         o.conv2d(src, pl['wflip'][0], g_out, flags=EPI_ACCUM if accumulate else 0)
+
+    def _dgrad_chain(self, pl, samples):
+        """Pre-activation gradients dp[2..0], da[L-1..0] of the applications `samples` (slice over the napp*B axis)."""
+        o, a, p = self.ops, self.a, self.params.p
+        T, nM = pl['T'], pl['nM']
+        S, Fl, L = a.spec_size, a.gen_nbfilters, a.gen_nbcnnlayers
+        SF = S * Fl
+        whole = samples.start == 0 and samples.stop == pl['nB']
+        r = slice(None) if whole else slice(samples.start * T, samples.stop * T)
+        o.gemm(pl['dd'][r], p['c.out.kernel'], pl['dp'][2][r], transB=True, aux=pl['p'][2][r])
+        o.gemm(pl['dp'][2][r], p['c.post.fc2.kernel'], pl['dp'][1][r], transB=True, aux=pl['p'][1][r])
+        o.gemm(pl['dp'][1][r], p['c.post.fc1.kernel'], pl['dp'][0][r], transB=True, aux=pl['p'][0][r])
+        o.gemm(pl['dp'][0][r], p['c.post.fc0.kernel'][:SF], pl['da'][L - 1].view(nM, SF)[r], transB=True,
+               aux=pl['a'][L - 1].view(nM, SF)[r])
+        for i in range(L - 1, 0, -1):
+            if whole:
+                o.conv2d(pl['da'][i], pl['wflip'][i], pl['da'][i - 1], aux=pl['a'][i - 1])
+            else:
+                o.conv2d(pl['da'][i][samples], pl['wflip'][i], pl['da'][i - 1][samples], aux=pl['a'][i - 1][samples])
 
     def tangent_forward(self, pl, rows):
         """Forward-mode sweep of the linearised critic (LeakyReLU masks frozen) on the applications `rows`, whose
@@ -524,6 +547,11 @@ class Critic(object):
                     dnext = pl['dcB'] if dcur is pl['dcA'] else pl['dcA']
                     o.gemm(_im2col_view(pl['ctx_dzp'], T, W), pl['ctx_kflip'].view(W * H, H), dnext, aux=pl['ctx_y'][i - 1])
                     dcur = dnext
+            # bias gradients of the post layers: first-order applications only, straight from dp / dd
+            fM = first_order_apps * M
+            for i in (1, 2):
+                o.colsum(pl['dp'][i][:fM], g['c.post.fc%d.bias' % i])
+            o.colsum(pl['dd'][:fM], g['c.out.bias'])
         pl['ctx_grads_done'] = True
 
     def param_grads(self, pl, first_order_apps=2):
@@ -539,6 +567,7 @@ class Critic(object):
         if not pl.get('ctx_grads_done'):
             self.param_grads_ctx(pl, first_order_apps)
         pl['ctx_grads_done'] = False
+        o.wait_lane_event(pl.pop('side_event', None))      # the other applications' dp / da (side lane) are complete
         for i in range(L):
             ain = pl['a'][i - 1] if i > 0 else pl['s0']
             o.conv2d_wgrad(ain, pl['da'][i], g['c.spec.cnn%d.kernel' % i], dbias=g['c.spec.cnn%d.bias' % i],
@@ -546,7 +575,5 @@ class Critic(object):
         o.gemm(pl['a'][L - 1].view(nM, SF), pl['dp'][0], g['c.post.fc0.kernel'][:SF], transA=True)
         for i in (1, 2):
             o.gemm(pl['p'][i - 1], pl['dp'][i], g['c.post.fc%d.kernel' % i], transA=True)
-            o.colsum(pl['dp'][i][:fM], g['c.post.fc%d.bias' % i])
         o.gemm(pl['p'][2], pl['dd'], g['c.out.kernel'], transA=True)
-        o.colsum(pl['dd'][:fM], g['c.out.bias'])
         o.join_lanes()

@@ -170,6 +170,18 @@ class CudaOps(object):
         if self.nterms > 0:
             self.shadow(t)
 
+    def lane_event(self):
+        """Inside side_lane(): marks the point reached there; the main lane can wait for it without a full join."""
+        if not self.lanes or self._lane != 1:
+            return None
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        return ev
+
+    def wait_lane_event(self, ev):
+        if ev is not None:
+            torch.cuda.current_stream(self.device).wait_event(ev)
+
     def join_lanes(self):
         if self.lanes and self._side is not None:
             torch.cuda.current_stream(self.device).wait_stream(self._side)

@@ -63,6 +63,12 @@ class CpuOpsDouble(object):
     def join_lanes(self):
         pass
 
+    def lane_event(self):
+        return None
+
+    def wait_lane_event(self, ev):
+        pass
+
     def preshare(self, t):
         pass
 
