@@ -211,3 +211,33 @@ def test_next_batch_prefetch_is_bit_identical(cuda_ops):
     for a_, b_ in zip(finals[0][1:], finals[1][1:]):
         assert torch.equal(a_, b_)
     assert all(np.isfinite(c[0]) for c in finals[0][0])
+
+
+@pytest.mark.parametrize('kw,B,T', [(MID, 3, 57), (DEMO, 4, 96)])
+def test_two_lane_execution_is_bit_identical_to_inline(cuda_ops, kw, B, T):
+    """The step forks independent branches onto a side stream (ops.side_lane): BLSTM branch, critic ctx branch, the data
+    gradients of the real / fake applications.  Every kernel is deterministic, so any missing dependency between the lanes
+    shows up as a difference against the same step issued in line on one stream; repeated to give a race several chances."""
+    ao, wg, wc, wgt, wct, X, Y, alpha, st = setup(cuda_ops, kw, B, T)
+    Xd, Yd, ad = torch.tensor(X).cuda(), torch.tensor(Y).cuda(), torch.tensor(alpha).cuda()
+
+    def run(lanes):
+        cuda_ops.lanes = lanes
+        st.critic_step(Xd, Yd, alpha=ad, apply=False)
+        gc = st.C.params.grad.clone()
+        lc = st.losses[W.L_REAL:W.L_CRITIC + 1].clone()      # the generator slots still hold the previous run's values
+        st.generator_step(Xd, Yd, apply=False)
+        torch.cuda.synchronize()
+        return gc, lc, st.G.params.grad.clone(), st.losses.clone()
+
+    keep = cuda_ops.lanes
+    try:
+        state = st.G.params.state.clone()
+        ref = run(False)
+        for _ in range(5):
+            st.G.params.state.copy_(state)      # BN moving statistics move in the generator step
+            got = run(True)
+            for a, b in zip(ref, got):
+                assert torch.equal(a, b)
+    finally:
+        cuda_ops.lanes = keep
