@@ -385,6 +385,9 @@ class Critic(object):
         pl['dp'] = [o.empty(nM, H) for _ in range(3)]
         pl['da'] = [o.empty(nB, T, S, Fl) for _ in range(L)]
         pl['wflip'] = [o.empty(a.gen_winlen, a.spec_freqlen, Fl, 1 if i == 0 else Fl) for i in range(L)]
+        if napp > 1:       # row ranges (applications) of these matrices are GEMM operands of their own
+            for t in pl['p'] + pl['dp'] + [pl['a'][L - 1].view(nM, S * Fl)]:
+                o.share_rows(t)
         pl['dct'] = o.empty(M, H)
         pl['dcA'] = o.empty(M, H)
         pl['dcB'] = o.empty(M, H)

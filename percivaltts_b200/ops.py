@@ -87,6 +87,65 @@ class Shadow(object):
         return self.buf.data_ptr()
 
 
+class ShadowRows(object):
+    """Rows [r0, r0 + rows) of a parent Shadow, addressed in place (same pitch, same plane stride)."""
+
+    def __init__(self, parent, r0, rows):
+        self.parent, self.r0, self.rows = parent, int(r0), int(rows)
+        self.cols, self.parts, self.ld, self.part_stride = parent.cols, parent.parts, parent.ld, parent.part_stride
+
+    @property
+    def ptr(self):
+        return self.parent.ptr + 2 * self.r0 * self.ld
+
+
+class _RowParent(object):
+    """A contiguous [R, C] activation matrix whose row ranges are used as GEMM operands on their own (the batched critic
+    applications): one shadow for the whole matrix, freshness tracked per row interval."""
+
+    def __init__(self, t, shadow):
+        self.t, self.shadow = t, shadow
+        self.lo, self.hi = _extent(t)
+        self.rowbytes = t.stride(0) * 4
+        self.fresh = []            # disjoint sorted [a, b) row intervals that are up to date
+
+    def missing(self, a, b):
+        out, cur = [], a
+        for x, y in self.fresh:
+            if y <= cur:
+                continue
+            if x >= b:
+                break
+            if x > cur:
+                out.append((cur, x))
+            cur = max(cur, y)
+        if cur < b:
+            out.append((cur, b))
+        return out
+
+    def add(self, a, b):
+        iv = sorted(self.fresh + [(a, b)])
+        merged = [iv[0]]
+        for x, y in iv[1:]:
+            if x <= merged[-1][1]:
+                merged[-1] = (merged[-1][0], max(merged[-1][1], y))
+            else:
+                merged.append((x, y))
+        self.fresh = merged
+
+    def drop(self, a, b):
+        out = []
+        for x, y in self.fresh:
+            if y <= a or x >= b:
+                out.append((x, y))
+            else:
+                if x < a:
+                    out.append((x, a))
+                if y > b:
+                    out.append((b, y))
+        self.fresh = out
+
+
 PRECISIONS = {'fp32': 6, 'fp32x3': 3, 'bf16': 1, 'simt': 0}      # -> tcgen05.mma products per k-slice
 PLANES = {6: 3, 3: 2, 1: 1, 0: 0}
 
@@ -119,6 +178,7 @@ class CudaOps(object):
                                    # refresh_persistent(); a range dies with its buffer (the addresses may be reused)
         self._persist = {}         # view key -> (Shadow, view)
         self._tracking = False
+        self._parents = []         # _RowParent list (share_rows)
         self._red = {}
         self._wg = {}
         self._lse_ws = None
@@ -199,14 +259,14 @@ class CudaOps(object):
         memory it came from (every writer reports through _wrote).  Outside a scope every GEMM re-splits its operands."""
         outer = self._tracking
         if not outer:
-            self._fresh.clear()
+            self._clear_fresh()
         self._tracking = True
         try:
             yield self
         finally:
             self._tracking = outer
             if not outer:
-                self._fresh.clear()
+                self._clear_fresh()
 
     def register_persistent(self, flat):
         """Declare a parameter buffer: shadows of views into it stay valid until refresh_persistent(flat)."""
@@ -232,11 +292,43 @@ class CudaOps(object):
             if lo <= key[0] < hi:
                 self._split(view, sh)
 
+    def _clear_fresh(self):
+        self._fresh.clear()
+        for par in self._parents:
+            par.fresh = []
+
+    def share_rows(self, t):
+        """Declare a contiguous [R, C] activation matrix whose row ranges are GEMM operands of their own: every such view
+        then addresses rows of ONE shadow, and a row is split once per step no matter through which view it is used."""
+        if self.nterms == 0:
+            return
+        assert t.dim() == 2 and t.is_contiguous()
+        self._parents.append(_RowParent(t, Shadow(self.device, t.shape[0], t.shape[1], PLANES[self.nterms])))
+
+    def _row_parent(self, t):
+        if t.dim() != 2 or not self._parents:
+            return None, 0
+        ptr = t.data_ptr()
+        for par in self._parents:
+            if par.lo <= ptr < par.hi and t.shape[1] == par.t.shape[1] and (t.shape[0] == 1 or t.stride(0) == par.t.stride(0)) \
+                    and (ptr - par.lo) % par.rowbytes == 0:
+                return par, (ptr - par.lo) // par.rowbytes
+        return None, 0
+
     def _wrote(self, t):
-        if self._fresh and t is not None:
+        if t is None:
+            return
+        if self._fresh:
             lo, hi = _extent(t)
             for key in [k for k, (a, b) in self._fresh.items() if a < hi and lo < b]:
                 del self._fresh[key]
+        for par in self._parents:
+            if par.fresh:
+                lo, hi = _extent(t)
+                if lo < par.hi and par.lo < hi:
+                    a = max(lo - par.lo, 0) // par.rowbytes
+                    b = (min(hi, par.hi) - par.lo + par.rowbytes - 1) // par.rowbytes
+                    par.drop(a, b)
 
     def _split(self, t, sh):
         p, ld, seg, ss, rows, cols = _mat(t)
@@ -245,6 +337,14 @@ class CudaOps(object):
 
     def shadow(self, t):
         """Up-to-date bf16 shadow of the 2-D / segmented 3-D fp32 view t."""
+        par, r0 = self._row_parent(t)
+        if par is not None:
+            r1 = r0 + t.shape[0]
+            for a, b in (par.missing(r0, r1) if self._tracking else [(r0, r1)]):
+                self._split(par.t[a:b], ShadowRows(par.shadow, a, b - a))
+            if self._tracking:
+                par.add(r0, r1)
+            return ShadowRows(par.shadow, r0, t.shape[0])
         key = (t.data_ptr(), tuple(t.shape), tuple(t.stride()))
         sh = self._shadows.get(key)
         if sh is None:

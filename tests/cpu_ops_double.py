@@ -63,6 +63,9 @@ class CpuOpsDouble(object):
     def join_lanes(self):
         pass
 
+    def share_rows(self, t):
+        pass
+
     def lane_event(self):
         return None
 
