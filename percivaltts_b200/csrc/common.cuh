@@ -90,4 +90,8 @@ __device__ __forceinline__ double block_sum_d(double v, double* scratch) {
     return r;
 }
 
+// norm.cu: second stage of the deterministic column reductions, for producers that write the per-CTA partials themselves
+int pctts_colreduce_slots(long rows, int C);
+int pctts_colreduce_final_launch(void* workspace, long rows, int C, int nblk, cudaStream_t st);
+
 static inline int pctts_div_up(long a, long b) { return (int)((a + b - 1) / b); }

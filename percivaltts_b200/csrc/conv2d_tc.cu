@@ -57,6 +57,7 @@ struct C2Params {
     long xpitch, ypitch, auxpitch, xbatch, ybatch, auxbatch;
     int flags;
     long long* trace;    // developer probe (pctts_conv2d_tc_set_trace): clock64() stamps of CTA 0, 8 per tile
+    double* stats;       // optional: per-CTA partial [grid][2][4] of sum y, sum y^2 per output channel (fused BatchNorm statistics)
 };
 
 // shared-memory matrix descriptor, no swizzle (INTERLEAVE), K-major: core matrix = 8 rows x 16 bytes, contiguous
@@ -127,6 +128,7 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
     extern __shared__ __align__(16) uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[2], empty_bar[2], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_slot;
+    __shared__ double stat_red[4][8];
     using L = C2Smem<PARTS>;
     constexpr int BLKCOLS = 16 * PARTS;
     constexpr int BUFCOLS = C2_MAXBLK * BLKCOLS;
@@ -307,6 +309,7 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
             for (int co = 0; co < 4; ++co) bias4[co] = __ldg(p.bias + co);
         }
         const int rows_valid = TT * G;
+        double st1[4] = {0.0, 0.0, 0.0, 0.0}, st2[4] = {0.0, 0.0, 0.0, 0.0};
         int it = 0;
         for (int ti = blockIdx.x; ti < p.ntiles; ti += gridDim.x, ++it) {
             const int s = it & 1;
@@ -371,6 +374,13 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
                                     o[0] += d4.x, o[1] += d4.y, o[2] += d4.z, o[3] += d4.w;
                                 }
                                 *reinterpret_cast<float4*>(dst + 4 * jo) = make_float4(o[0], o[1], o[2], o[3]);
+                                if (p.stats) {
+#pragma unroll
+                                    for (int co = 0; co < 4; ++co) {
+                                        st1[co] += (double)o[co];
+                                        st2[co] += (double)o[co] * (double)o[co];
+                                    }
+                                }
                             }
                         }
                     }
@@ -380,9 +390,18 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
             mbar_arrive(smem_u32(&acc_empty[s]));
             if (tr) p.trace[it * 8 + 7] = clock64();
         }
+        if (p.stats) {      // fixed-order reduction: lanes (shuffle tree), then the four epilogue warps in index order
+#pragma unroll
+            for (int co = 0; co < 4; ++co) {
+                const double a = warp_sum_d(st1[co]), b = warp_sum_d(st2[co]);
+                if (lane == 0) stat_red[q][co] = a, stat_red[q][4 + co] = b;
+            }
+        }
     }
     tc_fence_before();
     __syncthreads();
+    if (p.stats && tid < 8)
+        p.stats[(long)blockIdx.x * 8 + tid] = ((stat_red[0][tid] + stat_red[1][tid]) + stat_red[2][tid]) + stat_red[3][tid];
     if (warp == C2_PW) tmem_dealloc<C2_TMEM_COLS>(tmem_base);
     if (p.trace && blockIdx.x == 0 && tid == 0) p.trace[31 * 8 + 2] = clock64();
 }
@@ -434,9 +453,10 @@ extern "C" int pctts_conv2d_tc_supported(int F, int CIN, int COUT, int KH, int K
     return (CIN == 4 && COUT == 4 && KH == 5 && KW == 5 && pad_t == 2 && pad_f == 2 && F >= 1 && G <= 128) ? 1 : 0;
 }
 
-extern "C" int pctts_conv2d_tc_fwd(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T,
-                                   int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch,
-                                   long auxpitch, long xbatch, long ybatch, long auxbatch, int flags, int nterms, void* stream) {
+static int conv2d_tc_run(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T,
+                         int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch,
+                         long auxpitch, long xbatch, long ybatch, long auxbatch, int flags, int nterms, void* stats_workspace,
+                         void* stream) {
     if (!x || !w || !y || NB < 0 || T < 0 || F <= 0) return PCTTS_EINVAL;
     if (!pctts_conv2d_tc_supported(F, CIN, COUT, KH, KW, pad_t, pad_f)) return PCTTS_EUNSUPPORTED;
     if (nterms != 1 && nterms != 3 && nterms != 6) return PCTTS_EINVAL;
@@ -460,8 +480,33 @@ extern "C" int pctts_conv2d_tc_fwd(const float* x, const float* w, const float* 
     p.xpitch = xpitch, p.ypitch = ypitch, p.auxpitch = auxpitch, p.xbatch = xbatch, p.ybatch = ybatch, p.auxbatch = auxbatch;
     p.flags = flags;
     p.trace = g_c2_trace;
+    p.stats = (double*)stats_workspace;      // the partials sit at the base of a column-reduction workspace (norm.cu)
     cudaStream_t st = (cudaStream_t)stream;
-    if (nterms == 6) return launch_c2<3>(p, st);
-    if (nterms == 3) return launch_c2<2>(p, st);
-    return launch_c2<1>(p, st);
+    int rc;
+    if (nterms == 6) rc = launch_c2<3>(p, st);
+    else if (nterms == 3) rc = launch_c2<2>(p, st);
+    else rc = launch_c2<1>(p, st);
+    if (rc != PCTTS_OK || !stats_workspace) return rc;
+    return pctts_colreduce_final_launch(stats_workspace, (long)NB * T * F, 4, p.ntiles < 148 ? p.ntiles : 148, st);
+}
+
+extern "C" int pctts_conv2d_tc_fwd(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T,
+                                   int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch,
+                                   long auxpitch, long xbatch, long ybatch, long auxbatch, int flags, int nterms, void* stream) {
+    return conv2d_tc_run(x, w, bias, aux, y, NB, T, F, CIN, COUT, KH, KW, pad_t, pad_f, xpitch, ypitch, auxpitch, xbatch, ybatch,
+                         auxbatch, flags, nterms, nullptr, stream);
+}
+
+// The same convolution with the BatchNorm statistics of its output fused into the epilogue: workspace (a column-reduction
+// workspace for rows = NB*T*F, C = 4, see pctts_colreduce_workspace_bytes) receives sums = [sum y, sum y^2] exactly as
+// pctts_bn_stats(y) would, without re-reading y.  PCTTS_EUNSUPPORTED when the workspace has fewer than 148 partial slots.
+extern "C" int pctts_conv2d_tc_fwd_stats(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB,
+                                         int T, int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch,
+                                         long ypitch, long auxpitch, long xbatch, long ybatch, long auxbatch, int flags, int nterms,
+                                         void* workspace, void* stream) {
+    if (!workspace) return PCTTS_EINVAL;
+    if (pctts_colreduce_slots((long)NB * T * F, 4) < 148) return PCTTS_EUNSUPPORTED;
+    if (NB == 0 || T == 0) return PCTTS_EUNSUPPORTED;
+    return conv2d_tc_run(x, w, bias, aux, y, NB, T, F, CIN, COUT, KH, KW, pad_t, pad_f, xpitch, ypitch, auxpitch, xbatch, ybatch,
+                         auxbatch, flags, nterms, workspace, stream);
 }

@@ -218,6 +218,17 @@ extern "C" int pctts_bn_stats(const float* x, long rows, int C, void* workspace,
     return PCTTS_OK;
 }
 
+// used by producers that fuse the first reduction stage into their epilogue (conv2d_tc.cu): nblk partials [2][C] at the base
+// of the workspace -> sums
+int pctts_colreduce_slots(long rows, int C) { return reduce_grid(rows, C); }
+int pctts_colreduce_final_launch(void* workspace, long rows, int C, int nblk, cudaStream_t st) {
+    if (nblk > reduce_grid(rows, C)) return PCTTS_EINVAL;
+    Ws w = carve(workspace, rows, C);
+    pctts_launch(colreduce_final_kernel, pctts_div_up(2 * C, RT / 32), RT, 0, st, w.partial, w.sums, nblk, C);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
 extern "C" void* pctts_colreduce_sums_ptr(void* workspace, long rows, int C) { return (void*)carve(workspace, rows, C).sums; }
 
 extern "C" int pctts_bn_finalize(void* workspace, long rows, int C, double count, float eps, float momentum, float* mean,

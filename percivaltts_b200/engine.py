@@ -161,12 +161,14 @@ class Generator(object):
         return pl
 
     # ---- forward ----------------------------------------------------------------------------------------------
-    def _bn_fwd(self, z2, y2, bn, training, update_stats, sync):
+    def _bn_fwd(self, z2, y2, bn, training, update_stats, sync, ws=None):
+        """ws: the batch sums when the producer of z2 already reduced them (Conv2D epilogue)."""
         o, p = self.ops, self.params.p
         g, b = p[bn.prefix + '.gamma'], p[bn.prefix + '.beta']
         mm, mv = p[bn.prefix + '.moving_mean'], p[bn.prefix + '.moving_var']
         if training:
-            ws = o.bn_stats(z2)
+            if ws is None:
+                ws = o.bn_stats(z2)
             sync.allreduce(ws.sums)
             o.bn_finalize(ws, bn.rows * sync.world, A.BN_EPS, A.BN_MOMENTUM, bn.mean, bn.invstd,
                           mm if update_stats else None, mv if update_stats else None)
@@ -214,9 +216,9 @@ class Generator(object):
         o.gemm(lctx, p['g.spec.proj.kernel'], pl['s'], bias=p['g.spec.proj.bias'])
         amap = pl['s'].view(B, T, S, 1)
         for i in range(a.gen_nbcnnlayers):
-            o.conv2d(amap, p['g.spec.cnn%d.kernel' % i], pl['cv_z'][i])
+            ws = o.conv2d(amap, p['g.spec.cnn%d.kernel' % i], pl['cv_z'][i], stats=training)
             self._bn_fwd(pl['cv_z'][i].view(M * S, Fl), pl['cv_a'][i].view(M * S, Fl), pl['cv_bn'][i], training,
-                         update_stats, sync)
+                         update_stats, sync, ws=ws)
             amap = pl['cv_a'][i]
         o.conv2d(amap, p['g.spec.out.kernel'], out[:, :, 1:1 + S].unsqueeze(-1), bias=p['g.spec.out.bias'])
         # NM: pFC x (L//2), Dense(sigmoid)   (modeltts_common.py:117-121)

@@ -171,6 +171,7 @@ class CudaOps(object):
             raise ValueError('unknown precision %r (one of %s)' % (precision, sorted(PRECISIONS)))
         self.precision = precision
         self.nterms = PRECISIONS[precision]
+        self.fuse_bn_stats = os.environ.get('PCTTS_FUSE_BN_STATS', '1') != '0'   # BN sums in the Conv2D epilogue
         self.conv2d_tc = os.environ.get('PCTTS_CONV2D_TC', '1') != '0'   # tcgen05 implicit-GEMM Conv2D (4->4, 5x5)
         self._shadows = {}         # view key -> Shadow
         self._fresh = {}           # view key -> (lo, hi): activation shadows valid inside the current step scope
@@ -457,8 +458,10 @@ class CudaOps(object):
         self.gemm(xp.as_strided((B, T, W * CIN), (Tp * CIN, CIN, 1)), dz, dw.view(W * CIN, COUT), transA=True)
 
     # -- 2-D convolutions ------------------------------------------------------------------------------------
-    def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0):
-        """y = epilogue(conv2d_same(x, w)); x [N,T,F,Cin], w [KH,KW,Cin,Cout] contiguous, y/aux [N,T,F,Cout] views."""
+    def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0, stats=False):
+        """y = epilogue(conv2d_same(x, w)); x [N,T,F,Cin], w [KH,KW,Cin,Cout] contiguous, y/aux [N,T,F,Cout] views.
+        stats=True also returns the ReduceWorkspace holding the BatchNorm sums [sum y, sum y^2] of the (contiguous) output:
+        fused into the tensor-core kernel's epilogue where that kernel applies, a bn_stats() pass otherwise."""
         N, T, F, CIN = x.shape
         KH, KW, ci, COUT = w.shape
         assert ci == CIN and tuple(y.shape) == (N, T, F, COUT) and w.is_contiguous()
@@ -476,12 +479,23 @@ class CudaOps(object):
         if (self.nterms > 0 and self.conv2d_tc and self.lib.pctts_conv2d_tc_supported(F, CIN, COUT, KH, KW, pad_t, pad_f)
                 and not ((px | py | (pa or 0)) & 15) and not ((xp | yp | ap | xb | yb | ab) & 3)):
             # implicit GEMM on the tensor cores (4 -> 4 channels, 5x5): forward, data gradient (flipped kernels), GP tangent sweep
+            if stats and self.fuse_bn_stats and y.is_contiguous():
+                ws = self.reduce_ws(N * T * F, COUT)
+                rc = self.lib.pctts_conv2d_tc_fwd_stats(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t,
+                                                        pad_f, xp, yp, ap, xb, yb, ab, flags, self.nterms, ws.ptr, self._stream())
+                if rc != -2:      # PCTTS_EUNSUPPORTED: map too small for 148 partial slots
+                    self.launches += 1      # conv + the second reduction stage
+                    self._ck(rc, 'pctts_conv2d_tc_fwd_stats')
+                    return ws
             self._ck(self.lib.pctts_conv2d_tc_fwd(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
                                                   xp, yp, ap, xb, yb, ab, flags, self.nterms, self._stream()),
                      'pctts_conv2d_tc_fwd')
-            return
-        self._ck(self.lib.pctts_conv2d_fwd(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
-                                           xp, yp, ap, xb, yb, ab, flags, self._stream()), 'pctts_conv2d_fwd')
+        else:
+            self._ck(self.lib.pctts_conv2d_fwd(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
+                                               xp, yp, ap, xb, yb, ab, flags, self._stream()), 'pctts_conv2d_fwd')
+        if stats:
+            return self.bn_stats(y.view(N * T * F, COUT))
+        return None
 
     def conv2d_flip(self, w, wt):
         KH, KW, CIN, COUT = w.shape

@@ -128,7 +128,7 @@ class CpuOpsDouble(object):
         xp = F.pad(x.permute(0, 3, 1, 2), (pad_f, KW - 1 - pad_f, pad_t, KH - 1 - pad_t))
         return F.conv2d(xp, w.permute(3, 2, 0, 1)).permute(0, 2, 3, 1)
 
-    def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0):
+    def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0, stats=False):
         self.launches += 1
         KH, KW = w.shape[0], w.shape[1]
         pad_t, pad_f = ((KH - 1) // 2, (KW - 1) // 2) if pad is None else pad
@@ -143,6 +143,9 @@ class CpuOpsDouble(object):
             y.add_(R)
         else:
             y.copy_(R)
+        if stats:
+            return self.bn_stats(y.reshape(-1, y.shape[-1]))
+        return None
 
     def conv2d_flip(self, w, wt):
         self.launches += 1

@@ -96,3 +96,20 @@ def test_conv2d_tc_unsupported_shapes_take_the_cuda_core_kernel(tc_ops):
     got = torch.zeros(2, 11, 17, 4, device='cuda')
     tc_ops.conv2d(dev(x), dev(w), got)
     assert relerr(got, want) < 2e-5
+
+
+@pytest.mark.parametrize('N,T,F', [(10, 400, 129), (3, 250, 65), (2, 40, 33)])   # the last is too small: falls back to bn_stats
+def test_fused_batchnorm_statistics(cuda_ops, N, T, F):
+    """BatchNorm sums [sum y, sum y^2] from the Conv2D epilogue (pctts_conv2d_tc_fwd_stats) equal the sums of a separate pass
+    over the stored output (pctts_bn_stats) to fp64 round-off, and the stored output is unchanged by the fusion."""
+    x, w = dev(rnd(N, T, F, 4)), dev(rnd(5, 5, 4, 4, seed=1) * 0.2)
+    y0, y1 = torch.empty(N, T, F, 4, device='cuda'), torch.empty(N, T, F, 4, device='cuda')
+    cuda_ops.conv2d(x, w, y0)
+    want = cuda_ops.bn_stats(y0.view(-1, 4)).sums.clone()
+    ws = cuda_ops.conv2d(x, w, y1, stats=True)
+    assert torch.equal(y0, y1)
+    got = ws.sums
+    assert float(((got - want).abs() / want.abs().clamp_min(1e-30)).max()) < 1e-12
+    yd = y0.double().view(-1, 4)
+    ref = torch.stack([yd.sum(0), (yd * yd).sum(0)])
+    assert float(((got - ref).abs() / ref.abs().clamp_min(1e-30)).max()) < 1e-10
