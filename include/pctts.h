@@ -74,9 +74,10 @@ int pctts_gemm_tc(int transA, int transB, int M, int N, int K, float alpha, cons
                   const float* addmod, int addrows, int flags, int nterms, int splits, float* workspace, void* stream);
 /* Conv1D 'same' (networktts.py:116-120) without materialising im2col: xsh = shadow of the time-padded input [B*(T+W-1), CIN],
  * wsh = shadow of the keras kernel [W*CIN, COUT]; y [B*T, COUT] (row pitch ldy) = epilogue(conv); aux uses y's addressing. */
+long pctts_conv1d_tc_fwd_workspace(int B, int T, int W, int CIN, int COUT);   /* floats (0: none needed); host call */
 int pctts_conv1d_tc_fwd(const void* xsh, long ldx, long x_part_stride, const void* wsh, long ldw, long w_part_stride, float* y,
                         long ldy, int B, int T, int W, int CIN, int COUT, const float* bias, const float* aux, int flags, int nterms,
-                        void* stream);
+                        float* workspace, void* stream);
 /* dw[W*CIN, COUT] (+)= sum_{b,t} xpad[b,t+w,c] dz[b,t,n];  dzsh = shadow of dz [B*T, COUT] */
 int pctts_conv1d_tc_wgrad(const void* xsh, long ldx, long x_part_stride, const void* dzsh, long lddz, long dz_part_stride, float* dw,
                           int B, int T, int W, int CIN, int COUT, int accumulate, int nterms, void* stream);

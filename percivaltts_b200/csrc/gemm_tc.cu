@@ -348,9 +348,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     if (tr0 && threadIdx.x == 64) p.trace[16 + 3] = clock64();
 }
 
-// C (+)= alpha * sum_z partial[z], fixed order (deterministic)
+// C (+)= epilogue(alpha * sum_z partial[z]), fixed order (deterministic); epilogue = bias, LeakyReLU, LeakyReLU' mask (aux is
+// addressed like C)
 __global__ void tc_splitk_reduce_kernel(const float* __restrict__ partial, int splits, long rows, int N, float* __restrict__ C,
-                                        long ldc, float alpha, int accum) {
+                                        long ldc, float alpha, int accum, const float* __restrict__ bias,
+                                        const float* __restrict__ aux, int flags) {
     pdl_entry();
     const long total = rows * N;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -360,6 +362,9 @@ __global__ void tc_splitk_reduce_kernel(const float* __restrict__ partial, int s
         const int n = (int)(i - m * N);
         float* c = C + m * ldc + n;
         s *= alpha;
+        if (flags & PCTTS_EPI_BIAS) s += __ldg(bias + n);
+        if (flags & PCTTS_EPI_LRELU) s = lrelu_f(s);
+        if (flags & PCTTS_EPI_DLRELU_AUX) s *= dlrelu_from_out(aux[m * ldc + n]);
         *c = accum ? *c + s : s;
     }
 }
@@ -466,7 +471,8 @@ int launch_tc(const Launch& L, Params p, int bn, float* C, long ldc, float alpha
         const long total = p.crows * p.N;
         int blocks = pctts_div_up(total, 256);
         if (blocks > 148 * 8) blocks = 148 * 8;
-        pctts_launch(tc_splitk_reduce_kernel, blocks, 256, 0, st, p.partial, L.splits, p.crows, p.N, C, ldc, alpha, accum);
+        pctts_launch(tc_splitk_reduce_kernel, blocks, 256, 0, st, p.partial, L.splits, p.crows, p.N, C, ldc, alpha, accum, p.bias, p.aux,
+                     p.flags & (PCTTS_EPI_BIAS | PCTTS_EPI_LRELU | PCTTS_EPI_DLRELU_AUX));
         PCTTS_LAUNCH_CHECK();
     }
     return PCTTS_OK;
@@ -565,9 +571,24 @@ extern "C" int pctts_gemm_tc(int transA, int transB, int M, int N, int K, float 
 // 'same' Conv1D forward as a virtual-im2col GEMM.  xsh: bf16 planes of the time-padded input [B, T+W-1, CIN] (row pitch ldx);
 // wsh: bf16 planes of the keras kernel [W*CIN, COUT] (row pitch ldw);  y [B*T, COUT] fp32 = epilogue(im2col(x) . w).
 // Accumulator rows run over the flat padded row space r = b*(T+W-1) + t'; rows with t' >= T are computed and dropped.
+// split of the reduction (taps x channel blocks) over two CTAs per output tile: with COUT = 256 and ~4000 frames the 128 x 128
+// tiling gives 66 tiles for 148 SMs, and the 128 x 64 tiling that fills them is bound by the shared-memory operand reads
+// (48 % of the tensor peak); two K halves of 128 x 128 tiles fill 132 SMs at the full MMA rate
+static int conv1d_fwd_splits(long rows, int COUT, int num_kb) {
+    const long m_tiles = (rows + BM - 1) / BM;
+    const long t128 = m_tiles * ((COUT + 127) / 128);
+    return (COUT >= 128 && t128 < 100 && 2 * t128 <= 148 && num_kb >= 32) ? 2 : 1;
+}
+
+/* floats of workspace pctts_conv1d_tc_fwd wants (0: none) */
+extern "C" long pctts_conv1d_tc_fwd_workspace(int B, int T, int W, int CIN, int COUT) {
+    const int num_kb = ((CIN + BK - 1) / BK) * W;
+    return conv1d_fwd_splits((long)B * (T + W - 1), COUT, num_kb) > 1 ? 2L * B * T * COUT : 0;
+}
+
 extern "C" int pctts_conv1d_tc_fwd(const void* xsh, long ldx, long x_part_stride, const void* wsh, long ldw, long w_part_stride,
                                    float* y, long ldy, int B, int T, int W, int CIN, int COUT, const float* bias, const float* aux,
-                                   int flags, int nterms, void* stream) {
+                                   int flags, int nterms, float* workspace, void* stream) {
     if (!xsh || !wsh || !y || B <= 0 || T <= 0 || W <= 0 || CIN <= 0 || COUT <= 0) return PCTTS_EINVAL;
     if (nterms != 1 && nterms != 3 && nterms != 6) return PCTTS_EINVAL;
     if (flags & (PCTTS_EPI_ATOMIC | PCTTS_EPI_ADDMOD)) return PCTTS_EUNSUPPORTED;
@@ -579,8 +600,10 @@ extern "C" int pctts_conv1d_tc_fwd(const void* xsh, long ldx, long x_part_stride
     Launch L;
     Params p;
     L.m_tiles = (int)((rows + BM - 1) / BM);
-    const int bn = pick_bn(L.m_tiles, COUT);
     const int kb_seg = (CIN + BK - 1) / BK;
+    int splits = workspace ? conv1d_fwd_splits(rows, COUT, kb_seg * W) : 1;
+    if (splits > 1 && ((flags & ~(PCTTS_EPI_BIAS | PCTTS_EPI_LRELU | PCTTS_EPI_DLRELU_AUX)) || (aux && ldy != COUT))) splits = 1;
+    const int bn = splits > 1 ? 128 : pick_bn(L.m_tiles, COUT);
     // A: K-major over the flat padded activation matrix; k-block (w, j): 64 channels from j*64, rows shifted down by w
     p.a.mn_major = 0, p.a.t_div = 1 << 30;
     zero3(p.a.t_lo), zero3(p.a.t_hi), zero3(p.a.k_lo), zero3(p.a.k_hi);
@@ -597,13 +620,13 @@ extern "C" int pctts_conv1d_tc_fwd(const void* xsh, long ldx, long x_part_stride
     L.b_strides[0] = ldw * 2, L.b_strides[1] = L.b_dims[1] * ldw * 2, L.b_strides[2] = w_part_stride * 2;
     p.kb_div = kb_seg;
     p.num_kb = kb_seg * W;
-    p.kb_per_split = p.num_kb;
-    L.splits = 1;
+    p.kb_per_split = (p.num_kb + splits - 1) / splits;
+    L.splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
     p.nterms = nterms;
     p.C = y, p.ldc = ldy, p.N = COUT;
     p.seg_len = Tp, p.seg_valid = T, p.nseg = B;
     p.alpha = 1.f, p.bias = bias, p.aux = aux, p.addmod = nullptr, p.addrows = 0, p.flags = flags;
-    p.partial = nullptr;
+    p.partial = L.splits > 1 ? workspace : nullptr;
     p.crows = (long)B * T;
     return launch_tc(L, p, bn, y, ldy, 1.f, 0, (cudaStream_t)stream);
 }

@@ -437,9 +437,13 @@ class CudaOps(object):
                 assert tuple(aux.shape) == tuple(y.shape) and aux.stride() == y.stride()
             shx, shw = self.shadow(xp.view(B * Tp, CIN)), self.shadow(kernel.view(W * CIN, COUT))
             self._wrote(y)
+            need = self.lib.pctts_conv1d_tc_fwd_workspace(B, T, W, CIN, COUT)      # two K halves per tile when the tiling is short of CTAs
+            ws = self._splitk(need) if need else None
+            if ws is not None:
+                self.launches += 1
             self._ck(self.lib.pctts_conv1d_tc_fwd(shx.ptr, shx.ld, shx.part_stride, shw.ptr, shw.ld, shw.part_stride, y.data_ptr(),
                                                   y.stride(0), B, T, W, CIN, COUT, _ptr(bias), _ptr(aux), flags, self.nterms,
-                                                  self._stream()), 'pctts_conv1d_tc_fwd')
+                                                  _ptr(ws), self._stream()), 'pctts_conv1d_tc_fwd')
             return
         self.gemm(xp.as_strided((B, T, W * CIN), (Tp * CIN, CIN, 1)), kernel.view(W * CIN, COUT), y, bias=bias, aux=aux, flags=flags)
 
