@@ -11,6 +11,8 @@
 // segstride = (T+W-1)*C) without materialising it.
 #include "common.cuh"
 #include "pctts.h"
+#include <stdint.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -178,6 +180,106 @@ __global__ void __launch_bounds__(NT) gemm_f32_kernel(int M, int N, int K, Mat A
     }
 }
 
+
+// ---- degenerate shapes of the Dense(1) heads (networks_critic.py:96, modeltts_common.py:84): the 128 x 64 tiles above spend
+// 17-37 us on what is a matrix-vector product, an outer product or a weighted column sum of a 12 MB matrix -----------------------
+__device__ __forceinline__ void epi_store(const Mat& C, const Epi& e, int m, int n, int N, float v) {
+    float* Cp = const_cast<float*>(C.p);
+    const long off = row_off(C, m) + n;
+    v *= e.alpha;
+    if (e.flags & PCTTS_EPI_BIAS) v += __ldg(e.bias + n);
+    if (e.flags & PCTTS_EPI_ADDMOD) v += __ldg(e.addmod + (long)(m % e.addrows) * N + n);
+    if (e.flags & PCTTS_EPI_LRELU) v = lrelu_f(v);
+    if (e.flags & PCTTS_EPI_SIGMOID) v = sigmoid_f(v);
+    if (e.flags & PCTTS_EPI_DLRELU_AUX) v *= dlrelu_from_out(e.aux[off]);
+    if (e.flags & PCTTS_EPI_ATOMIC) {
+        atomicAdd(Cp + off, v);
+    } else {
+        if (e.flags & PCTTS_EPI_ACCUM) v += Cp[off];
+        Cp[off] = v;
+    }
+}
+
+// N == 1, A not transposed: y[m] = epilogue(sum_k A[m,k] b[k]); one warp per row, lanes stride k (coalesced), shuffle tree
+__global__ void __launch_bounds__(256) gemv_rows_kernel(int M, int K, Mat A, Mat B, int tb, Mat C, Epi e) {
+    pdl_entry();
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    for (int m = blockIdx.x * wpb + (threadIdx.x >> 5); m < M; m += gridDim.x * wpb) {
+        const float* a = A.p + row_off(A, m);
+        float s = 0.f;
+        if (tb) {
+            for (int k = lane; k < K; k += 32) s = fmaf(a[k], __ldg(B.p + k), s);
+        } else {
+            for (int k = lane; k < K; k += 32) s = fmaf(a[k], __ldg(B.p + row_off(B, k)), s);
+        }
+        s = warp_sum(s);
+        if (lane == 0) epi_store(C, e, m, 0, 1, s);
+    }
+}
+
+// K == 1: C[m,n] = epilogue(a[m] b[n])
+__global__ void __launch_bounds__(256) outer_kernel(int M, int N, Mat A, int ta, Mat B, int tb, Mat C, Epi e) {
+    pdl_entry();
+    const long total = (long)M * N;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int m = (int)(i / N), n = (int)(i - (long)m * N);
+        const float a = ta ? A.p[m] : A.p[row_off(A, m)];
+        const float b = tb ? __ldg(B.p + row_off(B, n)) : __ldg(B.p + n);
+        epi_store(C, e, m, n, N, a * b);
+    }
+}
+
+// N == 1, A transposed (stored [K, M], 16-byte aligned rows), split over k: partial[z][m] = sum_{k in slab z} A[k,m] b[k].
+// A warp covers 128 columns (one float4 per lane) and walks a sub-slab of the CTA's rows eight at a time (4 KB in flight per
+// warp: the first version, one scalar column per thread, kept 184 KB in flight on the whole GPU and took 60 us for 12 MB);
+// the sub-slabs of a CTA are summed in index order through shared memory.
+__global__ void __launch_bounds__(256) wcolsum_kernel(int M, int K, Mat A, Mat B, int tb, int kchunk, int mg, int ksub,
+                                                      float* __restrict__ partial) {
+    pdl_entry();
+    __shared__ float4 red[8][32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = warp % mg, ks = warp / mg;                    // column group, row sub-slab of this warp
+    const int mgrp = blockIdx.x * mg + g;
+    const int m = mgrp * 128 + lane * 4;
+    const int k0 = blockIdx.y * kchunk, k1 = min(K, k0 + kchunk);
+    const int per = (k1 - k0 + ksub - 1) / ksub;
+    const int ka = k0 + ks * per, kb = min(k1, ka + per);
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ks < ksub && m < M) {
+        int k = ka;
+        for (; k + 7 < kb; k += 8) {
+            float4 v[8];
+            float bb[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                v[u] = *reinterpret_cast<const float4*>(A.p + (long)(k + u) * A.ld + m);
+                bb[u] = tb ? __ldg(B.p + k + u) : __ldg(B.p + (long)(k + u) * B.ld);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                s.x = fmaf(v[u].x, bb[u], s.x), s.y = fmaf(v[u].y, bb[u], s.y);
+                s.z = fmaf(v[u].z, bb[u], s.z), s.w = fmaf(v[u].w, bb[u], s.w);
+            }
+        }
+        for (; k < kb; ++k) {
+            const float4 v = *reinterpret_cast<const float4*>(A.p + (long)k * A.ld + m);
+            const float bk = tb ? __ldg(B.p + k) : __ldg(B.p + (long)k * B.ld);
+            s.x = fmaf(v.x, bk, s.x), s.y = fmaf(v.y, bk, s.y), s.z = fmaf(v.z, bk, s.z), s.w = fmaf(v.w, bk, s.w);
+        }
+    }
+    red[warp][lane] = s;
+    __syncthreads();
+    if (ks == 0 && m < M) {
+        float4 t = red[g][lane];
+        for (int j = 1; j < ksub; ++j) {
+            const float4 o = red[j * mg + g][lane];
+            t.x += o.x, t.y += o.y, t.z += o.z, t.w += o.w;
+        }
+        *reinterpret_cast<float4*>(partial + (long)blockIdx.y * M + m) = t;
+    }
+}
+
 // C = alpha * sum_z partial[z] (+ C when accumulating), fixed summation order => deterministic
 __global__ void splitk_reduce_kernel(const float* __restrict__ partial, int splits, int M, int N, Mat C, float alpha, int accum) {
     pdl_entry();
@@ -203,6 +305,33 @@ int launch(int ta, int tb, int M, int N, int K, Mat A, Mat B, Mat C, Epi e, cuda
         splits = (K + kchunk - 1) / kchunk;
     }
     if (splits <= 1) partial = nullptr;
+    static const bool fast1 = !(getenv("PCTTS_NO_DENSE1") && atoi(getenv("PCTTS_NO_DENSE1")));
+    if (fast1 && K == 1 && !partial) {
+        int blocks = pctts_div_up((long)M * N, 256);
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        pctts_launch(outer_kernel, blocks, 256, 0, st, M, N, A, ta, B, tb, C, e);
+        PCTTS_LAUNCH_CHECK();
+        return PCTTS_OK;
+    }
+    if (fast1 && N == 1 && !ta && !partial && K >= 1) {
+        int blocks = pctts_div_up(M, 8);
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        pctts_launch(gemv_rows_kernel, blocks, 256, 0, st, M, K, A, B, tb, C, e);
+        PCTTS_LAUNCH_CHECK();
+        return PCTTS_OK;
+    }
+    if (fast1 && N == 1 && ta && partial && A.seg <= 0 && (tb || B.seg <= 0) && (M & 3) == 0 && (A.ld & 3) == 0 &&
+        (((uintptr_t)A.p | (uintptr_t)partial) & 15) == 0) {
+        const int groups = pctts_div_up(M, 128);
+        const int mg = groups < 8 ? groups : 8, ksub = 8 / mg;
+        dim3 g1(pctts_div_up(groups, mg), splits);
+        pctts_launch(wcolsum_kernel, g1, 256, 0, st, M, K, A, B, tb, kchunk, mg, ksub, partial);
+        PCTTS_LAUNCH_CHECK();
+        int blocks = pctts_div_up(M, 256);
+        pctts_launch(splitk_reduce_kernel, blocks, 256, 0, st, partial, splits, M, N, C, e.alpha, (e.flags & PCTTS_EPI_ACCUM) ? 1 : 0);
+        PCTTS_LAUNCH_CHECK();
+        return PCTTS_OK;
+    }
     dim3 grid(pctts_div_up(N, BN), pctts_div_up(M, BM), partial ? splits : 1);
     if (!ta && !tb) pctts_launch(gemm_f32_kernel<false, false>, grid, NT, 0, st, M, N, K, A, B, C, e, kchunk, partial);
     else if (!ta && tb) pctts_launch(gemm_f32_kernel<false, true>, grid, NT, 0, st, M, N, K, A, B, C, e, kchunk, partial);

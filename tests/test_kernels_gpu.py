@@ -36,6 +36,9 @@ GEMM_CASES = [
     # M, N, K, transA, transB
     (300, 70, 45, False, False), (129, 64, 16, False, True), (64, 33, 257, True, False), (17, 5, 9, True, True),
     (1000, 256, 300, False, False), (256, 1, 515, True, False), (515, 256, 1, False, True), (1, 1, 40, False, False),
+    # Dense(1) heads: matrix-vector, outer product, weighted column sum (split over k) fast paths of gemm_simt.cu
+    (1003, 1, 256, False, False), (1003, 1, 512, False, True), (777, 256, 1, False, False), (300, 33, 1, True, True),
+    (256, 1, 3001, True, False), (512, 1, 4000, True, True),
 ]
 
 
