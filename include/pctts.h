@@ -98,12 +98,14 @@ int pctts_conv2d_tc_supported(int F, int CIN, int COUT, int KH, int KW, int pad_
 int pctts_conv2d_tc_fwd(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T, int F,
                         int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch, long auxpitch,
                         long xbatch, long ybatch, long auxbatch, int flags, int nterms, void* stream);
-/* the same, with the BatchNorm statistics of y fused into the epilogue (networktts.py:124: BatchNormalization after Conv2D):
- * `workspace` = a column-reduction workspace for rows = NB*T*F, C = 4; afterwards it holds what pctts_bn_stats(y) would have
- * produced.  PCTTS_EUNSUPPORTED for maps too small to own 148 partial slots (use pctts_bn_stats then). */
-int pctts_conv2d_tc_fwd_stats(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T, int F,
+/* the same, fused with the BatchNormalization layers around it (networktts.py:122-126): in_mean / in_invstd / in_gamma / in_beta
+ * (all or none; 4 floats each) = apply LeakyReLU(BN(.)) of the previous layer to x on load (x is its pre-BN map; the activation
+ * map is never written); workspace (or NULL) = a column-reduction workspace for rows = NB*T*F, C = 4 receiving what
+ * pctts_bn_stats(y) would produce.  PCTTS_EUNSUPPORTED for maps too small to own 148 partial slots. */
+int pctts_conv2d_tc_fwd_fused(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T, int F,
                               int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch, long auxpitch,
-                              long xbatch, long ybatch, long auxbatch, int flags, int nterms, void* workspace, void* stream);
+                              long xbatch, long ybatch, long auxbatch, int flags, int nterms, const float* in_mean,
+                              const float* in_invstd, const float* in_gamma, const float* in_beta, void* workspace, void* stream);
 int pctts_conv2d_flip_weights(const float* w, float* wt, int KH, int KW, int CIN, int COUT, void* stream);
 long pctts_conv2d_wgrad_workspace(int NB, int T, int CIN, int COUT, int KH, int KW); /* floats; host call */
 /* dw[kt,kf,ci,co] (+)= scale * sum_{n,t,f} x[n,t+kt-pad_t,f+kf-pad_f,ci] dy[n,t,f,co]   (deterministic two-stage) */

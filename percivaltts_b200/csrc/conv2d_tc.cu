@@ -57,6 +57,8 @@ struct C2Params {
     long xpitch, ypitch, auxpitch, xbatch, ybatch, auxbatch;
     int flags;
     long long* trace;    // developer probe (pctts_conv2d_tc_set_trace): clock64() stamps of CTA 0, 8 per tile
+    const float *bn_mean, *bn_invstd, *bn_gamma, *bn_beta;   // optional: the input is a pre-BatchNorm map; BatchNorm + LeakyReLU
+                                                             // are applied to every in-range pixel on load (fused bn_apply)
     double* stats;       // optional: per-CTA partial [grid][2][4] of sum y, sum y^2 per output channel (fused BatchNorm statistics)
 };
 
@@ -160,7 +162,8 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
     const int my_tiles = (p.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
     const int nitems = my_tiles * npass;
     // item k = (tile it = k / npass, pass k % npass): the loads of item k+1 are in flight while item k is converted
-    auto issue = [&](int k, float4 (&va)[C2_UNR], float4 (&vb)[C2_UNR]) {
+    auto issue = [&](int k, float4 (&va)[C2_UNR], float4 (&vb)[C2_UNR], uint32_t& inrange) {
+        inrange = 0u;
         const int it = k / npass, pass = k - it * npass;
         const int ti = blockIdx.x + it * gridDim.x;
         const int n = ti / p.tiles_per_sample;
@@ -176,7 +179,8 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
                 if (t >= 0 && t < p.T && f < p.F) {
                     const float* src = xb + (long)t * p.xpitch + (long)f * 4;
                     va[u] = *reinterpret_cast<const float4*>(src);
-                    if (f + 1 < p.F) vb[u] = *reinterpret_cast<const float4*>(src + 4);
+                    inrange |= 1u << (2 * u);
+                    if (f + 1 < p.F) vb[u] = *reinterpret_cast<const float4*>(src + 4), inrange |= 2u << (2 * u);
                 }
             }
         }
@@ -187,7 +191,22 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
     __shared__ float wsm[KT * KW5 * 16];
     if (tid < KT * KW5 * 16) wsm[tid] = __ldg(p.w + tid);
     float4 ca[C2_UNR], cb[C2_UNR], na[C2_UNR], nb[C2_UNR];
-    if (warp < C2_PW && nitems > 0) issue(0, ca, cb);   // first tile's loads fly while the weight operand is built
+    uint32_t cmask = 0u, nmask = 0u;
+    if (warp < C2_PW && nitems > 0) issue(0, ca, cb, cmask);   // first tile's loads fly while the weight operand is built
+    // fused BatchNorm + LeakyReLU of the input (same expression as bn_apply_kernel); zero padding stays zero
+    const bool bn_in = p.bn_mean != nullptr;
+    float bm[4] = {0.f, 0.f, 0.f, 0.f}, bi[4] = {1.f, 1.f, 1.f, 1.f}, bg[4] = {1.f, 1.f, 1.f, 1.f}, bb[4] = {0.f, 0.f, 0.f, 0.f};
+    if (bn_in) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            bm[c] = __ldg(p.bn_mean + c), bi[c] = __ldg(p.bn_invstd + c), bg[c] = __ldg(p.bn_gamma + c), bb[c] = __ldg(p.bn_beta + c);
+    }
+    auto bn_act = [&](float4& v) {
+        v.x = lrelu_f((v.x - bm[0]) * bi[0] * bg[0] + bb[0]);
+        v.y = lrelu_f((v.y - bm[1]) * bi[1] * bg[1] + bb[1]);
+        v.z = lrelu_f((v.z - bm[2]) * bi[2] * bg[2] + bb[2]);
+        v.w = lrelu_f((v.w - bm[3]) * bi[3] * bg[3] + bb[3]);
+    };
     __syncthreads();
 
     // ---- block-Toeplitz weight operand, all planes: Bmat[mma j = (kt,h)][chunk c][row n = 16*plane + 4*jo + co][8 k]
@@ -222,7 +241,7 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
             const int s = it & 1;
             const uint32_t ph = (uint32_t)(it >> 1) & 1u;
             uint8_t* const st = smem_al + L::b_bytes + (size_t)s * stage_bytes;
-            if (k + 1 < nitems) issue(k + 1, na, nb);
+            if (k + 1 < nitems) issue(k + 1, na, nb, nmask);
             const bool tr = p.trace && blockIdx.x == 0 && tid == 0 && it < 32;
             if (pass == 0) {
                 if (tr) p.trace[it * 8 + 0] = clock64();
@@ -240,6 +259,10 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
             for (int u = 0; u < C2_UNR; ++u) {
                 const int idx = pass * PASS + u * C2_PROD + tid;
                 if (idx < npairs) {
+                    if (bn_in) {
+                        if (cmask & (1u << (2 * u))) bn_act(ca[u]);
+                        if (cmask & (2u << (2 * u))) bn_act(cb[u]);
+                    }
                     const float v[8] = {ca[u].x, ca[u].y, ca[u].z, ca[u].w, cb[u].x, cb[u].y, cb[u].z, cb[u].w};
                     uint4 e[PARTS];
                     split8<PARTS>(v, e);
@@ -256,6 +279,7 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
             }
 #pragma unroll
             for (int u = 0; u < C2_UNR; ++u) ca[u] = na[u], cb[u] = nb[u];
+            cmask = nmask;
         }
     } else if (warp == C2_PW) {
         // ------------------------------------------------ MMA issuer ------------------------------------------------
@@ -455,8 +479,8 @@ extern "C" int pctts_conv2d_tc_supported(int F, int CIN, int COUT, int KH, int K
 
 static int conv2d_tc_run(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T,
                          int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch,
-                         long auxpitch, long xbatch, long ybatch, long auxbatch, int flags, int nterms, void* stats_workspace,
-                         void* stream) {
+                         long auxpitch, long xbatch, long ybatch, long auxbatch, int flags, int nterms, const float* const* in_bn,
+                         void* stats_workspace, void* stream) {
     if (!x || !w || !y || NB < 0 || T < 0 || F <= 0) return PCTTS_EINVAL;
     if (!pctts_conv2d_tc_supported(F, CIN, COUT, KH, KW, pad_t, pad_f)) return PCTTS_EUNSUPPORTED;
     if (nterms != 1 && nterms != 3 && nterms != 6) return PCTTS_EINVAL;
@@ -480,6 +504,8 @@ static int conv2d_tc_run(const float* x, const float* w, const float* bias, cons
     p.xpitch = xpitch, p.ypitch = ypitch, p.auxpitch = auxpitch, p.xbatch = xbatch, p.ybatch = ybatch, p.auxbatch = auxbatch;
     p.flags = flags;
     p.trace = g_c2_trace;
+    p.bn_mean = in_bn ? in_bn[0] : nullptr, p.bn_invstd = in_bn ? in_bn[1] : nullptr;
+    p.bn_gamma = in_bn ? in_bn[2] : nullptr, p.bn_beta = in_bn ? in_bn[3] : nullptr;
     p.stats = (double*)stats_workspace;      // the partials sit at the base of a column-reduction workspace (norm.cu)
     cudaStream_t st = (cudaStream_t)stream;
     int rc;
@@ -494,19 +520,25 @@ extern "C" int pctts_conv2d_tc_fwd(const float* x, const float* w, const float* 
                                    int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch,
                                    long auxpitch, long xbatch, long ybatch, long auxbatch, int flags, int nterms, void* stream) {
     return conv2d_tc_run(x, w, bias, aux, y, NB, T, F, CIN, COUT, KH, KW, pad_t, pad_f, xpitch, ypitch, auxpitch, xbatch, ybatch,
-                         auxbatch, flags, nterms, nullptr, stream);
+                         auxbatch, flags, nterms, nullptr, nullptr, stream);
 }
 
-// The same convolution with the BatchNorm statistics of its output fused into the epilogue: workspace (a column-reduction
-// workspace for rows = NB*T*F, C = 4, see pctts_colreduce_workspace_bytes) receives sums = [sum y, sum y^2] exactly as
-// pctts_bn_stats(y) would, without re-reading y.  PCTTS_EUNSUPPORTED when the workspace has fewer than 148 partial slots.
-extern "C" int pctts_conv2d_tc_fwd_stats(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB,
+// The same convolution fused with the BatchNormalization layers around it (networktts.py:122-126, pCNN2D = Conv2D + BN + LReLU):
+//  * in_mean / in_invstd / in_gamma / in_beta (all four or none, 4 floats each): x is the PREVIOUS layer's pre-BatchNorm map and
+//    LeakyReLU(BN(x)) is formed on load, so the activation map is never written (forward-only uses: the frozen generator);
+//  * workspace (or NULL): a column-reduction workspace for rows = NB*T*F, C = 4 (pctts_colreduce_workspace_bytes) that receives
+//    sums = [sum y, sum y^2] of the output exactly as pctts_bn_stats(y) would, without re-reading y.
+// PCTTS_EUNSUPPORTED when a workspace is given but has fewer than 148 partial slots (small maps).
+extern "C" int pctts_conv2d_tc_fwd_fused(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB,
                                          int T, int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch,
                                          long ypitch, long auxpitch, long xbatch, long ybatch, long auxbatch, int flags, int nterms,
+                                         const float* in_mean, const float* in_invstd, const float* in_gamma, const float* in_beta,
                                          void* workspace, void* stream) {
-    if (!workspace) return PCTTS_EINVAL;
-    if (pctts_colreduce_slots((long)NB * T * F, 4) < 148) return PCTTS_EUNSUPPORTED;
-    if (NB == 0 || T == 0) return PCTTS_EUNSUPPORTED;
+    const int nbn = (in_mean != nullptr) + (in_invstd != nullptr) + (in_gamma != nullptr) + (in_beta != nullptr);
+    if (nbn != 0 && nbn != 4) return PCTTS_EINVAL;
+    if (workspace && pctts_colreduce_slots((long)NB * T * F, 4) < 148) return PCTTS_EUNSUPPORTED;
+    if (workspace && (NB == 0 || T == 0)) return PCTTS_EUNSUPPORTED;
+    const float* in_bn[4] = {in_mean, in_invstd, in_gamma, in_beta};
     return conv2d_tc_run(x, w, bias, aux, y, NB, T, F, CIN, COUT, KH, KW, pad_t, pad_f, xpitch, ypitch, auxpitch, xbatch, ybatch,
-                         auxbatch, flags, nterms, workspace, stream);
+                         auxbatch, flags, nterms, nbn ? in_bn : nullptr, workspace, stream);
 }

@@ -161,8 +161,9 @@ class Generator(object):
         return pl
 
     # ---- forward ----------------------------------------------------------------------------------------------
-    def _bn_fwd(self, z2, y2, bn, training, update_stats, sync, ws=None):
-        """ws: the batch sums when the producer of z2 already reduced them (Conv2D epilogue)."""
+    def _bn_fwd(self, z2, y2, bn, training, update_stats, sync, ws=None, apply=True):
+        """ws: the batch sums when the producer of z2 already reduced them (Conv2D epilogue).  apply=False: only the
+        statistics (bn.mean / bn.invstd) -- the consumer applies BatchNorm + LeakyReLU on load."""
         o, p = self.ops, self.params.p
         g, b = p[bn.prefix + '.gamma'], p[bn.prefix + '.beta']
         mm, mv = p[bn.prefix + '.moving_mean'], p[bn.prefix + '.moving_var']
@@ -172,11 +173,12 @@ class Generator(object):
             sync.allreduce(ws.sums)
             o.bn_finalize(ws, bn.rows * sync.world, A.BN_EPS, A.BN_MOMENTUM, bn.mean, bn.invstd,
                           mm if update_stats else None, mv if update_stats else None)
-            o.bn_apply(z2, y2, bn.mean, bn.invstd, g, b, A.BN_EPS, 0, 1)
+            if apply:
+                o.bn_apply(z2, y2, bn.mean, bn.invstd, g, b, A.BN_EPS, 0, 1)
         else:
             o.bn_apply(z2, y2, mm, mv, g, b, A.BN_EPS, 1, 1)
 
-    def forward(self, pl, ctx, out, training=True, update_stats=False, sync=None, spec_only=False):
+    def forward(self, pl, ctx, out, training=True, update_stats=False, sync=None, spec_only=False, materialize=True):
         """ctx [B,T,ctxsize] -> out [B,T,O] (both contiguous device tensors).  training: BN uses batch statistics
         (all-reduced through `sync`); update_stats: also move the BN moving averages (generator step only).
         spec_only: evaluate the ctx trunk and the spectral branch only and leave the F0 / noise-mask columns of `out`
@@ -215,11 +217,21 @@ class Generator(object):
         # Spec: Dense projection, [B,T,S,1] map, pCNN2D stack, Conv2D(1)   (modeltts_common.py:95-101)
         o.gemm(lctx, p['g.spec.proj.kernel'], pl['s'], bias=p['g.spec.proj.bias'])
         amap = pl['s'].view(B, T, S, 1)
-        for i in range(a.gen_nbcnnlayers):
-            ws = o.conv2d(amap, p['g.spec.cnn%d.kernel' % i], pl['cv_z'][i], stats=training)
-            self._bn_fwd(pl['cv_z'][i].view(M * S, Fl), pl['cv_a'][i].view(M * S, Fl), pl['cv_bn'][i], training,
-                         update_stats, sync, ws=ws)
-            amap = pl['cv_a'][i]
+        L = a.gen_nbcnnlayers
+        pending = None      # BatchNorm of the previous layer still to be applied (on load) by the next convolution
+        for i in range(L):
+            ws = o.conv2d(amap, p['g.spec.cnn%d.kernel' % i], pl['cv_z'][i], stats=training, in_bn=pending)
+            # forward-only use (frozen generator of the critic step): nothing reads the activation map but the next
+            # convolution, which forms it on load -- it is written for the last layer only (input of the output Conv2D)
+            keep = materialize or not training or i == L - 1
+            bn = pl['cv_bn'][i]
+            self._bn_fwd(pl['cv_z'][i].view(M * S, Fl), pl['cv_a'][i].view(M * S, Fl), bn, training, update_stats, sync,
+                         ws=ws, apply=keep)
+            if keep:
+                pending, amap = None, pl['cv_a'][i]
+            else:
+                pending = (bn.mean, bn.invstd, p[bn.prefix + '.gamma'], p[bn.prefix + '.beta'], pl['cv_a'][i])
+                amap = pl['cv_z'][i]
         o.conv2d(amap, p['g.spec.out.kernel'], out[:, :, 1:1 + S].unsqueeze(-1), bias=p['g.spec.out.bias'])
         # NM: pFC x (L//2), Dense(sigmoid)   (modeltts_common.py:117-121)
         n2 = lctx

@@ -462,10 +462,12 @@ class CudaOps(object):
         self.gemm(xp.as_strided((B, T, W * CIN), (Tp * CIN, CIN, 1)), dz, dw.view(W * CIN, COUT), transA=True)
 
     # -- 2-D convolutions ------------------------------------------------------------------------------------
-    def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0, stats=False):
+    def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0, stats=False, in_bn=None):
         """y = epilogue(conv2d_same(x, w)); x [N,T,F,Cin], w [KH,KW,Cin,Cout] contiguous, y/aux [N,T,F,Cout] views.
         stats=True also returns the ReduceWorkspace holding the BatchNorm sums [sum y, sum y^2] of the (contiguous) output:
-        fused into the tensor-core kernel's epilogue where that kernel applies, a bn_stats() pass otherwise."""
+        fused into the tensor-core kernel's epilogue where that kernel applies, a bn_stats() pass otherwise.
+        in_bn = (mean, invstd, gamma, beta, scratch): x is a pre-BatchNorm map and the convolution reads LeakyReLU(BN(x)) --
+        formed on load by the tensor-core kernel (nothing is written), else materialised into `scratch` first."""
         N, T, F, CIN = x.shape
         KH, KW, ci, COUT = w.shape
         assert ci == CIN and tuple(y.shape) == (N, T, F, COUT) and w.is_contiguous()
@@ -480,20 +482,31 @@ class CudaOps(object):
             assert tuple(aux.shape) == tuple(y.shape)
             pa, ab, ap = _map4(aux)
         self._wrote(y)
-        if (self.nterms > 0 and self.conv2d_tc and self.lib.pctts_conv2d_tc_supported(F, CIN, COUT, KH, KW, pad_t, pad_f)
-                and not ((px | py | (pa or 0)) & 15) and not ((xp | yp | ap | xb | yb | ab) & 3)):
+        tc = (self.nterms > 0 and self.conv2d_tc and self.lib.pctts_conv2d_tc_supported(F, CIN, COUT, KH, KW, pad_t, pad_f)
+              and not ((px | py | (pa or 0)) & 15) and not ((xp | yp | ap | xb | yb | ab) & 3))
+        bnp = (None, None, None, None)
+        if in_bn is not None:
+            mean, invstd, gamma, beta, scratch = in_bn
+            if tc and self.fuse_bn_stats:
+                bnp = (mean.data_ptr(), invstd.data_ptr(), gamma.data_ptr(), beta.data_ptr())
+            else:
+                self.bn_apply(x.view(N * T * F, CIN), scratch.view(N * T * F, CIN), mean, invstd, gamma, beta, 0.0, 0, 1)
+                x = scratch
+                px, xb, xp = _map4(x)
+        if tc:
             # implicit GEMM on the tensor cores (4 -> 4 channels, 5x5): forward, data gradient (flipped kernels), GP tangent sweep
             if stats and self.fuse_bn_stats and y.is_contiguous():
                 ws = self.reduce_ws(N * T * F, COUT)
-                rc = self.lib.pctts_conv2d_tc_fwd_stats(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t,
-                                                        pad_f, xp, yp, ap, xb, yb, ab, flags, self.nterms, ws.ptr, self._stream())
+                rc = self.lib.pctts_conv2d_tc_fwd_fused(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t,
+                                                        pad_f, xp, yp, ap, xb, yb, ab, flags, self.nterms, bnp[0], bnp[1], bnp[2],
+                                                        bnp[3], ws.ptr, self._stream())
                 if rc != -2:      # PCTTS_EUNSUPPORTED: map too small for 148 partial slots
                     self.launches += 1      # conv + the second reduction stage
-                    self._ck(rc, 'pctts_conv2d_tc_fwd_stats')
+                    self._ck(rc, 'pctts_conv2d_tc_fwd_fused')
                     return ws
-            self._ck(self.lib.pctts_conv2d_tc_fwd(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
-                                                  xp, yp, ap, xb, yb, ab, flags, self.nterms, self._stream()),
-                     'pctts_conv2d_tc_fwd')
+            self._ck(self.lib.pctts_conv2d_tc_fwd_fused(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
+                                                        xp, yp, ap, xb, yb, ab, flags, self.nterms, bnp[0], bnp[1], bnp[2], bnp[3],
+                                                        None, self._stream()), 'pctts_conv2d_tc_fwd_fused')
         else:
             self._ck(self.lib.pctts_conv2d_fwd(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
                                                xp, yp, ap, xb, yb, ab, flags, self._stream()), 'pctts_conv2d_fwd')

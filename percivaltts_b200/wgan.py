@@ -84,7 +84,7 @@ class WGANStepper(object):
             self.C.forward_ctx(cpl, X)
         # frozen generator, learning phase 1: batch statistics, no moving-average update (:121-128)
         self.G.forward(gpl, X, bf['fake'], training=True, update_stats=False, sync=sync,
-                       spec_only=not self.critic_step_full_generator)
+                       spec_only=not self.critic_step_full_generator, materialize=False)
         if alpha is None:
             o.uniform(bf['alpha'], self.seed, self.counter)
             alpha = bf['alpha']

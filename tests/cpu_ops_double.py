@@ -128,7 +128,12 @@ class CpuOpsDouble(object):
         xp = F.pad(x.permute(0, 3, 1, 2), (pad_f, KW - 1 - pad_f, pad_t, KH - 1 - pad_t))
         return F.conv2d(xp, w.permute(3, 2, 0, 1)).permute(0, 2, 3, 1)
 
-    def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0, stats=False):
+    def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0, stats=False, in_bn=None):
+        if in_bn is not None:
+            mean, invstd, gamma, beta, scratch = in_bn
+            C = x.shape[-1]
+            self.bn_apply(x.reshape(-1, C), scratch.view(-1, C), mean, invstd, gamma, beta, 0.0, 0, 1)
+            x = scratch
         self.launches += 1
         KH, KW = w.shape[0], w.shape[1]
         pad_t, pad_f = ((KH - 1) // 2, (KW - 1) // 2) if pad is None else pad

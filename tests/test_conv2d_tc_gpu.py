@@ -113,3 +113,22 @@ def test_fused_batchnorm_statistics(cuda_ops, N, T, F):
     yd = y0.double().view(-1, 4)
     ref = torch.stack([yd.sum(0), (yd * yd).sum(0)])
     assert float(((got - ref).abs() / ref.abs().clamp_min(1e-30)).max()) < 1e-10
+
+
+@pytest.mark.parametrize('N,T,F', [(10, 400, 129), (2, 37, 30)])
+def test_fused_input_batchnorm(cuda_ops, N, T, F):
+    """LeakyReLU(BN(x)) formed on load by the convolution (in_bn) equals the convolution of the materialised activation map
+    bit for bit (same arithmetic, same order), zero padding included."""
+    x, w = dev(rnd(N, T, F, 4)), dev(rnd(5, 5, 4, 4, seed=1) * 0.2)
+    mean, invstd = dev(rnd(4, seed=2) * 0.3), dev(rnd(4, seed=3).abs() + 0.5)
+    gamma, beta = dev(rnd(4, seed=4)), dev(rnd(4, seed=5) + 0.7)      # beta != 0: a transformed zero pad would show
+    act = torch.empty_like(x)
+    cuda_ops.bn_apply(x.view(-1, 4), act.view(-1, 4), mean, invstd, gamma, beta, 0.0, 0, 1)
+    y0, y1 = torch.empty_like(x), torch.empty_like(x)
+    cuda_ops.conv2d(act, w, y0)
+    scratch = torch.full_like(x, float('nan'))
+    ws = cuda_ops.conv2d(x, w, y1, stats=True, in_bn=(mean, invstd, gamma, beta, scratch))
+    assert torch.equal(y0, y1)
+    assert bool(torch.isnan(scratch).all())          # nothing was materialised
+    want = cuda_ops.bn_stats(y0.view(-1, 4)).sums.clone()
+    assert float(((ws.sums - want).abs() / want.abs().clamp_min(1e-30)).max()) < 1e-12
