@@ -317,14 +317,15 @@ def run_b200(args):
     achieved = flops / (t_conv1d * 1e-3) / 1e12
     products = max(ops.nterms, 1)
     roofline = {'bound': 'tensor',
-                'kernel': 'gemm_tc_kernel (Conv1D k=21 425->256 forward as virtual-im2col tcgen05 GEMM, M=4000 N=256 K=8925)',
+                'kernel': 'gemm_tc_kernel<128,3> + tc_splitk_reduce (Conv1D k=21 425->256 forward as virtual-im2col tcgen05 GEMM, M=4000 N=256 K=8925, two K halves per 128x128 tile)',
                 'achieved': achieved, 'peak': peak_tf, 'unit': 'TFLOP/s', 'frac': achieved / peak_tf,
                 'peak_source': 'MEASURED_PEAKS.json bf16_tflops (burst)' if peaks else 'fallback 1590 TFLOP/s',
-                # dram__bytes_read.sum + dram__bytes_write.sum of this launch from the ncu --set full capture
-                # profiles/r01_e_ncu_full_conv1d_gemm_tc.txt (24.625 MB read = the bf16 operand planes, 10.9 MB activations +
-                # 13.7 MB weights, each read once; the 4.1 MB fp32 output stays in L2); valid for the fp32 (3-plane) mode
-                'traffic': 24.626e6 if ops.precision == 'fp32' else None, 'traffic_unit': 'B/launch',
-                'ncu_tensor_pipe_pct': 48.5 if ops.precision == 'fp32' else None,
+                # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture
+                # profiles/r01_i_ncu_full_conv1d_gemm_tc.txt: gemm_tc_kernel<128,3> 24.63 MB read (the bf16 operand planes, 10.9 MB
+                # activations + 13.7 MB weights, each read once) + the split-K reduce 8.20 MB (cold-cache replay: in the step the
+                # partials are still in L2); the 4.1 MB fp32 output stays in L2.  Valid for the fp32 (3-plane) mode.
+                'traffic': 32.83e6 if ops.precision == 'fp32' else None, 'traffic_unit': 'B/launch',
+                'ncu_tensor_pipe_pct': 70.7 if ops.precision == 'fp32' else None,
                 'kernel_ms': t_conv1d, 'flop_per_launch': flops,
                 'precision': ops.precision, 'tensor_products_per_flop': products,
                 'tensor_pipe_frac': products * achieved / peak_tf,
