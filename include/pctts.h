@@ -152,7 +152,7 @@ int pctts_lstm_bwd(const float* dhout, const float* U0, const float* U1, const f
 /* ---- WGAN-GP pieces (optimizertts_wgan.py:44-79) ------------------------------------------------------------------------ */
 /* s0 [3B,T,S] = [real | fake | alpha*real+(1-alpha)*fake] restricted to feature columns off..off+S-1  (:44-51, critic :58) */
 int pctts_critic_pack_inputs(const float* real, const float* fake, const float* alpha, float* s0, int B, int T, int O, int S,
-                             int off, void* stream);
+                             int off, int skip_real, void* stream);   /* skip_real: the first block is already in place */
 int pctts_fill_segments(float* p, long n0, float v0, long n1, float v1, long n2, float v2, void* stream);
 int pctts_sum_scaled(const float* x, long n, double scale, float* losses, int slot, void* stream);   /* wasserstein_loss :70-71 */
 int pctts_gp_norms(const float* g, int B, long per_sample, float* ss, void* stream);                 /* :59-64 */

@@ -19,7 +19,8 @@ inline int ew_blocks(long n, int per_thread = 4) {
 // S0[0:B] = real[:,:,off:off+S], S0[B:2B] = fake[...], S0[2B:3B] = alpha*real + (1-alpha)*fake   (spec columns only:
 // the critic reads nothing else from its feature input, networks_critic.py:58)
 __global__ void critic_pack_kernel(const float* __restrict__ real, const float* __restrict__ fake,
-                                   const float* __restrict__ alpha, float* __restrict__ s0, int B, int T, int O, int S, int off) {
+                                   const float* __restrict__ alpha, float* __restrict__ s0, int B, int T, int O, int S, int off,
+                                   int skip_real) {
     pdl_entry();
     const long per = (long)B * T * S;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < per; i += (long)gridDim.x * blockDim.x) {
@@ -28,7 +29,7 @@ __global__ void critic_pack_kernel(const float* __restrict__ real, const float* 
         const int b = (int)(bt / T);
         const float r = real[bt * O + off + f], k = fake[bt * O + off + f];
         const float a = alpha[b];
-        s0[i] = r;
+        if (!skip_real) s0[i] = r;
         s0[per + i] = k;
         s0[2 * per + i] = a * r + (1.f - a) * k;
     }
@@ -219,11 +220,11 @@ __global__ void incr64_kernel(unsigned long long* c) {
 }  // namespace
 
 extern "C" int pctts_critic_pack_inputs(const float* real, const float* fake, const float* alpha, float* s0, int B, int T, int O,
-                                        int S, int off, void* stream) {
+                                        int S, int off, int skip_real, void* stream) {
     if (!real || !fake || !alpha || !s0 || off < 0 || off + S > O) return PCTTS_EINVAL;
     const long per = (long)B * T * S;
     if (per == 0) return PCTTS_OK;
-    pctts_launch(critic_pack_kernel, ew_blocks(per), ET, 0, (cudaStream_t)stream, real, fake, alpha, s0, B, T, O, S, off);
+    pctts_launch(critic_pack_kernel, ew_blocks(per), ET, 0, (cudaStream_t)stream, real, fake, alpha, s0, B, T, O, S, off, skip_real);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

@@ -438,22 +438,28 @@ class Critic(object):
         o.gemm(x2, w0[SF:], pl['ctxterm'], bias=p['c.post.fc0.bias'])
         pl['ctx_in'], pl['ctx_last'] = ctx, x2
 
-    def forward_spec(self, pl, s0):
-        """Spectral branch on all applications (networks_critic.py:58-70) and the post layers; needs forward_ctx()."""
+    def forward_spec(self, pl, s0, samples=None):
+        """Spectral branch (networks_critic.py:58-70) and the post layers on the applications `samples` (a slice over the
+        napp*B sample axis, whole applications; default all); needs forward_ctx()."""
         o, a, p = self.ops, self.a, self.params.p
-        nM = pl['nM']
+        T, nM = pl['T'], pl['nM']
         S, Fl, L = a.spec_size, a.gen_nbfilters, a.gen_nbcnnlayers
         SF = S * Fl
         w0 = p['c.post.fc0.kernel']
-        amap = s0
+        if samples is None or (samples.start == 0 and samples.stop == pl['nB']):
+            sm, r = slice(None), slice(None)
+        else:
+            assert samples.start % pl['B'] == 0 and samples.stop % pl['B'] == 0
+            sm, r = samples, slice(samples.start * T, samples.stop * T)
+        amap = s0[sm]
         for i in range(L):
-            o.conv2d(amap, p['c.spec.cnn%d.kernel' % i], pl['a'][i], bias=p['c.spec.cnn%d.bias' % i], flags=EPI_LRELU)
-            amap = pl['a'][i]
+            o.conv2d(amap, p['c.spec.cnn%d.kernel' % i], pl['a'][i][sm], bias=p['c.spec.cnn%d.bias' % i], flags=EPI_LRELU)
+            amap = pl['a'][i][sm]
         # post layers (networks_critic.py:89-96); concat([spec, ctx]) . W0 = spec . W0[:SF] + ctx . W0[SF:]
-        o.gemm(amap.view(nM, SF), w0[:SF], pl['p'][0], addmod=pl['ctxterm'], flags=EPI_LRELU)
+        o.gemm(pl['a'][L - 1].view(nM, SF)[r], w0[:SF], pl['p'][0][r], addmod=pl['ctxterm'], flags=EPI_LRELU)
         for i in (1, 2):
-            o.gemm(pl['p'][i - 1], p['c.post.fc%d.kernel' % i], pl['p'][i], bias=p['c.post.fc%d.bias' % i], flags=EPI_LRELU)
-        o.gemm(pl['p'][2], p['c.out.kernel'], pl['d'], bias=p['c.out.bias'])
+            o.gemm(pl['p'][i - 1][r], p['c.post.fc%d.kernel' % i], pl['p'][i][r], bias=p['c.post.fc%d.bias' % i], flags=EPI_LRELU)
+        o.gemm(pl['p'][2][r], p['c.out.kernel'], pl['d'][r], bias=p['c.out.bias'])
         pl['s0'] = s0
         return pl['d']
 

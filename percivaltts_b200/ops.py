@@ -626,12 +626,12 @@ class CudaOps(object):
                                          dhout.shape[2], cluster_size, batch_chunk, self._stream()), 'pctts_lstm_bwd')
 
     # -- WGAN-GP pieces --------------------------------------------------------------------------------------
-    def critic_pack_inputs(self, real, fake, alpha, s0, S, off):
+    def critic_pack_inputs(self, real, fake, alpha, s0, S, off, skip_real=False):
         B, T, O = real.shape
         assert real.is_contiguous() and fake.is_contiguous() and s0.is_contiguous() and tuple(s0.shape) == (3 * B, T, S)
         self._wrote(s0)
         self._ck(self.lib.pctts_critic_pack_inputs(real.data_ptr(), fake.data_ptr(), alpha.data_ptr(), s0.data_ptr(), B, T, O, S,
-                                                   off, self._stream()), 'pctts_critic_pack_inputs')
+                                                   off, int(skip_real), self._stream()), 'pctts_critic_pack_inputs')
 
     def fill_segments(self, p, n0, v0, n1=0, v1=0.0, n2=0, v2=0.0):
         assert p.is_contiguous() and p.numel() == n0 + n1 + n2

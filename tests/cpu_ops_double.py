@@ -284,12 +284,13 @@ class CpuOpsDouble(object):
                 dhrec = dzt @ U[d].t()
 
     # ---- WGAN-GP pieces --------------------------------------------------------------------------------------
-    def critic_pack_inputs(self, real, fake, alpha, s0, S, off):
+    def critic_pack_inputs(self, real, fake, alpha, s0, S, off, skip_real=False):
         self.launches += 1
         B = real.shape[0]
         r, k = real[:, :, off:off + S], fake[:, :, off:off + S]
         a = alpha.reshape(B, 1, 1)
-        s0[0:B] = r
+        if not skip_real:
+            s0[0:B] = r
         s0[B:2 * B] = k
         s0[2 * B:] = a * r + (1 - a) * k
 
