@@ -181,6 +181,15 @@ int pctts_pml_linbnd2fwbnd(const float* in, const int* idx, const float* wgt, fl
 int pctts_pml_fwbnd2linbnd(const float* in, const int* idx, const float* wgt, float* out, long T, int K, int nbins, int smooth,
                            int do_exp, void* stream);
 
+/* ---- data-parallel exchange of the sync-BatchNorm sums over NVLink peer memory ------------------------------ */
+/* One-shot all-reduce (sum, rank order => bit-identical on every rank) of n <= nmax doubles: every rank owns a zero-initialised
+ * symmetric buffer of pctts_peer_allreduce_bytes(world, nmax) bytes mapped into all peers; peer_bases (HOST array) holds the
+ * address of rank r's buffer in this process.  All ranks must issue the same calls in the same order.  *err (device) becomes 1
+ * if a peer did not arrive within ~2 s.  Asynchronous, capturable. */
+long pctts_peer_allreduce_bytes(int world, int nmax);
+int pctts_peer_allreduce_f64(double* x, int n, const unsigned long long* peer_bases, int rank, int world, int nmax, int* err,
+                             void* stream);
+
 #ifdef __cplusplus
 }
 #endif

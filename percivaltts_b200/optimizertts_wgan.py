@@ -88,6 +88,7 @@ class OptimizerTTSWGAN(optimizertts.OptimizerTTS):
                 from .parallel import DistSync
                 sync = DistSync()
                 sync.warmup(ops.device)
+                sync.enable_peer(ops.device)
         self.sync = sync
         generator = self._model.kerasmodel.device_module(ops)
         critic = self.critic.kerasmodel.device_module(ops)

@@ -8,10 +8,15 @@ against the single-device step on the concatenated batch:
     sees the statistics of the whole batch, as the reference does,
   * the flat critic / generator gradient buffers are all-reduced (SUM) right before Adam.
 """
+import ctypes
 import os
 
 import torch
 import torch.distributed as dist
+
+from . import _lib
+
+PEER_NMAX = 1024      # doubles per exchange through peer memory ([2, C] BatchNorm sums, C <= 512)
 
 
 class DistSync(object):
@@ -22,12 +27,67 @@ class DistSync(object):
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.calls = 0
+        self.peer_calls = 0
+        self._peer = None
+        self.peer_error = None
 
     def allreduce(self, t):
         if self.world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+            if self._peer is not None and t.dtype == torch.float64 and t.is_contiguous() and 0 < t.numel() <= PEER_NMAX:
+                # sync-BatchNorm sums: one-shot exchange through NVLink peer memory (csrc/peer.cu), not an NCCL launch
+                lib, bases, err = self._peer
+                _lib.check(lib.pctts_peer_allreduce_f64(t.data_ptr(), t.numel(), ctypes.cast(bases, ctypes.c_void_p), self.rank,
+                                                        self.world, PEER_NMAX, err.data_ptr(),
+                                                        torch.cuda.current_stream(t.device).cuda_stream),
+                           'pctts_peer_allreduce_f64')
+                self.peer_calls += 1
+            else:
+                dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
             self.calls += 1
         return t
+
+    def enable_peer(self, device):
+        """Map a symmetric buffer across the ranks (torch.distributed._symmetric_memory over NVLink) for the small fp64
+        exchanges; returns False (and NCCL keeps doing them) when the platform cannot.  Collective: every rank calls it."""
+        if self.world < 2 or device.type != 'cuda' or os.environ.get('PCTTS_PEER_AR', '1') == '0':
+            return False
+        ok = torch.zeros(1, device=device)
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            lib = _lib.load()
+            nbytes = lib.pctts_peer_allreduce_bytes(self.world, PEER_NMAX)
+            buf = symm_mem.empty((nbytes + 7) // 8, dtype=torch.float64, device=device)
+            group = self.group if self.group is not None else dist.group.WORLD
+            hdl = symm_mem.rendezvous(buf, group.group_name)
+            buf.zero_()
+            bases = (ctypes.c_ulonglong * self.world)(*[int(p) for p in hdl.buffer_ptrs])
+            err = torch.zeros(1, dtype=torch.int32, device=device)
+            self._peer_keep = (buf, hdl)
+            peer = (lib, bases, err)
+            ok.fill_(1.0)
+        except Exception as e:      # noqa: BLE001 -- any failure here means "use NCCL"
+            peer = None
+            self.peer_error = repr(e)
+        torch.cuda.synchronize(device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)      # all ranks or none (also the barrier after zeroing)
+        if float(ok) < 1.0:
+            return False
+        self._peer = peer
+        # first exchange outside any capture: checks the mapping end to end
+        t = torch.full((4,), float(self.rank + 1), dtype=torch.float64, device=device)
+        self.allreduce(t)
+        torch.cuda.synchronize(device)
+        good = bool((t == self.world * (self.world + 1) / 2.0).all()) and int(peer[2]) == 0
+        flag = torch.tensor([1.0 if good else 0.0], device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if float(flag) < 1.0:
+            self._peer = None
+            return False
+        return True
+
+    def peer_failed(self):
+        """True if an exchange timed out waiting for a peer (the step's results are then invalid)."""
+        return self._peer is not None and int(self._peer[2]) != 0
 
     def warmup(self, device):
         """First collective outside any CUDA-graph capture (communicator setup is not capturable)."""
@@ -58,6 +118,7 @@ def init_from_env(backend=None):
         dist.init_process_group(backend or ('nccl' if device.type == 'cuda' else 'gloo'), **kw)
     sync = DistSync()
     sync.warmup(device)
+    sync.enable_peer(device)
     return sync, device
 
 

@@ -23,6 +23,7 @@ def main():
     faulthandler.dump_traceback_later(90, exit=True)
     sync, device = parallel.init_from_env()
     rank, world = sync.rank, sync.world
+    print('rank %d: peer-memory exchange %s' % (rank, 'on' if sync._peer is not None else 'off (%s)' % sync.peer_error), flush=True)
     ops = CudaOps()
     ao, a = O.Arch(**KW), A.Arch(**KW)
     wg = O.perturb_params(O.init_params(O.generator_param_shapes(ao), seed=1))
