@@ -307,3 +307,27 @@ def test_small_movers_and_uniform(cuda_ops):
     assert int(counter.item()) == 2
     assert float(u.min()) >= 0.0 and float(u.max()) < 1.0
     assert abs(float(u.mean()) - 0.5) < 0.03 and not torch.equal(u, u1)
+
+
+def test_peer_allreduce_single_rank_protocol(cuda_ops):
+    """csrc/peer.cu with world = 1 (the rank is its own peer): the publish / flag / wait / rank-ordered-sum protocol runs on one
+    GPU -- values come back unchanged, the sequence number advances, both parity slots get used, no time-out is raised.  (The
+    multi-rank exchange is checked against NCCL semantics by tools/dp_gpu_check.py on 2 GPUs.)"""
+    import ctypes
+    lib = cuda_ops.lib
+    nmax = 64
+    nbytes = lib.pctts_peer_allreduce_bytes(1, nmax)
+    assert nbytes > 0 and lib.pctts_peer_allreduce_bytes(17, nmax) < 0
+    buf = torch.zeros((nbytes + 7) // 8, dtype=torch.float64, device='cuda')
+    bases = (ctypes.c_ulonglong * 1)(buf.data_ptr())
+    err = torch.zeros(1, dtype=torch.int32, device='cuda')
+    st = torch.cuda.current_stream().cuda_stream
+    for k in range(5):
+        x = torch.arange(37, dtype=torch.float64, device='cuda') * (k + 1) + 0.25
+        want = x.clone()
+        rc = lib.pctts_peer_allreduce_f64(x.data_ptr(), 37, ctypes.cast(bases, ctypes.c_void_p), 0, 1, nmax, err.data_ptr(), st)
+        assert rc == 0
+        torch.cuda.synchronize()
+        assert torch.equal(x, want) and int(err) == 0
+        assert int(buf.view(torch.int64)[0]) == k + 1          # sequence number
+    assert lib.pctts_peer_allreduce_f64(x.data_ptr(), nmax + 1, ctypes.cast(bases, ctypes.c_void_p), 0, 1, nmax, err.data_ptr(), st) == -1
