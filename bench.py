@@ -159,7 +159,8 @@ def cpu_baseline_cycle(threads):
 
 def run_reference(args):
     """--impl reference: the reference's TensorFlow-1.9 / python-2 step cannot run here, so the timed CPU arm
-    is the oracle port with all host threads.  Each step is a bounded sample: 2 of the 10 utterances of a batch."""
+    is the oracle port with all host threads.  A step is one train_on_batch on the full B=10 batch (~0.7 s on 16 cores), the
+    same unit as the B200 arm; only a run asked for more than 150 steps drops to 4 utterances per step to stay within minutes."""
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
@@ -171,7 +172,7 @@ def run_reference(args):
     tr = O.OracleTrainer(a, O.init_params(O.generator_param_shapes(a), seed=1), O.init_params(O.critic_param_shapes(a), seed=2),
                          dtype=torch.float32)
     tr.generator_updates = 25
-    Bs = 2
+    Bs = B_PER_GPU if args.steps <= 150 else 4
     X, Y, alpha = O.synthetic_batch(a, Bs, T_FRAMES, seed=123)
     for i in range(max(args.warmup, 1)):
         tr.train_on_batch(i + 1, X, Y, alpha)
@@ -180,7 +181,7 @@ def run_reference(args):
         tr.train_on_batch(i, X, Y, alpha)
     dt = time.perf_counter() - t0
     value = args.steps * Bs * T_FRAMES / dt
-    sample = '%d steps of train_on_batch on 2 of the 10 utterances per batch (T=400), generator every 5th step' % args.steps
+    sample = '%d steps of train_on_batch on %d of the 10 utterances per batch (T=400), generator every 5th step' % (args.steps, Bs)
     print(json.dumps({
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': 1e3 * dt / args.steps, 'higher_is_better': True, 'scaling': 'weak',
