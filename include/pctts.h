@@ -65,6 +65,8 @@ int pctts_split_bf16(const float* src, long ld, int seg, long segstride, long ro
                      long part_stride, int parts, void* stream);
 int pctts_gemm_tc_splits(int M, int N, int K);                 /* host call: recommended split-K factor (1 = none) */
 long pctts_gemm_tc_workspace(int M, int N, int splits);        /* host call: floats of split-K workspace */
+long pctts_gemm_tc_tail_workspace(int M, int N, int K);        /* host call: floats with which a splits = 1 call cuts the m-tiles of a
+                                                                  partly filled last wave of CTAs along K (0: no use for it) */
 int pctts_gemm_tc_set_trace(void* buf);  /* developer probe: 64*8 int64 clock stamps of CTA (0,0,0) of the next launches; NULL = off */
 /* C[M,N] = epilogue(alpha * op(A) op(B)) from the shadows of the STORED matrices (A: [M,K], or [K,M] when transA; B: [K,N], or
  * [N,K] when transB); C / aux fp32 with row pitch ldc; flags as for pctts_gemm_f32 except ATOMIC; splits > 1 needs the workspace
@@ -78,9 +80,11 @@ long pctts_conv1d_tc_fwd_workspace(int B, int T, int W, int CIN, int COUT);   /*
 int pctts_conv1d_tc_fwd(const void* xsh, long ldx, long x_part_stride, const void* wsh, long ldw, long w_part_stride, float* y,
                         long ldy, int B, int T, int W, int CIN, int COUT, const float* bias, const float* aux, int flags, int nterms,
                         float* workspace, void* stream);
-/* dw[W*CIN, COUT] (+)= sum_{b,t} xpad[b,t+w,c] dz[b,t,n];  dzsh = shadow of dz [B*T, COUT] */
+/* dw[W*CIN, COUT] (+)= sum_{b,t} xpad[b,t+w,c] dz[b,t,n];  dzsh = shadow of dz [B*T, COUT]; workspace (or NULL): the floats
+ * pctts_conv1d_tc_wgrad_workspace asks for (tail split of the last wave of tiles, see pctts_gemm_tc_tail_workspace) */
+long pctts_conv1d_tc_wgrad_workspace(int B, int T, int W, int CIN, int COUT);
 int pctts_conv1d_tc_wgrad(const void* xsh, long ldx, long x_part_stride, const void* dzsh, long lddz, long dz_part_stride, float* dw,
-                          int B, int T, int W, int CIN, int COUT, int accumulate, int nterms, void* stream);
+                          int B, int T, int W, int CIN, int COUT, int accumulate, int nterms, float* workspace, void* stream);
 
 /* ---- Conv2D 'same', stride 1, NHWC, HWIO (networktts.py:122-126; modeltts_common.py:98,100; networks_critic.py:67) ------ */
 /* y[n,t,f,:] = epilogue(sum_{kt,kf,ci} x[n,t+kt-pad_t,f+kf-pad_f,ci] w[kt,kf,ci,:]).  xpitch/ypitch/auxpitch = floats between

@@ -185,21 +185,21 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
             }
         }
     };
+    if (p.trace && blockIdx.x == 0 && tid == 0) p.trace[31 * 8 + 3] = clock64();
     pdl_wait();
-    // the 400 kernel weights arrive with ONE round trip (the Toeplitz build below used to fetch them in ~6 dependent __ldg
-    // rounds per thread: 4.6 k cycles of prologue per launch, measured with the clock trace)
     __shared__ float wsm[KT * KW5 * 16];
-    if (tid < KT * KW5 * 16) wsm[tid] = __ldg(p.w + tid);
     float4 ca[C2_UNR], cb[C2_UNR], na[C2_UNR], nb[C2_UNR];
     uint32_t cmask = 0u, nmask = 0u;
-    if (warp < C2_PW && nitems > 0) issue(0, ca, cb, cmask);   // first tile's loads fly while the weight operand is built
     // fused BatchNorm + LeakyReLU of the input (same expression as bn_apply_kernel); zero padding stays zero
     const bool bn_in = p.bn_mean != nullptr;
     float bm[4] = {0.f, 0.f, 0.f, 0.f}, bi[4] = {1.f, 1.f, 1.f, 1.f}, bg[4] = {1.f, 1.f, 1.f, 1.f}, bb[4] = {0.f, 0.f, 0.f, 0.f};
-    if (bn_in) {
+    if (warp < C2_PW) {
+        if (nitems > 0) issue(0, ca, cb, cmask);      // the first tile's loads fly during the set-up below
+        if (bn_in) {
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
-            bm[c] = __ldg(p.bn_mean + c), bi[c] = __ldg(p.bn_invstd + c), bg[c] = __ldg(p.bn_gamma + c), bb[c] = __ldg(p.bn_beta + c);
+            for (int c = 0; c < 4; ++c)
+                bm[c] = __ldg(p.bn_mean + c), bi[c] = __ldg(p.bn_invstd + c), bg[c] = __ldg(p.bn_gamma + c), bb[c] = __ldg(p.bn_beta + c);
+        }
     }
     auto bn_act = [&](float4& v) {
         v.x = lrelu_f((v.x - bm[0]) * bi[0] * bg[0] + bb[0]);
@@ -207,32 +207,47 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
         v.z = lrelu_f((v.z - bm[2]) * bi[2] * bg[2] + bb[2]);
         v.w = lrelu_f((v.w - bm[3]) * bi[3] * bg[3] + bb[3]);
     };
-    __syncthreads();
-
-    // ---- block-Toeplitz weight operand, all planes: Bmat[mma j = (kt,h)][chunk c][row n = 16*plane + 4*jo + co][8 k]
-    {
-        __nv_bfloat16* B = reinterpret_cast<__nv_bfloat16*>(smem_al);
-        const int total = NMMA * 2 * 16 * 8;          // (j, c, n16, kk)
-        for (int i = tid; i < total; i += C2_THREADS) {
-            const int kk = i & 7, n16 = (i >> 3) & 15, c = (i >> 7) & 1, j = i >> 8;
-            const int kt = j >> 1, h = j & 1;
-            const int k16 = c * 8 + kk, u = 4 * h + (k16 >> 2), ci = k16 & 3;
-            const int jo = n16 >> 2, co = n16 & 3, kf = u - jo;
-            float v = (kf >= 0 && kf < KW5) ? wsm[((kt * KW5 + kf) * 4 + ci) * 4 + co] : 0.f;
-#pragma unroll
-            for (int pl = 0; pl < PARTS; ++pl) {
-                const __nv_bfloat16 hv = __float2bfloat16_rn(v);
-                B[(size_t)j * (L::b_mma / 2) + (size_t)c * (L::b_chunk / 2) + (size_t)(16 * pl + n16) * 8 + kk] = hv;
-                v -= __bfloat162float(hv);
-            }
-        }
-    }
-    fence_proxy_async();
     tc_fence_before();
-    __syncthreads();
+    __syncthreads();      // barriers initialised, TMEM base published
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
-    if (p.trace && blockIdx.x == 0 && tid == 0) p.trace[31 * 8 + 1] = clock64();
+    if (p.trace && blockIdx.x == 0 && tid == 0) p.trace[31 * 8 + 4] = clock64();
+
+    // The producers go straight to their first tile.  Meanwhile the MMA and epilogue warps (160 threads, idle until that tile is
+    // filled) fetch the 400 kernel weights in ONE round trip and build the block-Toeplitz weight operand, all planes:
+    // Bmat[mma j = (kt,h)][chunk c][row n = 16*plane + 4*jo + co][8 k], one 16-byte row per thread and plane.  (Built by all
+    // 416 threads in front of the roles, the operand kept the first MMA 9.8 k cycles away from kernel entry: clock trace.)
+    if (warp >= C2_PW) {
+        constexpr int NB_THREADS = C2_THREADS - C2_PROD;
+        const int bt = tid - C2_PROD;
+        for (int i = bt; i < KT * KW5 * 16; i += NB_THREADS) wsm[i] = __ldg(p.w + i);
+        asm volatile("bar.sync 2, %0;" ::"n"(NB_THREADS) : "memory");
+        for (int e = bt; e < NMMA * 2 * 16; e += NB_THREADS) {
+            const int n16 = e & 15, c = (e >> 4) & 1, j = e >> 5;
+            const int kt = j >> 1, h = j & 1, jo = n16 >> 2, co = n16 & 3;
+            float v[8];
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk) {
+                const int u = 4 * h + 2 * c + (kk >> 2), ci = kk & 3, kf = u - jo;
+                v[kk] = (kf >= 0 && kf < KW5) ? wsm[((kt * KW5 + kf) * 4 + ci) * 4 + co] : 0.f;
+            }
+            uint8_t* const dst = smem_al + (size_t)j * L::b_mma + (size_t)c * L::b_chunk + (size_t)n16 * 16;
+#pragma unroll
+            for (int pl = 0; pl < PARTS; ++pl) {
+                uint32_t w4[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const __nv_bfloat16 lo = __float2bfloat16_rn(v[2 * i]), hi = __float2bfloat16_rn(v[2 * i + 1]);
+                    w4[i] = pack_bf16(lo, hi);
+                    v[2 * i] -= __bfloat162float(lo), v[2 * i + 1] -= __bfloat162float(hi);
+                }
+                *reinterpret_cast<uint4*>(dst + (size_t)pl * 16 * 16) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+            }
+        }
+        fence_proxy_async();
+        asm volatile("bar.sync 2, %0;" ::"n"(NB_THREADS) : "memory");
+        if (p.trace && blockIdx.x == 0 && tid == C2_PROD) p.trace[31 * 8 + 1] = clock64();
+    }
 
     if (warp < C2_PW) {
         // ------------------------------------------------ producers ------------------------------------------------

@@ -64,8 +64,13 @@ struct Params {
     const float* addmod;
     int addrows;
     int flags;
-    float* partial;   // split-K: raw sums, plane z at partial + z * crows * N (dense rows of N floats)
+    float* partial;   // split-K: raw sums, plane z at partial + z * prows * N (dense rows of N floats, row = crow - prow0)
     long crows;
+    // tail split (wave quantisation): the first tail_dp m-tiles run over the whole K range and store directly; every later
+    // m-tile is cut into tail_splits K ranges whose raw sums go to `partial` (rows prow0.. of C, prows of them).  Plain
+    // split-K is tail_splits = 0 with blockIdx.z as the split index, prow0 = 0, prows = crows.
+    int tail_dp = 0, tail_splits = 0;
+    long prow0 = 0, prows = -1;   // prows < 0: filled in by launch_tc (= crows)
 };
 
 __device__ __forceinline__ void coords(const Geom& g, int t, int kb_lo, int kb_hi, int (&c)[3]) {
@@ -96,9 +101,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool tr0 = p.trace && (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
     if (tr0 && threadIdx.x == 0) p.trace[3] = clock64();
-    const int nt = blockIdx.x, mt = blockIdx.y;
-    const int kb_begin = blockIdx.z * p.kb_per_split;
-    const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
+    const int nt = blockIdx.x;
+    int mt = blockIdx.y, zsplit = blockIdx.z;
+    float* part = p.partial;
+    int kb_begin, kb_end;
+    if (p.tail_splits > 0) {
+        if (mt < p.tail_dp) {
+            kb_begin = 0, kb_end = p.num_kb, part = nullptr;
+        } else {
+            const int j = mt - p.tail_dp;
+            mt = p.tail_dp + j / p.tail_splits;
+            zsplit = j - (mt - p.tail_dp) * p.tail_splits;
+            kb_begin = zsplit * p.kb_per_split;
+            kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
+        }
+    } else {
+        kb_begin = zsplit * p.kb_per_split;
+        kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
+    }
     const int nkb = kb_end - kb_begin;
     const int CH = p.chunk_kb;
     const int nchunks = (nkb + CH - 1) / CH;
@@ -295,15 +315,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         if (nval > 0) {
             const bool full4 = nval >= 4;
             float bias4[4] = {0.f, 0.f, 0.f, 0.f};
-            if (flags & PCTTS_EPI_BIAS) {
+            if ((flags & PCTTS_EPI_BIAS) && !part) {     // raw sums go to the split-K planes; the reduce adds the bias once
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
                     if (j < nval) bias4[j] = __ldg(p.bias + nb + j);
             }
             const float alpha = p.alpha;
-            const long ldo = p.partial ? (long)p.N : p.ldc;
-            float* const obase = p.partial ? p.partial + (long)blockIdx.z * p.crows * p.N + nb : p.C + nb;
-            const int eflags = p.partial ? 0 : flags;
+            const long ldo = part ? (long)p.N : p.ldc;
+            float* const obase = part ? part + ((long)zsplit * p.prows - p.prow0) * p.N + nb : p.C + nb;
+            const int eflags = part ? 0 : flags;
             const bool ovec = full4 && ((ldo & 3) == 0) && ((((uintptr_t)obase) & 15) == 0);
 #pragma unroll 1
             for (int row = et / V; row < BM; row += RSTEP) {
@@ -319,7 +339,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     for (int j = 0; j < 4; ++j) {
                         if (j < nval) {
                             float y = x[j];
-                            if (!p.partial) y *= alpha;
+                            if (!part) y *= alpha;
                             y += bias4[j];
                             if (eflags & PCTTS_EPI_ADDMOD) y += __ldg(addp + j);
                             if (eflags & PCTTS_EPI_LRELU) y = lrelu_f(y);
@@ -427,6 +447,50 @@ int pick_bn(int m_tiles, int N) {
     return t128 >= 100 ? 128 : 64;
 }
 
+// Tail split against wave quantisation: with more output tiles than SMs, the tiles of the full waves run as they are and the
+// m-tiles of the last, partly filled wave are cut along K so that their pieces fill the machine once more (e.g. the Conv1D
+// weight gradient: 168 tiles of 70 k-blocks = 2 waves for 1.14 waves of work -> 148 tiles + 20 tiles x 7 ranges of 10).
+// Returns the number of K ranges (0: leave the launch alone) and the count of whole-K m-tiles in *dp.
+int pick_tail(int m_tiles, int n_tiles, int num_kb, int* dp) {
+    *dp = 0;
+    static const int off = getenv("PCTTS_NO_TAIL_SPLIT") ? atoi(getenv("PCTTS_NO_TAIL_SPLIT")) : 0;
+    const int tiles = m_tiles * n_tiles;
+    if (off || tiles <= 148 || n_tiles > 148 || num_kb < 12) return 0;
+    const int dpm = (tiles / 148) * 148 / n_tiles;
+    const int tail_tiles = (m_tiles - dpm) * n_tiles;
+    if (tail_tiles <= 0 || tail_tiles > 74) return 0;      // nothing left over / the last wave is at least half full anyway
+    int s = 148 / tail_tiles;
+    if (s > num_kb / 4) s = num_kb / 4;
+    if (s < 2) return 0;
+    *dp = dpm;
+    return s;
+}
+
+// first output row of m-tile mt under the (seg_len, seg_valid) row map of Params
+long tile_first_row(int mt, int seg_len, int seg_valid) {
+    const long r = (long)mt * BM;
+    const long seg = r / seg_len, tt = r - seg * seg_len;
+    return seg * seg_valid + (tt < seg_valid ? tt : seg_valid);
+}
+
+// fills the tail-split fields of p; `workspace` must hold splits * prows * N floats (see *_workspace host calls)
+void apply_tail(const Launch& L, Params& p, int bn, float* workspace) {
+    int dp = 0;
+    const int s = workspace ? pick_tail(L.m_tiles, (p.N + bn - 1) / bn, p.num_kb, &dp) : 0;
+    if (s < 2) return;
+    p.tail_dp = dp, p.tail_splits = s;
+    p.kb_per_split = (p.num_kb + s - 1) / s;
+    p.prow0 = tile_first_row(dp, p.seg_len, p.seg_valid);
+    p.prows = p.crows - p.prow0;
+    p.partial = workspace;
+}
+
+long tail_workspace(int m_tiles, int N, int bn, int num_kb, int seg_len, int seg_valid, long crows) {
+    int dp = 0;
+    const int s = pick_tail(m_tiles, (N + bn - 1) / bn, num_kb, &dp);
+    return s < 2 ? 0 : (long)s * (crows - tile_first_row(dp, seg_len, seg_valid)) * N;
+}
+
 template <int BN, int PARTS>
 int launch_bn(const Launch& L, Params p, cudaStream_t st) {
     CUtensorMap mapA, mapB;
@@ -456,6 +520,7 @@ int launch_bn(const Launch& L, Params p, cudaStream_t st) {
         attr_done = true;
     }
     dim3 grid((p.N + BN - 1) / BN, L.m_tiles, L.splits);
+    if (p.tail_splits > 0) grid.y = p.tail_dp + (L.m_tiles - p.tail_dp) * p.tail_splits, grid.z = 1;
     pctts_launch(gemm_tc_kernel<BN, PARTS>, grid, NUM_THREADS, smem, st, mapA, mapB, p);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
@@ -463,16 +528,18 @@ int launch_bn(const Launch& L, Params p, cudaStream_t st) {
 
 int launch_tc(const Launch& L, Params p, int bn, float* C, long ldc, float alpha, int accum, cudaStream_t st) {
     int rc;
+    if (p.prows < 0) p.prows = p.crows;
     if (p.nterms == 6) rc = bn == 128 ? launch_bn<128, 3>(L, p, st) : launch_bn<64, 3>(L, p, st);
     else if (p.nterms == 3) rc = bn == 128 ? launch_bn<128, 2>(L, p, st) : launch_bn<64, 2>(L, p, st);
     else rc = bn == 128 ? launch_bn<128, 1>(L, p, st) : launch_bn<64, 1>(L, p, st);
     if (rc) return rc;
     if (p.partial) {
-        const long total = p.crows * p.N;
+        const long total = p.prows * p.N;
         int blocks = pctts_div_up(total, 256);
         if (blocks > 148 * 8) blocks = 148 * 8;
-        pctts_launch(tc_splitk_reduce_kernel, blocks, 256, 0, st, p.partial, L.splits, p.crows, p.N, C, ldc, alpha, accum, p.bias, p.aux,
-                     p.flags & (PCTTS_EPI_BIAS | PCTTS_EPI_LRELU | PCTTS_EPI_DLRELU_AUX));
+        const int nz = p.tail_splits > 0 ? p.tail_splits : L.splits;
+        pctts_launch(tc_splitk_reduce_kernel, blocks, 256, 0, st, p.partial, nz, p.prows, p.N, C + p.prow0 * ldc, ldc, alpha, accum, p.bias,
+                     p.aux ? p.aux + p.prow0 * ldc : nullptr, p.flags & (PCTTS_EPI_BIAS | PCTTS_EPI_LRELU | PCTTS_EPI_DLRELU_AUX));
         PCTTS_LAUNCH_CHECK();
     }
     return PCTTS_OK;
@@ -529,6 +596,12 @@ extern "C" int pctts_gemm_tc_splits(int M, int N, int K) {
     return splits < 1 ? 1 : splits;
 }
 
+/* floats of workspace with which pctts_gemm_tc (splits = 1) cuts the m-tiles of a partly filled last wave along K (0: no use) */
+extern "C" long pctts_gemm_tc_tail_workspace(int M, int N, int K) {
+    const int m_tiles = (M + BM - 1) / BM;
+    return tail_workspace(m_tiles, N, pick_bn(m_tiles, N), (K + BK - 1) / BK, 1 << 30, M, M);
+}
+
 extern "C" int pctts_gemm_tc(int transA, int transB, int M, int N, int K, float alpha, const void* Ash, long lda, long a_part_stride,
                              const void* Bsh, long ldb, long b_part_stride, float* C, long ldc, const float* bias, const float* aux,
                              const float* addmod, int addrows, int flags, int nterms, int splits, float* workspace, void* stream) {
@@ -565,6 +638,8 @@ extern "C" int pctts_gemm_tc(int transA, int transB, int M, int N, int K, float 
     p.alpha = alpha, p.bias = bias, p.aux = aux, p.addmod = addmod, p.addrows = addrows, p.flags = flags;
     p.partial = L.splits > 1 ? workspace : nullptr;
     p.crows = M;
+    if (L.splits == 1 && !(flags & ~(PCTTS_EPI_BIAS | PCTTS_EPI_LRELU | PCTTS_EPI_DLRELU_AUX | PCTTS_EPI_ACCUM)))
+        apply_tail(L, p, bn, workspace);
     return launch_tc(L, p, bn, C, ldc, alpha, (flags & PCTTS_EPI_ACCUM) ? 1 : 0, (cudaStream_t)stream);
 }
 
@@ -633,8 +708,14 @@ extern "C" int pctts_conv1d_tc_fwd(const void* xsh, long ldx, long x_part_stride
 
 // Conv1D weight gradient dw[w*CIN + c, n] (+)= sum_{b,t} xpad[b, t+w, c] dz[b, t, n].
 // xsh as above; dzsh: bf16 planes of dz [B*T, COUT] (row pitch lddz).  M-tile = (tap w, 128 channels), k-block = (b, 64 frames).
+extern "C" long pctts_conv1d_tc_wgrad_workspace(int B, int T, int W, int CIN, int COUT) {
+    const int ct = (CIN + BM - 1) / BM, m_tiles = ct * W;
+    return tail_workspace(m_tiles, COUT, pick_bn(m_tiles, COUT), ((T + BK - 1) / BK) * B, ct * BM, CIN, (long)W * CIN);
+}
+
 extern "C" int pctts_conv1d_tc_wgrad(const void* xsh, long ldx, long x_part_stride, const void* dzsh, long lddz, long dz_part_stride,
-                                     float* dw, int B, int T, int W, int CIN, int COUT, int accumulate, int nterms, void* stream) {
+                                     float* dw, int B, int T, int W, int CIN, int COUT, int accumulate, int nterms,
+                                     float* workspace, void* stream) {
     if (!xsh || !dzsh || !dw || B <= 0 || T <= 0 || W <= 0 || CIN <= 0 || COUT <= 0) return PCTTS_EINVAL;
     if (nterms != 1 && nterms != 3 && nterms != 6) return PCTTS_EINVAL;
     const int parts = nterms == 6 ? 3 : (nterms == 3 ? 2 : 1);
@@ -670,5 +751,6 @@ extern "C" int pctts_conv1d_tc_wgrad(const void* xsh, long ldx, long x_part_stri
     p.flags = accumulate ? PCTTS_EPI_ACCUM : 0;
     p.partial = nullptr;
     p.crows = (long)W * CIN;
+    apply_tail(L, p, bn, workspace);
     return launch_tc(L, p, bn, dw, COUT, 1.f, accumulate, (cudaStream_t)stream);
 }

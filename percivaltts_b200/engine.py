@@ -480,6 +480,10 @@ class Critic(object):
             # side lane, followed there by everything else that hangs off them (ctx branch, bias sums).
             with o.side_lane():
                 self._dgrad_chain(pl, slice(0, g_rows.start))
+                # the spectral kernels' gradient over these applications' rows; the lane that carries the tangent sweep adds
+                # the gradient-penalty rows' share afterwards (param_grads), so its long chain ends with a third of the work
+                self._conv_wgrads(pl, slice(0, g_rows.start), first=True)
+                pl['conv_wgrads_apps'] = g_rows.start // pl['B']
                 pl['side_event'] = o.lane_event()
                 self.param_grads_ctx(pl, ctx_grads_apps)
             self._dgrad_chain(pl, g_rows)
@@ -577,6 +581,15 @@ class Critic(object):
             o.colsum(pl['dd'][:fM], g['c.out.bias'])
         pl['ctx_grads_done'] = True
 
+    def _conv_wgrads(self, pl, samples, first):
+        """Weight gradients of the spectral Conv2D stack over the applications `samples` (slice over the napp*B axis): written
+        together with the bias gradients (`first`: first-order applications), or accumulated without them (tangent rows)."""
+        o, g = self.ops, self.params.g
+        for i in range(self.a.gen_nbcnnlayers):
+            ain = pl['a'][i - 1] if i > 0 else pl['s0']
+            o.conv2d_wgrad(ain[samples], pl['da'][i][samples], g['c.spec.cnn%d.kernel' % i],
+                           dbias=g['c.spec.cnn%d.bias' % i] if first else None, accumulate=not first)
+
     def param_grads(self, pl, first_order_apps=2):
         """Gradients of every critic parameter from the stored layer inputs (activations, or tangents on the GP rows)
         and pre-activation gradients.  Kernels use all napp applications; biases and the ctx branch only the first
@@ -591,10 +604,14 @@ class Critic(object):
             self.param_grads_ctx(pl, first_order_apps)
         pl['ctx_grads_done'] = False
         o.wait_lane_event(pl.pop('side_event', None))      # the other applications' dp / da (side lane) are complete
-        for i in range(L):
-            ain = pl['a'][i - 1] if i > 0 else pl['s0']
-            o.conv2d_wgrad(ain, pl['da'][i], g['c.spec.cnn%d.kernel' % i], dbias=g['c.spec.cnn%d.bias' % i],
-                           bias_samples=first_order_apps * B)
+        # spectral kernels: first-order applications (with the biases), then the gradient-penalty rows accumulated on top --
+        # always as these two launches per layer, whichever lane ran the first, so that both schedules give the same bits
+        done = pl.pop('conv_wgrads_apps', 0)
+        assert done in (0, first_order_apps)
+        if not done:
+            self._conv_wgrads(pl, slice(0, first_order_apps * B), first=True)
+        if pl['nB'] > first_order_apps * B:
+            self._conv_wgrads(pl, slice(first_order_apps * B, pl['nB']), first=False)
         o.gemm(pl['a'][L - 1].view(nM, SF), pl['dp'][0], g['c.post.fc0.kernel'][:SF], transA=True)
         for i in (1, 2):
             o.gemm(pl['p'][i - 1], pl['dp'][i], g['c.post.fc%d.kernel' % i], transA=True)

@@ -395,6 +395,11 @@ class CudaOps(object):
                 splits = self.lib.pctts_gemm_tc_splits(M, N, K)
                 if splits > 1:
                     ws = self._splitk(self.lib.pctts_gemm_tc_workspace(M, N, splits))
+            if splits == 1 and (flags & ~(EPI_BIAS | EPI_LRELU | EPI_DLRELU_AUX | EPI_ACCUM)) == 0:
+                need = self.lib.pctts_gemm_tc_tail_workspace(M, N, K)     # more tiles than SMs: K-split of the last wave's tiles
+                if need:
+                    ws = self._splitk(need)
+                    self.launches += 1
             self._ck(self.lib.pctts_gemm_tc(int(transA), int(transB), M, N, K, float(alpha), sha.ptr, sha.ld, sha.part_stride,
                                             shb.ptr, shb.ld, shb.part_stride, pc, ldc, _ptr(bias), _ptr(aux), _ptr(addmod),
                                             addrows, flags, self.nterms, splits, _ptr(ws), self._stream()), 'pctts_gemm_tc')
@@ -455,8 +460,12 @@ class CudaOps(object):
         assert tuple(dz.shape) == (B * T, COUT) and dz.is_contiguous()
         if self.nterms > 0 and COUT >= 8:
             shx, shz = self.shadow(xp.view(B * Tp, CIN)), self.shadow(dz)
+            need = self.lib.pctts_conv1d_tc_wgrad_workspace(B, T, W, CIN, COUT)
+            ws = self._splitk(need) if need else None
+            if ws is not None:
+                self.launches += 1
             self._ck(self.lib.pctts_conv1d_tc_wgrad(shx.ptr, shx.ld, shx.part_stride, shz.ptr, shz.ld, shz.part_stride,
-                                                    dw.data_ptr(), B, T, W, CIN, COUT, 0, self.nterms, self._stream()),
+                                                    dw.data_ptr(), B, T, W, CIN, COUT, 0, self.nterms, _ptr(ws), self._stream()),
                      'pctts_conv1d_tc_wgrad')
             return
         self.gemm(xp.as_strided((B, T, W * CIN), (Tp * CIN, CIN, 1)), dz, dw.view(W * CIN, COUT), transA=True)

@@ -101,6 +101,27 @@ def test_gemm_tc_splitk_weight_gradients(cuda_ops):
         assert torch.equal(again, got), 'split-K reduction must be deterministic'
 
 
+def test_gemm_tc_tail_split_of_the_last_wave(cuda_ops):
+    """More output tiles than SMs (critic post FC on the batched [real | fake | interp] rows: 188 tiles): the m-tiles of the
+    partly filled last wave are cut along K and summed by the deterministic reduce, which then also carries the epilogue."""
+    for M, N, K in ((12000, 256, 772), (11901, 250, 800)):
+        assert cuda_ops.lib.pctts_gemm_tc_tail_workspace(M, N, K) > 0
+        A, B = rnd(M, K), rnd(K, N, seed=1)
+        bias, aux = rnd(N, seed=2), rnd(M, N, seed=3)
+        for flags, kw in ((0, {}), (OPS.EPI_LRELU, dict(bias=bias)), (0, dict(aux=aux)), (OPS.EPI_ACCUM, dict(bias=bias))):
+            C0 = rnd(M, N, seed=5)
+            want = C0.clone()
+            REF.gemm(A, B, want, alpha=0.7, flags=flags, **kw)
+            got = dev(C0)
+            cuda_ops.gemm(dev(A), dev(B), got, alpha=0.7, flags=flags, **dict((k, dev(v)) for k, v in kw.items()))
+            assert err(got, want) < TOL6, (M, N, K, flags, list(kw), err(got, want))
+            again = dev(C0)
+            cuda_ops.gemm(dev(A), dev(B), again, alpha=0.7, flags=flags, **dict((k, dev(v)) for k, v in kw.items()))
+            assert torch.equal(again, got)
+    assert cuda_ops.lib.pctts_conv1d_tc_wgrad_workspace(10, 400, 21, 425, 256) > 0        # 168 tiles of 70 k-blocks
+    assert cuda_ops.lib.pctts_gemm_tc_tail_workspace(4000, 256, 256) == 0                 # 64 tiles: nothing to cut
+
+
 def test_gemm_tc_sliced_3d_operands(cuda_ops):
     """LSTM recurrent-kernel gradient pattern: sliced [B, T-1, H] views of [B, T, 2H] / [B, T, 4H] buffers."""
     Bn, T, H = 3, 50, 64

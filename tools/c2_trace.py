@@ -31,4 +31,5 @@ for i in range(32):
     print(i, [int(v) - t0 if int(v) else None for v in t[i]])
 
 print('kernel entry -> roles start: %d cycles; entry -> exit: %d cycles' % (int(t[31, 1] - t[31, 0]), int(t[31, 2] - t[31, 0])))
+print('prologue stamps rel. entry: setup %d, producers start %d, weight operand built %d' % tuple(int(t[31, k] - t[31, 0]) for k in (3, 4, 1)))
 print('entry rel. first stamp', int(t[31, 0]) - t0)
