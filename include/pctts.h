@@ -105,11 +105,14 @@ int pctts_conv2d_tc_fwd(const float* x, const float* w, const float* bias, const
 /* the same, fused with the BatchNormalization layers around it (networktts.py:122-126): in_mean / in_invstd / in_gamma / in_beta
  * (all or none; 4 floats each) = apply LeakyReLU(BN(.)) of the previous layer to x on load (x is its pre-BN map; the activation
  * map is never written); workspace (or NULL) = a column-reduction workspace for rows = NB*T*F, C = 4 receiving what
- * pctts_bn_stats(y) would produce.  PCTTS_EUNSUPPORTED for maps too small to own 148 partial slots. */
+ * pctts_bn_stats(y) would produce; final_stage = 0 stops after the per-CTA partials (pctts_conv2d_tc_stat_partials of them), which
+ * pctts_bn_finalize_partials then consumes.  PCTTS_EUNSUPPORTED for maps too small to own 148 partial slots. */
+int pctts_conv2d_tc_stat_partials(int NB, int T, int F);   /* host call */
 int pctts_conv2d_tc_fwd_fused(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T, int F,
                               int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch, long auxpitch,
                               long xbatch, long ybatch, long auxbatch, int flags, int nterms, const float* in_mean,
-                              const float* in_invstd, const float* in_gamma, const float* in_beta, void* workspace, void* stream);
+                              const float* in_invstd, const float* in_gamma, const float* in_beta, void* workspace, int final_stage,
+                              void* stream);
 int pctts_conv2d_flip_weights(const float* w, float* wt, int KH, int KW, int CIN, int COUT, void* stream);
 long pctts_conv2d_wgrad_workspace(int NB, int T, int CIN, int COUT, int KH, int KW); /* floats; host call */
 /* dw[kt,kf,ci,co] (+)= scale * sum_{n,t,f} x[n,t+kt-pad_t,f+kf-pad_f,ci] dy[n,t,f,co]   (deterministic two-stage) */
@@ -128,6 +131,12 @@ long pctts_colreduce_workspace_bytes(long rows, int C);            /* host call;
 void* pctts_colreduce_sums_ptr(void* workspace, long rows, int C); /* host call; double sums[2][C] inside the workspace
                                                                       (all-reduce these across ranks for sync-BN) */
 int pctts_bn_stats(const float* x, long rows, int C, void* workspace, void* stream);  /* sums = [sum x, sum x^2] */
+/* single replica (no all-reduce between the statistics and their use): first stage only (pctts_colreduce_nblk partials), then
+ * second stage + finalize in ONE launch -- bit-identical to pctts_bn_stats + pctts_bn_finalize */
+int pctts_bn_stats_partial(const float* x, long rows, int C, void* workspace, void* stream);
+int pctts_colreduce_nblk(long rows, int C);   /* host call */
+int pctts_bn_finalize_partials(void* workspace, long rows, int C, int nblk, double count, float eps, float momentum, float* mean,
+                               float* invstd, float* moving_mean, float* moving_var, void* stream);
 int pctts_bn_finalize(void* workspace, long rows, int C, double count, float eps, float momentum, float* mean, float* invstd,
                       float* moving_mean, float* moving_var, void* stream);          /* moving_* may be NULL (frozen) */
 int pctts_bn_apply(const float* x, float* y, const float* mean, const float* invstd_or_var, const float* gamma,

@@ -495,7 +495,7 @@ extern "C" int pctts_conv2d_tc_supported(int F, int CIN, int COUT, int KH, int K
 static int conv2d_tc_run(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB, int T,
                          int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch,
                          long auxpitch, long xbatch, long ybatch, long auxbatch, int flags, int nterms, const float* const* in_bn,
-                         void* stats_workspace, void* stream) {
+                         void* stats_workspace, int final_stage, void* stream) {
     if (!x || !w || !y || NB < 0 || T < 0 || F <= 0) return PCTTS_EINVAL;
     if (!pctts_conv2d_tc_supported(F, CIN, COUT, KH, KW, pad_t, pad_f)) return PCTTS_EUNSUPPORTED;
     if (nterms != 1 && nterms != 3 && nterms != 6) return PCTTS_EINVAL;
@@ -527,7 +527,7 @@ static int conv2d_tc_run(const float* x, const float* w, const float* bias, cons
     if (nterms == 6) rc = launch_c2<3>(p, st);
     else if (nterms == 3) rc = launch_c2<2>(p, st);
     else rc = launch_c2<1>(p, st);
-    if (rc != PCTTS_OK || !stats_workspace) return rc;
+    if (rc != PCTTS_OK || !stats_workspace || !final_stage) return rc;
     return pctts_colreduce_final_launch(stats_workspace, (long)NB * T * F, 4, p.ntiles < 148 ? p.ntiles : 148, st);
 }
 
@@ -535,7 +535,7 @@ extern "C" int pctts_conv2d_tc_fwd(const float* x, const float* w, const float* 
                                    int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long ypitch,
                                    long auxpitch, long xbatch, long ybatch, long auxbatch, int flags, int nterms, void* stream) {
     return conv2d_tc_run(x, w, bias, aux, y, NB, T, F, CIN, COUT, KH, KW, pad_t, pad_f, xpitch, ypitch, auxpitch, xbatch, ybatch,
-                         auxbatch, flags, nterms, nullptr, nullptr, stream);
+                         auxbatch, flags, nterms, nullptr, nullptr, 1, stream);
 }
 
 // The same convolution fused with the BatchNormalization layers around it (networktts.py:122-126, pCNN2D = Conv2D + BN + LReLU):
@@ -543,17 +543,30 @@ extern "C" int pctts_conv2d_tc_fwd(const float* x, const float* w, const float* 
 //    LeakyReLU(BN(x)) is formed on load, so the activation map is never written (forward-only uses: the frozen generator);
 //  * workspace (or NULL): a column-reduction workspace for rows = NB*T*F, C = 4 (pctts_colreduce_workspace_bytes) that receives
 //    sums = [sum y, sum y^2] of the output exactly as pctts_bn_stats(y) would, without re-reading y.
+//    final_stage = 0 leaves the pctts_conv2d_tc_stat_partials(NB, T, F) per-CTA partials at the base of the workspace for
+//    pctts_bn_finalize_partials (second stage + finalize in one launch) instead of running the second stage here.
 // PCTTS_EUNSUPPORTED when a workspace is given but has fewer than 148 partial slots (small maps).
+/* number of per-CTA statistic partials pctts_conv2d_tc_fwd_fused writes for a map of this size (host call) */
+extern "C" int pctts_conv2d_tc_stat_partials(int NB, int T, int F) {
+    if (NB <= 0 || T <= 0 || F <= 0) return 0;
+    const int G = (F + 2 + 3) / 4;
+    int nblk = 0;
+    const int TT = pick_tt(NB, T, G, &nblk);
+    if (TT < 1) return 0;
+    const long ntiles = (long)NB * ((T + TT - 1) / TT);
+    return ntiles < 148 ? (int)ntiles : 148;
+}
+
 extern "C" int pctts_conv2d_tc_fwd_fused(const float* x, const float* w, const float* bias, const float* aux, float* y, int NB,
                                          int T, int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch,
                                          long ypitch, long auxpitch, long xbatch, long ybatch, long auxbatch, int flags, int nterms,
                                          const float* in_mean, const float* in_invstd, const float* in_gamma, const float* in_beta,
-                                         void* workspace, void* stream) {
+                                         void* workspace, int final_stage, void* stream) {
     const int nbn = (in_mean != nullptr) + (in_invstd != nullptr) + (in_gamma != nullptr) + (in_beta != nullptr);
     if (nbn != 0 && nbn != 4) return PCTTS_EINVAL;
     if (workspace && pctts_colreduce_slots((long)NB * T * F, 4) < 148) return PCTTS_EUNSUPPORTED;
     if (workspace && (NB == 0 || T == 0)) return PCTTS_EUNSUPPORTED;
     const float* in_bn[4] = {in_mean, in_invstd, in_gamma, in_beta};
     return conv2d_tc_run(x, w, bias, aux, y, NB, T, F, CIN, COUT, KH, KW, pad_t, pad_f, xpitch, ypitch, auxpitch, xbatch, ybatch,
-                         auxbatch, flags, nterms, nbn ? in_bn : nullptr, workspace, stream);
+                         auxbatch, flags, nterms, nbn ? in_bn : nullptr, workspace, final_stage, stream);
 }

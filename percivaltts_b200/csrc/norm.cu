@@ -122,6 +122,38 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sums, double count
     }
 }
 
+// Stage 2 of the statistics and the finalize step in one launch (single replica: nothing to all-reduce in between).  One warp
+// per channel sums both moments over the CTA partials exactly as colreduce_final_kernel does (lanes stride, butterfly), so the
+// result is bit-identical to the two-launch path; sums[] is still written for readers of the workspace.
+__global__ void __launch_bounds__(RT) bn_final_finalize_kernel(const double* __restrict__ partial, double* __restrict__ sums,
+                                                               int nblk, double count, int C, float eps, float momentum,
+                                                               float* __restrict__ mean, float* __restrict__ invstd,
+                                                               float* __restrict__ moving_mean, float* __restrict__ moving_var) {
+    pdl_entry();
+    const int c = blockIdx.x * (RT / 32) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (c >= C) return;
+    double q1 = 0.0, q2 = 0.0;
+    for (int b = lane; b < nblk; b += 32) {
+        q1 += partial[(long)b * 2 * C + c];
+        q2 += partial[(long)b * 2 * C + C + c];
+    }
+    q1 = warp_sum_d(q1);
+    q2 = warp_sum_d(q2);
+    if (lane == 0) {
+        sums[c] = q1, sums[C + c] = q2;
+        const double m = q1 / count;
+        double v = q2 / count - m * m;
+        if (v < 0.0) v = 0.0;
+        mean[c] = (float)m;
+        invstd[c] = (float)(1.0 / sqrt(v + (double)eps));
+        if (moving_mean) {
+            moving_mean[c] = momentum * moving_mean[c] + (1.f - momentum) * (float)m;
+            moving_var[c] = momentum * moving_var[c] + (1.f - momentum) * (float)v;
+        }
+    }
+}
+
 __global__ void bn_apply_kernel(const float* __restrict__ x, float* __restrict__ y, const float* __restrict__ mean,
                                 const float* __restrict__ invstd_or_var, const float* __restrict__ gamma,
                                 const float* __restrict__ beta, long total, int C, float eps, int use_var, int lrelu) {
@@ -198,10 +230,11 @@ Ws carve(void* workspace, long rows, int C) {
     } while (0)
 
 template <int MODE>
-int run_colreduce(const RedArgs& a, const Ws& w, cudaStream_t st) {
+int run_colreduce(const RedArgs& a, const Ws& w, cudaStream_t st, bool final_stage = true) {
     const int grid = reduce_grid(a.rows, a.C);
     pctts_launch(colreduce_kernel<MODE>, grid, RT, 0, st, a, w.partial);
     PCTTS_LAUNCH_CHECK();
+    if (!final_stage) return PCTTS_OK;
     pctts_launch(colreduce_final_kernel, pctts_div_up(2 * a.C, RT / 32), RT, 0, st, w.partial, w.sums, grid, a.C);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
@@ -215,6 +248,29 @@ extern "C" int pctts_bn_stats(const float* x, long rows, int C, void* workspace,
     Ws w = carve(workspace, rows, C);
     RedArgs a{x, nullptr, nullptr, nullptr, nullptr, nullptr, rows, C, 0};
     PCTTS_CUDA_RC(run_colreduce<MODE_STATS>(a, w, (cudaStream_t)stream));
+    return PCTTS_OK;
+}
+
+// First stage only: nblk = pctts_colreduce_nblk(rows, C) partials [2][C] at the base of the workspace, to be consumed by
+// pctts_bn_finalize_partials (single replica: statistics second stage + finalize in one launch).
+extern "C" int pctts_bn_stats_partial(const float* x, long rows, int C, void* workspace, void* stream) {
+    if (!x || !workspace || rows <= 0 || C <= 0) return PCTTS_EINVAL;
+    Ws w = carve(workspace, rows, C);
+    RedArgs a{x, nullptr, nullptr, nullptr, nullptr, nullptr, rows, C, 0};
+    PCTTS_CUDA_RC(run_colreduce<MODE_STATS>(a, w, (cudaStream_t)stream, false));
+    return PCTTS_OK;
+}
+
+extern "C" int pctts_colreduce_nblk(long rows, int C) { return (rows <= 0 || C <= 0) ? 0 : reduce_grid(rows, C); }
+
+extern "C" int pctts_bn_finalize_partials(void* workspace, long rows, int C, int nblk, double count, float eps, float momentum,
+                                          float* mean, float* invstd, float* moving_mean, float* moving_var, void* stream) {
+    if (!workspace || !mean || !invstd || count <= 0 || rows <= 0 || C <= 0) return PCTTS_EINVAL;
+    if (nblk < 1 || nblk > reduce_grid(rows, C)) return PCTTS_EINVAL;
+    Ws w = carve(workspace, rows, C);
+    pctts_launch(bn_final_finalize_kernel, pctts_div_up(C, RT / 32), RT, 0, (cudaStream_t)stream, w.partial, w.sums, nblk, count, C,
+                 eps, momentum, mean, invstd, moving_mean, moving_var);
+    PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
 

@@ -169,7 +169,7 @@ class Generator(object):
         mm, mv = p[bn.prefix + '.moving_mean'], p[bn.prefix + '.moving_var']
         if training:
             if ws is None:
-                ws = o.bn_stats(z2)
+                ws = o.bn_stats(z2, final=sync.world > 1 or not getattr(o, 'bn_single_launch', True))    # single replica: the second stage rides in bn_finalize's launch
             sync.allreduce(ws.sums)
             o.bn_finalize(ws, bn.rows * sync.world, A.BN_EPS, A.BN_MOMENTUM, bn.mean, bn.invstd,
                           mm if update_stats else None, mv if update_stats else None)
@@ -220,7 +220,8 @@ class Generator(object):
         L = a.gen_nbcnnlayers
         pending = None      # BatchNorm of the previous layer still to be applied (on load) by the next convolution
         for i in range(L):
-            ws = o.conv2d(amap, p['g.spec.cnn%d.kernel' % i], pl['cv_z'][i], stats=training, in_bn=pending)
+            ws = o.conv2d(amap, p['g.spec.cnn%d.kernel' % i], pl['cv_z'][i], stats=training, in_bn=pending,
+                          stats_final=sync.world > 1 or not getattr(o, 'bn_single_launch', True))
             # forward-only use (frozen generator of the critic step): nothing reads the activation map but the next
             # convolution, which forms it on load -- it is written for the last layer only (input of the output Conv2D)
             keep = materialize or not training or i == L - 1

@@ -172,6 +172,7 @@ class CudaOps(object):
         self.precision = precision
         self.nterms = PRECISIONS[precision]
         self.fuse_bn_stats = os.environ.get('PCTTS_FUSE_BN_STATS', '1') != '0'   # BN sums in the Conv2D epilogue
+        self.bn_single_launch = os.environ.get('PCTTS_BN_SINGLE_LAUNCH', '1') != '0'   # second stage inside bn_finalize (1 replica)
         self.conv2d_tc = os.environ.get('PCTTS_CONV2D_TC', '1') != '0'   # tcgen05 implicit-GEMM Conv2D (4->4, 5x5)
         self._shadows = {}         # view key -> Shadow
         self._fresh = {}           # view key -> (lo, hi): activation shadows valid inside the current step scope
@@ -471,12 +472,14 @@ class CudaOps(object):
         self.gemm(xp.as_strided((B, T, W * CIN), (Tp * CIN, CIN, 1)), dz, dw.view(W * CIN, COUT), transA=True)
 
     # -- 2-D convolutions ------------------------------------------------------------------------------------
-    def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0, stats=False, in_bn=None):
+    def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0, stats=False, in_bn=None, stats_final=True):
         """y = epilogue(conv2d_same(x, w)); x [N,T,F,Cin], w [KH,KW,Cin,Cout] contiguous, y/aux [N,T,F,Cout] views.
         stats=True also returns the ReduceWorkspace holding the BatchNorm sums [sum y, sum y^2] of the (contiguous) output:
         fused into the tensor-core kernel's epilogue where that kernel applies, a bn_stats() pass otherwise.
         in_bn = (mean, invstd, gamma, beta, scratch): x is a pre-BatchNorm map and the convolution reads LeakyReLU(BN(x)) --
-        formed on load by the tensor-core kernel (nothing is written), else materialised into `scratch` first."""
+        formed on load by the tensor-core kernel (nothing is written), else materialised into `scratch` first.
+        stats_final=False (single replica): the workspace is left with its first-stage partials (ws.pending), which
+        bn_finalize() folds into its own launch."""
         N, T, F, CIN = x.shape
         KH, KW, ci, COUT = w.shape
         assert ci == CIN and tuple(y.shape) == (N, T, F, COUT) and w.is_contiguous()
@@ -508,19 +511,20 @@ class CudaOps(object):
                 ws = self.reduce_ws(N * T * F, COUT)
                 rc = self.lib.pctts_conv2d_tc_fwd_fused(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t,
                                                         pad_f, xp, yp, ap, xb, yb, ab, flags, self.nterms, bnp[0], bnp[1], bnp[2],
-                                                        bnp[3], ws.ptr, self._stream())
+                                                        bnp[3], ws.ptr, int(stats_final), self._stream())
                 if rc != -2:      # PCTTS_EUNSUPPORTED: map too small for 148 partial slots
-                    self.launches += 1      # conv + the second reduction stage
+                    self.launches += int(stats_final)      # conv + the second reduction stage
                     self._ck(rc, 'pctts_conv2d_tc_fwd_fused')
+                    ws.pending = 0 if stats_final else self.lib.pctts_conv2d_tc_stat_partials(N, T, F)
                     return ws
             self._ck(self.lib.pctts_conv2d_tc_fwd_fused(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
                                                         xp, yp, ap, xb, yb, ab, flags, self.nterms, bnp[0], bnp[1], bnp[2], bnp[3],
-                                                        None, self._stream()), 'pctts_conv2d_tc_fwd_fused')
+                                                        None, 1, self._stream()), 'pctts_conv2d_tc_fwd_fused')
         else:
             self._ck(self.lib.pctts_conv2d_fwd(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
                                                xp, yp, ap, xb, yb, ab, flags, self._stream()), 'pctts_conv2d_fwd')
         if stats:
-            return self.bn_stats(y.view(N * T * F, COUT))
+            return self.bn_stats(y.view(N * T * F, COUT), final=stats_final)
         return None
 
     def conv2d_flip(self, w, wt):
@@ -557,15 +561,27 @@ class CudaOps(object):
                  'pctts_conv2d_wgrad')
 
     # -- batch normalisation ---------------------------------------------------------------------------------
-    def bn_stats(self, x):
-        """-> ReduceWorkspace whose .sums = [sum x, sum x^2] over the rows of the contiguous [rows, C] tensor x."""
+    def bn_stats(self, x, final=True):
+        """-> ReduceWorkspace whose .sums = [sum x, sum x^2] over the rows of the contiguous [rows, C] tensor x.
+        final=False (single replica, nothing to all-reduce): first stage only; bn_finalize() runs the second stage."""
         rows, C = x.shape
         assert x.is_contiguous()
         ws = self.reduce_ws(rows, C)
-        self._ck(self.lib.pctts_bn_stats(x.data_ptr(), rows, C, ws.ptr, self._stream()), 'pctts_bn_stats')
+        if final:
+            self._ck(self.lib.pctts_bn_stats(x.data_ptr(), rows, C, ws.ptr, self._stream()), 'pctts_bn_stats')
+            ws.pending = 0
+        else:
+            self._ck(self.lib.pctts_bn_stats_partial(x.data_ptr(), rows, C, ws.ptr, self._stream()), 'pctts_bn_stats_partial')
+            ws.pending = self.lib.pctts_colreduce_nblk(rows, C)
         return ws
 
     def bn_finalize(self, ws, count, eps, momentum, mean, invstd, moving_mean=None, moving_var=None):
+        if getattr(ws, 'pending', 0):
+            self._ck(self.lib.pctts_bn_finalize_partials(ws.ptr, ws.rows, ws.C, ws.pending, float(count), float(eps), float(momentum),
+                                                         mean.data_ptr(), invstd.data_ptr(), _ptr(moving_mean), _ptr(moving_var),
+                                                         self._stream()), 'pctts_bn_finalize_partials')
+            ws.pending = 0
+            return
         self._ck(self.lib.pctts_bn_finalize(ws.ptr, ws.rows, ws.C, float(count), float(eps), float(momentum), mean.data_ptr(),
                                             invstd.data_ptr(), _ptr(moving_mean), _ptr(moving_var), self._stream()),
                  'pctts_bn_finalize')

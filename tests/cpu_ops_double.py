@@ -128,7 +128,7 @@ class CpuOpsDouble(object):
         xp = F.pad(x.permute(0, 3, 1, 2), (pad_f, KW - 1 - pad_f, pad_t, KH - 1 - pad_t))
         return F.conv2d(xp, w.permute(3, 2, 0, 1)).permute(0, 2, 3, 1)
 
-    def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0, stats=False, in_bn=None):
+    def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0, stats=False, in_bn=None, stats_final=True):
         if in_bn is not None:
             mean, invstd, gamma, beta, scratch = in_bn
             C = x.shape[-1]
@@ -176,7 +176,7 @@ class CpuOpsDouble(object):
             dw.copy_(R)
 
     # ---- batch norm ------------------------------------------------------------------------------------------
-    def bn_stats(self, x):
+    def bn_stats(self, x, final=True):
         self.launches += 1
         ws = self.reduce_ws(*x.shape)
         xd = x.double()

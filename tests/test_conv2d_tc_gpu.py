@@ -115,6 +115,39 @@ def test_fused_batchnorm_statistics(cuda_ops, N, T, F):
     assert float(((got - ref).abs() / ref.abs().clamp_min(1e-30)).max()) < 1e-10
 
 
+@pytest.mark.parametrize('N,T,F', [(10, 400, 129), (3, 250, 65), (2, 40, 33)])
+def test_single_launch_second_stage_and_finalize(cuda_ops, N, T, F):
+    """Single replica: statistics second stage + finalize in one launch (pctts_bn_finalize_partials) from the partials of the
+    Conv2D epilogue or of pctts_bn_stats_partial -- mean / invstd / moving averages / sums bit-identical to the two-launch path."""
+    x, w = dev(rnd(N, T, F, 4)), dev(rnd(5, 5, 4, 4, seed=1) * 0.2)
+    y = torch.empty(N, T, F, 4, device='cuda')
+    rows = N * T * F
+
+    def finalize(ws):
+        mean, invstd = torch.empty(4, device='cuda'), torch.empty(4, device='cuda')
+        mm, mv = torch.full((4,), 0.25, device='cuda'), torch.full((4,), 1.5, device='cuda')
+        cuda_ops.bn_finalize(ws, rows, 1e-3, 0.99, mean, invstd, mm, mv)
+        return mean, invstd, mm, mv, ws.sums.clone()
+
+    ref = finalize(cuda_ops.conv2d(x, w, y, stats=True))
+    ws = cuda_ops.conv2d(x, w, y, stats=True, stats_final=False)
+    assert ws.pending > 0
+    got = finalize(ws)
+    assert ws.pending == 0 and all(torch.equal(a, b) for a, b in zip(ref, got))
+    ref = finalize(cuda_ops.bn_stats(y.view(-1, 4)))
+    got = finalize(cuda_ops.bn_stats(y.view(-1, 4), final=False))
+    assert all(torch.equal(a, b) for a, b in zip(ref, got))
+    z = dev(rnd(4000, 256, seed=7))                    # a dense layer's pre-activations
+    refz = cuda_ops.bn_stats(z).sums.clone()
+    wz = cuda_ops.bn_stats(z, final=False)
+    mean, invstd = torch.empty(256, device='cuda'), torch.empty(256, device='cuda')
+    cuda_ops.bn_finalize(wz, 4000, 1e-3, 0.99, mean, invstd)
+    assert torch.equal(wz.sums, refz)
+    zd = z.double()
+    assert float((mean.double() - zd.mean(0)).abs().max()) < 1e-6
+    assert float((invstd.double() - 1.0 / torch.sqrt(zd.var(0, unbiased=False) + 1e-3)).abs().max()) < 1e-5
+
+
 @pytest.mark.parametrize('N,T,F', [(10, 400, 129), (2, 37, 30)])
 def test_fused_input_batchnorm(cuda_ops, N, T, F):
     """LeakyReLU(BN(x)) formed on load by the convolution (in_bn) equals the convolution of the materialised activation map
