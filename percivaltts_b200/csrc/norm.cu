@@ -61,16 +61,18 @@ __global__ void __launch_bounds__(RT) colreduce_kernel(RedArgs a, double* __rest
         const int c = (C >= RT) ? tid + cc * RT : tid % C;
         const int rl = (C >= RT) ? 0 : tid / C;
         if (c < C && rl < rpb) {
-            // two independent chains for a little more memory-level parallelism
-            double p1 = 0.0, p2 = 0.0;
+            // four independent chains: the loop is bound by the latency of its 4-byte loads, not by arithmetic
+            double p1 = 0.0, p2 = 0.0, u1 = 0.0, u2 = 0.0, v1 = 0.0, v2 = 0.0;
             long r = r_begin + rl;
-            for (; r + rpb < r_end; r += 2 * rpb) {
+            for (; r + 3L * rpb < r_end; r += 4L * rpb) {
                 red_terms<MODE>(a, r, c, q1, q2);
                 red_terms<MODE>(a, r + rpb, c, p1, p2);
+                red_terms<MODE>(a, r + 2L * rpb, c, u1, u2);
+                red_terms<MODE>(a, r + 3L * rpb, c, v1, v2);
             }
-            if (r < r_end) red_terms<MODE>(a, r, c, q1, q2);
-            q1 += p1;
-            q2 += p2;
+            for (; r < r_end; r += rpb) red_terms<MODE>(a, r, c, q1, q2);
+            q1 = (q1 + p1) + (u1 + v1);
+            q2 = (q2 + p2) + (u2 + v2);
         }
         s1[tid] = q1;
         s2[tid] = q2;
@@ -88,6 +90,72 @@ __global__ void __launch_bounds__(RT) colreduce_kernel(RedArgs a, double* __rest
             partial[((long)blockIdx.x * 2 + 1) * C + c] = q2;
         }
         __syncthreads();
+    }
+}
+
+// Stage 1 for C = 4 (the Conv2D maps: rows = pixels, 16 bytes each): one float4 per pixel and array, four pixels in flight per
+// thread, fp64 accumulators per channel, fixed-order reduction (lanes: butterfly; warps: index order).
+template <int MODE>
+__global__ void __launch_bounds__(RT) colreduce_c4_kernel(RedArgs a, double* __restrict__ partial) {
+    pdl_entry();
+    __shared__ double red[RT / 32][8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long rows_per_cta = (a.rows + gridDim.x - 1) / gridDim.x;
+    const long r_begin = (long)blockIdx.x * rows_per_cta;
+    const long r_end = min(a.rows, r_begin + rows_per_cta);
+    const float4* const x4 = reinterpret_cast<const float4*>(a.x);
+    const float4* const d4 = reinterpret_cast<const float4*>(a.dy);
+    float mean[4] = {0.f, 0.f, 0.f, 0.f}, ivs[4] = {1.f, 1.f, 1.f, 1.f}, gam[4] = {1.f, 1.f, 1.f, 1.f}, bet[4] = {0.f, 0.f, 0.f, 0.f};
+    if (MODE == MODE_BNBWD) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) mean[c] = a.mean[c], ivs[c] = a.invstd[c], gam[c] = a.gamma[c], bet[c] = a.beta[c];
+    }
+    double q1[4] = {0.0, 0.0, 0.0, 0.0}, q2[4] = {0.0, 0.0, 0.0, 0.0};
+    auto terms = [&](const float4& xv4, const float4& dv4) {
+        const float xv[4] = {xv4.x, xv4.y, xv4.z, xv4.w}, dv[4] = {dv4.x, dv4.y, dv4.z, dv4.w};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            if (MODE == MODE_STATS) {
+                q1[c] += xv[c];
+                q2[c] += (double)xv[c] * xv[c];
+            } else if (MODE == MODE_COLSUM) {
+                q1[c] += xv[c];
+            } else {
+                const float xh = (xv[c] - mean[c]) * ivs[c];
+                float dz = dv[c];
+                if (a.lrelu) {
+                    const float z = gam[c] * xh + bet[c];
+                    dz *= (z > 0.f ? 1.f : PCTTS_LRELU_ALPHA);
+                }
+                q1[c] += dz;
+                q2[c] += (double)dz * xh;
+            }
+        }
+    };
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    long r = r_begin + tid;
+    for (; r + 3L * RT < r_end; r += 4L * RT) {
+        float4 xv[4], dv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            xv[u] = x4[r + (long)u * RT];
+            dv[u] = MODE == MODE_BNBWD ? d4[r + (long)u * RT] : zero4;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) terms(xv[u], dv[u]);
+    }
+    for (; r < r_end; r += RT) terms(x4[r], MODE == MODE_BNBWD ? d4[r] : zero4);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const double s1 = warp_sum_d(q1[c]), s2 = warp_sum_d(q2[c]);
+        if (lane == 0) red[warp][c] = s1, red[warp][4 + c] = s2;
+    }
+    __syncthreads();
+    if (tid < 8) {
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < RT / 32; ++w) t += red[w][tid];
+        partial[(long)blockIdx.x * 8 + tid] = t;       // [2][4]: tid = moment * 4 + channel
     }
 }
 
@@ -167,6 +235,67 @@ __global__ void bn_apply_kernel(const float* __restrict__ x, float* __restrict__
     }
 }
 
+// The same for C % 4 == 0 and 16-byte aligned maps: one float4 per thread and iteration (the scalar loop above keeps ~1.2 MB
+// in flight on the whole GPU and runs at load latency).  Per-element expression unchanged: bit-identical output.
+constexpr int NORM_SMEM_C = 1024;
+__global__ void __launch_bounds__(256) bn_apply_vec4_kernel(const float4* __restrict__ x, float4* __restrict__ y,
+                                                            const float* __restrict__ mean, const float* __restrict__ invstd_or_var,
+                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                            long total4, int C, float eps, int use_var, int lrelu) {
+    pdl_entry();
+    __shared__ float s_m[NORM_SMEM_C], s_i[NORM_SMEM_C], s_g[NORM_SMEM_C], s_b[NORM_SMEM_C];
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        s_m[c] = mean[c], s_g[c] = gamma[c], s_b[c] = beta[c];
+        s_i[c] = use_var ? rsqrtf(invstd_or_var[c] + eps) : invstd_or_var[c];
+    }
+    __syncthreads();
+    const int C4 = C >> 2;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total4; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C4) * 4;
+        const float4 v = x[i];
+        float o[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float t = (o[j] - s_m[c + j]) * s_i[c + j] * s_g[c + j] + s_b[c + j];
+            if (lrelu) t = lrelu_f(t);
+            o[j] = t;
+        }
+        y[i] = make_float4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+__global__ void __launch_bounds__(256) bn_bwd_apply_vec4_kernel(const float4* __restrict__ x, const float4* __restrict__ dy,
+                                                                float4* __restrict__ dx, const float* __restrict__ mean,
+                                                                const float* __restrict__ invstd, const float* __restrict__ gamma,
+                                                                const float* __restrict__ beta, const double* __restrict__ sums,
+                                                                double count, long total4, int C, int lrelu) {
+    pdl_entry();
+    __shared__ float s_m[NORM_SMEM_C], s_i[NORM_SMEM_C], s_g[NORM_SMEM_C], s_b[NORM_SMEM_C], s_1[NORM_SMEM_C], s_2[NORM_SMEM_C];
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        s_m[c] = mean[c], s_i[c] = invstd[c], s_g[c] = gamma[c], s_b[c] = beta[c];
+        s_1[c] = (float)(sums[c] / count), s_2[c] = (float)(sums[C + c] / count);     // once per CTA, not two fp64 divisions per element
+    }
+    __syncthreads();
+    const int C4 = C >> 2;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total4; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C4) * 4;
+        const float4 xv4 = x[i], dv4 = dy[i];
+        const float xv[4] = {xv4.x, xv4.y, xv4.z, xv4.w}, dv[4] = {dv4.x, dv4.y, dv4.z, dv4.w};
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float xh = (xv[j] - s_m[c + j]) * s_i[c + j];
+            float dz = dv[j];
+            if (lrelu) {
+                const float z = s_g[c + j] * xh + s_b[c + j];
+                dz *= (z > 0.f ? 1.f : PCTTS_LRELU_ALPHA);
+            }
+            o[j] = s_g[c + j] * s_i[c + j] * (dz - s_1[c + j] - xh * s_2[c + j]);
+        }
+        dx[i] = make_float4(o[0], o[1], o[2], o[3]);
+    }
+}
+
 // dx = gamma*invstd*(dz - mean(dz) - xhat*mean(dz*xhat)); dgamma = sum(dz*xhat); dbeta = sum(dz)
 __global__ void bn_bwd_apply_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dx,
                                     const float* __restrict__ mean, const float* __restrict__ invstd,
@@ -193,6 +322,11 @@ __global__ void sums_to_grads_kernel(const double* __restrict__ sums, int C, flo
     if (c >= C) return;
     if (g1) g1[c] = (accumulate ? g1[c] : 0.f) + (float)(sums[c] * scale);
     if (g2) g2[c] = (accumulate ? g2[c] : 0.f) + (float)(sums[C + c] * scale);
+}
+
+bool norm_vec() {      // PCTTS_NORM_VEC=0: the scalar kernels only (A/B measurements)
+    static const bool on = !(getenv("PCTTS_NORM_VEC") && atoi(getenv("PCTTS_NORM_VEC")) == 0);
+    return on;
 }
 
 int reduce_grid(long rows, int C) {
@@ -232,7 +366,10 @@ Ws carve(void* workspace, long rows, int C) {
 template <int MODE>
 int run_colreduce(const RedArgs& a, const Ws& w, cudaStream_t st, bool final_stage = true) {
     const int grid = reduce_grid(a.rows, a.C);
-    pctts_launch(colreduce_kernel<MODE>, grid, RT, 0, st, a, w.partial);
+    if (a.C == 4 && norm_vec() && !(((uintptr_t)a.x | (uintptr_t)a.dy) & 15))
+        pctts_launch(colreduce_c4_kernel<MODE>, grid, RT, 0, st, a, w.partial);
+    else
+        pctts_launch(colreduce_kernel<MODE>, grid, RT, 0, st, a, w.partial);
     PCTTS_LAUNCH_CHECK();
     if (!final_stage) return PCTTS_OK;
     pctts_launch(colreduce_final_kernel, pctts_div_up(2 * a.C, RT / 32), RT, 0, st, w.partial, w.sums, grid, a.C);
@@ -303,7 +440,13 @@ extern "C" int pctts_bn_apply(const float* x, float* y, const float* mean, const
     if (total == 0) return PCTTS_OK;
     int blocks = pctts_div_up(total, 256 * 4);
     if (blocks > 148 * 8) blocks = 148 * 8;
-    pctts_launch(bn_apply_kernel, blocks, 256, 0, (cudaStream_t)stream, x, y, mean, invstd_or_var, gamma, beta, total, C, eps, use_var, lrelu);
+    if (norm_vec() && (C & 3) == 0 && C <= NORM_SMEM_C && !(((uintptr_t)x | (uintptr_t)y) & 15)) {
+        blocks = pctts_div_up(total / 4, 256);
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        pctts_launch(bn_apply_vec4_kernel, blocks, 256, 0, (cudaStream_t)stream, (const float4*)x, (float4*)y, mean, invstd_or_var, gamma,
+                     beta, total / 4, C, eps, use_var, lrelu);
+    } else
+        pctts_launch(bn_apply_kernel, blocks, 256, 0, (cudaStream_t)stream, x, y, mean, invstd_or_var, gamma, beta, total, C, eps, use_var, lrelu);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
@@ -329,7 +472,13 @@ extern "C" int pctts_bn_bwd_apply(const float* x, const float* dy, float* dx, co
     const long total = rows * C;
     int blocks = pctts_div_up(total, 256 * 4);
     if (blocks > 148 * 8) blocks = 148 * 8;
-    pctts_launch(bn_bwd_apply_kernel, blocks, 256, 0, st, x, dy, dx, mean, invstd, gamma, beta, w.sums, count, total, C, lrelu);
+    if (norm_vec() && (C & 3) == 0 && C <= NORM_SMEM_C && !(((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dx) & 15)) {
+        blocks = pctts_div_up(total / 4, 256);
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        pctts_launch(bn_bwd_apply_vec4_kernel, blocks, 256, 0, st, (const float4*)x, (const float4*)dy, (float4*)dx, mean, invstd, gamma,
+                     beta, w.sums, count, total / 4, C, lrelu);
+    } else
+        pctts_launch(bn_bwd_apply_kernel, blocks, 256, 0, st, x, dy, dx, mean, invstd, gamma, beta, w.sums, count, total, C, lrelu);
     PCTTS_LAUNCH_CHECK();
     if (dgamma || dbeta) {
         pctts_launch(sums_to_grads_kernel, pctts_div_up(C, 128), 128, 0, st, w.sums, C, dbeta, dgamma, accumulate, (double)grad_scale);

@@ -154,7 +154,8 @@ def test_conv2d_strided_feature_views(cuda_ops):
     close(outg, outw, 2e-5)
 
 
-@pytest.mark.parametrize('rows,C', [(4000, 256), (1000 * 17, 4), (333, 2), (77, 300), (5, 8)])
+@pytest.mark.parametrize('rows,C', [(4000, 256), (1000 * 17, 4), (333, 2), (77, 300), (5, 8), (10 * 400 * 129, 4), (1031, 4),
+                                    (9, 1028), (12000, 256)])
 def test_batchnorm_forward_backward(cuda_ops, rows, C):
     x, dy = rnd(rows, C) * 2 + 0.3, rnd(rows, C, seed=1)
     gamma, beta = rnd(C, seed=2) + 1.5, rnd(C, seed=3) * 0.1
