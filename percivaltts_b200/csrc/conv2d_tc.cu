@@ -59,6 +59,8 @@ struct C2Params {
     long long* trace;    // developer probe (pctts_conv2d_tc_set_trace): clock64() stamps of CTA 0, 8 per tile
     const float *bn_mean, *bn_invstd, *bn_gamma, *bn_beta;   // optional: the input is a pre-BatchNorm map; BatchNorm + LeakyReLU
                                                              // are applied to every in-range pixel on load (fused bn_apply)
+    int aux_prefetch;    // bit 0: the epilogue prefetches the tile's aux rows into L1 while the MMAs run; bit 1: the producers'
+                         // input loads do not allocate in L1 (PCTTS_C2_AUX_PREFETCH, default 3)
     double* stats;       // optional: per-CTA partial [grid][2][4] of sum y, sum y^2 per output channel (fused BatchNorm statistics)
 };
 
@@ -84,6 +86,16 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16])
 
 __device__ __forceinline__ uint32_t pack_bf16(__nv_bfloat16 a, __nv_bfloat16 b) {
     return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);
+}
+
+// streaming 16-byte load of the input map: read once per tile, kept out of L1 so that the epilogue's prefetched mask rows stay
+__device__ __forceinline__ float4 ldg_stream4(const float* p, int no_alloc) {
+    float4 v;
+    if (no_alloc)
+        asm("ld.global.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    else
+        v = *reinterpret_cast<const float4*>(p);
+    return v;
 }
 
 // 8 floats (2 pixels x 4 channels) -> PARTS 16-byte bf16 entries.  Every plane but the last takes the top 16 bits of the running
@@ -178,9 +190,9 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
                 const int t = t0 - 2 + tt, f = 2 * j;
                 if (t >= 0 && t < p.T && f < p.F) {
                     const float* src = xb + (long)t * p.xpitch + (long)f * 4;
-                    va[u] = *reinterpret_cast<const float4*>(src);
+                    va[u] = ldg_stream4(src, p.aux_prefetch & 2);
                     inrange |= 1u << (2 * u);
-                    if (f + 1 < p.F) vb[u] = *reinterpret_cast<const float4*>(src + 4), inrange |= 2u << (2 * u);
+                    if (f + 1 < p.F) vb[u] = ldg_stream4(src + 4, p.aux_prefetch & 2), inrange |= 2u << (2 * u);
                 }
             }
         }
@@ -357,6 +369,20 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
             const int t0 = (ti - n * p.tiles_per_sample) * TT;
             const bool tr = p.trace && blockIdx.x == 0 && tid == C2_PROD + 32 && it < 32;
             if (tr) p.trace[it * 8 + 5] = clock64();
+            if ((flags & PCTTS_EPI_DLRELU_AUX) && (p.aux_prefetch & 1)) {
+                // the mask rows this thread will need, requested while the tile's MMAs run: otherwise every 128-row block pays
+                // one exposed global-load round trip between tcgen05.ld and its stores
+                for (int blk = 0; blk < p.nblk; ++blk) {
+                    const int r = blk * 128 + q * 32 + lane;
+                    if (r < rows_valid) {
+                        const int to = r / G, g = r - to * G;
+                        if (t0 + to < p.T && 4 * g < p.F) {
+                            const float* ax = p.aux + (long)n * p.auxbatch + (long)(t0 + to) * p.auxpitch + (long)g * 16;
+                            asm volatile("prefetch.global.L1 [%0];" ::"l"(ax));
+                        }
+                    }
+                }
+            }
             mbar_wait(smem_u32(&acc_full[s]), ph);
             tc_fence_after();
             if (tr) p.trace[it * 8 + 6] = clock64();
@@ -519,6 +545,8 @@ static int conv2d_tc_run(const float* x, const float* w, const float* bias, cons
     p.xpitch = xpitch, p.ypitch = ypitch, p.auxpitch = auxpitch, p.xbatch = xbatch, p.ybatch = ybatch, p.auxbatch = auxbatch;
     p.flags = flags;
     p.trace = g_c2_trace;
+    static const int aux_pf = getenv("PCTTS_C2_AUX_PREFETCH") ? atoi(getenv("PCTTS_C2_AUX_PREFETCH")) : 3;
+    p.aux_prefetch = aux_pf;
     p.bn_mean = in_bn ? in_bn[0] : nullptr, p.bn_invstd = in_bn ? in_bn[1] : nullptr;
     p.bn_gamma = in_bn ? in_bn[2] : nullptr, p.bn_beta = in_bn ? in_bn[3] : nullptr;
     p.stats = (double*)stats_workspace;      // the partials sit at the base of a column-reduction workspace (norm.cu)
