@@ -66,6 +66,46 @@ __global__ void gp_norm_kernel(const float* __restrict__ g, long per_sample, flo
     if (threadIdx.x == 0) ss[blockIdx.x] = (float)s;
 }
 
+// The same with GPN_SLICES CTAs per sample (the norm sits on the critical chain of the critic step: gradient -> norm -> penalty
+// -> tangent sweep, and 10 CTAs of strided 4-byte loads ran at load latency): every CTA leaves an fp64 partial, the last one to
+// arrive (ticket) sums the slices in index order -- deterministic -- and re-arms the ticket for the next launch / graph replay.
+constexpr int GPN_SLICES = 16, GPN_MAXB = 256;
+__device__ double g_gpn_partial[GPN_MAXB * GPN_SLICES];
+__device__ unsigned int g_gpn_ticket[GPN_MAXB];
+
+__global__ void __launch_bounds__(256) gp_norm_sliced_kernel(const float* __restrict__ g, long per_sample, float* __restrict__ ss) {
+    pdl_entry();
+    __shared__ double scratch[32];
+    __shared__ int s_last;
+    const int b = blockIdx.y, sl = blockIdx.x;
+    const long chunk = (per_sample + GPN_SLICES - 1) / GPN_SLICES;
+    const long lo = min(per_sample, sl * chunk), hi = min(per_sample, lo + chunk);
+    const float* p = g + (long)b * per_sample;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    long i = lo + threadIdx.x;
+    for (; i + 3L * blockDim.x < hi; i += 4L * blockDim.x) {
+        const float v0 = p[i], v1 = p[i + blockDim.x], v2 = p[i + 2L * blockDim.x], v3 = p[i + 3L * blockDim.x];
+        s0 += (double)v0 * v0, s1 += (double)v1 * v1, s2 += (double)v2 * v2, s3 += (double)v3 * v3;
+    }
+    for (; i < hi; i += blockDim.x) {
+        const float v = p[i];
+        s0 += (double)v * v;
+    }
+    const double s = block_sum_d((s0 + s1) + (s2 + s3), scratch);
+    if (threadIdx.x == 0) {
+        g_gpn_partial[b * GPN_SLICES + sl] = s;
+        __threadfence();
+        s_last = atomicAdd(&g_gpn_ticket[b], 1u) == GPN_SLICES - 1;
+        if (s_last) {
+            __threadfence();
+            double t = 0.0;
+            for (int k = 0; k < GPN_SLICES; ++k) t += *(volatile double*)&g_gpn_partial[b * GPN_SLICES + k];
+            ss[b] = (float)t;
+            g_gpn_ticket[b] = 0u;
+        }
+    }
+}
+
 // r0[b,:] = lambda * 2 (n_b - 1) / (n_b * Bglobal) * g[b,:];  losses[gp_slot] = sum_b (1-n_b)^2 / Bglobal  (local share)
 __global__ void gp_scale_kernel(const float* __restrict__ g, const float* __restrict__ ss, float* __restrict__ r0, int B,
                                 long per_sample, float lambda, float inv_bglobal, float* __restrict__ losses, int gp_slot) {
@@ -246,7 +286,10 @@ extern "C" int pctts_sum_scaled(const float* x, long n, double scale, float* los
 
 extern "C" int pctts_gp_norms(const float* g, int B, long per_sample, float* ss, void* stream) {
     if (!g || !ss || B <= 0) return PCTTS_EINVAL;
-    pctts_launch(gp_norm_kernel, B, 1024, 0, (cudaStream_t)stream, g, per_sample, ss);
+    if (B <= GPN_MAXB && per_sample >= 4096)
+        pctts_launch(gp_norm_sliced_kernel, dim3(GPN_SLICES, B), 256, 0, (cudaStream_t)stream, g, per_sample, ss);
+    else
+        pctts_launch(gp_norm_kernel, B, 1024, 0, (cudaStream_t)stream, g, per_sample, ss);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

@@ -230,6 +230,22 @@ def test_lstm_forward_and_bptt(cuda_ops, B, T, H):
     close(h1, hout[:, :, :H], 1e-4, 'lstm single direction')
 
 
+def test_gp_norms_sliced_demo_size(cuda_ops):
+    """Per-sample squared gradient norm at the demo size (16 CTAs per sample, ticketed deterministic finish): against fp64,
+    repeated launches (the ticket re-arms itself) bit-identical, ragged per-sample length."""
+    for B, n in ((10, 400 * 129), (3, 4097)):
+        g = rnd(B, n, seed=3) * 0.05
+        want = (g * g).sum(1)
+        gd, ssd = dev(g), torch.zeros(B, device='cuda')
+        cuda_ops.gp_norms(gd, ssd)
+        close(ssd, want, 1e-6, 'ss sliced')
+        first = ssd.clone()
+        for _ in range(3):
+            ssd.zero_()
+            cuda_ops.gp_norms(gd, ssd)
+            assert torch.equal(ssd, first)
+
+
 def test_wgan_gp_pieces(cuda_ops):
     B, T, O, S = 4, 31, 23, 17
     real, fake, alpha = rnd(B, T, O), rnd(B, T, O, seed=1), torch.rand(B, dtype=torch.float64)
