@@ -482,7 +482,12 @@ int pick_tt(int NB, int T, int G, int* nblk_out) {
         if (nblk > C2_MAXBLK) break;
         const long tiles = (long)NB * ((T + tt - 1) / tt);
         const long waves = (tiles + 147) / 148;
-        const double cost = (double)waves * (nblk + 0.3 + 0.02 * (tt + 4));
+        // in units of one 128-row block of MMAs (~1 k cycles, clock trace): per tile the blocks plus ~0.6 of hand-over gaps; per
+        // CTA once the first tile's fill and the last tile's drain, which grow with the tile (~0.5 + ~0.75 per block) -- on the
+        // B-sized maps (2 tiles per CTA) they weigh as much as a whole tile, so smaller tiles win there
+        static const int old_cost = getenv("PCTTS_C2_OLD_COST") ? atoi(getenv("PCTTS_C2_OLD_COST")) : 0;
+        const double cost = old_cost ? (double)waves * (nblk + 0.3 + 0.02 * (tt + 4))
+                                     : (double)waves * (nblk + 0.6) + 1.25 * nblk - 1e-3 * tt;
         if (cost <= best) best = cost, best_tt = tt, best_blk = nblk;
     }
     *nblk_out = best_blk;
