@@ -234,13 +234,16 @@ def run_b200(args):
             tr.generator_step_device(s)
 
     # ---- value: device-resident loop ---------------------------------------------------------------------------------
+    # the sampler starts in front of the warm-up: nvidia-smi's own start-up (NVML initialisation takes driver locks and was seen
+    # to stall the launching thread for 100s of ms) then falls into the untimed steps, its polling into the timed ones
+    clocks = ClockSampler(device.index or 0)
+    if rank == 0:
+        clocks.start()
+        time.sleep(0.5)
     for i in range(args.warmup):
         resident_step(i)
     torch.cuda.synchronize(device)
     barrier()
-    clocks = ClockSampler(device.index or 0)
-    if rank == 0:
-        clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize(device)
     e0.record()

@@ -428,6 +428,44 @@ __global__ void split_bf16_kernel(const float* __restrict__ src, long ld, int se
     }
 }
 
+// The same for cols % 4 == 0, 16-byte aligned rows (ld % 4 == 0): 8 columns per thread -- two float4 loads, one 16-byte store per
+// plane -- and 32-bit index arithmetic.  Same rounding steps as above: bit-identical planes.
+__device__ __forceinline__ uint32_t bf16x2_rn(float a, float b, float& ra, float& rb) {
+    const __nv_bfloat16 ha = __float2bfloat16_rn(a), hb = __float2bfloat16_rn(b);
+    ra = a - __bfloat162float(ha), rb = b - __bfloat162float(hb);
+    return (uint32_t)__bfloat16_as_ushort(ha) | ((uint32_t)__bfloat16_as_ushort(hb) << 16);
+}
+
+__global__ void __launch_bounds__(256) split_bf16_vec8_kernel(const float* __restrict__ src, long ld, int seg, long segstride, int rows,
+                                                              int cols, __nv_bfloat16* __restrict__ dst, long ld_dst, long part_stride,
+                                                              int parts) {
+    pdl_entry();
+    const int groups = (int)(ld_dst >> 3);
+    const int total = rows * groups;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int r = i / groups;
+        const int c = (i - r * groups) * 8;
+        long off;
+        if (seg > 0) {
+            const int sgm = r / seg;
+            off = (long)sgm * segstride + (long)(r - sgm * seg) * ld;
+        } else {
+            off = (long)r * ld;
+        }
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+        if (c < cols) a = *reinterpret_cast<const float4*>(src + off + c);
+        if (c + 4 < cols) b = *reinterpret_cast<const float4*>(src + off + c + 4);
+        float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        __nv_bfloat16* d = dst + (long)r * ld_dst + c;
+        for (int pl = 0; pl < parts; ++pl) {
+            uint32_t w[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) w[j] = bf16x2_rn(v[2 * j], v[2 * j + 1], v[2 * j], v[2 * j + 1]);
+            *reinterpret_cast<uint4*>(d + (long)pl * part_stride) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+    }
+}
+
 long long* g_trace = nullptr;
 
 struct Launch {
@@ -568,6 +606,17 @@ extern "C" int pctts_split_bf16(const float* src, long ld, int seg, long segstri
                                 long part_stride, int parts, void* stream) {
     if (!src || !dst || rows < 0 || cols <= 0 || ld_dst < cols || (ld_dst & 7) || parts < 1 || parts > 3) return PCTTS_EINVAL;
     if (rows == 0) return PCTTS_OK;
+    static const int no_vec = getenv("PCTTS_SPLIT_VEC") ? atoi(getenv("PCTTS_SPLIT_VEC")) == 0 : 0;
+    if (!no_vec && (cols & 3) == 0 && (ld & 3) == 0 && (segstride & 3) == 0 && !((uintptr_t)src & 15) && !((uintptr_t)dst & 15) &&
+        (part_stride & 7) == 0 && rows * (ld_dst / 8) < (1L << 31)) {
+        const long groups = rows * (ld_dst / 8);
+        int blocks = pctts_div_up(groups, 256);
+        if (blocks > 148 * 16) blocks = 148 * 16;
+        pctts_launch(split_bf16_vec8_kernel, blocks, 256, 0, (cudaStream_t)stream, src, ld, seg, segstride, (int)rows, cols,
+                     (__nv_bfloat16*)dst, ld_dst, part_stride, parts);
+        PCTTS_LAUNCH_CHECK();
+        return PCTTS_OK;
+    }
     const long total = rows * (ld_dst / 2);
     int blocks = pctts_div_up(total, 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
