@@ -389,6 +389,42 @@ __global__ void tc_splitk_reduce_kernel(const float* __restrict__ partial, int s
     }
 }
 
+// The same, four columns per thread (N % 4 == 0, 16-byte aligned rows of C / aux / partial): same order of additions per element.
+__global__ void __launch_bounds__(256) tc_splitk_reduce_vec4_kernel(const float4* __restrict__ partial, int splits, int rows, int N4,
+                                                                    float* __restrict__ C, long ldc, float alpha, int accum,
+                                                                    const float* __restrict__ bias, const float* __restrict__ aux,
+                                                                    int flags) {
+    pdl_entry();
+    const int total = rows * N4;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int z = 0; z < splits; ++z) {
+            const float4 v = partial[(long)z * total + i];
+            s.x += v.x, s.y += v.y, s.z += v.z, s.w += v.w;
+        }
+        const int m = i / N4, n = (i - m * N4) * 4;
+        float o[4] = {s.x * alpha, s.y * alpha, s.z * alpha, s.w * alpha};
+        if (flags & PCTTS_EPI_BIAS) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) o[j] += __ldg(bias + n + j);
+        }
+        if (flags & PCTTS_EPI_LRELU) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) o[j] = lrelu_f(o[j]);
+        }
+        float4* c = reinterpret_cast<float4*>(C + (long)m * ldc + n);
+        if (flags & PCTTS_EPI_DLRELU_AUX) {
+            const float4 a = *reinterpret_cast<const float4*>(aux + (long)m * ldc + n);
+            o[0] *= dlrelu_from_out(a.x), o[1] *= dlrelu_from_out(a.y), o[2] *= dlrelu_from_out(a.z), o[3] *= dlrelu_from_out(a.w);
+        }
+        if (accum) {
+            const float4 d = *c;
+            o[0] += d.x, o[1] += d.y, o[2] += d.z, o[3] += d.w;
+        }
+        *c = make_float4(o[0], o[1], o[2], o[3]);
+    }
+}
+
 // x -> bf16 hi (+ lo) planes; one thread per pair of columns
 __global__ void split_bf16_kernel(const float* __restrict__ src, long ld, int seg, long segstride, long rows, int cols,
                                   __nv_bfloat16* __restrict__ dst, long ld_dst, long part_stride, int parts) {
@@ -576,8 +612,17 @@ int launch_tc(const Launch& L, Params p, int bn, float* C, long ldc, float alpha
         int blocks = pctts_div_up(total, 256);
         if (blocks > 148 * 8) blocks = 148 * 8;
         const int nz = p.tail_splits > 0 ? p.tail_splits : L.splits;
-        pctts_launch(tc_splitk_reduce_kernel, blocks, 256, 0, st, p.partial, nz, p.prows, p.N, C + p.prow0 * ldc, ldc, alpha, accum, p.bias,
-                     p.aux ? p.aux + p.prow0 * ldc : nullptr, p.flags & (PCTTS_EPI_BIAS | PCTTS_EPI_LRELU | PCTTS_EPI_DLRELU_AUX));
+        float* const c0 = C + p.prow0 * ldc;
+        const float* const aux0 = p.aux ? p.aux + p.prow0 * ldc : nullptr;
+        const int rflags = p.flags & (PCTTS_EPI_BIAS | PCTTS_EPI_LRELU | PCTTS_EPI_DLRELU_AUX);
+        static const int no_vec = getenv("PCTTS_REDUCE_VEC") ? atoi(getenv("PCTTS_REDUCE_VEC")) == 0 : 0;
+        if (!no_vec && (p.N & 3) == 0 && (ldc & 3) == 0 && !(((uintptr_t)c0 | (uintptr_t)aux0 | (uintptr_t)p.partial) & 15) && total < (1L << 31)) {
+            blocks = pctts_div_up(total / 4, 256);
+            if (blocks > 148 * 8) blocks = 148 * 8;
+            pctts_launch(tc_splitk_reduce_vec4_kernel, blocks, 256, 0, st, (const float4*)p.partial, nz, (int)p.prows, p.N / 4, c0, ldc, alpha,
+                         accum, p.bias, aux0, rflags);
+        } else
+            pctts_launch(tc_splitk_reduce_kernel, blocks, 256, 0, st, p.partial, nz, p.prows, p.N, c0, ldc, alpha, accum, p.bias, aux0, rflags);
         PCTTS_LAUNCH_CHECK();
     }
     return PCTTS_OK;
