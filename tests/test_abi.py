@@ -54,3 +54,24 @@ def test_product_never_imports_the_oracle():
                 txt = open(os.path.join(dirpath, fn)).read()
                 assert 'import oracle' not in txt and 'from oracle' not in txt and 'cpu_ops_double' not in txt.replace(
                     'tests/cpu_ops_double.py', ''), fn
+
+
+def test_host_planning_calls_need_no_gpu():
+    """The workspace / partition planners of the C ABI are host code: launch geometry of the demo shapes, checked without a device."""
+    lib = _lib.load()
+    # Conv1D k=21 425->256 forward, M = 4000: 66 tiles of 128 x 128 -> two K halves per tile, 2 x [4000, 256] floats of workspace
+    assert lib.pctts_conv1d_tc_fwd_workspace(10, 400, 21, 425, 256) == 2 * 4000 * 256
+    # its weight gradient: 84 x 2 = 168 tiles on 148 SMs -> 74 whole m-tiles, the other 10 (output rows 7906..8924) cut into 7 K ranges
+    assert lib.pctts_conv1d_tc_wgrad_workspace(10, 400, 21, 425, 256) == 7 * (21 * 425 - (18 * 425 + 256)) * 256
+    # critic post layer on the batched rows: 94 x 2 = 188 tiles, 13 k-blocks -> 3 ranges over rows 9472..11999
+    assert lib.pctts_gemm_tc_tail_workspace(12000, 256, 772) == 3 * (12000 - 74 * 128) * 256
+    assert lib.pctts_gemm_tc_tail_workspace(4000, 256, 256) == 0          # fewer tiles than SMs
+    assert lib.pctts_gemm_tc_tail_workspace(12000, 256, 256) == 0         # 4 k-blocks: nothing to cut
+    assert lib.pctts_gemm_tc_splits(256, 256, 4000) > 1 and lib.pctts_gemm_tc_splits(4000, 256, 256) == 1
+    # BatchNorm statistics: partial slots of the column reduction and of the Conv2D epilogue
+    assert lib.pctts_colreduce_nblk(10 * 400 * 129, 4) == 296 and lib.pctts_colreduce_nblk(4000, 256) == 296
+    assert lib.pctts_colreduce_nblk(0, 4) == 0
+    assert lib.pctts_conv2d_tc_stat_partials(10, 400, 129) == 148
+    assert 0 < lib.pctts_conv2d_tc_stat_partials(2, 40, 33) < 148
+    assert lib.pctts_conv2d_tc_supported(129, 4, 4, 5, 5, 2, 2) == 1 and lib.pctts_conv2d_tc_supported(129, 1, 4, 5, 5, 2, 2) == 0
+    assert lib.pctts_peer_allreduce_bytes(8, 1024) > 2 * 1024 * 8 and lib.pctts_peer_allreduce_bytes(17, 1024) == -1
