@@ -38,6 +38,7 @@ class DeviceTrainer(object):
         self.d2h_bytes = 0
         # double-buffered prefetch of the NEXT batch (train_on_batch(..., next_batch=)): pinned + device staging, own copy stream
         self._pf = None
+        self._pf_placed = None     # shape state whose input buffers already hold the prefetched batch
         self._pf_slot = 0
         self._pf_bufs = [None, None]
         self._copy_stream = None
@@ -98,8 +99,8 @@ class DeviceTrainer(object):
     # ---- the reference's per-batch entry point ---------------------------------------------------------------------
     def stage(self, s, X, Y, alpha=None):
         """numpy [B,T,*] float32 -> pinned -> device (async on the current stream)."""
-        s.Xh.copy_(torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32)))
-        s.Yh.copy_(torch.from_numpy(np.ascontiguousarray(Y, dtype=np.float32)))
+        np.copyto(s.Xh.numpy(), np.asarray(X, dtype=np.float32).reshape(s.Xh.shape))
+        np.copyto(s.Yh.numpy(), np.asarray(Y, dtype=np.float32).reshape(s.Yh.shape))
         s.X.copy_(s.Xh, non_blocking=True)
         s.Y.copy_(s.Yh, non_blocking=True)
         self.h2d_bytes += s.Xh.numel() * 4 + s.Yh.numel() * 4
@@ -124,8 +125,10 @@ class DeviceTrainer(object):
                 Yd=torch.empty(need[1], dtype=torch.float32, device=self.ops.device), ev=torch.cuda.Event())
         if self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream(device=self.ops.device)
-        b['Xh'][:X.size].copy_(torch.from_numpy(X.reshape(-1)))
-        b['Yh'][:Y.size].copy_(torch.from_numpy(Y.reshape(-1)))
+        # plain single-threaded memcpy (numpy, GIL released): it hides behind the step on the GPU anyway, whereas torch's copy_ fans
+        # out over every core and leaves the OpenMP workers spinning beside the thread that has to launch the next step
+        np.copyto(b['Xh'].numpy()[:X.size], X.reshape(-1))
+        np.copyto(b['Yh'].numpy()[:Y.size], Y.reshape(-1))
         with torch.cuda.stream(self._copy_stream):
             b['Xd'][:X.size].copy_(b['Xh'][:X.size], non_blocking=True)
             b['Yd'][:Y.size].copy_(b['Yh'][:Y.size], non_blocking=True)
@@ -143,13 +146,15 @@ class DeviceTrainer(object):
         pf = self._pf
         if pf is not None and alpha is None and (pf[0] is X or (pf[2] == tuple(X.shape) and np.shares_memory(pf[0], X))) \
                 and (pf[1] is Y or (pf[3] == tuple(Y.shape) and np.shares_memory(pf[1], Y))):
-            b = self._pf_bufs[self._pf_slot]
-            torch.cuda.current_stream(self.ops.device).wait_event(b['ev'])
-            s.X.view(-1).copy_(b['Xd'][:s.X.numel()], non_blocking=True)
-            s.Y.view(-1).copy_(b['Yd'][:s.Y.numel()], non_blocking=True)
+            if self._pf_placed is not s:     # else: the previous call already moved it into this shape's input buffers
+                b = self._pf_bufs[self._pf_slot]
+                torch.cuda.current_stream(self.ops.device).wait_event(b['ev'])
+                s.X.view(-1).copy_(b['Xd'][:s.X.numel()], non_blocking=True)
+                s.Y.view(-1).copy_(b['Yd'][:s.Y.numel()], non_blocking=True)
         else:
             self.stage(s, X, Y, alpha)
         self._pf = None
+        self._pf_placed = None
         self.critic_step_device(s, explicit_alpha=alpha is not None)
         trained_gen = False
         if batchid % W.critic_runs(self.generator_updates) == 0:
@@ -159,6 +164,14 @@ class DeviceTrainer(object):
         self.d2h_bytes += W.NLOSS * 4
         if next_batch is not None:
             self._prefetch(next_batch[0], next_batch[1])
+            if self._pf is not None and tuple(self._pf[2][:2]) == (B, T):
+                # same (B, T): the staged batch moves into the step's input buffers behind this step's kernels (stream order), so
+                # the next call starts with its graph launch instead of two copies
+                b = self._pf_bufs[self._pf_slot]
+                torch.cuda.current_stream(self.ops.device).wait_event(b['ev'])
+                s.X.view(-1).copy_(b['Xd'][:s.X.numel()], non_blocking=True)
+                s.Y.view(-1).copy_(b['Yd'][:s.Y.numel()], non_blocking=True)
+                self._pf_placed = s
         if self.ops.device.type == 'cuda':
             torch.cuda.current_stream(self.ops.device).synchronize()
         critic_cost = float(s.lossh[W.L_CRITIC])

@@ -199,17 +199,20 @@ def test_next_batch_prefetch_is_bit_identical(cuda_ops):
     from percivaltts_b200.trainer import DeviceTrainer
     batches = [O.synthetic_batch(O.Arch(**MID), 2, 40, seed=300 + i)[:2] for i in range(5)]
     finals = []
-    for prefetch in (False, True):
+    for prefetch in (False, True, 'wrong hint'):
         ao, wg, wc, wgt, wct, X, Y, alpha, st = setup(cuda_ops, MID, 2, 40)
         tr = DeviceTrainer(st)
         costs = []
         for i, (Xb, Yb) in enumerate(batches):
             nxt = batches[i + 1] if prefetch and i + 1 < len(batches) else None
+            if prefetch == 'wrong hint' and i == 1:
+                nxt = batches[0]          # staged (and placed behind this step) but not what the next call brings
             costs.append(tr.train_on_batch(i * 5, Xb, Yb, next_batch=nxt))
         finals.append((costs, st.C.params.flat.clone(), st.G.params.flat.clone(), st.G.params.state.clone()))
-    assert finals[0][0] == finals[1][0]
-    for a_, b_ in zip(finals[0][1:], finals[1][1:]):
-        assert torch.equal(a_, b_)
+    for other in finals[1:]:
+        assert finals[0][0] == other[0]
+        for a_, b_ in zip(finals[0][1:], other[1:]):
+            assert torch.equal(a_, b_)
     assert all(np.isfinite(c[0]) for c in finals[0][0])
 
 
