@@ -194,11 +194,17 @@ int pctts_pml_linbnd2fwbnd(const float* in, const int* idx, const float* wgt, fl
 int pctts_pml_fwbnd2linbnd(const float* in, const int* idx, const float* wgt, float* out, long T, int K, int nbins, int smooth,
                            int do_exp, void* stream);
 
+/* ---- generation tail (modeltts.py:154-165 denormalise; vocoders.py:194-202 synthesis front half) ---------------------------- */
+/* v = cmp * std + mean per column (mean = std = NULL: none); out [T,O] = v (optional), f0 [T] = exp(v[:,0]), spec [T,S] = v[:,1:1+S],
+ * nm [T,NM] = v[:,1+S:1+S+NM] (each optional): contiguous inputs for pctts_pml_fwbnd2linbnd */
+int pctts_denorm_split(const float* cmp, const float* mean, const float* stdv, long T, int O, int S, int NM, float* out, float* f0,
+                       float* spec, float* nm, void* stream);
+
 /* ---- data-parallel exchange of the sync-BatchNorm sums over NVLink peer memory ------------------------------ */
 /* One-shot all-reduce (sum, rank order => bit-identical on every rank) of n <= nmax doubles: every rank owns a zero-initialised
  * symmetric buffer of pctts_peer_allreduce_bytes(world, nmax) bytes mapped into all peers; peer_bases (HOST array) holds the
  * address of rank r's buffer in this process.  All ranks must issue the same calls in the same order.  *err (device) becomes 1
- * if a peer did not arrive within ~2 s.  Asynchronous, capturable. */
+ * if a peer did not arrive within ~60 s (the caller must read it back: the sums are then invalid).  Asynchronous, capturable. */
 long pctts_peer_allreduce_bytes(int world, int nmax);
 int pctts_peer_allreduce_f64(double* x, int n, const unsigned long long* peer_bases, int rank, int world, int nmax, int* err,
                              void* stream);

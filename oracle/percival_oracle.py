@@ -435,15 +435,63 @@ def generator_step(a, wg, wc, ctx, real, errtype='WLSWGAN', fs=16000, LScoef=0.2
                 valid=valid.detach(), grads=gd, new_stats=new_stats)
 
 
+def generic_param_shapes(ctxsize, spec_size, nm_size, hiddenwidth, nlayers=3):
+    """Ordered [(name, shape, trainable)] of Generic(['FC']*nlayers) + network_final for PML without MLPG
+    (modeltts_common.py:36-55; pFC networktts.py:59-63; lo_f0spec / lo_nm networktts.py:196-197)."""
+    out, cin = [], ctxsize
+    for i in range(nlayers):
+        out.append(('g.fc%d.kernel' % i, (cin, hiddenwidth)))
+        out += _bn_entries('g.fc%d.bn' % i, hiddenwidth)
+        cin = hiddenwidth
+    out += [('g.f0spec.kernel', (cin, 1 + spec_size)), ('g.f0spec.bias', (1 + spec_size,)),
+            ('g.nm.kernel', (cin, nm_size)), ('g.nm.bias', (nm_size,))]
+    return [(n, s, not (n.endswith('moving_mean') or n.endswith('moving_var'))) for n, s in out]
+
+
+def generic_forward(w, ctx, training, new_stats=None):
+    """Generic FC graph: pFC = Dense(no bias) + BN + LeakyReLU (networktts.py:59-63) per layer, then
+    concat[Dense(1+S), Dense(NM, sigmoid)] (networktts.py:196-197,225).  The layer count is read off the weights."""
+    x, i = ctx, 0
+    while 'g.fc%d.kernel' % i in w:
+        x = lrelu(batchnorm(x @ w['g.fc%d.kernel' % i], w, 'g.fc%d.bn' % i, training, new_stats))
+        i += 1
+    f0spec = x @ w['g.f0spec.kernel'] + w['g.f0spec.bias']
+    nm = torch.sigmoid(x @ w['g.nm.kernel'] + w['g.nm.bias'])
+    return torch.cat([f0spec, nm], dim=-1)
+
+
 def lse_step(a, wg, ctx, real):
-    """OptimizerTTS LSE graph (optimizertts.py:56-57,386-402) on the DCNN generator."""
+    """OptimizerTTS LSE graph (optimizertts.py:56-57,386-402): loss = mean((y - model(x))^2), training-mode BatchNorm.
+    The model is the DCNN generator, or the Generic FC stack when `a` is None."""
     new_stats = OrderedDict()
-    pred = generator_forward(a, wg, ctx, training=True, new_stats=new_stats)
+    if a is None:
+        pred = generic_forward(wg, ctx, training=True, new_stats=new_stats)
+    else:
+        pred = generator_forward(a, wg, ctx, training=True, new_stats=new_stats)
     loss = ((real - pred) ** 2).mean()
     names = [k for k, v in wg.items() if v.requires_grad]
     grads = torch.autograd.grad(loss, [wg[k] for k in names], allow_unused=True)
     gd = OrderedDict((k, torch.zeros_like(wg[k]) if g is None else g.detach()) for k, g in zip(names, grads))
     return dict(loss=loss.detach(), pred=pred.detach(), grads=gd, new_stats=new_stats)
+
+
+class LSETrainer(object):
+    """OptimizerTTS.train_on_batch of the LSE scheme (optimizertts.py:378-402): Adam(lr=10^-3.39794, 0.9, 0.999, eps=1e-8),
+    returned cost = sqrt(loss)."""
+
+    def __init__(self, a, wg, dtype=torch.float32, lr=10 ** -3.39794, beta1=0.9, beta2=0.999, eps=1e-8):
+        self.a = a
+        self.wg = to_torch(wg, dtype, requires_grad=True)
+        self.opt = Adam(lr, beta1, beta2, eps)
+        self.dtype = dtype
+
+    def train_on_batch(self, X, Y):
+        r = lse_step(self.a, self.wg, torch.as_tensor(X, dtype=self.dtype), torch.as_tensor(Y, dtype=self.dtype))
+        self.opt.update(self.wg, r['grads'])
+        with torch.no_grad():
+            for k, v in r['new_stats'].items():
+                self.wg[k].copy_(v)
+        return math.sqrt(float(r['loss'])), r
 
 
 class Adam(object):

@@ -107,3 +107,16 @@ def compress_spectrum(SPEC, fs, spec_size):
 def decompress_spectrum(COMPSPEC, fs, dftlen):
     """vocoders.py:147-150 ('fwbnd' branch, pp_mcep=False)"""
     return np.exp(fwbnd2linbnd(COMPSPEC, fs, dftlen, smooth=True))
+
+
+def generation_tail(CMP, mean, std, fs, dftlen, spec_size, nm_size):
+    """De-normalisation + vocoder front half of generation, float64:
+    modeltts.py:156-158 (CMP*std + mean), vocoders.py:194-202 (f0 = exp(CMP[:,0]); SPEC = decompress_spectrum;
+    NM = fwbnd2linbnd(CMP[:, 1+S:1+S+NM])).  -> (CMP de-normalised, f0, SPEC, NM)"""
+    CMP = np.asarray(CMP, dtype=np.float64)
+    if mean is not None:
+        CMP = CMP * np.asarray(std, dtype=np.float64)[np.newaxis] + np.asarray(mean, dtype=np.float64)[np.newaxis]
+    f0 = np.exp(CMP[:, 0])
+    SPEC = decompress_spectrum(CMP[:, 1:1 + spec_size], fs, dftlen)
+    NM = fwbnd2linbnd(CMP[:, 1 + spec_size:1 + spec_size + nm_size], fs, dftlen)
+    return CMP, f0, SPEC, NM

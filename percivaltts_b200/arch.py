@@ -54,6 +54,28 @@ class Arch(object):
         return dict((k, getattr(self, k)) for k in self.FIELDS)
 
 
+class GenericArch(object):
+    """What Generic(ctxsize, vocoder, layertypes=[...], cfgarch) reads (modeltts_common.py:36-55): only 'FC' layers are on the
+    B200 path (the recurrent / gated / dropout builders of networktts.py:130-175 are not)."""
+
+    FIELDS = ('ctxsize', 'spec_size', 'nm_size', 'hiddenwidth', 'layertypes')
+
+    def __init__(self, ctxsize, spec_size, nm_size, hiddenwidth, layertypes=('FC', 'FC', 'FC')):
+        self.ctxsize, self.spec_size, self.nm_size = int(ctxsize), int(spec_size), int(nm_size)
+        self.hiddenwidth = int(hiddenwidth)
+        self.layertypes = list(layertypes)
+        for lt in self.layertypes:
+            if lt != 'FC':
+                raise ValueError('Unknown layer type ' + str(lt))     # networktts.py:171,177
+
+    @property
+    def outsize(self):
+        return 1 + self.spec_size + self.nm_size
+
+    def as_dict(self):
+        return dict((k, getattr(self, k)) for k in self.FIELDS)
+
+
 def _bn(prefix, ch):
     return [(prefix + '.gamma', (ch,), True), (prefix + '.beta', (ch,), True),
             (prefix + '.moving_mean', (ch,), False), (prefix + '.moving_var', (ch,), False)]

@@ -14,6 +14,7 @@ def get_ops():
     """The process-wide kernel interface (raises without a B200 or without libpctts.so)."""
     global _ops
     if _ops is None:
+        get_sync()                # under torchrun: rendezvous and torch.cuda.set_device(LOCAL_RANK) come first
         from .ops import CudaOps
         _ops = CudaOps()
     return _ops
@@ -23,6 +24,20 @@ def set_ops(ops):
     """Dependency injection for tests of the host logic (tests/cpu_ops_double.py)."""
     global _ops
     _ops = ops
+
+
+_sync = None
+
+
+def get_sync():
+    """The process-wide data-parallel exchange: under torchrun (WORLD_SIZE > 1) torch.distributed is initialised on first use
+    (NCCL, device = LOCAL_RANK) and a parallel.DistSync returned; otherwise None (single replica)."""
+    global _sync
+    import os
+    if _sync is None and int(os.environ.get('WORLD_SIZE', '1')) > 1:
+        from . import parallel
+        _sync, _ = parallel.init_from_env()
+    return _sync
 
 
 def set_seed(seed):

@@ -257,6 +257,30 @@ __global__ void uniform_kernel(float* __restrict__ out, int n, unsigned long lon
 __global__ void incr64_kernel(unsigned long long* c) {
     pdl_entry(); if (threadIdx.x == 0 && blockIdx.x == 0) *c += 1ull; }
 
+// Generation tail (modeltts.py:154-165 `denormalise`, vocoders.py:194-202 `synthesis`): CMP * std + mean per feature column,
+// split into the vocoder's streams so that the band decompression kernels read contiguous [T,K] inputs:
+//   out [T,O] (optional) the de-normalised features, f0 [T] = exp(out[:,0]), spec [T,S] = out[:,1:1+S], nm [T,NM] = out[:,1+S:1+S+NM]
+__global__ void denorm_split_kernel(const float* __restrict__ cmp, const float* __restrict__ mean, const float* __restrict__ stdv,
+                                    long T, int O, int S, int NM, float* __restrict__ out, float* __restrict__ f0,
+                                    float* __restrict__ spec, float* __restrict__ nm) {
+    pdl_entry();
+    const long n = T * O;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        const long t = i / O;
+        const int c = (int)(i - t * O);
+        float v = cmp[i];
+        if (mean) v = v * __ldg(stdv + c) + __ldg(mean + c);
+        if (out) out[i] = v;
+        if (c == 0) {
+            if (f0) f0[t] = expf(v);
+        } else if (c < 1 + S) {
+            if (spec) spec[t * S + (c - 1)] = v;
+        } else if (c < 1 + S + NM) {
+            if (nm) nm[t * NM + (c - 1 - S)] = v;
+        }
+    }
+}
+
 }  // namespace
 
 extern "C" int pctts_critic_pack_inputs(const float* real, const float* fake, const float* alpha, float* s0, int B, int T, int O,
@@ -364,6 +388,15 @@ extern "C" int pctts_pad_time(float* dst, const float* src, int B, int T, int C,
     const long n = (long)B * (T + left + right) * C;
     if (n == 0) return PCTTS_OK;
     pctts_launch(pad_time_kernel, ew_blocks(n), ET, 0, (cudaStream_t)stream, dst, src, B, T, C, left, right);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
+extern "C" int pctts_denorm_split(const float* cmp, const float* mean, const float* stdv, long T, int O, int S, int NM, float* out,
+                                  float* f0, float* spec, float* nm, void* stream) {
+    if (!cmp || T < 0 || O <= 0 || S < 0 || NM < 0 || 1 + S + NM > O || ((mean == nullptr) != (stdv == nullptr))) return PCTTS_EINVAL;
+    if (T == 0) return PCTTS_OK;
+    pctts_launch(denorm_split_kernel, ew_blocks(T * O), ET, 0, (cudaStream_t)stream, cmp, mean, stdv, T, O, S, NM, out, f0, spec, nm);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

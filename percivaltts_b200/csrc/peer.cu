@@ -20,7 +20,9 @@
 namespace {
 
 constexpr int PEER_MAX_WORLD = 16;
-constexpr long long PEER_SPIN_LIMIT = 4000000000LL;      // ~2 s of SM clocks: a missing peer ends in *err = 1, not in a hang
+constexpr long long PEER_SPIN_LIMIT = 120000000000LL;   // ~60 s of SM clocks: ordinary rank skew (a rank capturing a graph, a slow batch
+                                                         // load) is waited out like NCCL would; a peer that never comes ends in *err = 1 --
+                                                         // which the trainer reads back with the losses of every step and raises on
 
 __host__ __device__ inline long peer_data_offset(int world) { return 64 + ((2L * world * 8 + 127) / 128) * 128; }
 
@@ -90,7 +92,7 @@ extern "C" long pctts_peer_allreduce_bytes(int world, int nmax) {
 }
 
 /* x[0:n] (fp64, device, in place) <- sum over the ranks, in rank order.  peer_bases: HOST array of `world` addresses, the
- * symmetric buffer of rank r as mapped into this process; err: device int set to 1 if a peer did not show up in ~2 s. */
+ * symmetric buffer of rank r as mapped into this process; err: device int set to 1 if a peer did not show up in ~60 s. */
 extern "C" int pctts_peer_allreduce_f64(double* x, int n, const unsigned long long* peer_bases, int rank, int world, int nmax,
                                         int* err, void* stream) {
     if (!x || !peer_bases || !err || world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world || n < 0 || n > nmax)

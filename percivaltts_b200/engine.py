@@ -93,7 +93,119 @@ class _BN(object):
         self.invstd = ops.zeros(C)
 
 
-class Generator(object):
+class _BNNet(object):
+    """BatchNormalization(axis=-1) + LeakyReLU forward / backward shared by the generator-type networks
+    (pFC / pCNN1D / pCNN2D with bn=True, networktts.py:59-63,116-126)."""
+
+    def plan(self, B, T, with_backward=True):
+        key = (B, T, bool(with_backward))
+        pl = self._plans.get(key)
+        if pl is None:
+            pl = self._plans[key] = self._make_plan(B, T, with_backward)
+        return pl
+
+    def release(self, B, T, with_backward=None):
+        """Drop the buffers of one batch shape (the owner's LRU; with_backward selects the training or the inference plan)."""
+        for bwd in ((False, True) if with_backward is None else (bool(with_backward),)):
+            self._plans.pop((B, T, bwd), None)
+
+    def _bn_fwd(self, z2, y2, bn, training, update_stats, sync, ws=None, apply=True):
+        """ws: the batch sums when the producer of z2 already reduced them (Conv2D epilogue).  apply=False: only the
+        statistics (bn.mean / bn.invstd) -- the consumer applies BatchNorm + LeakyReLU on load."""
+        o, p = self.ops, self.params.p
+        g, b = p[bn.prefix + '.gamma'], p[bn.prefix + '.beta']
+        mm, mv = p[bn.prefix + '.moving_mean'], p[bn.prefix + '.moving_var']
+        if training:
+            if ws is None:
+                ws = o.bn_stats(z2, final=sync.world > 1 or not getattr(o, 'bn_single_launch', True))    # single replica: the second stage rides in bn_finalize's launch
+            sync.allreduce(ws.sums)
+            o.bn_finalize(ws, bn.rows * sync.world, A.BN_EPS, A.BN_MOMENTUM, bn.mean, bn.invstd,
+                          mm if update_stats else None, mv if update_stats else None)
+            if apply:
+                o.bn_apply(z2, y2, bn.mean, bn.invstd, g, b, A.BN_EPS, 0, 1)
+        else:
+            o.bn_apply(z2, y2, mm, mv, g, b, A.BN_EPS, 1, 1)
+
+    def _bn_bwd(self, z2, dy2, dz2, bn, sync):
+        o, p, g = self.ops, self.params.p, self.params.g
+        gam, bet = p[bn.prefix + '.gamma'], p[bn.prefix + '.beta']
+        ws = o.bn_bwd_reduce(z2, dy2, bn.mean, bn.invstd, gam, bet, 1)
+        sync.allreduce(ws.sums)
+        # dgamma / dbeta come from the all-reduced sums, i.e. every rank holds the global value: pre-divide by world so
+        # that the all-reduce(sum) of the flat gradient buffer does not count them `world` times
+        o.bn_bwd_apply(ws, z2, dy2, dz2, bn.mean, bn.invstd, gam, bet, bn.rows * sync.world, 1,
+                       g[bn.prefix + '.gamma'], g[bn.prefix + '.beta'], grad_scale=1.0 / sync.world)
+
+
+class GenericFC(_BNNet):
+    """Generic(['FC', ...]) + network_final for the PML vocoder without MLPG (modeltts_common.py:36-55):
+    pFC = Dense(no bias) + BN + LeakyReLU per layer (networktts.py:59-63,138-141), then
+    concat[Dense(1+spec), Dense(nm, sigmoid)] (networktts.py:196-197,225).  ctx [B,T,ctxsize] -> [B,T,1+spec+nm]."""
+
+    def __init__(self, ops, arch, params=None):
+        self.ops, self.a = ops, arch
+        self.params = params if params is not None else ParamStore(ops, A.generic_param_shapes(
+            arch.ctxsize, arch.spec_size, arch.nm_size, arch.hiddenwidth, arch.layertypes))
+        self._plans = {}
+
+    def _make_plan(self, B, T, bwd):
+        o, a = self.ops, self.a
+        M, H, L = B * T, a.hiddenwidth, len(a.layertypes)
+        pl = dict(B=B, T=T, M=M)
+        pl['z'] = [o.empty(M, H) for _ in range(L)]
+        pl['y'] = [o.empty(M, H) for _ in range(L)]
+        pl['bn'] = [_BN(o, 'g.fc%d.bn' % i, M, H) for i in range(L)]
+        if bwd:
+            pl['dA'], pl['dB'] = o.empty(M, H), o.empty(M, H)
+            pl['dfs'] = o.empty(M, 1 + a.spec_size)
+            pl['dz_nm'] = o.empty(M, a.nm_size)
+        return pl
+
+    def forward(self, pl, ctx, out, training=True, update_stats=False, sync=None):
+        o, a, p = self.ops, self.a, self.params.p
+        sync = sync or LocalSync()
+        M, S = pl['M'], a.spec_size
+        x2 = ctx.reshape(M, a.ctxsize)
+        for i in range(len(a.layertypes)):
+            o.gemm(x2, p['g.fc%d.kernel' % i], pl['z'][i])
+            self._bn_fwd(pl['z'][i], pl['y'][i], pl['bn'][i], training, update_stats, sync)
+            x2 = pl['y'][i]
+        out2 = out.view(M, a.outsize)
+        o.gemm(x2, p['g.f0spec.kernel'], out2[:, 0:1 + S], bias=p['g.f0spec.bias'])
+        o.gemm(x2, p['g.nm.kernel'], out2[:, 1 + S:], bias=p['g.nm.bias'], flags=EPI_SIGMOID)
+        pl['ctx_in'], pl['last'] = ctx, x2
+        return out
+
+    def backward(self, pl, out, dout, sync=None):
+        """dout = d(loss)/d(out) [B,T,O]; fills params.g for every trainable parameter."""
+        o, a, p, g = self.ops, self.a, self.params.p, self.params.g
+        sync = sync or LocalSync()
+        M, S, O, L = pl['M'], a.spec_size, a.outsize, len(a.layertypes)
+        out2, dout2 = out.view(M, O), dout.view(M, O)
+        xlast = pl['last']
+        o.sigmoid_bwd(dout2[:, 1 + S:], out2[:, 1 + S:], pl['dz_nm'])
+        o.gemm(xlast, pl['dz_nm'], g['g.nm.kernel'], transA=True)
+        o.colsum(pl['dz_nm'], g['g.nm.bias'])
+        o.copy2d(pl['dfs'], dout2[:, 0:1 + S])
+        o.gemm(xlast, pl['dfs'], g['g.f0spec.kernel'], transA=True)
+        o.colsum(pl['dfs'], g['g.f0spec.bias'])
+        if L == 0:
+            return
+        dcur = pl['dA']
+        o.gemm(pl['dz_nm'], p['g.nm.kernel'], dcur, transB=True)
+        o.gemm(pl['dfs'], p['g.f0spec.kernel'], dcur, transB=True, flags=EPI_ACCUM)
+        for i in range(L - 1, -1, -1):
+            xin = pl['y'][i - 1] if i > 0 else pl['ctx_in'].reshape(M, a.ctxsize)
+            dz = pl['dB'] if dcur is pl['dA'] else pl['dA']
+            self._bn_bwd(pl['z'][i], dcur, dz, pl['bn'][i], sync)
+            o.gemm(xin, dz, g['g.fc%d.kernel' % i], transA=True)
+            if i > 0:
+                dnext = pl['dA'] if dz is pl['dB'] else pl['dB']
+                o.gemm(dz, p['g.fc%d.kernel' % i], dnext, transB=True)
+                dcur = dnext
+
+
+class Generator(_BNNet):
     """DCNNF0SpecNoiseFeatures (modeltts_common.py:61-126): ctx [B,T,ctxsize] -> [B,T,1+spec+nm]."""
 
     def __init__(self, ops, arch, params=None):
@@ -104,13 +216,6 @@ class Generator(object):
         self._plans = {}
 
     # ---- buffers ----------------------------------------------------------------------------------------------
-    def plan(self, B, T, with_backward=True):
-        key = (B, T, bool(with_backward))
-        pl = self._plans.get(key)
-        if pl is None:
-            pl = self._plans[key] = self._make_plan(B, T, with_backward)
-        return pl
-
     def _make_plan(self, B, T, bwd):
         o, a = self.ops, self.a
         H, S, NM, O, Fl, W = a.hiddenwidth, a.spec_size, a.nm_size, a.outsize, a.gen_nbfilters, a.ctx_winlen
@@ -161,23 +266,6 @@ class Generator(object):
         return pl
 
     # ---- forward ----------------------------------------------------------------------------------------------
-    def _bn_fwd(self, z2, y2, bn, training, update_stats, sync, ws=None, apply=True):
-        """ws: the batch sums when the producer of z2 already reduced them (Conv2D epilogue).  apply=False: only the
-        statistics (bn.mean / bn.invstd) -- the consumer applies BatchNorm + LeakyReLU on load."""
-        o, p = self.ops, self.params.p
-        g, b = p[bn.prefix + '.gamma'], p[bn.prefix + '.beta']
-        mm, mv = p[bn.prefix + '.moving_mean'], p[bn.prefix + '.moving_var']
-        if training:
-            if ws is None:
-                ws = o.bn_stats(z2, final=sync.world > 1 or not getattr(o, 'bn_single_launch', True))    # single replica: the second stage rides in bn_finalize's launch
-            sync.allreduce(ws.sums)
-            o.bn_finalize(ws, bn.rows * sync.world, A.BN_EPS, A.BN_MOMENTUM, bn.mean, bn.invstd,
-                          mm if update_stats else None, mv if update_stats else None)
-            if apply:
-                o.bn_apply(z2, y2, bn.mean, bn.invstd, g, b, A.BN_EPS, 0, 1)
-        else:
-            o.bn_apply(z2, y2, mm, mv, g, b, A.BN_EPS, 1, 1)
-
     def forward(self, pl, ctx, out, training=True, update_stats=False, sync=None, spec_only=False, materialize=True):
         """ctx [B,T,ctxsize] -> out [B,T,O] (both contiguous device tensors).  training: BN uses batch statistics
         (all-reduced through `sync`); update_stats: also move the BN moving averages (generator step only).
@@ -248,16 +336,6 @@ class Generator(object):
         return out
 
     # ---- backward ---------------------------------------------------------------------------------------------
-    def _bn_bwd(self, z2, dy2, dz2, bn, sync):
-        o, p, g = self.ops, self.params.p, self.params.g
-        gam, bet = p[bn.prefix + '.gamma'], p[bn.prefix + '.beta']
-        ws = o.bn_bwd_reduce(z2, dy2, bn.mean, bn.invstd, gam, bet, 1)
-        sync.allreduce(ws.sums)
-        # dgamma / dbeta come from the all-reduced sums, i.e. every rank holds the global value: pre-divide by world so
-        # that the all-reduce(sum) of the flat gradient buffer does not count them `world` times
-        o.bn_bwd_apply(ws, z2, dy2, dz2, bn.mean, bn.invstd, gam, bet, bn.rows * sync.world, 1,
-                       g[bn.prefix + '.gamma'], g[bn.prefix + '.beta'], grad_scale=1.0 / sync.world)
-
     def backward(self, pl, out, dout, sync=None):
         """dout = d(loss)/d(out) [B,T,O]; fills params.g for every trainable generator parameter."""
         o, a, p, g = self.ops, self.a, self.params.p, self.params.g
@@ -378,6 +456,11 @@ class Critic(object):
         if pl is None:
             pl = self._plans[key] = self._make_plan(napp, B, T)
         return pl
+
+    def release(self, B, T):
+        """Drop the buffers of one batch shape (trainer's LRU)."""
+        for key in [k for k in self._plans if k[1:] == (B, T)]:
+            del self._plans[key]
 
     def _make_plan(self, napp, B, T):
         o, a = self.ops, self.a

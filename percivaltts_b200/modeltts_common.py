@@ -2,7 +2,8 @@
 Model definitions (reference percivaltts/modeltts_common.py:36-126).
 
 DCNNF0SpecNoiseFeatures is the paper's generator; its graph is executed by engine.Generator.
-Generic is kept for its parameter inventory (the reference's pinned count_params()==2195 known answer).
+Generic (FC layers) is executed by engine.GenericFC; with OptimizerTTS's LSE hooks it is the reference's plain
+least-squares training path (optimizertts.py:378-436).  count_params()==2195 is the reference's pinned known answer.
 """
 from . import arch as A
 from . import modeltts
@@ -17,9 +18,10 @@ class Generic(modeltts.ModelTTS):
             return
         if vocoder.mlpg_wins is not None:
             raise NotImplementedError('MLPG output layers are not on the B200 path')
+        arch = A.GenericArch(ctxsize, vocoder.specsize(), vocoder.noisesize(), cfgarch.arch_hiddenwidth, layertypes)
         shapes = A.generic_param_shapes(ctxsize, vocoder.specsize(), vocoder.noisesize(), cfgarch.arch_hiddenwidth,
                                         layertypes)
-        self.kerasmodel = modeltts.NativeNetwork('generic', None, shapes)
+        self.kerasmodel = modeltts.NativeNetwork('generic', arch, shapes)
         self.kerasmodel.summary()
 
 

@@ -186,6 +186,8 @@ class CudaOps(object):
         self._lse_ws = None
         self._splitk_ws = {}       # lane -> split-K workspace
         self._ws_keep = []
+        self._tag = None           # batch-shape tag (shape_scope): per-shape scratch is recorded under it and freed by release_shape()
+        self._tagged = {}          # tag -> list of (dict, key) entries created while the tag was active
         self._lane = 0             # 0 = the caller's stream; 1 = the side stream of side_lane()
         self._side = None
         self.lanes = os.environ.get('PCTTS_LANES', '1') != '0'   # run independent branches of a step on two streams
@@ -200,11 +202,37 @@ class CudaOps(object):
         _lib.check(rc, what)
 
     def reduce_ws(self, rows, C):
-        key = (self._lane, int(rows), int(C))
+        key = (self._tag, self._lane, int(rows), int(C))
         ws = self._red.get(key)
         if ws is None:
-            ws = self._red[key] = ReduceWorkspace(self.lib, key[1], key[2], self.device)
+            ws = self._red[key] = ReduceWorkspace(self.lib, key[2], key[3], self.device)
+            self._note(self._red, key)
         return ws
+
+    # -- per-batch-shape scratch (operand shadows of activations, reduction / weight-gradient workspaces, row parents) --------
+    @contextlib.contextmanager
+    def shape_scope(self, tag):
+        """Scratch allocated inside belongs to the batch shape `tag` and is freed as a whole by release_shape(tag): the step's
+        buffers are created per (B, T), and a training run meets many T (shortest utterance of each batch)."""
+        outer, self._tag = self._tag, tag
+        try:
+            yield self
+        finally:
+            self._tag = outer
+
+    def _note(self, table, key):
+        if self._tag is not None:
+            self._tagged.setdefault(self._tag, []).append((table, key))
+
+    def release_shape(self, tag):
+        """Free everything recorded under `tag` (captured graphs that used it must be dropped by the caller first)."""
+        for table, key in self._tagged.pop(tag, []):
+            if isinstance(table, list):
+                if key in table:
+                    table.remove(key)
+            else:
+                table.pop(key, None)
+        self._fresh.clear()
 
     # -- two-lane execution: independent branches of a step on two streams (fork / join, capturable) ------------------
     @contextlib.contextmanager
@@ -305,7 +333,9 @@ class CudaOps(object):
         if self.nterms == 0:
             return
         assert t.dim() == 2 and t.is_contiguous()
-        self._parents.append(_RowParent(t, Shadow(self.device, t.shape[0], t.shape[1], PLANES[self.nterms])))
+        par = _RowParent(t, Shadow(self.device, t.shape[0], t.shape[1], PLANES[self.nterms]))
+        self._parents.append(par)
+        self._note(self._parents, par)
 
     def _row_parent(self, t):
         if t.dim() != 2 or not self._parents:
@@ -349,10 +379,12 @@ class CudaOps(object):
             return ShadowRows(par.shadow, r0, t.shape[0])
         key = (t.data_ptr(), tuple(t.shape), tuple(t.stride()))
         sh = self._shadows.get(key)
+        ptr = key[0]
         if sh is None:
             _, _, _, _, rows, cols = _mat(t)
             sh = self._shadows[key] = Shadow(self.device, rows, cols, PLANES[self.nterms])
-        ptr = key[0]
+            if not self._is_persistent(ptr):
+                self._note(self._shadows, key)
         if self._is_persistent(ptr):
             if key not in self._persist:
                 self._persist[key] = (sh, t)
@@ -541,9 +573,11 @@ class CudaOps(object):
         assert ci == CIN and tuple(dy.shape) == (N, T, F, COUT) and dw.is_contiguous()
         pad_t, pad_f = ((KH - 1) // 2, (KW - 1) // 2) if pad is None else pad
         key = (N, T, CIN, COUT, KH, KW)
-        ws = self._wg.get((self._lane,) + key)
+        wkey = (self._tag, self._lane) + key
+        ws = self._wg.get(wkey)
         if ws is None:
-            ws = self._wg[(self._lane,) + key] = self.empty(max(self.lib.pctts_conv2d_wgrad_workspace(*key), 148 * (KH * KW * CIN * COUT + COUT)))
+            ws = self._wg[wkey] = self.empty(max(self.lib.pctts_conv2d_wgrad_workspace(*key), 148 * (KH * KW * CIN * COUT + COUT)))
+            self._note(self._wg, wkey)
         px, xb, xp = _map4(x)
         pd, db, dp = _map4(dy)
         nb = N if bias_samples is None else int(bias_samples)
@@ -731,6 +765,19 @@ class CudaOps(object):
         assert counter.dtype == torch.int64
         self._ck(self.lib.pctts_uniform(out.data_ptr(), out.numel(), int(seed), counter.data_ptr(), self._stream()),
                  'pctts_uniform')
+
+    # -- generation tail -------------------------------------------------------------------------------------
+    def denorm_split(self, cmp, mean, std, S, NM, out=None, f0=None, spec=None, nm=None):
+        """cmp [T,O] * std + mean (None: no de-normalisation) -> out [T,O], f0 [T] = exp(col 0), spec [T,S], nm [T,NM] (each
+        optional): modeltts.py:154-165 (denormalise) + the slicing / exp of vocoders.py:194-201."""
+        T, O = cmp.shape
+        assert cmp.is_contiguous() and (mean is None) == (std is None)
+        for t, shape in ((out, (T, O)), (f0, (T,)), (spec, (T, S)), (nm, (T, NM))):
+            assert t is None or (tuple(t.shape) == shape and t.is_contiguous()), (shape,)
+        if mean is not None:
+            assert mean.numel() == O and std.numel() == O and mean.is_contiguous() and std.is_contiguous()
+        self._ck(self.lib.pctts_denorm_split(cmp.data_ptr(), _ptr(mean), _ptr(std), T, O, S, NM, _ptr(out), _ptr(f0), _ptr(spec),
+                                             _ptr(nm), self._stream()), 'pctts_denorm_split')
 
     # -- PML band compression --------------------------------------------------------------------------------
     def pml_linbnd2fwbnd(self, x, idx, wgt, out, log_abs):

@@ -6,7 +6,8 @@ update_validation_cost(costs, X_vals, Y_vals), saveTrainingStateLossSpecific(fst
 loadTrainingStateLossSpecific(fstate).
 
 The loop stays host python (it is the caller of the hot path, not part of it); plots are out of scope.
-The plain 'LSE' training of the reference (:378-436) is not on the B200 path: use OptimizerTTSWGAN.
+The base class itself is the reference's plain least-squares ('LSE') optimizer (:378-436): its step runs on the GPU through
+lse.LSEStepper (forward, loss + gradient, backward, Adam: the same kernels as the WGAN-GP path).
 """
 import copy
 import glob
@@ -63,26 +64,63 @@ class OptimizerTTS(object):
         print('Training configuration')
         self.cfg.print_content()
 
-    # ---- hooks to be overridden ---------------------------------------------------------------------------------
-    def default_options(self, cfg):
-        return cfg
-
+    # ---- hooks; the defaults are the LSE (MSE) scheme of the reference (optimizertts.py:375-436) ---------------------------
     supports_prefetch = False      # train_on_batch() takes next_batch=(X, Y) (B200 addition; the reference loads synchronously)
 
-    def prepare(self):
-        raise NotImplementedError('prepare() has to be provided by the loss-specific sub-class')
+    def default_options(self, cfg):
+        """optimizertts.py:378-384"""
+        cfg.train_lse_learningrate_log10 = -3.39794      # 10**-3.39794 = 0.0004
+        cfg.train_lse_adam_beta1 = 0.9
+        cfg.train_lse_adam_beta2 = 0.999
+        cfg.train_lse_adam_epsilon_log10 = -8
+        return cfg
+
+    def prepare(self, sync=None, ops=None):
+        """optimizertts.py:386-397: Adam on lse_loss = mean((y - model(x))^2)."""
+        print('    Prepare LSE training')
+        from . import backend_b200
+        from .lse import LSEStepper
+        ops = ops or backend_b200.get_ops()
+        module = self._model.kerasmodel.device_module(ops)
+        cfg = self.cfg
+        self.lse = LSEStepper(ops, module, lr=float(10 ** cfg.train_lse_learningrate_log10), beta1=float(cfg.train_lse_adam_beta1),
+                              beta2=float(cfg.train_lse_adam_beta2), eps=float(10 ** cfg.train_lse_adam_epsilon_log10),
+                              sync=sync if sync is not None else backend_b200.get_sync())
+        print('    optimizer: Adam')
 
     def train_on_batch(self, batchid, X_trab, Y_trab):
-        raise NotImplementedError('train_on_batch() has to be provided by the loss-specific sub-class')
+        """optimizertts.py:399-404: one update, returns sqrt(loss) (host numpy in, python float out)."""
+        import torch
+        dev = self.lse.ops.device
+        Xd = torch.from_numpy(np.ascontiguousarray(X_trab, dtype=np.float32)).to(dev)
+        Yd = torch.from_numpy(np.ascontiguousarray(Y_trab, dtype=np.float32)).to(dev)
+        self.lse.step(Xd, Yd)
+        return float(np.sqrt(float(self.lse.losses[0])))
 
     def update_validation_cost(self, costs, X_vals, Y_vals):
-        raise NotImplementedError('update_validation_cost() has to be provided by the loss-specific sub-class')
+        """optimizertts.py:406-412"""
+        costs['model_rmse_validation'].append(data.cost_model_prediction_rmse(self._model, [X_vals], Y_vals))
+        return costs['model_rmse_validation'][-1]
 
     def saveTrainingStateLossSpecific(self, fstate):
-        pass
+        """optimizertts.py:414-424 saved the compiled Keras model with its optimizer; here weights + Adam slots (rank 0)."""
+        if getattr(self.lse.sync, 'rank', 0) != 0:
+            return
+        store = self.lse.M.params
+        self._model.kerasmodel.save_weights(fstate + '.model.weights.npz')
+        np.savez(fstate + '.model.optimizer.npz', m=store.m.cpu().numpy(), v=store.v.cpu().numpy(), step=store.step.cpu().numpy())
 
     def loadTrainingStateLossSpecific(self, fstate):
-        pass
+        import torch
+        if getattr(self, 'lse', None) is None:
+            self.prepare()
+        self._model.kerasmodel.load_weights(fstate + '.model.weights.npz')
+        store = self.lse.M.params
+        with np.load(fstate + '.model.optimizer.npz') as z:
+            if z['m'].shape[0] == store.m.shape[0]:
+                store.m.copy_(torch.from_numpy(z['m']))
+                store.v.copy_(torch.from_numpy(z['v']))
+                store.step.copy_(torch.from_numpy(z['step']))
 
     # ---- training state (optimizertts.py:103-145) -------------------------------------------------------------------
     def saveTrainingState(self, fstate, extras=None, printfn=print):
@@ -132,6 +170,16 @@ class OptimizerTTS(object):
             print('    scaled number of epochs: min={} max={}'.format(cfg.train_min_nbepochs, cfg.train_max_nbepochs))
 
         self.prepare()
+        # data parallel (torchrun, one process per GPU): every rank draws the SAME global batch (same numpy RNG stream) and keeps
+        # its utterances [r*B/N, (r+1)*B/N); files are written by rank 0 only; validation decisions are rank 0's
+        sync = getattr(self, 'sync', None) or getattr(getattr(self, 'lse', None), 'sync', None)
+        world, rank = getattr(sync, 'world', 1), getattr(sync, 'rank', 0)
+        if cfg.train_batch_size % world:
+            raise ValueError('train_batch_size={} does not split over {} ranks'.format(cfg.train_batch_size, world))
+
+        def shard(A):
+            n = A.shape[0] // world
+            return A[rank * n:(rank + 1) * n]
 
         costs = defaultdict(list)
         epochs_modelssaved, epochs_durs = [], []
@@ -162,9 +210,10 @@ class OptimizerTTS(object):
             costs_tra_batches, load_times, train_times = [], [], []
             def load_batch(bid):
                 fid_lst_trab = [fid_lst_tra[bidx] for bidx in rndidxb[bid]]
-                return data.load_inoutset(indir, outdir, wdir, fid_lst_trab, length=cfg.train_batch_length,
-                                          lengthmax=cfg.train_batch_lengthmax,
-                                          maskpadtype=cfg.train_batch_padtype, cropmode=cfg.train_batch_cropmode)
+                Xb, Yb, Wb = data.load_inoutset(indir, outdir, wdir, fid_lst_trab, length=cfg.train_batch_length,
+                                                lengthmax=cfg.train_batch_lengthmax,
+                                                maskpadtype=cfg.train_batch_padtype, cropmode=cfg.train_batch_cropmode)
+                return (shard(Xb), shard(Yb), shard(Wb)) if world > 1 else (Xb, Yb, Wb)
             # one batch of look-ahead: batch i+1 is read (same order of numpy RNG draws as the reference, which loads batch by
             # batch, optimizertts.py:231-232) before batch i trains, so that its host->device copy overlaps the kernels of batch i
             t0 = time.time()
@@ -190,6 +239,8 @@ class OptimizerTTS(object):
             costs['model_training'].append(np.mean(costs_tra_batches) if costs_tra_batches else float('nan'))
 
             cost_val = self.update_validation_cost(costs, X_vals, Y_vals)
+            if world > 1:
+                cost_val = sync.broadcast_scalar(cost_val)      # the random interpolation weights differ per replica
 
             print_log('    E{}/{} {}  cost_tra={:.6f} (load:{}s train:{}s)  cost_val={:.6f} ({:.4f}% RMSE)  {} MiB GPU {} MiB RAM'.format(
                 epoch, cfg.train_max_nbepochs, trialstr, costs['model_training'][-1], time2str(np.sum(load_times)),
@@ -198,12 +249,14 @@ class OptimizerTTS(object):
             if np.isnan(cost_val):
                 raise ValueError('ERROR: Validation cost is nan!')
 
-            self._model.save(fbase + '-last.h5', printfn=print_log, extras={'cost_val': cost_val})
+            if rank == 0:
+                self._model.save(fbase + '-last.h5', printfn=print_log, extras={'cost_val': cost_val})
             if epoch >= cfg.train_min_nbepochs:
                 if best_val is None or cost_val < best_val:
                     best_val = cost_val
-                    self._model.save(params_savefile, printfn=print_log, extras={'cost_val': cost_val},
-                                     infostr='(E{} C{:.4f})'.format(epoch, best_val))
+                    if rank == 0:
+                        self._model.save(params_savefile, printfn=print_log, extras={'cost_val': cost_val},
+                                         infostr='(E{} C{:.4f})'.format(epoch, best_val))
                     epochs_modelssaved.append(epoch)
                     nbnodecepochs = 0
                 else:
@@ -212,9 +265,12 @@ class OptimizerTTS(object):
             epochs_durs.append(time.time() - timeepochstart)
             print_log('    ET: {}   train ~time left: {}'.format(
                 time2str(epochs_durs[-1]), time2str(np.median(epochs_durs[-10:]) * (cfg.train_max_nbepochs - epoch))))
-            self.saveTrainingState(fstate, printfn=print_log, extras={
-                'cost_val': cost_val, 'best_val': best_val, 'costs': costs, 'epochs_modelssaved': epochs_modelssaved,
-                'epochs_durs': epochs_durs, 'nbnodecepochs': nbnodecepochs, 'epoch': epoch})
+            if rank == 0:
+                self.saveTrainingState(fstate, printfn=print_log, extras={
+                    'cost_val': cost_val, 'best_val': best_val, 'costs': costs, 'epochs_modelssaved': epochs_modelssaved,
+                    'epochs_durs': epochs_durs, 'nbnodecepochs': nbnodecepochs, 'epoch': epoch})
+            if world > 1:
+                sync.barrier()          # the files of this epoch exist before any rank goes on (or returns)
             if nbnodecepochs >= cfg.train_cancel_nodecepochs:
                 print_log('WARNING: validation error did not decrease for {} epochs. Early stop!'.format(cfg.train_cancel_nodecepochs))
                 break

@@ -85,6 +85,28 @@ class DistSync(object):
             return False
         return True
 
+    def broadcast_scalar(self, x, src=0):
+        """The python float of rank `src` on every rank (model-selection decisions must agree across the replicas)."""
+        dev = torch.device('cuda', torch.cuda.current_device()) if dist.get_backend(self.group) == 'nccl' else torch.device('cpu')
+        t = torch.tensor([float(x)], dtype=torch.float64, device=dev)
+        dist.broadcast(t, src=src, group=self.group)
+        return float(t.item())
+
+    def barrier(self):
+        dist.barrier(group=self.group)
+
+    @property
+    def peer_err(self):
+        """Device int32 [1] raised by a timed-out peer exchange (None without peer memory)."""
+        return self._peer[2] if self._peer is not None else None
+
+    def check_peer(self):
+        """Raise if a peer-memory exchange timed out since the last check (one 4-byte device read: call it where the step's
+        losses are read anyway)."""
+        if self._peer is not None and int(self._peer[2]) != 0:
+            raise _lib.PcttsError('a sync-BatchNorm exchange over NVLink peer memory timed out waiting for a peer rank: the '
+                                  'statistics of this step are invalid (rank %d of %d)' % (self.rank, self.world))
+
     def peer_failed(self):
         """True if an exchange timed out waiting for a peer (the step's results are then invalid)."""
         return self._peer is not None and int(self._peer[2]) != 0

@@ -5,6 +5,9 @@ OptimizerTTSWGAN.train_on_batch (reference percivaltts/optimizertts_wgan.py:216-
 
 One process drives one GPU; under torch.distributed every rank runs the same code on its shard of the batch.
 """
+import os
+from collections import OrderedDict
+
 import numpy as np
 import torch
 
@@ -23,16 +26,28 @@ class _ShapeState(object):
         self.Xh = torch.empty(B, T, a.ctxsize, dtype=torch.float32, pin_memory=cuda)
         self.Yh = torch.empty(B, T, a.outsize, dtype=torch.float32, pin_memory=cuda)
         self.lossh = torch.zeros(W.NLOSS, dtype=torch.float32, pin_memory=cuda)
+        self.errh = torch.zeros(1, dtype=torch.int32, pin_memory=cuda)       # peer-exchange time-out flag, read with the losses
         self.g_critic = self.g_critic_alpha = self.g_gen = None
 
 
 class DeviceTrainer(object):
-    def __init__(self, stepper, use_graphs=True, max_shapes=8):
+    """Per batch shape (B, T) the trainer owns ONE entry -- static input buffers, the stepper's and both networks' buffers, the
+    kernels' scratch recorded under the shape tag, and (for shapes that recur) three captured CUDA graphs.  The entries live in an
+    LRU bounded by count and by measured device bytes: a training run meets many T (T = shortest utterance of the batch capped
+    at lengthmax, data.py:250-262; validation one T per utterance), and evicting an entry frees all of it together.
+    A shape is run eagerly the first `graph_after` times it is seen and captured after that (capture = warm-up + 3 captures,
+    seconds against a ~3 ms step)."""
+
+    def __init__(self, stepper, use_graphs=True, max_shapes=None, max_bytes=None, graph_after=1):
         self.st = stepper
         self.ops = stepper.ops
         self.use_graphs = bool(use_graphs) and self.ops.device.type == 'cuda'
-        self.max_shapes = max_shapes
-        self._shapes = {}
+        self.max_shapes = int(max_shapes if max_shapes is not None else os.environ.get('PCTTS_SHAPE_CACHE', '128'))
+        self.max_bytes = int(max_bytes if max_bytes is not None else float(os.environ.get('PCTTS_SHAPE_CACHE_GB', '32')) * 2 ** 30)
+        self.graph_after = int(graph_after)
+        self._shapes = OrderedDict()
+        self._seen = {}
+        self.evictions = 0
         self.generator_updates = 0
         self.h2d_bytes = 0
         self.d2h_bytes = 0
@@ -44,16 +59,40 @@ class DeviceTrainer(object):
         self._copy_stream = None
 
     # ---- shape state / graph capture ---------------------------------------------------------------------------
-    def shape_state(self, B, T):
+    def _mem(self):
+        return torch.cuda.memory_allocated(self.ops.device) if self.ops.device.type == 'cuda' else 0
+
+    def _evict(self, keep):
+        """Drop least-recently-used shapes until the cache is within its limits (never the entry `keep`)."""
+        while len(self._shapes) > 1 and (len(self._shapes) > self.max_shapes or
+                                         sum(e.bytes for e in self._shapes.values()) > self.max_bytes):
+            key = next(k for k in self._shapes if k != keep)
+            old = self._shapes.pop(key)
+            if self._pf_placed is old:
+                self._pf_placed = None
+            old.g_critic = old.g_critic_alpha = old.g_gen = None      # the graphs (and their private pools) go first
+            del old
+            self.st.release(*key)
+            self.evictions += 1
+
+    def shape_state(self, B, T, capture=True):
+        """The entry of (B, T), created on first use; capture=True also makes sure its CUDA graphs exist."""
         key = (B, T)
         s = self._shapes.get(key)
         if s is None:
-            if len(self._shapes) >= self.max_shapes:
-                self._shapes.pop(next(iter(self._shapes)))
+            m0 = self._mem()
             s = self._shapes[key] = _ShapeState(self.ops, self.st.a, B, T)
-            if self.use_graphs:
-                self._capture(s)
+            s.m0, s.bytes = m0, 0
+        else:
+            self._shapes.move_to_end(key)
+        if capture and self.use_graphs and s.g_critic is None:
+            self._capture(s)
+            self._account(s)
         return s
+
+    def _account(self, s):
+        s.bytes = max(s.bytes, self._mem() - s.m0)
+        self._evict(keep=(s.B, s.T))
 
     def _capture(self, s):
         """Warm up eagerly on a side stream (allocates every plan buffer and workspace; parameters, BN moving
@@ -84,17 +123,29 @@ class DeviceTrainer(object):
 
     # ---- steps on resident device data ---------------------------------------------------------------------------
     def critic_step_device(self, s, explicit_alpha=False):
-        if self.use_graphs:
+        if s.g_critic is not None:
             (s.g_critic_alpha if explicit_alpha else s.g_critic).replay()
         else:
             self.st.critic_step(s.X, s.Y, alpha=s.alpha if explicit_alpha else None, apply=True)
+            self._account(s)
 
     def generator_step_device(self, s):
-        if self.use_graphs:
+        if s.g_gen is not None:
             s.g_gen.replay()
         else:
             self.st.generator_step(s.X, s.Y, apply=True)
+            self._account(s)
         self.generator_updates += 1
+
+    # ---- validation on resident device data (optimizertts_wgan.py:244-268) ------------------------------------------------
+    def evaluate_device(self, Xd, Yd, out_row):
+        """Inference-mode losses of one utterance batch (device tensors [B,T,*]) -> out_row [NLOSS] (device), no host sync.
+        Validation shapes are run eagerly (one T per utterance, each seen once per epoch) through the same shape cache."""
+        B, T = int(Xd.shape[0]), int(Xd.shape[1])
+        s = self.shape_state(B, T, capture=False)
+        self.st.evaluate_losses(Xd, Yd)
+        out_row.copy_(self.st.losses, non_blocking=True)
+        self._account(s)
 
     # ---- the reference's per-batch entry point ---------------------------------------------------------------------
     def stage(self, s, X, Y, alpha=None):
@@ -142,7 +193,9 @@ class DeviceTrainer(object):
         like the reference's float(critic_returns), optimizertts_wgan.py:220-221).
         next_batch = (X, Y) of the following call, if known: it is staged to the device while this batch computes."""
         B, T = int(X.shape[0]), int(X.shape[1])
-        s = self.shape_state(B, T)
+        seen = self._seen.get((B, T), 0)
+        self._seen[(B, T)] = seen + 1
+        s = self.shape_state(B, T, capture=seen >= self.graph_after)
         pf = self._pf
         if pf is not None and alpha is None and (pf[0] is X or (pf[2] == tuple(X.shape) and np.shares_memory(pf[0], X))) \
                 and (pf[1] is Y or (pf[3] == tuple(Y.shape) and np.shares_memory(pf[1], Y))):
@@ -162,6 +215,10 @@ class DeviceTrainer(object):
             trained_gen = True
         s.lossh.copy_(self.st.losses, non_blocking=True)
         self.d2h_bytes += W.NLOSS * 4
+        perr = getattr(self.st.sync, 'peer_err', None)
+        if perr is not None:
+            s.errh.copy_(perr, non_blocking=True)
+            self.d2h_bytes += 4
         if next_batch is not None:
             self._prefetch(next_batch[0], next_batch[1])
             if self._pf is not None and tuple(self._pf[2][:2]) == (B, T):
@@ -174,6 +231,9 @@ class DeviceTrainer(object):
                 self._pf_placed = s
         if self.ops.device.type == 'cuda':
             torch.cuda.current_stream(self.ops.device).synchronize()
+        if perr is not None and int(s.errh[0]) != 0:
+            # a sync-BatchNorm exchange gave up waiting for a peer: statistics, gradients and the update of this step are garbage
+            self.st.sync.check_peer()
         critic_cost = float(s.lossh[W.L_CRITIC])
         gen_cost = float(s.lossh[W.L_GEN]) if trained_gen else None
         return critic_cost, gen_cost

@@ -105,20 +105,70 @@ class VocoderPML(VocoderF0Spec):
         """[T, nm_size] -> [T, dftlen/2+1], plain linear interpolation (vocoders.py:202)."""
         return sp.fwbnd2linbnd(NM, self.fs, self.dftlen)
 
-    def decompress_features(self, CMP):
-        """The device-side part of synthesis() (vocoders.py:194-202): -> (f0 [T], SPEC [T,bins], NM [T,bins])."""
-        CMP = np.asarray(CMP, dtype=np.float32)
-        f0 = np.exp(CMP[:, 0])
-        SPEC = self.decompress_spectrum(CMP[:, 1:1 + self.spec_size])
-        NM = self.decompress_noisemask(CMP[:, 1 + self.spec_size:1 + self.spec_size + self.nm_size])
-        return f0, SPEC, NM
+    def decompress_features_device(self, cmp, mean=None, std=None, ops=None, keep_cmp=False):
+        """The generation tail on the device, chained without leaving HBM:
+            cmp [T,O] (device, the generator's output) -> de-normalise with mean4norm / std4norm (modeltts.py:154-165) ->
+            f0 = exp(.[:,0]), SPEC = exp(fwbnd2linbnd(.[:,1:1+S], smooth)), NM = fwbnd2linbnd(.[:,1+S:]) (vocoders.py:194-202).
+        Returns one flat device buffer laid out [f0 (T) | SPEC (T*bins) | NM (T*bins) | de-normalised cmp (T*O) if keep_cmp] and
+        the views (f0, SPEC, NM, CMP or None) into it: ONE device->host copy brings everything the synthesiser needs."""
+        import torch
+        ops = ops or sp.backend_b200.get_ops()
+        T, O = cmp.shape
+        S, NMs, bins = self.spec_size, self.nm_size, self.dftlen // 2 + 1
+        if 1 + S + NMs > O:
+            raise ValueError('feature vectors of size {} cannot hold f0 + {} + {} bands'.format(O, S, NMs))
+        flat = ops.empty(T * (1 + 2 * bins + (O if keep_cmp else 0)))
+        f0 = flat[:T]
+        SPEC = flat[T:T + T * bins].view(T, bins)
+        NM = flat[T + T * bins:T + 2 * T * bins].view(T, bins)
+        den = flat[T + 2 * T * bins:].view(T, O) if keep_cmp else None
+        if T == 0:
+            return flat, (f0, SPEC, NM, den)
+        spec_c, nm_c = ops.empty(T, S), ops.empty(T, NMs)
+        md = sd = None
+        if mean is not None:
+            md = torch.as_tensor(np.asarray(mean, dtype=np.float32)).to(ops.device) if not torch.is_tensor(mean) else mean
+            sd = torch.as_tensor(np.asarray(std, dtype=np.float32)).to(ops.device) if not torch.is_tensor(std) else std
+            if md.numel() != O or sd.numel() != O:
+                raise ValueError('mean4norm / std4norm have {} / {} entries for {} features'.format(md.numel(), sd.numel(), O))
+        ops.denorm_split(cmp, md, sd, S, NMs, out=den, f0=f0, spec=spec_c, nm=nm_c)
+        sp.fwbnd2linbnd_device(spec_c, self.fs, self.dftlen, smooth=True, do_exp=True, out=SPEC, ops=ops)
+        sp.fwbnd2linbnd_device(nm_c, self.fs, self.dftlen, out=NM, ops=ops)
+        return flat, (f0, SPEC, NM, den)
+
+    def decompress_features(self, CMP, mean=None, std=None):
+        """The device-side part of synthesis() (vocoders.py:194-202): -> (f0 [T], SPEC [T,bins], NM [T,bins]) numpy.
+        One host->device copy of the [T,O] features, the chain above, one device->host copy."""
+        ops = sp.backend_b200.get_ops()
+        CMP = np.ascontiguousarray(CMP, dtype=np.float32)
+        T, bins = CMP.shape[0], self.dftlen // 2 + 1
+        flat, _ = self.decompress_features_device(sp._to_device(CMP, ops), mean, std, ops=ops)
+        host = flat.cpu().numpy()
+        return host[:T], host[T:T + T * bins].reshape(T, bins), host[T + T * bins:T + 2 * T * bins].reshape(T, bins)
+
+    def objmeasures_add(self, CMP, REF):
+        """vocoders.py:208-218: RMS errors of f0 [Hz], spectral bands [dB] and noise mask between generated and reference features."""
+        log2db = 20.0 / np.log(10.0)
+        S, NMs = self.spec_size, self.nm_size
+        self.features_err.setdefault('F0[Hz]', []).append(np.sqrt(np.mean((np.exp(REF[:, 0]) - np.exp(CMP[:, 0])) ** 2)))
+        self.features_err.setdefault('SPEC[dB]', []).append(
+            np.sqrt(np.mean((log2db * REF[:, 1:1 + S] - log2db * CMP[:, 1:1 + S]) ** 2, 0)))
+        self.features_err.setdefault('NM', []).append(np.sqrt(np.mean((REF[:, 1 + S:1 + S + NMs] - CMP[:, 1 + S:1 + S + NMs]) ** 2, 0)))
 
     def analysisf(self, *args, **kwargs):
         raise NotImplementedError('waveform analysis (REAPER / pulsemodel) is outside the B200 hot path')
 
-    def synthesis(self, CMP, pp_mcep=False, pp_f0_smooth=None):
-        raise NotImplementedError('pulse-by-pulse waveform synthesis (pulsemodel) is outside the B200 hot path; '
-                                  'decompress_features() returns its inputs')
+    def synthesis(self, CMP, pp_mcep=False, pp_f0_smooth=None, synthesizer=None):
+        """vocoders.py:194-206.  Everything up to pulsemodel.synthesis.synthesize runs on the device (decompress_features);
+        the pulse-by-pulse waveform synthesis itself is outside the B200 hot path: pass it in as
+        `synthesizer(fs, f0s [T,2] = (time, f0), SPEC, NM) -> waveform`."""
+        if pp_mcep:
+            raise NotImplementedError('MCEP post-processing (SPTK) is not on the B200 path')
+        if synthesizer is None:
+            raise NotImplementedError('pulse-by-pulse waveform synthesis (pulsemodel) is outside the B200 hot path; pass '
+                                      'synthesizer=, or use decompress_features() for its inputs')
+        f0, SPEC, NM = self.decompress_features(CMP)
+        return synthesizer(self.fs, np.vstack((self.shift * np.arange(len(f0)), f0)).T, SPEC, NM)
 
 
 class VocoderWORLD(VocoderF0Spec):

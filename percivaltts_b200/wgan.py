@@ -19,7 +19,7 @@ from . import arch as A
 from .engine import Generator, Critic, LocalSync
 
 # slots of the device loss vector
-L_REAL, L_FAKE, L_GP, L_CRITIC, L_GW, L_GLS, L_GEN = 0, 1, 2, 3, 4, 5, 6
+L_REAL, L_FAKE, L_GP, L_CRITIC, L_GW, L_GLS, L_GEN, L_SSE = 0, 1, 2, 3, 4, 5, 6, 7
 NLOSS = 8
 
 
@@ -70,10 +70,21 @@ class WGANStepper(object):
                 g=o.empty(B, T, a.spec_size, 1), ss=o.zeros(B), dpred=o.empty(B, T, a.outsize))
         return b
 
+    def release(self, B, T):
+        """Free every per-shape buffer of (B, T): step buffers, both networks' training plans, the kernels' scratch recorded under
+        the shape tag.  The caller drops the CUDA graphs captured for the shape first."""
+        self._bufs.pop((B, T), None)
+        self.G.release(B, T, with_backward=True)
+        self.C.release(B, T)
+        self.ops.release_shape((B, T))
+
+    def _scoped(self, fn, X, *args, **kw):
+        with self.ops.shape_scope((int(X.shape[0]), int(X.shape[1]))), self.ops.step_scope():
+            return fn(X, *args, **kw)
+
     # ------------------------------------------------------------------------------------------------------------
-    def critic_step(self, *args, **kw):
-        with self.ops.step_scope():
-            return self._critic_step(*args, **kw)
+    def critic_step(self, X, *args, **kw):
+        return self._scoped(self._critic_step, X, *args, **kw)
 
     def _critic_step(self, X, Y, alpha=None, apply=True):
         """One critic update on device tensors X [B,T,ctx], Y [B,T,O].  alpha [B] overrides the random
@@ -122,9 +133,8 @@ class WGANStepper(object):
             sync.allreduce(self.C.params.grad)
             self.C.params.adam(*self.copt, eps=self.adam_eps)
 
-    def generator_step(self, *args, **kw):
-        with self.ops.step_scope():
-            return self._generator_step(*args, **kw)
+    def generator_step(self, X, *args, **kw):
+        return self._scoped(self._generator_step, X, *args, **kw)
 
     def _generator_step(self, X, Y, apply=True):
         """One generator update (BN moving statistics move here, like in the reference's generator_model)."""
@@ -161,13 +171,13 @@ class WGANStepper(object):
             sync.allreduce(self.G.params.grad)
             self.G.params.adam(*self.gopt, eps=self.adam_eps)
 
-    def evaluate_losses(self, *args, **kw):
-        with self.ops.step_scope():
-            return self._evaluate_losses(*args, **kw)
+    def evaluate_losses(self, X, *args, **kw):
+        return self._scoped(self._evaluate_losses, X, *args, **kw)
 
     def _evaluate_losses(self, X, Y, alpha=None):
         """Critic and generator objectives on one batch in inference mode (BN moving statistics), no update:
-        what critic_model.evaluate / generator_model.evaluate return in update_validation_cost (:244-262)."""
+        what critic_model.evaluate / generator_model.evaluate return in update_validation_cost (:244-262); losses[L_SSE] is the
+        sum of squared prediction errors of the batch (data.cost_model_prediction_rmse, data.py:360-375) from the same forward."""
         o, a = self.ops, self.a
         B, T, _ = X.shape
         M, S, O = B * T, a.spec_size, a.outsize
@@ -196,10 +206,11 @@ class WGANStepper(object):
             o.loss_combine(self.losses, L_GEN, L_GW, self.wbar, L_GLS, 1.0)
         else:
             o.loss_combine(self.losses, L_GEN, L_GW, 1.0)
+        o.lse_loss_grad(bf['fake'], Y, None, None, 1.0, 0.0, self.losses, L_SSE)
 
-    def predict(self, *args, **kw):
-        with self.ops.step_scope():
-            return self._predict(*args, **kw)
+    def predict(self, X, *args, **kw):
+        with self.ops.shape_scope(('predict', int(X.shape[0]), int(X.shape[1]))), self.ops.step_scope():
+            return self._predict(X, *args, **kw)
 
     def _predict(self, X, out=None):
         """Generator inference forward (BN moving statistics): ModelTTS.predict (modeltts.py:68-69)."""

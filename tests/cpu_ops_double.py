@@ -56,6 +56,13 @@ class CpuOpsDouble(object):
         import contextlib
         return contextlib.nullcontext(self)
 
+    def shape_scope(self, tag):
+        import contextlib
+        return contextlib.nullcontext(self)
+
+    def release_shape(self, tag):
+        pass
+
     def side_lane(self):
         import contextlib
         return contextlib.nullcontext(self)
@@ -372,6 +379,18 @@ class CpuOpsDouble(object):
         counter += 1
 
     # ---- PML -------------------------------------------------------------------------------------------------
+    def denorm_split(self, cmp, mean, std, S, NM, out=None, f0=None, spec=None, nm=None):
+        v = cmp if mean is None else cmp * std + mean
+        if out is not None:
+            out.copy_(v)
+        if f0 is not None:
+            f0.copy_(torch.exp(v[:, 0]))
+        if spec is not None:
+            spec.copy_(v[:, 1:1 + S])
+        if nm is not None:
+            nm.copy_(v[:, 1 + S:1 + S + NM])
+        self.launches += 1
+
     def pml_linbnd2fwbnd(self, x, idx, wgt, out, log_abs):
         self.launches += 1
         j = idx.long()

@@ -85,3 +85,14 @@ def test_shard_batch_rejects_uneven_split():
     with pytest.raises(ValueError):
         shard_batch(np.zeros((5, 3, 2)), 0, 2)
     assert shard_batch(np.arange(8).reshape(4, 2), 1, 2).tolist() == [[4, 5], [6, 7]]
+
+
+def test_two_rank_train_through_the_public_api(tmp_path):
+    """`torchrun run.py`-style data parallelism through the public API alone (gloo, 2 ranks, CPU test double): the backend
+    rendezvous from the environment, the epoch loop shards every global batch, rank 0 writes the files, replicas end identical."""
+    import subprocess
+    env = dict(os.environ, PCTTS_DP_WORKDIR=str(tmp_path / 'work'), CUDA_VISIBLE_DEVICES='')
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr', '127.0.0.1',
+           '--master-port', str(_free_port()), os.path.join(ROOT, 'tools', 'dp_api_check.py')]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
+    assert r.returncode == 0 and 'DP API OK' in r.stdout, (r.stdout[-3000:], r.stderr[-3000:])

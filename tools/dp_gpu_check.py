@@ -20,7 +20,7 @@ KW = dict(ctxsize=60, spec_size=33, nm_size=9, hiddenwidth=32, ctx_nbcnnlayers=1
 
 def main():
     import faulthandler
-    faulthandler.dump_traceback_later(90, exit=True)
+    faulthandler.dump_traceback_later(300, exit=True)
     sync, device = parallel.init_from_env()
     rank, world = sync.rank, sync.world
     print('rank %d: peer-memory exchange %s' % (rank, 'on' if sync._peer is not None else 'off (%s)' % sync.peer_error), flush=True)
@@ -63,6 +63,36 @@ def main():
     for i in range(6):
         Xb, Yb, _ = O.synthetic_batch(ao, Bg, T, seed=20 + i)
         tr.train_on_batch(i * 5, parallel.shard_batch(Xb, rank, world), parallel.shard_batch(Yb, rank, world))
+    # soak of the peer-memory exchange: 200 replays of a captured graph holding 8 exchanges of different sizes (the parity
+    # double-buffering of slots / flags under replay at this world size), results checked, time-out flag must stay 0
+    soak_ok = True
+    if world > 1 and sync._peer is not None:
+        sizes = [8, 512, 64, 1024, 8, 8, 256, 16]
+        bufs = [torch.zeros(n, dtype=torch.float64, device=device) for n in sizes]
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for b in bufs:
+                sync.allreduce(b)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for j, b in enumerate(bufs):
+                b.copy_(torch.arange(b.numel(), dtype=torch.float64, device=device) * (rank + 1) + j)
+                sync.allreduce(b)
+        for it in range(200):
+            g.replay()
+            if it % 50 == 49:
+                torch.cuda.synchronize()
+                for j, b in enumerate(bufs):
+                    want = torch.arange(b.numel(), dtype=torch.float64, device=device) * (world * (world + 1) / 2.0) + j * world
+                    soak_ok = soak_ok and bool(torch.equal(b, want))
+        torch.cuda.synchronize()
+        soak_ok = soak_ok and not sync.peer_failed()
+        print('rank %d: peer all-reduce soak (200 graph replays x %d exchanges) %s, err flag %d'
+              % (rank, len(sizes), 'ok' if soak_ok else 'FAILED', int(sync.peer_err)), flush=True)
+    ok = ok and soak_ok
     flat = torch.cat([st.C.params.flat, st.G.params.flat, st.G.params.state])
     ref = flat.clone()
     if world > 1:
