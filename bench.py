@@ -190,6 +190,115 @@ def run_reference(args):
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}))
 
 
+def step_min_flops(a, B, T):
+    """Algorithmic flops (2 x multiply-adds of every contraction) of one critic step and one generator step in the minimum-work
+    variant this build executes: the critic's ctx branch once per batch, the frozen generator's spectral branch
+    only in the critic step.  Backward = one data-gradient + one weight-gradient contraction per forward contraction where the
+    gradient is needed; the gradient penalty adds the input-gradient chain, the tangent sweep and the weight gradients of the
+    interpolated application."""
+    M, H, S, Fl, W, L = B * T, a.hiddenwidth, a.spec_size, a.gen_nbfilters, a.ctx_winlen, a.gen_nbcnnlayers
+    KK = a.gen_winlen * a.spec_freqlen
+    conv1d = 2.0 * M * W * a.ctxsize * H
+    fc = 2.0 * M * H * H
+    c2_first, c2_mid, c2_last = 2.0 * M * S * KK * 1 * Fl, 2.0 * M * S * KK * Fl * Fl, 2.0 * M * S * KK * Fl * 1
+    g_ctx = a.ctx_nbcnnlayers * conv1d + 2 * fc
+    g_spec = 2.0 * M * H * S + c2_first + (L - 1) * c2_mid + c2_last
+    g_f0 = 2 * (2.0 * M * H * 4 * H) + 2 * (2.0 * M * H * 4 * H) + 2.0 * M * 2 * H
+    g_nm = (L // 2) * fc + 2.0 * M * H * a.nm_size
+    g_fwd = g_ctx + g_spec + g_f0 + g_nm
+    c_ctx = a.ctx_nbcnnlayers * conv1d + 2 * fc + fc                       # + the ctx rows of the first post layer
+    c_app = c2_first + (L - 1) * c2_mid + 2.0 * M * S * Fl * H + 2 * fc + 2.0 * M * H          # spectral stack + post layers, one application
+    critic = (g_ctx + g_spec) + c_ctx + 3 * c_app            # forward: frozen generator (spectral) + ctx once + 3 applications
+    critic += 2 * c_ctx - conv1d                               # ctx-branch backward: weight gradients everywhere, data gradients but into the labels
+    critic += 3 * (2 * c_app) + c_app                          # 3 applications: data + weight gradients; + the tangent sweep of the penalty
+    gen = g_fwd + c_ctx + c_app + c_app + 2 * g_fwd - conv1d   # G fwd, D fwd, D input gradient, G backward (data + weight)
+    return {'critic': critic, 'generator': gen}
+
+
+def kernel_rooflines(st, ops, B, T, device, peak_tf, peak_hbm, critic_ms, gen_ms):
+    """Each hot kernel timed ALONE in this run (CUDA events on the launching stream, L2 flushed by a 1 GiB fill before every
+    launch), against the roofline that bounds it; algorithmic bytes / flops per launch as stated in DESIGN.md section 4.
+    `share_of_critic_step` = kernel_ms x launches per critic step / measured critic step (two lanes overlap, so the shares are
+    upper bounds of the exposed time); the ncu launch list under profiles/ holds the serialised per-launch times."""
+    import torch
+    a = st.a
+    S, Fl, H, W = a.spec_size, a.gen_nbfilters, a.hiddenwidth, a.ctx_winlen
+    L = a.gen_nbcnnlayers
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.float32, device=device)
+
+    def timed(fn, iters=12):
+        for _ in range(3):
+            fn()
+        tot = 0.0
+        for _ in range(iters):
+            flush.zero_()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            fn()
+            a1.record()
+            a1.synchronize()
+            tot += a0.elapsed_time(a1)
+        return tot / iters
+
+    out = []
+    products = max(ops.nterms, 1)
+    with ops.shape_scope((B, T)), ops.step_scope():
+        gpl, cpl = st.G.plan(B, T), st.C.plan(3, B, T)
+        bf = st.buffers(B, T)
+        cp, gp = st.C.params.p, st.G.params.p
+        # -- Conv2D 5x5 4->4 on the batched critic map [3B,T,S,4] (forward: bias + LeakyReLU) -- HBM bound
+        x3, y3 = cpl['a'][1], cpl['a'][2]
+        t = timed(lambda: ops.conv2d(x3, cp['c.spec.cnn2.kernel'], y3, bias=cp['c.spec.cnn2.bias'], flags=2))
+        nbytes = 2.0 * x3.numel() * 4
+        out.append({'name': 'conv2d_4to4_critic_3B', 'kernel': 'conv2d_tc_kernel<%d> on [3B,T,%d,4] (critic forward layer)' % ({6: 3, 3: 2, 1: 1}.get(ops.nterms, 0), S),
+                    'bound': 'hbm', 'achieved': nbytes / (t * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s',
+                    'frac': nbytes / (t * 1e-3) / 1e9 / peak_hbm, 'kernel_ms': t, 'bytes_per_launch': nbytes, 'traffic': None,
+                    'launches_per_critic_step': 2 * (L - 1), 'share_of_critic_step': t * 2 * (L - 1) / critic_ms,
+                    'algorithmic': 'one fp32 map read + one written: 2 x 3B x T x %d x 4 ch x 4 B' % S})
+        # -- the same layer on a B-sized map (frozen generator / data-gradient / tangent chains)
+        x1, y1 = gpl['cv_a'][1], gpl['cv_z'][2]
+        t = timed(lambda: ops.conv2d(x1, gp['g.spec.cnn2.kernel'], y1))
+        nb1 = 2.0 * x1.numel() * 4
+        out.append({'name': 'conv2d_4to4_B', 'kernel': 'conv2d_tc_kernel on [B,T,%d,4]' % S, 'bound': 'hbm',
+                    'achieved': nb1 / (t * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s', 'frac': nb1 / (t * 1e-3) / 1e9 / peak_hbm,
+                    'kernel_ms': t, 'bytes_per_launch': nb1, 'traffic': None, 'launches_per_critic_step': 3 * (L - 1),
+                    'share_of_critic_step': t * 3 * (L - 1) / critic_ms,
+                    'algorithmic': 'one fp32 map read + one written: 2 x B x T x %d x 4 ch x 4 B' % S})
+        # -- Conv2D 4->4 weight gradient over the first-order applications [2B,T,S,4]
+        xa, da = cpl['a'][1][:2 * B], cpl['da'][2][:2 * B]
+        gk, gb = st.C.params.g['c.spec.cnn2.kernel'], st.C.params.g['c.spec.cnn2.bias']
+        t = timed(lambda: ops.conv2d_wgrad(xa, da, gk, dbias=gb))
+        nbw = 2.0 * xa.numel() * 4
+        out.append({'name': 'conv2d_wgrad_4to4_2B', 'kernel': 'Conv2D 4->4 weight (+ bias) gradient on [2B,T,%d,4]' % S, 'bound': 'hbm',
+                    'achieved': nbw / (t * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s', 'frac': nbw / (t * 1e-3) / 1e9 / peak_hbm,
+                    'kernel_ms': t, 'bytes_per_launch': nbw, 'traffic': None, 'launches_per_critic_step': L - 1,
+                    'share_of_critic_step': t * 1.5 * (L - 1) / critic_ms,
+                    'algorithmic': 'activation map + gradient map read once: 2 x 2B x T x %d x 4 ch x 4 B (the B tangent rows are a second launch of half the size)' % S})
+        # -- Conv1D k=21 425->256 forward: virtual-im2col tcgen05 GEMM -- tensor bound
+        kern, xp, z = gp['g.ctx.cnn0.kernel'], gpl['ctx_xp'][0], gpl['ctx_z'][0]
+        t = timed(lambda: ops.conv1d(xp, kern, z, T), iters=20)
+        fl = 2.0 * B * T * W * a.ctxsize * H
+        ach = fl / (t * 1e-3) / 1e12
+        out.append({'name': 'conv1d_fwd', 'kernel': 'gemm_tc_kernel<128,PARTS> + split-K reduce (Conv1D k=%d %d->%d forward, M=%d N=%d K=%d)' % (W, a.ctxsize, H, B * T, H, W * a.ctxsize),
+                    'bound': 'tensor', 'achieved': ach, 'peak': peak_tf, 'unit': 'TFLOP/s', 'frac': ach / peak_tf, 'kernel_ms': t,
+                    'flop_per_launch': fl, 'traffic': None, 'precision': ops.precision, 'tensor_products_per_flop': products,
+                    'tensor_pipe_frac': products * ach / peak_tf, 'launches_per_critic_step': 2,
+                    'share_of_critic_step': 2 * t / critic_ms,
+                    'note': 'achieved counts ALGORITHMIC fp32 flops (2MNK); precision %s issues %d bf16 tcgen05 products per algorithmic '
+                            'product, so the tensor pipe itself runs at tensor_pipe_frac of the measured bf16 peak' % (ops.precision, products)})
+        # -- Conv1D weight gradient
+        dz = gpl['dB']
+        gkern = st.G.params.g['g.ctx.cnn0.kernel']
+        t = timed(lambda: ops.conv1d_wgrad(xp, dz, gkern, T))
+        ach = fl / (t * 1e-3) / 1e12
+        out.append({'name': 'conv1d_wgrad', 'kernel': 'gemm_tc_kernel<128,PARTS> tail-split (Conv1D weight gradient, M=%d N=%d K=%d)' % (W * a.ctxsize, H, B * T),
+                    'bound': 'tensor', 'achieved': ach, 'peak': peak_tf, 'unit': 'TFLOP/s', 'frac': ach / peak_tf, 'kernel_ms': t,
+                    'flop_per_launch': fl, 'traffic': None, 'tensor_pipe_frac': products * ach / peak_tf, 'launches_per_critic_step': 1,
+                    'share_of_critic_step': t / critic_ms})
+    del flush
+    return out
+
+
 def run_b200(args):
     import torch
     from percivaltts_b200 import modeltts_common, networks_critic, optimizertts_wgan, parallel, vocoders, _lib
@@ -212,6 +321,10 @@ def run_b200(args):
     tr, st, ops, lib = opti.trainer, opti.stepper, opti.stepper.ops, _lib.load()
     tr.generator_updates = opti.generator_updates = 25                 # steady-state schedule: critic_runs == 5
     B, T = B_PER_GPU, T_FRAMES
+    if args.global_batch:
+        if args.global_batch % world:
+            raise SystemExit('--global-batch %d does not split evenly over %d ranks' % (args.global_batch, world))
+        B = args.global_batch // world
     R = 4
     host = [synthetic_batch(B, T, 123 + 1000 * rank + i) for i in range(R)]
     s = tr.shape_state(B, T)                                             # eager warm-up + CUDA-graph capture
@@ -285,32 +398,20 @@ def run_b200(args):
     e2e_s = time.perf_counter() - t0
     barrier()
     e2e_s = max_over_ranks(e2e_s, device)
+    e2e_h2d, e2e_d2h = tr.h2d_bytes // args.steps, tr.d2h_bytes // args.steps
+    # the same loop through the reference's 3-argument hook (no next_batch hint): synchronous staging of every batch
+    tr.generator_updates = opti.generator_updates = 25
+    torch.cuda.synchronize(device)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        opti.train_on_batch(i, host[i % R][0], host[i % R][1])
+    torch.cuda.synchronize(device)
+    e2e_sync_s = max_over_ranks(time.perf_counter() - t0, device)
+    barrier()
     clk = clocks.stop() if rank == 0 else None
     e2e_value = frames / e2e_s
 
-    # ---- roofline of the dominant kernel: the Conv1D(k=21, 425->256) forward, a virtual-im2col tcgen05 GEMM ----
-    # Timed alone (burst peak applies): L2 flushed by a 1 GiB fill that is still running while the host enqueues the events and
-    # the launch, so the interval between the events holds the kernel only.  Operand shadows are split beforehand (step scope).
-    gpl = st.G.plan(B, T)
-    H, W = 256, 21
-    kern = st.G.params.p['g.ctx.cnn0.kernel']
-    xp, z = gpl['ctx_xp'][0], gpl['ctx_z'][0]
-    flush = torch.empty(256 * 1024 * 1024, dtype=torch.float32, device=device)
-    with ops.step_scope():
-        for _ in range(3):
-            ops.conv1d(xp, kern, z, T)
-        tot, iters = 0.0, 20
-        for _ in range(iters):
-            flush.zero_()
-            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a0.record()
-            ops.conv1d(xp, kern, z, T)
-            a1.record()
-            a1.synchronize()
-            tot += a0.elapsed_time(a1)
-    del flush
-    t_conv1d = tot / iters
-    flops = 2.0 * B * T * W * 425 * H
     peaks = {}
     try:
         with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as f:
@@ -318,43 +419,46 @@ def run_b200(args):
     except (OSError, ValueError):
         pass
     peak_tf = float(peaks.get('bf16_tflops', 1590.0))
-    achieved = flops / (t_conv1d * 1e-3) / 1e12
-    products = max(ops.nterms, 1)
-    roofline = {'bound': 'tensor',
-                'kernel': 'gemm_tc_kernel<128,3> + tc_splitk_reduce (Conv1D k=21 425->256 forward as virtual-im2col tcgen05 GEMM, M=4000 N=256 K=8925, two K halves per 128x128 tile)',
-                'achieved': achieved, 'peak': peak_tf, 'unit': 'TFLOP/s', 'frac': achieved / peak_tf,
-                'peak_source': 'MEASURED_PEAKS.json bf16_tflops (burst)' if peaks else 'fallback 1590 TFLOP/s',
-                # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture
-                # profiles/r01_i_ncu_full_conv1d_gemm_tc.txt: gemm_tc_kernel<128,3> 24.63 MB read (the bf16 operand planes, 10.9 MB
-                # activations + 13.7 MB weights, each read once) + the split-K reduce 8.20 MB (cold-cache replay: in the step the
-                # partials are still in L2); the 4.1 MB fp32 output stays in L2.  Valid for the fp32 (3-plane) mode.
-                'traffic': 32.83e6 if ops.precision == 'fp32' else None, 'traffic_unit': 'B/launch',
-                'ncu_tensor_pipe_pct': 70.7 if ops.precision == 'fp32' else None,
-                'kernel_ms': t_conv1d, 'flop_per_launch': flops,
-                'precision': ops.precision, 'tensor_products_per_flop': products,
-                'tensor_pipe_frac': products * achieved / peak_tf,
-                'note': 'achieved counts ALGORITHMIC fp32 flops (2MNK); precision %s issues %d bf16 tcgen05 products per '
-                        'algorithmic product, so the tensor pipe itself runs at tensor_pipe_frac of the measured bf16 peak' %
-                        (ops.precision, products)}
+    peak_hbm = float(peaks.get('hbm_gbs', 6650.0))
+    peak_src = 'MEASURED_PEAKS.json (burst: each kernel is timed alone)' if peaks else 'B200_PROFILING.md fallback (1590 TFLOP/s, 6650 GB/s)'
+    rooflines = kernel_rooflines(st, ops, B, T, device, peak_tf, peak_hbm, critic_ms, gen_ms) if not args.no_extras else []
+    for r in rooflines:
+        r['peak_source'] = peak_src
+    # `roofline` = the kernel with the largest measured share of the critic step; the others follow in `rooflines`
+    roofline = max(rooflines, key=lambda r: r.get('share_of_critic_step', 0.0)) if rooflines else None
+    flops = step_min_flops(st.a, B, T)
+    whole = {'variant': 'minimum work: critic ctx branch once per batch, frozen generator spectral branch only in the critic step '
+                        '(SURVEY.md 8d); algorithmic 2MNK flops of every contraction, forward + data/weight gradients + GP tangent sweep',
+             'critic_step_gflop': flops['critic'] / 1e9, 'generator_step_gflop': flops['generator'] / 1e9,
+             'critic_step_tflops': flops['critic'] / (critic_ms * 1e-3) / 1e12, 'generator_step_tflops': flops['generator'] / (gen_ms * 1e-3) / 1e12,
+             'critic_step_frac_of_bf16_peak': flops['critic'] / (critic_ms * 1e-3) / 1e12 / peak_tf,
+             'generator_step_frac_of_bf16_peak': flops['generator'] / (gen_ms * 1e-3) / 1e12 / peak_tf}
+    conv1d = next((r for r in rooflines if r['name'] == 'conv1d_fwd'), None)
 
     if rank != 0:
         return
     launches = args.steps * n_critic + ((args.steps + 4) // 5) * n_gen
     out = {
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
-        'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'strong' if args.global_batch else 'weak', 'vs_baseline': None,
         'dtype': 'bf16' if ops.precision == 'bf16' else 'f32',
         'data': 'synthetic',
-        'config': {'workload': WORKLOAD, 'global_batch_utterances': B * world, 'frames_per_step': B * T * world,
+        'config': {'workload': WORKLOAD if (ops.precision == 'fp32' and not args.global_batch) else
+                   WORKLOAD.replace('fp32', ops.precision).replace('B=10/GPU', 'B=%d/GPU' % B).replace('config #2', 'config #3' if ops.precision == 'bf16' else 'config #2 variant'),
+                   'global_batch_utterances': B * world, 'frames_per_step': B * T * world,
                    'schedule': '1 critic update per step + 1 generator update every 5th step (generator_updates>=25)',
                    'l2': 'per-step working set (activations of 3x batched critic + generator, ~0.6 GB) exceeds the 126 MB L2; '
                          'inputs cycle over 4 resident batches',
                    'parallelism': 'dp%d sync-BN + flat-gradient all-reduce' % world if world > 1 else 'single GPU'},
-        'critic_step_ms': critic_ms, 'generator_step_ms': gen_ms, 'conv_tc_util_pct': 100.0 * roofline['tensor_pipe_frac'], 'gemm_precision': ops.precision,
-        'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': tr.h2d_bytes // args.steps,
-                'd2h_bytes_per_step': tr.d2h_bytes // args.steps, 'ms_per_step': 1e3 * e2e_s / args.steps},
+        'critic_step_ms': critic_ms, 'generator_step_ms': gen_ms,
+        'conv_tc_util_pct': 100.0 * conv1d['tensor_pipe_frac'] if conv1d else None, 'gemm_precision': ops.precision,
+        'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': e2e_h2d,
+                'd2h_bytes_per_step': e2e_d2h, 'ms_per_step': 1e3 * e2e_s / args.steps,
+                'call': 'OptimizerTTSWGAN.train_on_batch(batchid, X, Y, next_batch=(X1, Y1)) -- the package\'s own epoch loop'},
+        'e2e_sync': {'value': frames / e2e_sync_s, 'unit': UNIT, 'ms_per_step': 1e3 * e2e_sync_s / args.steps,
+                     'call': 'OptimizerTTSWGAN.train_on_batch(batchid, X, Y) -- the reference\'s 3-argument hook, synchronous staging'},
         'gpu_launches': int(launches), 'kernels_per_critic_step': int(n_critic), 'kernels_per_generator_step': int(n_gen),
-        'clocks': clk, 'roofline': roofline,
+        'clocks': clk, 'roofline': roofline, 'rooflines': rooflines, 'whole_step': whole,
     }
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
@@ -362,6 +466,13 @@ def run_b200(args):
         out['cpu_baseline'] = {'value': v, 'unit': UNIT, 'cores': threads, 'kind': 'port',
                                'sample': 'one steady-state cycle (5 batches of B=10 x T=400: 5 critic + 1 generator update) of the '
                                          'torch-CPU fp32 oracle, %.1f s' % dt}
+    if world == 1 and not args.no_extras:
+        # BASELINE configs #4 and #5 (their own workloads; `value` above stays config #2)
+        sys.path.insert(0, os.path.join(ROOT, 'tools'))
+        import bench_gp
+        import bench_pml
+        out['config4_gp_microbench'] = bench_gp.run(ops, iters=6)
+        out['config5_pml_1M_frames'] = bench_pml.run(ops, cpu_frames=4000)
     print(json.dumps(out))
 
 
@@ -372,7 +483,14 @@ def main():
     ap.add_argument('--warmup', type=int, default=10)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--precision', default=None, choices=['fp32', 'fp32x3', 'bf16', 'simt'],
+                    help='GEMM arithmetic (default fp32 = config #2; bf16 = BASELINE config #3)')
+    ap.add_argument('--global-batch', type=int, default=None,
+                    help='strong scaling: total utterances per step, split evenly over the ranks (default: 10 per GPU, weak scaling)')
+    ap.add_argument('--no-extras', action='store_true', help='skip the config #4 / #5 microbenches and the per-kernel rooflines')
     args = ap.parse_args()
+    if args.precision:
+        os.environ['PCTTS_PRECISION'] = args.precision
     args.warmup = max(args.warmup, 3)
     if args.impl == 'reference':
         run_reference(args)

@@ -15,12 +15,11 @@ from percivaltts_b200.ops import CudaOps
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def main():
-    ops = CudaOps()
+def run(ops=None, total=1000000, chunk=250000, cpu_frames=10000):
+    ops = ops or CudaOps()
     peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json'))) if os.path.exists(os.path.join(ROOT, 'MEASURED_PEAKS.json')) else {}
     hbm = float(peaks.get('hbm_gbs', 6650.0))
     fs, dftlen, NB = 16000, 4096, 2049
-    total, chunk = 1000000, 250000
     g = torch.Generator(device='cuda').manual_seed(3)
     spec = torch.exp(torch.randn(chunk, NB, device='cuda', generator=g) * 2 - 6)
     nm = torch.rand(chunk, NB, device='cuda', generator=g)
@@ -51,15 +50,21 @@ def main():
             out[name]['decompressed_range'] = [float(back.min()), float(back.max())]
     # CPU baseline: numpy oracle, 10 k frames, single thread
     from oracle import pml_oracle as PO
-    xs = np.exp(np.random.RandomState(0).normal(-6, 2, size=(10000, NB)))
+    xs = np.exp(np.random.RandomState(0).normal(-6, 2, size=(cpu_frames, NB)))
     t0 = time.perf_counter()
     c = PO.linbnd2fwbnd(np.log(np.abs(xs)), fs, dftlen, 129)
     t1 = time.perf_counter()
     PO.fwbnd2linbnd(c, fs, dftlen, smooth=True)
     t2 = time.perf_counter()
-    out['cpu_oracle'] = {'frames': 10000, 'cores': 1, 'compress_frames_per_s': round(10000 / (t1 - t0)), 'decompress_frames_per_s': round(10000 / (t2 - t1))}
+    out['cpu_oracle'] = {'frames': cpu_frames, 'cores': 1, 'compress_frames_per_s': round(cpu_frames / (t1 - t0)), 'decompress_frames_per_s': round(cpu_frames / (t2 - t1))}
     out.update(config='pml_1M_frames', hbm_peak_GBps=hbm, bytes_per_frame={'compress_spec': (NB + 129) * 4, 'compress_nm': (NB + 33) * 4})
-    print(json.dumps(out))
+    del spec, nm
+    torch.cuda.empty_cache()
+    return out
+
+
+def main():
+    print(json.dumps(run()))
 
 
 if __name__ == '__main__':
