@@ -113,6 +113,26 @@ int pctts_conv2d_tc_fwd_fused(const float* x, const float* w, const float* bias,
                               long xbatch, long ybatch, long auxbatch, int flags, int nterms, const float* in_mean,
                               const float* in_invstd, const float* in_gamma, const float* in_beta, void* workspace, int final_stage,
                               void* stream);
+/* A chain of up to PCTTS_CHAIN_MAX_LAYERS Conv2D 5x5 'same' layers (<= 4 channels) in ONE launch (conv2d_chain.cu): a sample is owned
+ * by a thread-block cluster, the map tile stays in shared memory as bf16 operand planes from layer to layer, every layer is a
+ * tcgen05 implicit GEMM, the fp32 output of every layer is written once.  The critic's BatchNorm-free stack
+ * (networks_critic.py:66-68) forward, its data-gradient chain and the forward-mode sweep of the gradient penalty.
+ * x [NB,T,F,cin0] (cin0 = 1 or 4); layer l: w [5][5][cin][cout] (flip = 1: w is the forward kernel [5][5][cout][cin] and the data
+ * gradient kernel is formed on the fly), y [NB,T,F,cout] with cout = 4 (cout = 1 allowed for the last layer), optional bias,
+ * optional LeakyReLU' mask from aux [NB,T,F,4] (aux may alias y), flags PCTTS_EPI_BIAS | LRELU | DLRELU_AUX | ACCUM (last layer).
+ * pitches / batch strides in floats.  PCTTS_EUNSUPPORTED when pctts_conv2d_chain_supported() is 0 or an alignment rule fails. */
+#define PCTTS_CHAIN_MAX_LAYERS 9
+typedef struct pctts_chain_layer {
+    const float* w;
+    const float* bias;
+    const float* aux;
+    float* y;
+    long ybatch, ypitch, auxbatch, auxpitch;
+    int cin, cout, flags, flip;
+} pctts_chain_layer;
+int pctts_conv2d_chain_supported(int T, int F, int nterms);   /* host call: CTAs per sample (cluster size), 0 = unsupported */
+int pctts_conv2d_chain(const float* x, long xbatch, long xpitch, int cin0, int NB, int T, int F, int nlayers,
+                       const pctts_chain_layer* layers, int nterms, void* stream);
 int pctts_conv2d_flip_weights(const float* w, float* wt, int KH, int KW, int CIN, int COUT, void* stream);
 long pctts_conv2d_wgrad_workspace(int NB, int T, int CIN, int COUT, int KH, int KW); /* floats; host call */
 /* dw[kt,kf,ci,co] (+)= scale * sum_{n,t,f} x[n,t+kt-pad_t,f+kf-pad_f,ci] dy[n,t,f,co]   (deterministic two-stage) */

@@ -64,30 +64,6 @@ struct C2Params {
     double* stats;       // optional: per-CTA partial [grid][2][4] of sum y, sum y^2 per output channel (fused BatchNorm statistics)
 };
 
-// shared-memory matrix descriptor, no swizzle (INTERLEAVE), K-major: core matrix = 8 rows x 16 bytes, contiguous
-__device__ __forceinline__ uint64_t umma_desc_noswz(uint32_t addr, uint32_t lbo, uint32_t sbo) {
-    uint64_t d = 0;
-    d |= (uint64_t)((addr >> 4) & 0x3FFF);
-    d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
-    d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
-    d |= (uint64_t)1 << 46;
-    return d;
-}
-
-__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-        : "r"(taddr)
-        : "memory");
-}
-
-__device__ __forceinline__ uint32_t pack_bf16(__nv_bfloat16 a, __nv_bfloat16 b) {
-    return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);
-}
-
 // streaming 16-byte load of the input map: read once per tile, kept out of L1 so that the epilogue's prefetched mask rows stay
 __device__ __forceinline__ float4 ldg_stream4(const float* p, int no_alloc) {
     float4 v;
@@ -96,30 +72,6 @@ __device__ __forceinline__ float4 ldg_stream4(const float* p, int no_alloc) {
     else
         v = *reinterpret_cast<const float4*>(p);
     return v;
-}
-
-// 8 floats (2 pixels x 4 channels) -> PARTS 16-byte bf16 entries.  Every plane but the last takes the top 16 bits of the running
-// remainder (truncation: the remainder stays exact and three planes carry all 24 significand bits); the last plane rounds.
-template <int PARTS>
-__device__ __forceinline__ void split8(const float (&v)[8], uint4 (&out)[PARTS]) {
-    uint32_t w[PARTS][4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        float a = v[2 * i], b = v[2 * i + 1];
-#pragma unroll
-        for (int p = 0; p < PARTS; ++p) {
-            if (p + 1 < PARTS) {
-                const uint32_t ua = __float_as_uint(a) & 0xFFFF0000u, ub = __float_as_uint(b) & 0xFFFF0000u;
-                w[p][i] = __byte_perm(ua, ub, 0x7632);
-                a -= __uint_as_float(ua);
-                b -= __uint_as_float(ub);
-            } else {
-                w[p][i] = pack_bf16(__float2bfloat16_rn(a), __float2bfloat16_rn(b));
-            }
-        }
-    }
-#pragma unroll
-    for (int p = 0; p < PARTS; ++p) out[p] = make_uint4(w[p][0], w[p][1], w[p][2], w[p][3]);
 }
 
 // shared-memory carve-up (bytes, 16-byte aligned):

@@ -3,6 +3,7 @@
 // host-side tensor-map encoder (driver entry point fetched through the runtime, no link-time libcuda dependency).
 #pragma once
 #include <cuda.h>
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -118,6 +119,55 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t addr, uint32_t lbo, 
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, int a_mn_major, int b_mn_major) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
            ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ---- implicit-GEMM Conv2D helpers (conv2d_tc.cu, conv2d_chain.cu) ---------------------------------------------------------
+// shared-memory matrix descriptor, no swizzle (INTERLEAVE), K-major: core matrix = 8 rows x 16 bytes, contiguous
+__device__ __forceinline__ uint64_t umma_desc_noswz(uint32_t addr, uint32_t lbo, uint32_t sbo) {
+    uint64_t d = 0;
+    d |= (uint64_t)((addr >> 4) & 0x3FFF);
+    d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;
+    return d;
+}
+
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(__nv_bfloat16 a, __nv_bfloat16 b) {
+    return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);
+}
+
+// 8 floats (2 pixels x 4 channels) -> PARTS 16-byte bf16 entries.  Every plane but the last takes the top 16 bits of the running
+// remainder (truncation: the remainder stays exact and three planes carry all 24 significand bits); the last plane rounds.
+template <int PARTS>
+__device__ __forceinline__ void split8(const float (&v)[8], uint4 (&out)[PARTS]) {
+    uint32_t w[PARTS][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float a = v[2 * i], b = v[2 * i + 1];
+#pragma unroll
+        for (int p = 0; p < PARTS; ++p) {
+            if (p + 1 < PARTS) {
+                const uint32_t ua = __float_as_uint(a) & 0xFFFF0000u, ub = __float_as_uint(b) & 0xFFFF0000u;
+                w[p][i] = __byte_perm(ua, ub, 0x7632);
+                a -= __uint_as_float(ua);
+                b -= __uint_as_float(ub);
+            } else {
+                w[p][i] = pack_bf16(__float2bfloat16_rn(a), __float2bfloat16_rn(b));
+            }
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < PARTS; ++p) out[p] = make_uint4(w[p][0], w[p][1], w[p][2], w[p][3]);
 }
 
 // ---- host: tensor maps ---------------------------------------------------------------------------------------------

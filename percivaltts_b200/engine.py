@@ -462,6 +462,11 @@ class Critic(object):
         for key in [k for k in self._plans if k[1:] == (B, T)]:
             del self._plans[key]
 
+    def _chain(self, T):
+        """The spectral Conv2D stack runs as one multi-layer launch per chain (forward, data gradient, tangent sweep)."""
+        a = self.a
+        return a.gen_nbcnnlayers <= 8 and self.ops.conv2d_chain_ok(T, a.spec_size, a.gen_winlen, a.spec_freqlen, a.gen_nbfilters)
+
     def _make_plan(self, napp, B, T):
         o, a = self.ops, self.a
         H, S, Fl, W, L = a.hiddenwidth, a.spec_size, a.gen_nbfilters, a.ctx_winlen, a.gen_nbcnnlayers
@@ -536,9 +541,14 @@ class Critic(object):
             assert samples.start % pl['B'] == 0 and samples.stop % pl['B'] == 0
             sm, r = samples, slice(samples.start * T, samples.stop * T)
         amap = s0[sm]
-        for i in range(L):
-            o.conv2d(amap, p['c.spec.cnn%d.kernel' % i], pl['a'][i][sm], bias=p['c.spec.cnn%d.bias' % i], flags=EPI_LRELU)
-            amap = pl['a'][i][sm]
+        if self._chain(T):
+            # the BatchNorm-free stack (networks_critic.py:66-68) as ONE launch: tiles stay in shared memory from layer to layer
+            o.conv2d_chain(amap, [dict(w=p['c.spec.cnn%d.kernel' % i], bias=p['c.spec.cnn%d.bias' % i], y=pl['a'][i][sm],
+                                       flags=EPI_LRELU) for i in range(L)])
+        else:
+            for i in range(L):
+                o.conv2d(amap, p['c.spec.cnn%d.kernel' % i], pl['a'][i][sm], bias=p['c.spec.cnn%d.bias' % i], flags=EPI_LRELU)
+                amap = pl['a'][i][sm]
         # post layers (networks_critic.py:89-96); concat([spec, ctx]) . W0 = spec . W0[:SF] + ctx . W0[SF:]
         o.gemm(pl['a'][L - 1].view(nM, SF)[r], w0[:SF], pl['p'][0][r], addmod=pl['ctxterm'], flags=EPI_LRELU)
         for i in (1, 2):
@@ -555,8 +565,10 @@ class Critic(object):
         nM = pl['nM']
         S, Fl, L = a.spec_size, a.gen_nbfilters, a.gen_nbcnnlayers
         SF = S * Fl
-        for i in range(L - 1, -1, -1):
-            o.conv2d_flip(p['c.spec.cnn%d.kernel' % i], pl['wflip'][i])
+        chain = self._chain(pl['T'])
+        if not chain:      # the chain kernel forms the data-gradient kernels on the fly
+            for i in range(L - 1, -1, -1):
+                o.conv2d_flip(p['c.spec.cnn%d.kernel' % i], pl['wflip'][i])
         if g_rows is not None and ctx_grads_apps and getattr(o, 'lanes', False) and g_rows.start > 0 \
                 and g_rows.stop == pl['nB']:
             # critic step.  Only the interpolated applications' input gradient is on the critical path (norm -> penalty ->
@@ -570,16 +582,27 @@ class Critic(object):
                 pl['conv_wgrads_apps'] = g_rows.start // pl['B']
                 pl['side_event'] = o.lane_event()
                 self.param_grads_ctx(pl, ctx_grads_apps)
-            self._dgrad_chain(pl, g_rows)
+            self._dgrad_chain(pl, g_rows, final=(g_out, accumulate) if chain else None)
+        elif chain and (g_rows is None or (g_rows.start == 0 and g_rows.stop == pl['nB'])):
+            self._dgrad_chain(pl, slice(0, pl['nB']), final=(g_out, accumulate))
+            if ctx_grads_apps:
+                self.param_grads_ctx(pl, ctx_grads_apps)
         else:
             self._dgrad_chain(pl, slice(0, pl['nB']))
             if ctx_grads_apps:
                 self.param_grads_ctx(pl, ctx_grads_apps)
+            if chain:
+                o.conv2d_chain(pl['da'][0][g_rows], [dict(w=p['c.spec.cnn0.kernel'], flip=True, y=g_out,
+                                                          flags=EPI_ACCUM if accumulate else 0)])
+                return
+        if chain:
+            return
         src = pl['da'][0] if g_rows is None else pl['da'][0][g_rows]
         o.conv2d(src, pl['wflip'][0], g_out, flags=EPI_ACCUM if accumulate else 0)
 
-    def _dgrad_chain(self, pl, samples):
-        """Pre-activation gradients dp[2..0], da[L-1..0] of the applications `samples` (slice over the napp*B axis)."""
+    def _dgrad_chain(self, pl, samples, final=None):
+        """Pre-activation gradients dp[2..0], da[L-1..0] of the applications `samples` (slice over the napp*B axis).
+        final = (g_out, accumulate): also the gradient w.r.t. the spectral input of these applications (chain kernel only)."""
         o, a, p = self.ops, self.a, self.params.p
         T, nM = pl['T'], pl['nM']
         S, Fl, L = a.spec_size, a.gen_nbfilters, a.gen_nbcnnlayers
@@ -591,11 +614,18 @@ class Critic(object):
         o.gemm(pl['dp'][1][r], p['c.post.fc1.kernel'], pl['dp'][0][r], transB=True, aux=pl['p'][0][r])
         o.gemm(pl['dp'][0][r], p['c.post.fc0.kernel'][:SF], pl['da'][L - 1].view(nM, SF)[r], transB=True,
                aux=pl['a'][L - 1].view(nM, SF)[r])
+        sm = slice(None) if whole else samples
+        if self._chain(T):
+            layers = [dict(w=p['c.spec.cnn%d.kernel' % i], flip=True, aux=pl['a'][i - 1][sm], y=pl['da'][i - 1][sm])
+                      for i in range(L - 1, 0, -1)]
+            if final is not None:
+                layers.append(dict(w=p['c.spec.cnn0.kernel'], flip=True, y=final[0], flags=EPI_ACCUM if final[1] else 0))
+            if layers:
+                o.conv2d_chain(pl['da'][L - 1][sm], layers)
+            return
+        assert final is None
         for i in range(L - 1, 0, -1):
-            if whole:
-                o.conv2d(pl['da'][i], pl['wflip'][i], pl['da'][i - 1], aux=pl['a'][i - 1])
-            else:
-                o.conv2d(pl['da'][i][samples], pl['wflip'][i], pl['da'][i - 1][samples], aux=pl['a'][i - 1][samples])
+            o.conv2d(pl['da'][i][sm], pl['wflip'][i], pl['da'][i - 1][sm], aux=pl['a'][i - 1][sm])
 
     def tangent_forward(self, pl, rows):
         """Forward-mode sweep of the linearised critic (LeakyReLU masks frozen) on the applications `rows`, whose
@@ -608,10 +638,14 @@ class Critic(object):
         tmap = pl['s0'][rows]
         n = tmap.shape[0] * T
         r2 = slice(rows.start * T, rows.stop * T)
-        for i in range(L):
-            y = pl['a'][i][rows]
-            o.conv2d(tmap, p['c.spec.cnn%d.kernel' % i], y, aux=y)
-            tmap = y
+        if self._chain(T):
+            o.conv2d_chain(tmap, [dict(w=p['c.spec.cnn%d.kernel' % i], aux=pl['a'][i][rows], y=pl['a'][i][rows]) for i in range(L)])
+            tmap = pl['a'][L - 1][rows]
+        else:
+            for i in range(L):
+                y = pl['a'][i][rows]
+                o.conv2d(tmap, p['c.spec.cnn%d.kernel' % i], y, aux=y)
+                tmap = y
         o.gemm(tmap.view(n, SF), p['c.post.fc0.kernel'][:SF], pl['p'][0][r2], aux=pl['p'][0][r2])
         for i in (1, 2):
             o.gemm(pl['p'][i - 1][r2], p['c.post.fc%d.kernel' % i], pl['p'][i][r2], aux=pl['p'][i][r2])

@@ -9,6 +9,7 @@ The engine (percivaltts_b200/engine.py) is written against this interface; tests
 same interface with plain torch on the CPU *for testing the host logic only* (it is not importable from the package).
 """
 import contextlib
+import ctypes
 import os
 import weakref
 
@@ -146,6 +147,13 @@ class _RowParent(object):
         self.fresh = out
 
 
+class ChainLayerStruct(ctypes.Structure):
+    """pctts_chain_layer of include/pctts.h"""
+    _fields_ = [('w', ctypes.c_void_p), ('bias', ctypes.c_void_p), ('aux', ctypes.c_void_p), ('y', ctypes.c_void_p),
+                ('ybatch', ctypes.c_long), ('ypitch', ctypes.c_long), ('auxbatch', ctypes.c_long), ('auxpitch', ctypes.c_long),
+                ('cin', ctypes.c_int), ('cout', ctypes.c_int), ('flags', ctypes.c_int), ('flip', ctypes.c_int)]
+
+
 PRECISIONS = {'fp32': 6, 'fp32x3': 3, 'bf16': 1, 'simt': 0}      # -> tcgen05.mma products per k-slice
 PLANES = {6: 3, 3: 2, 1: 1, 0: 0}
 
@@ -174,6 +182,7 @@ class CudaOps(object):
         self.fuse_bn_stats = os.environ.get('PCTTS_FUSE_BN_STATS', '1') != '0'   # BN sums in the Conv2D epilogue
         self.bn_single_launch = os.environ.get('PCTTS_BN_SINGLE_LAUNCH', '1') != '0'   # second stage inside bn_finalize (1 replica)
         self.conv2d_tc = os.environ.get('PCTTS_CONV2D_TC', '1') != '0'   # tcgen05 implicit-GEMM Conv2D (4->4, 5x5)
+        self.conv_chain = os.environ.get('PCTTS_CONV_CHAIN', '1') != '0'   # the critic's BN-free Conv2D stack as ONE launch per chain
         self._shadows = {}         # view key -> Shadow
         self._fresh = {}           # view key -> (lo, hi): activation shadows valid inside the current step scope
         self._persist_ranges = []  # (weakref of the parameter buffer, lo, hi): shadows of views into it are refreshed by
@@ -558,6 +567,43 @@ class CudaOps(object):
         if stats:
             return self.bn_stats(y.view(N * T * F, COUT), final=stats_final)
         return None
+
+    def conv2d_chain_ok(self, T, F, KH, KW, channels):
+        """The multi-layer chain kernel (conv2d_chain.cu) applies: 5x5 kernels, 4 feature channels, a precision with tensor-core
+        operands, and a sequence length that fits 16 CTAs of shared memory per sample."""
+        return bool(self.conv_chain and self.conv2d_tc and self.nterms > 0 and KH == 5 and KW == 5 and channels == 4
+                    and self.lib.pctts_conv2d_chain_supported(int(T), int(F), self.nterms) > 0)
+
+    def conv2d_chain(self, x, layers):
+        """A chain of 'same' 5x5 Conv2D layers in one launch.  x [N,T,F,cin0]; layers: list of dicts with
+        w (keras kernel [5,5,cin,cout], or the FORWARD kernel [5,5,cout,cin] with flip=True: the data-gradient kernel is formed
+        on the fly), y [N,T,F,cout], optional bias, optional aux (LeakyReLU' mask source [N,T,F,4], may be y itself), flags."""
+        N, T, F, cin0 = x.shape
+        assert x.dtype == torch.float32 and (cin0 == 1 or x.stride(3) == 1) and (F == 1 or x.stride(2) == cin0)
+        arr = (ChainLayerStruct * len(layers))()
+        cin = cin0
+        for i, L in enumerate(layers):
+            w, y, flip = L['w'], L['y'], bool(L.get('flip', False))
+            KH, KW, d2, d3 = w.shape
+            cout = d2 if flip else d3
+            assert KH == 5 and KW == 5 and w.is_contiguous() and (d3 if flip else d2) == cin, ('chain kernel', w.shape, cin, flip)
+            assert tuple(y.shape) == (N, T, F, cout), (y.shape, (N, T, F, cout))
+            py, yb, yp = _map4(y)
+            flags = int(L.get('flags', 0))
+            bias, aux = L.get('bias'), L.get('aux')
+            pa, ab, ap = (None, 0, 0)
+            if bias is not None:
+                flags |= EPI_BIAS
+                assert bias.numel() == cout and bias.is_contiguous()
+            if aux is not None:
+                flags |= EPI_DLRELU_AUX
+                assert tuple(aux.shape) == (N, T, F, 4)
+                pa, ab, ap = _map4(aux)
+            self._wrote(y)
+            arr[i] = ChainLayerStruct(w.data_ptr(), _ptr(bias), pa, py, yb, yp, ab, ap, cin, cout, flags, int(flip))
+            cin = cout
+        self._ck(self.lib.pctts_conv2d_chain(x.data_ptr(), x.stride(0), x.stride(1), cin0, N, T, F, len(layers),
+                                             ctypes.cast(arr, ctypes.c_void_p), self.nterms, self._stream()), 'pctts_conv2d_chain')
 
     def conv2d_flip(self, w, wt):
         KH, KW, CIN, COUT = w.shape

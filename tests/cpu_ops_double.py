@@ -159,6 +159,21 @@ class CpuOpsDouble(object):
             return self.bn_stats(y.reshape(-1, y.shape[-1]))
         return None
 
+    def conv2d_chain_ok(self, T, F, KH, KW, channels):
+        return getattr(self, 'conv_chain', False) and KH == 5 and KW == 5 and channels == 4
+
+    def conv2d_chain(self, x, layers):
+        """Same semantics as CudaOps.conv2d_chain, layer by layer."""
+        cur = x
+        for L in layers:
+            w = L['w']
+            if L.get('flip', False):
+                wt = torch.empty(w.shape[0], w.shape[1], w.shape[3], w.shape[2], dtype=w.dtype)
+                self.conv2d_flip(w, wt)
+                w = wt
+            self.conv2d(cur, w, L['y'], bias=L.get('bias'), aux=L.get('aux'), flags=int(L.get('flags', 0)))
+            cur = L['y']
+
     def conv2d_flip(self, w, wt):
         self.launches += 1
         wt.copy_(torch.flip(w, dims=(0, 1)).permute(0, 1, 3, 2))

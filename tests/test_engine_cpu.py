@@ -125,3 +125,26 @@ def test_validation_losses_match_oracle_inference_mode():
 
 def test_critic_runs_schedule():
     assert [W.critic_runs(i) for i in (0, 24, 25, 499, 500, 501, 1000)] == [10, 10, 5, 5, 10, 5, 10]
+
+
+@pytest.mark.parametrize('B,T', [(3, 23), (1, 1)])
+def test_steps_with_the_chained_conv_stack_match_oracle_fp64(B, T):
+    """The critic's Conv2D stack issued as multi-layer chains (ops.conv2d_chain: forward, data gradient with on-the-fly kernel
+    flip and the input gradient as last layer, in-place tangent sweep) -- same results as the per-layer schedule."""
+    ao, wgt, wct, Xt, Yt, alpha, st = make_case(SMALL, B, T, torch.float64)
+    st.ops.conv_chain = True
+    assert st.C._chain(T)
+    rc = O.critic_step(ao, wgt, wct, Xt, Yt, alpha.reshape(-1, 1, 1))
+    st.critic_step(Xt.clone(), Yt.clone(), alpha=alpha, apply=False)
+    for slot, key in ((W.L_REAL, 'l_real'), (W.L_FAKE, 'l_fake'), (W.L_GP, 'gp'), (W.L_CRITIC, 'loss')):
+        assert abs(float(st.losses[slot]) - float(rc[key])) < 1e-10 * max(1.0, abs(float(rc[key])))
+    check_grads(st.C.params, rc['grads'], 1e-9)
+    rg = O.generator_step(ao, wgt, wct, Xt, Yt)
+    st.generator_step(Xt.clone(), Yt.clone(), apply=False)
+    assert abs(float(st.losses[W.L_GEN]) - float(rg['loss'])) < 1e-10
+    check_grads(st.G.params, rg['grads'], 1e-9)
+    ao, wgt, wct, Xt, Yt, alpha, st = make_case(SMALL, B, T, torch.float64)       # fresh BatchNorm moving statistics
+    st.ops.conv_chain = True
+    st.evaluate_losses(Xt.clone(), Yt.clone(), alpha=alpha)
+    rv = O.critic_step(ao, wgt, wct, Xt, Yt, alpha.reshape(-1, 1, 1), gen_training=False)
+    assert abs(float(st.losses[W.L_CRITIC]) - float(rv['loss'])) < 1e-10 * max(1.0, abs(float(rv['loss'])))
