@@ -253,16 +253,39 @@ def kernel_rooflines(st, ops, B, T, device, peak_tf, peak_hbm, critic_ms, gen_ms
         out.append({'name': 'conv2d_4to4_critic_3B', 'kernel': 'conv2d_tc_kernel<%d> on [3B,T,%d,4] (critic forward layer)' % ({6: 3, 3: 2, 1: 1}.get(ops.nterms, 0), S),
                     'bound': 'hbm', 'achieved': nbytes / (t * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s',
                     'frac': nbytes / (t * 1e-3) / 1e9 / peak_hbm, 'kernel_ms': t, 'bytes_per_launch': nbytes, 'traffic': None,
-                    'launches_per_critic_step': 2 * (L - 1), 'share_of_critic_step': t * 2 * (L - 1) / critic_ms,
+                    'launches_per_critic_step': 0 if st.C._chain(T) else 2 * (L - 1), 'share_of_critic_step': 0.0 if st.C._chain(T) else t * 2 * (L - 1) / critic_ms,
                     'algorithmic': 'one fp32 map read + one written: 2 x 3B x T x %d x 4 ch x 4 B' % S})
-        # -- the same layer on a B-sized map (frozen generator / data-gradient / tangent chains)
+        # -- the critic's 8-layer stack as ONE launch per chain (conv2d_chain.cu): forward on [3B,..], data gradient (+ input
+        #    gradient) and tangent sweep on [B,..]; bytes = every map the chain must read or write once (fp32)
+        if st.C._chain(T):
+            px = B * T * S * 4.0                                  # bytes of one single-channel map of B samples
+            s0 = bf['s0'].view(3 * B, T, S, 1)
+            fwd_layers = [dict(w=cp['c.spec.cnn%d.kernel' % i], bias=cp['c.spec.cnn%d.bias' % i], y=cpl['a'][i], flags=2) for i in range(L)]
+            t = timed(lambda: ops.conv2d_chain(s0, fwd_layers))
+            nb = 3 * px * (1 + 4 * L)
+            out.append({'name': 'conv2d_chain_fwd_3B', 'kernel': 'conv2d_chain_kernel<3>: %d Conv2D layers (1->4, 4->4 x%d) + bias + LeakyReLU on [3B,T,%d,.], 8-CTA cluster per sample' % (L, L - 1, S),
+                        'bound': 'hbm', 'achieved': nb / (t * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s', 'frac': nb / (t * 1e-3) / 1e9 / peak_hbm,
+                        'kernel_ms': t, 'bytes_per_launch': nb, 'traffic': None, 'launches_per_critic_step': 1,
+                        'share_of_critic_step': t / critic_ms, 'layers_per_launch': L, 'us_per_layer': 1e3 * t / L,
+                        'algorithmic': 'input map (1 ch) read + %d output maps (4 ch) written once: (1 + 4 x %d) x 3B x T x %d x 4 B; tiles stay in shared memory between layers' % (L, L, S)})
+            rows = slice(2 * B, 3 * B)
+            dg_layers = [dict(w=cp['c.spec.cnn%d.kernel' % i], flip=True, aux=cpl['a'][i - 1][rows], y=cpl['da'][i - 1][rows]) for i in range(L - 1, 0, -1)]
+            dg_layers.append(dict(w=cp['c.spec.cnn0.kernel'], flip=True, y=bf['g']))
+            t = timed(lambda: ops.conv2d_chain(cpl['da'][L - 1][rows], dg_layers))
+            nb = px * (4 + 8 * (L - 1) + 1)
+            out.append({'name': 'conv2d_chain_dgrad_B', 'kernel': 'conv2d_chain_kernel<3>: data-gradient chain (%d layers 4->4 with LeakyReLU\' masks + 4->1 input gradient) on [B,T,%d,.]' % (L - 1, S),
+                        'bound': 'hbm', 'achieved': nb / (t * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s', 'frac': nb / (t * 1e-3) / 1e9 / peak_hbm,
+                        'kernel_ms': t, 'bytes_per_launch': nb, 'traffic': None, 'launches_per_critic_step': 2,
+                        'share_of_critic_step': 3 * t / critic_ms, 'layers_per_launch': L, 'us_per_layer': 1e3 * t / L,
+                        'algorithmic': 'top gradient map + %d mask maps read, %d gradient maps + the 1-ch input gradient written (the second launch per step covers 2B samples on the side lane)' % (L - 1, L - 1)})
+        # -- one 4->4 layer on a B-sized map (the generator's stack: BatchNorm between the layers, one launch per layer)
         x1, y1 = gpl['cv_a'][1], gpl['cv_z'][2]
         t = timed(lambda: ops.conv2d(x1, gp['g.spec.cnn2.kernel'], y1))
         nb1 = 2.0 * x1.numel() * 4
         out.append({'name': 'conv2d_4to4_B', 'kernel': 'conv2d_tc_kernel on [B,T,%d,4]' % S, 'bound': 'hbm',
                     'achieved': nb1 / (t * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s', 'frac': nb1 / (t * 1e-3) / 1e9 / peak_hbm,
-                    'kernel_ms': t, 'bytes_per_launch': nb1, 'traffic': None, 'launches_per_critic_step': 3 * (L - 1),
-                    'share_of_critic_step': t * 3 * (L - 1) / critic_ms,
+                    'kernel_ms': t, 'bytes_per_launch': nb1, 'traffic': None, 'launches_per_critic_step': (L - 1) if st.C._chain(T) else 3 * (L - 1),
+                    'share_of_critic_step': t * ((L - 1) if st.C._chain(T) else 3 * (L - 1)) / critic_ms,
                     'algorithmic': 'one fp32 map read + one written: 2 x B x T x %d x 4 ch x 4 B' % S})
         # -- Conv2D 4->4 weight gradient over the first-order applications [2B,T,S,4]
         xa, da = cpl['a'][1][:2 * B], cpl['da'][2][:2 * B]

@@ -163,6 +163,8 @@ int pctts_bn_apply(const float* x, float* y, const float* mean, const float* inv
                    const float* beta, long rows, int C, float eps, int use_var, int lrelu, void* stream);
 int pctts_bn_bwd_reduce(const float* x, const float* dy, const float* mean, const float* invstd, const float* gamma,
                         const float* beta, long rows, int C, int lrelu, void* workspace, void* stream);
+int pctts_bn_bwd_reduce_partial(const float* x, const float* dy, const float* mean, const float* invstd, const float* gamma,
+                                const float* beta, long rows, int C, int lrelu, void* workspace, void* stream);  /* first stage only */
 int pctts_bn_bwd_apply(const float* x, const float* dy, float* dx, const float* mean, const float* invstd, const float* gamma,
                        const float* beta, long rows, int C, double count, int lrelu, float* dgamma, float* dbeta,
                        float grad_scale, int accumulate, void* workspace, void* stream); /* dgamma/dbeta *= grad_scale
@@ -228,6 +230,17 @@ int pctts_denorm_split(const float* cmp, const float* mean, const float* stdv, l
 long pctts_peer_allreduce_bytes(int world, int nmax);
 int pctts_peer_allreduce_f64(double* x, int n, const unsigned long long* peer_bases, int rank, int world, int nmax, int* err,
                              void* stream);
+
+/* sync-BatchNorm with the replica exchange inside the launch: second reduction stage over the nblk first-stage partials
+ * [nblk][2][C] (doubles), all-reduce over the replicas through a second symmetric buffer of pctts_bn_sync_bytes(world) bytes
+ * (peer_bases as above; world = 1 and peer_bases = NULL: no exchange), then mean / invstd / moving averages (finalize) or
+ * sums + dbeta / dgamma (bwd).  Bit-identical to second stage + pctts_peer_allreduce_f64 + finalize as separate launches. */
+long pctts_bn_sync_bytes(int world);
+int pctts_bn_sync_finalize(const double* partial, double* sums, int nblk, int C, double count, float eps, float momentum,
+                           float* mean, float* invstd, float* moving_mean, float* moving_var,
+                           const unsigned long long* peer_bases, int rank, int world, int* err, void* stream);
+int pctts_bn_sync_bwd(const double* partial, double* sums, int nblk, int C, float* dgamma, float* dbeta, float scale,
+                      int accumulate, const unsigned long long* peer_bases, int rank, int world, int* err, void* stream);
 
 #ifdef __cplusplus
 }

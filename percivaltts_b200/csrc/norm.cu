@@ -461,6 +461,18 @@ extern "C" int pctts_bn_bwd_reduce(const float* x, const float* dy, const float*
     return PCTTS_OK;
 }
 
+// Backward, phase 1, first stage only: pctts_colreduce_nblk(rows, C) partials [2][C] at the base of the workspace, consumed by
+// pctts_bn_sync_bwd (second stage + replica exchange + dgamma / dbeta in one launch).
+extern "C" int pctts_bn_bwd_reduce_partial(const float* x, const float* dy, const float* mean, const float* invstd,
+                                           const float* gamma, const float* beta, long rows, int C, int lrelu, void* workspace,
+                                           void* stream) {
+    if (!x || !dy || !mean || !invstd || !gamma || !beta || !workspace || rows <= 0) return PCTTS_EINVAL;
+    Ws w = carve(workspace, rows, C);
+    RedArgs a{x, dy, mean, invstd, gamma, beta, rows, C, lrelu};
+    PCTTS_CUDA_RC(run_colreduce<MODE_BNBWD>(a, w, (cudaStream_t)stream, false));
+    return PCTTS_OK;
+}
+
 // Backward, phase 2 (count = global row count when the sums were all-reduced across ranks).
 extern "C" int pctts_bn_bwd_apply(const float* x, const float* dy, float* dx, const float* mean, const float* invstd,
                                   const float* gamma, const float* beta, long rows, int C, double count, int lrelu,

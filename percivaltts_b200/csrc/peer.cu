@@ -104,3 +104,154 @@ extern "C" int pctts_peer_allreduce_f64(double* x, int n, const unsigned long lo
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// BatchNorm reductions with the replica exchange INSIDE the launch (sync-BN).
+//
+// Per BatchNorm layer the single-replica step runs  [first-stage partial sums] -> [second stage + finalize]  (forward) and
+// [first-stage partials] -> [second stage] -> [backward apply] -> [sums -> dgamma / dbeta]  (backward).  On replicas the second
+// stage, the peer-memory exchange and the finalize were three dependent launches per layer (41 layers' worth per critic +
+// generator step).  The kernels below do  second stage -> publish -> wait -> rank-ordered sum -> finalize (or -> sums + dgamma /
+// dbeta)  in ONE launch, one CTA per slice of 32 channels, each slice with its own sequence counter, flags and double-buffered
+// slots in a second symmetric buffer.  Arithmetic and summation orders are those of colreduce_final_kernel / peer_allreduce_kernel /
+// bn_finalize_kernel / sums_to_grads_kernel, so the results are bit-identical to the separate launches.  world == 1 (bases NULL)
+// skips the exchange: the same launch then serves the single replica (backward: one launch fewer per layer).
+//
+// Symmetric buffer per rank: seq u64 [SL_MAX] | flags u64 [2][SL_MAX][world] | data double [2][SL_MAX][64]
+namespace {
+
+constexpr int SL_MAX = 32;           // slices of 32 channels: C <= 1024
+constexpr int SL_COLS = 32;
+
+__host__ __device__ inline long sl_flags_off() { return (long)SL_MAX * 8; }
+__host__ __device__ inline long sl_data_off(int world) { return sl_flags_off() + ((2L * SL_MAX * world * 8 + 127) / 128) * 128; }
+
+struct BnSyncArgs {
+    const double* partial;   // [nblk][2][C]
+    double* sums;            // [2][C] (global result, read by bn_bwd_apply / readers of the workspace)
+    int nblk, C;
+    int mode;                // 0: forward finalize, 1: backward (sums + dgamma / dbeta)
+    double count;
+    float eps, momentum;
+    float *mean, *invstd, *moving_mean, *moving_var;      // mode 0
+    float *g1, *g2;                                       // mode 1: g1 (+)= scale * sums[0] (dbeta), g2 (+)= scale * sums[1] (dgamma)
+    double scale;
+    int accumulate;
+    int rank, world;
+    int* err;
+};
+
+__global__ void __launch_bounds__(256) bn_sync_kernel(BnSyncArgs a, PeerBases bases) {
+    pdl_entry();
+    __shared__ double loc[2 * SL_COLS];
+    __shared__ uint64_t s_seq;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int s = blockIdx.x, C = a.C;
+    const int c0 = s * SL_COLS;
+    const int ncol = min(SL_COLS, C - c0);
+    // second stage: one warp per element, lanes stride over the CTA partials, butterfly (colreduce_final_kernel's order)
+    for (int k = 0; k < 8; ++k) {
+        const int e = warp * 8 + k, m = e >> 5, j = e & 31;
+        double q = 0.0;
+        if (j < ncol)
+            for (int b = lane; b < a.nblk; b += 32) q += a.partial[(long)b * 2 * C + (long)m * C + c0 + j];
+        q = warp_sum_d(q);
+        if (lane == 0) loc[e] = q;
+    }
+    __syncthreads();
+    if (a.world > 1) {
+        uint8_t* const mine = reinterpret_cast<uint8_t*>(bases.b[a.rank]);
+        if (tid == 0) s_seq = reinterpret_cast<volatile uint64_t*>(mine)[s] + 1;
+        __syncthreads();
+        const uint64_t seq = s_seq;
+        const int par = (int)(seq & 1);
+        const long doff = sl_data_off(a.world) + ((long)par * SL_MAX + s) * 64 * 8;
+        if (tid < 64) reinterpret_cast<double*>(mine + doff)[tid] = loc[tid];
+        __threadfence_system();
+        __syncthreads();
+        if (tid < a.world) {
+            const long foff = sl_flags_off() + (((long)par * SL_MAX + s) * a.world) * 8;
+            st_release_sys(reinterpret_cast<uint64_t*>(bases.b[tid] + foff) + a.rank, seq);
+            const uint64_t* f = reinterpret_cast<const uint64_t*>(mine + foff) + tid;
+            const long long t0 = clock64();
+            while (ld_acquire_sys(f) < seq) {
+                if (clock64() - t0 > PEER_SPIN_LIMIT) {
+                    *a.err = 1;
+                    break;
+                }
+            }
+        }
+        __syncthreads();
+        if (tid < 64) {
+            double q = 0.0;
+            for (int r = 0; r < a.world; ++r) q += ld_relaxed_sys_f64(reinterpret_cast<const double*>(bases.b[r] + doff) + tid);
+            loc[tid] = q;
+        }
+        __syncthreads();
+        if (tid == 0) reinterpret_cast<volatile uint64_t*>(mine)[s] = seq;
+    }
+    if (tid < 64) {
+        const int m = tid >> 5, j = tid & 31;
+        if (j < ncol) a.sums[(long)m * C + c0 + j] = loc[tid];
+    }
+    if (tid < ncol) {
+        const int c = c0 + tid;
+        if (a.mode == 0) {
+            const double mu = loc[tid] / a.count;
+            double v = loc[SL_COLS + tid] / a.count - mu * mu;
+            if (v < 0.0) v = 0.0;
+            a.mean[c] = (float)mu;
+            a.invstd[c] = (float)(1.0 / sqrt(v + (double)a.eps));
+            if (a.moving_mean) {
+                a.moving_mean[c] = a.momentum * a.moving_mean[c] + (1.f - a.momentum) * (float)mu;
+                a.moving_var[c] = a.momentum * a.moving_var[c] + (1.f - a.momentum) * (float)v;
+            }
+        } else {
+            if (a.g1) a.g1[c] = (a.accumulate ? a.g1[c] : 0.f) + (float)(loc[tid] * a.scale);
+            if (a.g2) a.g2[c] = (a.accumulate ? a.g2[c] : 0.f) + (float)(loc[SL_COLS + tid] * a.scale);
+        }
+    }
+}
+
+int bn_sync_launch(BnSyncArgs& a, const unsigned long long* peer_bases, cudaStream_t st) {
+    if (a.C < 1 || a.C > SL_MAX * SL_COLS || a.nblk < 1) return PCTTS_EINVAL;
+    if (a.world > 1 && (!peer_bases || !a.err || a.world > PEER_MAX_WORLD || a.rank < 0 || a.rank >= a.world)) return PCTTS_EINVAL;
+    PeerBases b;
+    for (int r = 0; r < PEER_MAX_WORLD; ++r) b.b[r] = (a.world > 1 && r < a.world) ? peer_bases[r] : 0;
+    pctts_launch(bn_sync_kernel, pctts_div_up(a.C, SL_COLS), 256, 0, st, a, b);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
+}  // namespace
+
+/* bytes of the symmetric buffer of the sliced protocol (zeroed, then a barrier, before the first call) */
+extern "C" long pctts_bn_sync_bytes(int world) {
+    if (world < 1 || world > PEER_MAX_WORLD) return -1;
+    return sl_data_off(world) + 2L * SL_MAX * 64 * 8;
+}
+
+/* Forward BatchNorm statistics: second reduction stage over the nblk first-stage partials [nblk][2][C] (doubles) at `partial`,
+ * all-reduce over the replicas (world > 1), sums -> `sums` [2][C], mean / invstd (and the moving averages) -- one launch. */
+extern "C" int pctts_bn_sync_finalize(const double* partial, double* sums, int nblk, int C, double count, float eps, float momentum,
+                                      float* mean, float* invstd, float* moving_mean, float* moving_var,
+                                      const unsigned long long* peer_bases, int rank, int world, int* err, void* stream) {
+    if (!partial || !sums || !mean || !invstd || count <= 0) return PCTTS_EINVAL;
+    BnSyncArgs a{};
+    a.partial = partial, a.sums = sums, a.nblk = nblk, a.C = C, a.mode = 0, a.count = count, a.eps = eps, a.momentum = momentum;
+    a.mean = mean, a.invstd = invstd, a.moving_mean = moving_mean, a.moving_var = moving_var;
+    a.rank = rank, a.world = world, a.err = err;
+    return bn_sync_launch(a, peer_bases, (cudaStream_t)stream);
+}
+
+/* Backward BatchNorm sums [sum dz, sum dz*xhat]: second stage, all-reduce, sums -> `sums` (read by pctts_bn_bwd_apply), and
+ * dbeta (+)= scale * sums[0], dgamma (+)= scale * sums[1] -- one launch. */
+extern "C" int pctts_bn_sync_bwd(const double* partial, double* sums, int nblk, int C, float* dgamma, float* dbeta, float scale,
+                                 int accumulate, const unsigned long long* peer_bases, int rank, int world, int* err, void* stream) {
+    if (!partial || !sums) return PCTTS_EINVAL;
+    BnSyncArgs a{};
+    a.partial = partial, a.sums = sums, a.nblk = nblk, a.C = C, a.mode = 1, a.count = 1.0;
+    a.g1 = dbeta, a.g2 = dgamma, a.scale = (double)scale, a.accumulate = accumulate;
+    a.rank = rank, a.world = world, a.err = err;
+    return bn_sync_launch(a, peer_bases, (cudaStream_t)stream);
+}

@@ -109,6 +109,14 @@ class _BNNet(object):
         for bwd in ((False, True) if with_backward is None else (bool(with_backward),)):
             self._plans.pop((B, T, bwd), None)
 
+    def _fused_sync(self, sync):
+        """Second reduction stage, replica exchange and finalize ride in ONE launch: on a single replica, or when the replicas
+        exchange through NVLink peer memory (parallel.DistSync.enable_peer)."""
+        o = self.ops
+        if not getattr(o, 'bn_sync', False) or not getattr(o, 'bn_single_launch', True):
+            return False
+        return sync.world == 1 or getattr(sync, 'bn_handle', None) is not None
+
     def _bn_fwd(self, z2, y2, bn, training, update_stats, sync, ws=None, apply=True):
         """ws: the batch sums when the producer of z2 already reduced them (Conv2D epilogue).  apply=False: only the
         statistics (bn.mean / bn.invstd) -- the consumer applies BatchNorm + LeakyReLU on load."""
@@ -116,11 +124,16 @@ class _BNNet(object):
         g, b = p[bn.prefix + '.gamma'], p[bn.prefix + '.beta']
         mm, mv = p[bn.prefix + '.moving_mean'], p[bn.prefix + '.moving_var']
         if training:
+            fused = self._fused_sync(sync)
             if ws is None:
-                ws = o.bn_stats(z2, final=sync.world > 1 or not getattr(o, 'bn_single_launch', True))    # single replica: the second stage rides in bn_finalize's launch
-            sync.allreduce(ws.sums)
-            o.bn_finalize(ws, bn.rows * sync.world, A.BN_EPS, A.BN_MOMENTUM, bn.mean, bn.invstd,
-                          mm if update_stats else None, mv if update_stats else None)
+                ws = o.bn_stats(z2, final=not fused and (sync.world > 1 or not getattr(o, 'bn_single_launch', True)))
+            if fused and sync.world > 1 and getattr(ws, 'pending', 0) > 0:
+                o.bn_sync_finalize(ws, bn.rows * sync.world, A.BN_EPS, A.BN_MOMENTUM, bn.mean, bn.invstd,
+                                   mm if update_stats else None, mv if update_stats else None, sync)
+            else:
+                sync.allreduce(ws.sums)
+                o.bn_finalize(ws, bn.rows * sync.world, A.BN_EPS, A.BN_MOMENTUM, bn.mean, bn.invstd,
+                              mm if update_stats else None, mv if update_stats else None)
             if apply:
                 o.bn_apply(z2, y2, bn.mean, bn.invstd, g, b, A.BN_EPS, 0, 1)
         else:
@@ -129,10 +142,15 @@ class _BNNet(object):
     def _bn_bwd(self, z2, dy2, dz2, bn, sync):
         o, p, g = self.ops, self.params.p, self.params.g
         gam, bet = p[bn.prefix + '.gamma'], p[bn.prefix + '.beta']
-        ws = o.bn_bwd_reduce(z2, dy2, bn.mean, bn.invstd, gam, bet, 1)
-        sync.allreduce(ws.sums)
         # dgamma / dbeta come from the all-reduced sums, i.e. every rank holds the global value: pre-divide by world so
         # that the all-reduce(sum) of the flat gradient buffer does not count them `world` times
+        if self._fused_sync(sync):
+            ws = o.bn_bwd_reduce(z2, dy2, bn.mean, bn.invstd, gam, bet, 1, final=False)
+            o.bn_sync_bwd(ws, g[bn.prefix + '.gamma'], g[bn.prefix + '.beta'], 1.0 / sync.world, False, sync)
+            o.bn_bwd_apply(ws, z2, dy2, dz2, bn.mean, bn.invstd, gam, bet, bn.rows * sync.world, 1, None, None)
+            return
+        ws = o.bn_bwd_reduce(z2, dy2, bn.mean, bn.invstd, gam, bet, 1)
+        sync.allreduce(ws.sums)
         o.bn_bwd_apply(ws, z2, dy2, dz2, bn.mean, bn.invstd, gam, bet, bn.rows * sync.world, 1,
                        g[bn.prefix + '.gamma'], g[bn.prefix + '.beta'], grad_scale=1.0 / sync.world)
 
@@ -309,7 +327,7 @@ class Generator(_BNNet):
         pending = None      # BatchNorm of the previous layer still to be applied (on load) by the next convolution
         for i in range(L):
             ws = o.conv2d(amap, p['g.spec.cnn%d.kernel' % i], pl['cv_z'][i], stats=training, in_bn=pending,
-                          stats_final=sync.world > 1 or not getattr(o, 'bn_single_launch', True))
+                          stats_final=not self._fused_sync(sync))
             # forward-only use (frozen generator of the critic step): nothing reads the activation map but the next
             # convolution, which forms it on load -- it is written for the last layer only (input of the output Conv2D)
             keep = materialize or not training or i == L - 1

@@ -674,14 +674,42 @@ class CudaOps(object):
                                          gamma.data_ptr(), beta.data_ptr(), rows, C, float(eps), int(use_var), int(lrelu),
                                          self._stream()), 'pctts_bn_apply')
 
-    def bn_bwd_reduce(self, x, dy, mean, invstd, gamma, beta, lrelu):
+    def bn_bwd_reduce(self, x, dy, mean, invstd, gamma, beta, lrelu, final=True):
+        """final=False: first stage only (ws.pending partials), for bn_sync_bwd()."""
         rows, C = x.shape
         assert x.is_contiguous() and dy.is_contiguous()
         ws = self.reduce_ws(rows, C)
-        self._ck(self.lib.pctts_bn_bwd_reduce(x.data_ptr(), dy.data_ptr(), mean.data_ptr(), invstd.data_ptr(), gamma.data_ptr(),
-                                              beta.data_ptr(), rows, C, int(lrelu), ws.ptr, self._stream()),
-                 'pctts_bn_bwd_reduce')
+        fn = self.lib.pctts_bn_bwd_reduce if final else self.lib.pctts_bn_bwd_reduce_partial
+        self._ck(fn(x.data_ptr(), dy.data_ptr(), mean.data_ptr(), invstd.data_ptr(), gamma.data_ptr(),
+                    beta.data_ptr(), rows, C, int(lrelu), ws.ptr, self._stream()), 'pctts_bn_bwd_reduce')
+        ws.pending = 0 if final else self.lib.pctts_colreduce_nblk(rows, C)
         return ws
+
+    # -- BatchNorm second stage + replica exchange + finalize in ONE launch (csrc/peer.cu: bn_sync_kernel) --------------------
+    bn_sync = True
+
+    @staticmethod
+    def _peer_args(sync):
+        h = getattr(sync, 'bn_handle', None)
+        if h is None or sync.world == 1:
+            return None, 0, 1, None
+        bases, err = h
+        return ctypes.cast(bases, ctypes.c_void_p), sync.rank, sync.world, err.data_ptr()
+
+    def bn_sync_finalize(self, ws, count, eps, momentum, mean, invstd, moving_mean, moving_var, sync):
+        assert getattr(ws, 'pending', 0) > 0
+        bases, rank, world, err = self._peer_args(sync)
+        self._ck(self.lib.pctts_bn_sync_finalize(ws.ptr, ws.sums.data_ptr(), ws.pending, ws.C, float(count), float(eps), float(momentum),
+                                                 mean.data_ptr(), invstd.data_ptr(), _ptr(moving_mean), _ptr(moving_var), bases, rank,
+                                                 world, err, self._stream()), 'pctts_bn_sync_finalize')
+        ws.pending = 0
+
+    def bn_sync_bwd(self, ws, dgamma, dbeta, scale, accumulate, sync):
+        assert getattr(ws, 'pending', 0) > 0
+        bases, rank, world, err = self._peer_args(sync)
+        self._ck(self.lib.pctts_bn_sync_bwd(ws.ptr, ws.sums.data_ptr(), ws.pending, ws.C, _ptr(dgamma), _ptr(dbeta), float(scale),
+                                            int(accumulate), bases, rank, world, err, self._stream()), 'pctts_bn_sync_bwd')
+        ws.pending = 0
 
     def bn_bwd_apply(self, ws, x, dy, dx, mean, invstd, gamma, beta, count, lrelu, dgamma, dbeta, grad_scale=1.0,
                      accumulate=False):

@@ -29,6 +29,7 @@ class DistSync(object):
         self.calls = 0
         self.peer_calls = 0
         self._peer = None
+        self._bn = None            # (bases, err) of the sliced sync-BatchNorm protocol (second symmetric buffer)
         self.peer_error = None
 
     def allreduce(self, t):
@@ -62,11 +63,18 @@ class DistSync(object):
             buf.zero_()
             bases = (ctypes.c_ulonglong * self.world)(*[int(p) for p in hdl.buffer_ptrs])
             err = torch.zeros(1, dtype=torch.int32, device=device)
-            self._peer_keep = (buf, hdl)
+            # second symmetric buffer: BatchNorm second stage + exchange + finalize in one launch (one slot set per 32 channels)
+            nb2 = lib.pctts_bn_sync_bytes(self.world)
+            buf2 = symm_mem.empty((nb2 + 7) // 8, dtype=torch.float64, device=device)
+            hdl2 = symm_mem.rendezvous(buf2, group.group_name)
+            buf2.zero_()
+            bases2 = (ctypes.c_ulonglong * self.world)(*[int(p) for p in hdl2.buffer_ptrs])
+            self._peer_keep = (buf, hdl, buf2, hdl2)
             peer = (lib, bases, err)
+            bn = (bases2, err)
             ok.fill_(1.0)
         except Exception as e:      # noqa: BLE001 -- any failure here means "use NCCL"
-            peer = None
+            peer = bn = None
             self.peer_error = repr(e)
         torch.cuda.synchronize(device)
         dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)      # all ranks or none (also the barrier after zeroing)
@@ -83,6 +91,8 @@ class DistSync(object):
         if float(flag) < 1.0:
             self._peer = None
             return False
+        if os.environ.get('PCTTS_BN_SYNC_FUSED', '1') != '0':
+            self._bn = bn
         return True
 
     def broadcast_scalar(self, x, src=0):
@@ -94,6 +104,11 @@ class DistSync(object):
 
     def barrier(self):
         dist.barrier(group=self.group)
+
+    @property
+    def bn_handle(self):
+        """(peer bases, err flag) of the fused sync-BatchNorm launches, or None (exchange as separate launches)."""
+        return self._bn
 
     @property
     def peer_err(self):

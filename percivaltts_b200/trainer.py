@@ -100,8 +100,9 @@ class DeviceTrainer(object):
         st = self.st
         keep_state = st.G.params.state.clone()
         keep_counter = st.counter.clone()
-        s.X.zero_()
-        s.Y.zero_()
+        if not getattr(s, 'filled', False):      # a fresh entry: finite inputs for the warm-up; an entry that already ran eagerly (or
+            s.X.zero_()                          # holds the prefetched next batch) keeps its contents
+            s.Y.zero_()
         side = torch.cuda.Stream(device=self.ops.device)
         side.wait_stream(torch.cuda.current_stream(self.ops.device))
         with torch.cuda.stream(side):
@@ -154,6 +155,7 @@ class DeviceTrainer(object):
         np.copyto(s.Yh.numpy(), np.asarray(Y, dtype=np.float32).reshape(s.Yh.shape))
         s.X.copy_(s.Xh, non_blocking=True)
         s.Y.copy_(s.Yh, non_blocking=True)
+        s.filled = True
         self.h2d_bytes += s.Xh.numel() * 4 + s.Yh.numel() * 4
         if alpha is not None:
             s.alpha.copy_(torch.as_tensor(np.asarray(alpha, dtype=np.float32)), non_blocking=False)
@@ -228,6 +230,7 @@ class DeviceTrainer(object):
                 torch.cuda.current_stream(self.ops.device).wait_event(b['ev'])
                 s.X.view(-1).copy_(b['Xd'][:s.X.numel()], non_blocking=True)
                 s.Y.view(-1).copy_(b['Yd'][:s.Y.numel()], non_blocking=True)
+                s.filled = True
                 self._pf_placed = s
         if self.ops.device.type == 'cuda':
             torch.cuda.current_stream(self.ops.device).synchronize()

@@ -99,7 +99,16 @@ def test_critic_and_generator_step_vs_oracle(cuda_ops, kw, B, T):
     cpl = st.C.plan(3, B, T)
     for slot, key in ((W.L_REAL, 'l_real'), (W.L_FAKE, 'l_fake'), (W.L_GP, 'gp'), (W.L_CRITIC, 'loss')):
         assert abs(float(losses[slot]) - float(rc[key])) < TOL * max(abs(float(rc[key])), 1e-2), (key, losses, rc[key])
-    assert relerr(st.buffers(B, T)['g'].view(B, T, -1), rc['gp_grad'][:, :, 1:1 + ao.spec_size]) < TOL
+    # the penalty's input gradient: 1e-3 in relative L2 norm; element-wise (max norm) 1e-3 too, unless the oracle's own fp32
+    # evaluation shows LeakyReLU mask flips on this input (at B=10, T=400 the stack holds 16.5 M pre-activations; one within fp32
+    # round-off of zero takes the other slope in any fp32 evaluation and moves the gradient around that pixel by O(1e-2))
+    S0 = ao.spec_size
+    got_g, want_g = st.buffers(B, T)['g'].view(B, T, -1).detach().cpu().double(), rc['gp_grad'][:, :, 1:1 + S0].double()
+    g32 = rc32['gp_grad'][:, :, 1:1 + S0].double()
+    l2 = float(((got_g - want_g) ** 2).sum().sqrt() / (want_g ** 2).sum().sqrt())
+    e, e32 = relerr(got_g, want_g), relerr(g32, want_g)
+    print('gp input gradient B=%d T=%d: rel L2 %.2e  max-rel %.2e  (fp32 oracle max-rel %.2e)' % (B, T, l2, e, e32))
+    assert l2 < TOL and e < max(TOL, 3.0 * e32), (l2, e, e32)
     check_grads(st.C.params, rc['grads'], rc32['grads'])
     rg = O.generator_step(ao, wgt, wct, Xt, Yt)
     st.generator_step(Xd, Yd, apply=False)
