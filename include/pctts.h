@@ -130,6 +130,7 @@ typedef struct pctts_chain_layer {
     long ybatch, ypitch, auxbatch, auxpitch;
     int cin, cout, flags, flip;
 } pctts_chain_layer;
+int pctts_conv2d_chain_set_trace(void* buf);  /* developer probe: PCTTS_CHAIN_MAX_LAYERS*16 int64 clock stamps of CTA 0; NULL = off */
 int pctts_conv2d_chain_supported(int T, int F, int nterms);   /* host call: CTAs per sample (cluster size), 0 = unsupported */
 int pctts_conv2d_chain(const float* x, long xbatch, long xpitch, int cin0, int NB, int T, int F, int nlayers,
                        const pctts_chain_layer* layers, int nterms, void* stream);

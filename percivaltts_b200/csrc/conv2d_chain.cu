@@ -22,10 +22,11 @@
 // origin; odd layers walk downwards and write D entries ABOVE: a block's output then only lands on entries that no later block of
 // the layer reads (proof in DESIGN.md section 4.10), and the two origins alternate, so the slack is D entries, not L*D.
 //
-// Structure: 288 threads.  warps 0-7 = workers (initial tile load, block-Toeplitz build of the NEXT layer's weights, epilogue:
-// tcgen05.ld -> bias / LeakyReLU / mask -> fp32 store + bf16 planes of the next layer, halo exchange); warp 8 = MMA issuer.
-// TMEM accumulators are double-buffered in chunks of 5 blocks (240 columns each), so a chunk's epilogue runs under the next
-// chunk's MMAs.
+// Structure: 416 threads.  warps 0-11 = workers in three sets (initial tile load, block-Toeplitz build of the NEXT layer's weights, epilogue:
+// tcgen05.ld -> bias / LeakyReLU / mask -> fp32 store + bf16 planes of the next layer, halo exchange); warp 12 = MMA issuer.
+// TMEM holds 10 accumulator slots of one 128-row block each (48 columns at 3 planes), handed over one by one (an mbarrier pair per
+// slot): the MMAs of up to 10 blocks run ahead of the epilogue, set s drains blocks s, s+3, .., so only the last block's epilogue
+// is exposed at the end of a layer (clock trace: with two 5-block buffers the tail was ~5.5 k of a 27 k-cycle layer).
 #include "common.cuh"
 #include "pctts.h"
 #include "tc_common.cuh"
@@ -36,11 +37,12 @@ namespace {
 using namespace tcx;
 
 constexpr int CH_MAXL = PCTTS_CHAIN_MAX_LAYERS;
-constexpr int CH_WORK = 256;                 // worker threads (warps 0-7)
+constexpr int CH_SETS = 3;                   // worker sets: set s takes the blocks at positions s, s + 3, s + 6, .. of a layer
+constexpr int CH_WORK = CH_SETS * 128;       // worker threads (warps 0-11; warp w reads TMEM lane quarter w & 3)
 constexpr int CH_MW = CH_WORK / 32;          // index of the MMA warp
 constexpr int CH_THREADS = CH_WORK + 32;
-constexpr int CH_CHUNK = 5;                  // 128-row blocks per TMEM buffer
 constexpr int CH_TMEM_COLS = 512;
+constexpr int CH_MAXSLOT = 16;               // accumulator slots (one 128-row block each) in TMEM: 512 / (16 * PARTS), at most 16
 constexpr int CKT = 5, CKW = 5, CNMMA = CKT * 2;
 
 struct ChainLayer {
@@ -64,6 +66,7 @@ struct ChainParams {
     int E;                 // 16-byte entries per parity array
     int D;                 // slide between the two origins, in entries
     int nlayers;
+    long long* trace;      // developer probe (pctts_conv2d_chain_set_trace): clock64() stamps of CTA 0, 16 per layer
     ChainLayer L[CH_MAXL];
 };
 
@@ -98,12 +101,12 @@ template <int PARTS>
 __global__ void __launch_bounds__(CH_THREADS, 1) conv2d_chain_kernel(const ChainParams p) {
     pdl_entry();
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t acc_full[2], acc_empty[2];
+    __shared__ __align__(8) uint64_t acc_full[CH_MAXSLOT], acc_empty[CH_MAXSLOT];
     __shared__ uint32_t tmem_slot;
     __shared__ float wsm[CKT * CKW * 16];
     using S = ChSmem<PARTS>;
     constexpr int BLKCOLS = 16 * PARTS;
-    constexpr int BUFCOLS = CH_CHUNK * BLKCOLS;
+    constexpr int NSLOT = (CH_TMEM_COLS / BLKCOLS) < CH_MAXSLOT ? (CH_TMEM_COLS / BLKCOLS) : CH_MAXSLOT;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t smem_base = (smem_u32(smem_raw) + 15u) & ~15u;
@@ -120,13 +123,12 @@ __global__ void __launch_bounds__(CH_THREADS, 1) conv2d_chain_kernel(const Chain
     const int nfr = min(p.Fc, p.T - t0);                        // frames owned by this CTA (>= 1 by construction)
     const int rows_valid = nfr * G;
     const int nblk = (rows_valid + 127) / 128;
-    const int nchunk = (nblk + CH_CHUNK - 1) / CH_CHUNK;
     const int row_pairs = 2 * G;
 
     if (tid == 0) {
-        for (int s = 0; s < 2; ++s) {
+        for (int s = 0; s < NSLOT; ++s) {
             mbar_init(smem_u32(&acc_full[s]), 1);
-            mbar_init(smem_u32(&acc_empty[s]), CH_WORK);
+            mbar_init(smem_u32(&acc_empty[s]), 128);      // the four warps (TMEM lane quarters) of the set that drains the block
         }
         fence_barrier_init();
     }
@@ -232,41 +234,43 @@ __global__ void __launch_bounds__(CH_THREADS, 1) conv2d_chain_kernel(const Chain
     tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
 
-    uint32_t cc = 0;      // running chunk counter (TMEM buffer = cc & 1, mbarrier phase = (cc >> 1) & 1); same sequence in every role
+    // blocks are numbered through the whole launch: block `pos` of layer l is number bc = l * nblk + pos, its accumulator slot
+    // bc % NSLOT, its mbarrier phase (bc / NSLOT) & 1 -- the same arithmetic in every role
     for (int l = 0; l < p.nlayers; ++l) {
         const ChainLayer& Ly = p.L[l];
         const int Oin = (l & 1) ? 0 : D, Oout = (l & 1) ? D : 0;
         const bool asc = (l & 1) == 0;
         const bool last = l + 1 == p.nlayers;
+        const bool trm = p.trace && blockIdx.x == 0 && tid == CH_WORK, trw = p.trace && blockIdx.x == 0 && tid == 0;
+        long long* const tr = p.trace ? p.trace + l * 16 : nullptr;
         if (warp == CH_MW) {
             // ------------------------------------------------ MMA issuer ------------------------------------------------
+            if (trm) tr[0] = clock64();
             uint32_t idesc[PARTS];
 #pragma unroll
             for (int pa = 0; pa < PARTS; ++pa) idesc[pa] = umma_idesc_bf16(128, 16 * (PARTS - pa), 0, 0);
             const uint32_t a_lbo = even_off + 16u;
             const uint64_t bdesc0 = umma_desc_noswz(smem_base + (uint32_t)(l & 1) * S::b_bytes, S::b_chunk, 128u);
             const uint64_t adesc0 = umma_desc_noswz(act_u32 + (uint32_t)Oin * 16u, a_lbo, 128u);
-            for (int c = 0; c < nchunk; ++c, ++cc) {
-                const int s = cc & 1;
-                const uint32_t ph = (cc >> 1) & 1u;
+            for (int pos = 0; pos < nblk; ++pos) {
+                const uint32_t bc = (uint32_t)(l * nblk + pos);
+                const int s = (int)(bc % NSLOT);
+                const uint32_t ph = (bc / NSLOT) & 1u;
                 mbar_wait(smem_u32(&acc_empty[s]), ph ^ 1u);
                 tc_fence_after();
                 if (elect_one()) {
-                    const int pos0 = c * CH_CHUNK, pos1 = min(pos0 + CH_CHUNK, nblk);
-                    for (int pos = pos0; pos < pos1; ++pos) {
-                        const int blk = asc ? pos : nblk - 1 - pos;
-                        const uint32_t dcol = tmem_base + (uint32_t)(s * BUFCOLS + (pos - pos0) * BLKCOLS);
+                    const int blk = asc ? pos : nblk - 1 - pos;
+                    const uint32_t dcol = tmem_base + (uint32_t)(s * BLKCOLS);
 #pragma unroll
-                        for (int kt = 0; kt < CKT; ++kt) {
+                    for (int kt = 0; kt < CKT; ++kt) {
 #pragma unroll
-                            for (int h = 0; h < 2; ++h) {
-                                const uint32_t aoff = (uint32_t)(blk * 128 + kt * G + h);
-                                const uint64_t bd = bdesc0 + (uint64_t)((kt * 2 + h) * (S::b_mma >> 4));
+                        for (int h = 0; h < 2; ++h) {
+                            const uint32_t aoff = (uint32_t)(blk * 128 + kt * G + h);
+                            const uint64_t bd = bdesc0 + (uint64_t)((kt * 2 + h) * (S::b_mma >> 4));
 #pragma unroll
-                                for (int pa = 0; pa < PARTS; ++pa) {
-                                    const uint64_t ad = adesc0 + (uint64_t)(aoff + (uint32_t)pa * (plane_bytes >> 4));
-                                    umma_bf16(dcol + 16u * pa, ad, bd, idesc[pa], (kt | h | pa) == 0 ? 0u : 1u);
-                                }
+                            for (int pa = 0; pa < PARTS; ++pa) {
+                                const uint64_t ad = adesc0 + (uint64_t)(aoff + (uint32_t)pa * (plane_bytes >> 4));
+                                umma_bf16(dcol + 16u * pa, ad, bd, idesc[pa], (kt | h | pa) == 0 ? 0u : 1u);
                             }
                         }
                     }
@@ -274,12 +278,14 @@ __global__ void __launch_bounds__(CH_THREADS, 1) conv2d_chain_kernel(const Chain
                 }
                 __syncwarp();
             }
+            if (trm) tr[1] = clock64();
         } else {
             // ------------------------------------------------ workers ------------------------------------------------
             if (!last) {        // the next layer's weight operand, while this layer's first chunk of MMAs runs
                 build_bmat(l + 1);
                 fence_proxy_async();
             }
+            if (trw) tr[4] = clock64();
             const int q = warp & 3, set = warp >> 2;
             const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
             const int flags = Ly.flags;
@@ -306,20 +312,17 @@ __global__ void __launch_bounds__(CH_THREADS, 1) conv2d_chain_kernel(const Chain
                         ax[jo] = (4 * g + jo < p.F) ? *reinterpret_cast<const float4*>(a + 4 * jo) : make_float4(1.f, 1.f, 1.f, 1.f);
                 }
             };
-            // positions handled by this worker set: pos with (pos - chunk start) & 1 == set; walk them in order
-            int next_pos = -1;
-            for (int pos = 0; pos < nblk; ++pos)
-                if ((((pos % CH_CHUNK) & 1) == set)) { next_pos = pos; break; }
-            if (next_pos >= 0) fetch_aux(next_pos);
-            for (int c = 0; c < nchunk; ++c, ++cc) {
-                const int s = cc & 1;
-                const uint32_t ph = (cc >> 1) & 1u;
-                const int pos0 = c * CH_CHUNK, pos1 = min(pos0 + CH_CHUNK, nblk);
-                mbar_wait(smem_u32(&acc_full[s]), ph);
-                tc_fence_after();
-                for (int pos = pos0 + set; pos < pos1; pos += 2) {
+            // positions handled by this worker set: set, set + CH_SETS, ..
+            fetch_aux(set);
+            for (int pos = set; pos < nblk; pos += CH_SETS) {
+                {
+                    const uint32_t bc = (uint32_t)(l * nblk + pos);
+                    const int s = (int)(bc % NSLOT);
+                    const uint32_t ph = (bc / NSLOT) & 1u;
+                    mbar_wait(smem_u32(&acc_full[s]), ph);
+                    tc_fence_after();
                     const int blk = asc ? pos : nblk - 1 - pos;
-                    const uint32_t col = tmem_base + lane_addr + (uint32_t)(s * BUFCOLS + (pos - pos0) * BLKCOLS);
+                    const uint32_t col = tmem_base + lane_addr + (uint32_t)(s * BLKCOLS);
                     uint32_t c0[16];
                     float acc[16];
                     tmem_ld_32x16(col, c0);
@@ -346,12 +349,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) conv2d_chain_kernel(const Chain
                     float4 cur[4];
 #pragma unroll
                     for (int jo = 0; jo < 4; ++jo) cur[jo] = ax[jo];
-                    // the next block of this worker set: pos + 2 inside the chunk, else the first one of this set in the next chunk
-                    {
-                        int np = pos + 2;
-                        if (np >= pos1) np = pos1 + set;
-                        fetch_aux(np);
-                    }
+                    fetch_aux(pos + CH_SETS);          // the mask rows of this set's next block
                     const int r = blk * 128 + q * 32 + lane;
                     if (r < rows_valid) {
                         const int to = r / G, g = r - to * G;
@@ -403,13 +401,15 @@ __global__ void __launch_bounds__(CH_THREADS, 1) conv2d_chain_kernel(const Chain
                             store_planes(de - even_off, vb);
                         }
                     }
+                    if (!last) fence_proxy_async();
+                    tc_fence_before();
+                    mbar_arrive(smem_u32(&acc_empty[s]));
                 }
-                if (!last) fence_proxy_async();
-                tc_fence_before();
-                mbar_arrive(smem_u32(&acc_empty[s]));
             }
+            if (trw) tr[6] = clock64();
         }
         if (last) break;
+        if (trw) tr[11] = clock64();
         // ---- layer hand-over: every CTA of the cluster has stored its fp32 output; the halo frames of the next layer's tile come
         // from the neighbours' rows of that output (zeros outside the sample), the layout's edge entries are cleared
         tc_fence_before();
@@ -419,6 +419,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) conv2d_chain_kernel(const Chain
         } else {
             __syncthreads();
         }
+        if (trw) tr[12] = clock64();
         if (warp < CH_MW) {
             const float* ysrc = Ly.y + (long)n * Ly.ybatch;
             for (int idx = tid; idx < 4 * row_pairs; idx += CH_WORK) {
@@ -442,6 +443,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) conv2d_chain_kernel(const Chain
         }
         __syncthreads();
         tc_fence_after();
+        if (trw) tr[13] = clock64();
     }
     tc_fence_before();
     __syncthreads();
@@ -456,6 +458,13 @@ int chain_max_frames(int G, int parts) {
     const long rows = Emax - D - 4L * G - 8;            // nblk * 128 <= rows
     const long nblk = rows / 128;
     return nblk < 1 ? 0 : (int)((nblk * 128) / G);
+}
+
+// bf16 planes per fp32 operand: 3 / 2 / 1 for nterms = 6 / 3 / 1 (as in gemm_tc.cu); PCTTS_CHAIN_PARTS lowers it for A/B runs
+int chain_parts(int nterms) {
+    static const int cap = getenv("PCTTS_CHAIN_PARTS") ? atoi(getenv("PCTTS_CHAIN_PARTS")) : 3;
+    const int parts = nterms == 6 ? 3 : nterms == 3 ? 2 : nterms == 1 ? 1 : 0;
+    return (cap >= 1 && cap < parts) ? cap : parts;
 }
 
 int chain_pick_nc(int T, int fmax) {
@@ -508,13 +517,22 @@ int launch_chain(ChainParams& p, cudaStream_t st) {
     return PCTTS_OK;
 }
 
+long long* g_chain_trace = nullptr;
+
 }  // namespace
+
+/* developer probe: device buffer of PCTTS_CHAIN_MAX_LAYERS*16 int64 receiving clock64() stamps of CTA 0, per layer: [0] MMA warp
+ * starts, [1] last block issued, [4] next weight operand built, [6] this set's last epilogue done, [11] hand-over starts, [12] cluster barrier passed, [13] halo in place; NULL switches it off */
+extern "C" int pctts_conv2d_chain_set_trace(void* buf) {
+    g_chain_trace = (long long*)buf;
+    return PCTTS_OK;
+}
 
 /* CTAs per sample (cluster size: 1, 2, 4, 8 or 16) the chain kernel would use for maps [*, T, F, <=4] at this precision, or 0 when
  * the shape is not supported (T too long for 16 CTAs of shared memory, F too wide).  Host call. */
 extern "C" int pctts_conv2d_chain_supported(int T, int F, int nterms) {
     if (T < 1 || F < 1) return 0;
-    const int parts = nterms == 6 ? 3 : nterms == 3 ? 2 : nterms == 1 ? 1 : 0;
+    const int parts = chain_parts(nterms);
     if (!parts) return 0;
     const int G = (F + 2 + 3) / 4;
     if (G > 128) return 0;
@@ -525,7 +543,7 @@ extern "C" int pctts_conv2d_chain(const float* x, long xbatch, long xpitch, int 
                                   const pctts_chain_layer* layers, int nterms, void* stream) {
     if (!x || !layers || NB < 0 || T < 0 || F <= 0 || nlayers < 1 || nlayers > CH_MAXL) return PCTTS_EINVAL;
     if (cin0 != 1 && cin0 != 4) return PCTTS_EUNSUPPORTED;
-    const int parts = nterms == 6 ? 3 : nterms == 3 ? 2 : nterms == 1 ? 1 : 0;
+    const int parts = chain_parts(nterms);
     if (!parts) return PCTTS_EINVAL;
     if (NB == 0 || T == 0) return PCTTS_OK;
     ChainParams p;
@@ -542,6 +560,7 @@ extern "C" int pctts_conv2d_chain(const float* x, long xbatch, long xpitch, int 
     p.D = 2 * p.G + 2;
     p.E = p.D + p.nblk * 128 + 4 * p.G + 8;
     p.nlayers = nlayers;
+    p.trace = g_chain_trace;
     int cin = cin0;
     for (int l = 0; l < nlayers; ++l) {
         const pctts_chain_layer& s = layers[l];
