@@ -147,6 +147,23 @@ int pctts_conv2d_wgrad_bias(const float* x, const float* dy, float* dw, float* d
                             int F, int CIN, int COUT, int KH, int KW, int pad_t, int pad_f, long xpitch, long dypitch, long xbatch,
                             long dybatch, float scale, int accumulate, void* stream);
 
+/* The same gradients for up to PCTTS_WGRAD_MAX_LAYERS layers of a 5x5 'same' stack in ONE launch (+ one reduce launch): the CTAs of
+ * the grid are divided between the layers.  Layer l: x [NB,T,F,cin] (cin = 4, or 1 for the first layer of the stack), dy [NB,T,F,4],
+ * dw [5][5][cin][4] (+)= scale * sum, dbias [4] = sum over the first nb_bias samples (or NULL).  16-byte aligned dy (and x when
+ * cin = 4), pitches / batch strides in floats and multiples of 4; workspace of pctts_conv2d_wgrad_multi_workspace(nlayers) floats. */
+#define PCTTS_WGRAD_MAX_LAYERS 9
+typedef struct pctts_wgrad_layer {
+    const float* x;
+    const float* dy;
+    float* dw;
+    float* dbias;
+    long xbatch, xpitch, dybatch, dypitch;
+    int cin;
+} pctts_wgrad_layer;
+long pctts_conv2d_wgrad_multi_workspace(int nlayers);   /* floats; host call */
+int pctts_conv2d_wgrad_multi(const pctts_wgrad_layer* layers, int nlayers, int nb_bias, float* workspace, int NB, int T, int F,
+                             float scale, int accumulate, void* stream);
+
 /* ---- BatchNormalization(axis=-1) + LeakyReLU (networktts.py:61-62,118-119,124-125), data [rows, C] ------------------- */
 long pctts_colreduce_workspace_bytes(long rows, int C);            /* host call; zero the workspace once after allocation */
 void* pctts_colreduce_sums_ptr(void* workspace, long rows, int C); /* host call; double sums[2][C] inside the workspace

@@ -593,13 +593,16 @@ class Critic(object):
             # tangent sweep); the other applications' pre-activation gradients are needed by the weight gradients only:
             # side lane, followed there by everything else that hangs off them (ctx branch, bias sums).
             with o.side_lane():
-                self._dgrad_chain(pl, slice(0, g_rows.start))
+                first = slice(0, g_rows.start)
+                self._dgrad_chain(pl, first, part='fc')
+                # the ctx-branch gradients hang off dp[0] alone: a second side lane beside this one's convolutions
+                self.param_grads_ctx(pl, ctx_grads_apps)
+                self._dgrad_chain(pl, first, part='conv')
                 # the spectral kernels' gradient over these applications' rows; the lane that carries the tangent sweep adds
                 # the gradient-penalty rows' share afterwards (param_grads), so its long chain ends with a third of the work
                 self._conv_wgrads(pl, slice(0, g_rows.start), first=True)
                 pl['conv_wgrads_apps'] = g_rows.start // pl['B']
                 pl['side_event'] = o.lane_event()
-                self.param_grads_ctx(pl, ctx_grads_apps)
             self._dgrad_chain(pl, g_rows, final=(g_out, accumulate) if chain else None)
         elif chain and (g_rows is None or (g_rows.start == 0 and g_rows.stop == pl['nB'])):
             self._dgrad_chain(pl, slice(0, pl['nB']), final=(g_out, accumulate))
@@ -618,20 +621,24 @@ class Critic(object):
         src = pl['da'][0] if g_rows is None else pl['da'][0][g_rows]
         o.conv2d(src, pl['wflip'][0], g_out, flags=EPI_ACCUM if accumulate else 0)
 
-    def _dgrad_chain(self, pl, samples, final=None):
+    def _dgrad_chain(self, pl, samples, final=None, part='all'):
         """Pre-activation gradients dp[2..0], da[L-1..0] of the applications `samples` (slice over the napp*B axis).
-        final = (g_out, accumulate): also the gradient w.r.t. the spectral input of these applications (chain kernel only)."""
+        final = (g_out, accumulate): also the gradient w.r.t. the spectral input of these applications (chain kernel only).
+        part = 'fc' / 'conv': only the post layers (down to da[L-1]) / only the Conv2D stack."""
         o, a, p = self.ops, self.a, self.params.p
         T, nM = pl['T'], pl['nM']
         S, Fl, L = a.spec_size, a.gen_nbfilters, a.gen_nbcnnlayers
         SF = S * Fl
         whole = samples.start == 0 and samples.stop == pl['nB']
         r = slice(None) if whole else slice(samples.start * T, samples.stop * T)
-        o.gemm(pl['dd'][r], p['c.out.kernel'], pl['dp'][2][r], transB=True, aux=pl['p'][2][r])
-        o.gemm(pl['dp'][2][r], p['c.post.fc2.kernel'], pl['dp'][1][r], transB=True, aux=pl['p'][1][r])
-        o.gemm(pl['dp'][1][r], p['c.post.fc1.kernel'], pl['dp'][0][r], transB=True, aux=pl['p'][0][r])
-        o.gemm(pl['dp'][0][r], p['c.post.fc0.kernel'][:SF], pl['da'][L - 1].view(nM, SF)[r], transB=True,
-               aux=pl['a'][L - 1].view(nM, SF)[r])
+        if part != 'conv':
+            o.gemm(pl['dd'][r], p['c.out.kernel'], pl['dp'][2][r], transB=True, aux=pl['p'][2][r])
+            o.gemm(pl['dp'][2][r], p['c.post.fc2.kernel'], pl['dp'][1][r], transB=True, aux=pl['p'][1][r])
+            o.gemm(pl['dp'][1][r], p['c.post.fc1.kernel'], pl['dp'][0][r], transB=True, aux=pl['p'][0][r])
+            o.gemm(pl['dp'][0][r], p['c.post.fc0.kernel'][:SF], pl['da'][L - 1].view(nM, SF)[r], transB=True,
+                   aux=pl['a'][L - 1].view(nM, SF)[r])
+        if part == 'fc':
+            return
         sm = slice(None) if whole else samples
         if self._chain(T):
             layers = [dict(w=p['c.spec.cnn%d.kernel' % i], flip=True, aux=pl['a'][i - 1][sm], y=pl['da'][i - 1][sm])
@@ -684,7 +691,7 @@ class Critic(object):
             o.add(dct, pl['dp'][0][:M], pl['dp'][0][M:2 * M])
             for k in range(2, first_order_apps):
                 o.copy2d(dct, pl['dp'][0][k * M:(k + 1) * M], accumulate=True)
-        with o.side_lane():      # ctx-branch gradients (Conv1D wgrad, FCs) beside the spectral-branch weight gradients
+        with o.side_lane(second=True):      # ctx-branch gradients (Conv1D wgrad, FCs) beside the spectral-branch weight gradients
             o.colsum(dct, g['c.post.fc0.bias'])
             o.gemm(pl['ctx_last'], dct, g['c.post.fc0.kernel'][SF:], transA=True)
             dcur = pl['dcA']
@@ -721,10 +728,13 @@ class Critic(object):
         """Weight gradients of the spectral Conv2D stack over the applications `samples` (slice over the napp*B axis): written
         together with the bias gradients (`first`: first-order applications), or accumulated without them (tangent rows)."""
         o, g = self.ops, self.params.g
-        for i in range(self.a.gen_nbcnnlayers):
-            ain = pl['a'][i - 1] if i > 0 else pl['s0']
-            o.conv2d_wgrad(ain[samples], pl['da'][i][samples], g['c.spec.cnn%d.kernel' % i],
-                           dbias=g['c.spec.cnn%d.bias' % i] if first else None, accumulate=not first)
+        layers = [dict(x=(pl['a'][i - 1] if i > 0 else pl['s0'])[samples], dy=pl['da'][i][samples], dw=g['c.spec.cnn%d.kernel' % i],
+                       dbias=g['c.spec.cnn%d.bias' % i] if first else None) for i in range(self.a.gen_nbcnnlayers)]
+        if hasattr(o, 'conv2d_wgrad_multi_ok') and o.conv2d_wgrad_multi_ok(layers):
+            o.conv2d_wgrad_multi(layers, accumulate=not first)       # the whole stack in one launch
+            return
+        for L in layers:
+            o.conv2d_wgrad(L['x'], L['dy'], L['dw'], dbias=L['dbias'], accumulate=not first)
 
     def param_grads(self, pl, first_order_apps=2):
         """Gradients of every critic parameter from the stored layer inputs (activations, or tangents on the GP rows)

@@ -154,6 +154,13 @@ class ChainLayerStruct(ctypes.Structure):
                 ('cin', ctypes.c_int), ('cout', ctypes.c_int), ('flags', ctypes.c_int), ('flip', ctypes.c_int)]
 
 
+class WgradLayerStruct(ctypes.Structure):
+    """pctts_wgrad_layer of include/pctts.h"""
+    _fields_ = [('x', ctypes.c_void_p), ('dy', ctypes.c_void_p), ('dw', ctypes.c_void_p), ('dbias', ctypes.c_void_p),
+                ('xbatch', ctypes.c_long), ('xpitch', ctypes.c_long), ('dybatch', ctypes.c_long), ('dypitch', ctypes.c_long),
+                ('cin', ctypes.c_int)]
+
+
 PRECISIONS = {'fp32': 6, 'fp32x3': 3, 'bf16': 1, 'simt': 0}      # -> tcgen05.mma products per k-slice
 PLANES = {6: 3, 3: 2, 1: 1, 0: 0}
 
@@ -182,6 +189,7 @@ class CudaOps(object):
         self.fuse_bn_stats = os.environ.get('PCTTS_FUSE_BN_STATS', '1') != '0'   # BN sums in the Conv2D epilogue
         self.bn_single_launch = os.environ.get('PCTTS_BN_SINGLE_LAUNCH', '1') != '0'   # second stage inside bn_finalize (1 replica)
         self.conv2d_tc = os.environ.get('PCTTS_CONV2D_TC', '1') != '0'   # tcgen05 implicit-GEMM Conv2D (4->4, 5x5)
+        self.wgrad_multi = os.environ.get('PCTTS_WGRAD_MULTI', '1') != '0'   # weight gradients of a whole Conv2D stack in one launch
         self.conv_chain = os.environ.get('PCTTS_CONV_CHAIN', '1') != '0'   # the critic's BN-free Conv2D stack as ONE launch per chain
         self._shadows = {}         # view key -> Shadow
         self._fresh = {}           # view key -> (lo, hi): activation shadows valid inside the current step scope
@@ -199,6 +207,9 @@ class CudaOps(object):
         self._tagged = {}          # tag -> list of (dict, key) entries created while the tag was active
         self._lane = 0             # 0 = the caller's stream; 1 = the side stream of side_lane()
         self._side = None
+        self._side2 = None         # second side stream (side_lane(second=True)), joined by join_lanes()
+        self._side2_open = False
+        self.lane3 = os.environ.get('PCTTS_LANE3', '1') != '0'
         self.lanes = os.environ.get('PCTTS_LANES', '1') != '0'   # run independent branches of a step on two streams
         self.launches = 0          # number of C-ABI kernel-launching calls (reset by the caller)
 
@@ -245,24 +256,33 @@ class CudaOps(object):
 
     # -- two-lane execution: independent branches of a step on two streams (fork / join, capturable) ------------------
     @contextlib.contextmanager
-    def side_lane(self):
+    def side_lane(self, second=False):
         """Kernels issued inside run on a side stream, ordered after everything issued so far on the caller's stream, and
         concurrently with what the caller issues afterwards until join_lanes().  Scratch workspaces are per lane; operands
-        shared by both lanes must have their bf16 shadows taken BEFORE the fork (shadow()).  With PCTTS_LANES=0 the body
-        simply runs in line."""
-        if not self.lanes or self._lane != 0:
+        shared by lanes must have their bf16 shadows taken BEFORE the fork (shadow()).  second=True inside a side lane forks
+        a SECOND side stream off the first (three concurrent branches; PCTTS_LANE3=0: runs in line on the first side lane).
+        With PCTTS_LANES=0 the body simply runs in line."""
+        nest = second and self._lane == 1 and self.lane3
+        if not self.lanes or (self._lane != 0 and not nest):
             yield self
             return
-        if self._side is None:
-            self._side = torch.cuda.Stream(device=self.device)
-        main = torch.cuda.current_stream(self.device)
-        self._side.wait_stream(main)
-        self._lane = 1
+        cur = torch.cuda.current_stream(self.device)
+        if nest:
+            if self._side2 is None:
+                self._side2 = torch.cuda.Stream(device=self.device)
+            side, lane = self._side2, 2
+            self._side2_open = True
+        else:
+            if self._side is None:
+                self._side = torch.cuda.Stream(device=self.device)
+            side, lane = self._side, 1
+        side.wait_stream(cur)
+        outer, self._lane = self._lane, lane
         try:
-            with torch.cuda.stream(self._side):
+            with torch.cuda.stream(side):
                 yield self
         finally:
-            self._lane = 0
+            self._lane = outer
 
     def preshare(self, t):
         """Take the bf16 shadow of an operand both lanes are going to read (no-op for the CUDA-core GEMM mode)."""
@@ -284,6 +304,9 @@ class CudaOps(object):
     def join_lanes(self):
         if self.lanes and self._side is not None:
             torch.cuda.current_stream(self.device).wait_stream(self._side)
+        if self._side2_open:
+            torch.cuda.current_stream(self.device).wait_stream(self._side2)
+            self._side2_open = False
 
     def empty(self, *shape, dtype=torch.float32):
         return torch.empty(*shape, dtype=dtype, device=self.device)
@@ -639,6 +662,44 @@ class CudaOps(object):
         self._ck(self.lib.pctts_conv2d_wgrad(px, pd, dw.data_ptr(), ws.data_ptr(), N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
                                              xp, dp, xb, db, float(scale), int(accumulate), self._stream()),
                  'pctts_conv2d_wgrad')
+
+    def conv2d_wgrad_multi_ok(self, layers):
+        """The one-launch weight gradient of a whole 5x5 stack applies (4 output channels, 1 or 4 input channels, aligned maps)."""
+        if not self.wgrad_multi or not layers or len(layers) > 9:
+            return False
+        for L in layers:
+            x, dy, dw = L['x'], L['dy'], L['dw']
+            if tuple(dw.shape[:2]) != (5, 5) or dw.shape[3] != 4 or dw.shape[2] not in (1, 4) or x.shape[:3] != dy.shape[:3]:
+                return False
+            if dy.data_ptr() % 16 or dy.stride(0) % 4 or dy.stride(1) % 4 or dy.stride(3) != 1 or dy.stride(2) != 4:
+                return False
+            if dw.shape[2] == 4 and (x.data_ptr() % 16 or x.stride(0) % 4 or x.stride(1) % 4 or x.stride(3) != 1 or x.stride(2) != 4):
+                return False
+            if dw.shape[2] == 1 and x.stride(2) != 1:
+                return False
+        N, T, F, _ = layers[0]['dy'].shape
+        return 2 * ((20 * (F + 4)) + 16 * F) * 16 <= 200 * 1024
+
+    def conv2d_wgrad_multi(self, layers, scale=1.0, accumulate=False, bias_samples=None):
+        """Weight (and bias) gradients of a stack of 5x5 'same' Conv2D layers in one launch (conv2d_wgrad44.cu).  layers: dicts with
+        x [N,T,F,cin], dy [N,T,F,4], dw [5,5,cin,4], optional dbias [4] (sum over the first bias_samples samples)."""
+        N, T, F, _ = layers[0]['dy'].shape
+        n = len(layers)
+        wkey = (self._tag, self._lane, 'multi', n)
+        ws = self._wg.get(wkey)
+        if ws is None:
+            ws = self._wg[wkey] = self.empty(int(self.lib.pctts_conv2d_wgrad_multi_workspace(n)))
+            self._note(self._wg, wkey)
+        arr = (WgradLayerStruct * n)()
+        for i, L in enumerate(layers):
+            x, dy, dw, db = L['x'], L['dy'], L['dw'], L.get('dbias')
+            assert tuple(dy.shape) == (N, T, F, 4) and tuple(x.shape[:3]) == (N, T, F) and dw.is_contiguous()
+            assert db is None or (db.numel() == 4 and db.is_contiguous())
+            arr[i] = WgradLayerStruct(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), _ptr(db), x.stride(0), x.stride(1), dy.stride(0),
+                                      dy.stride(1), int(dw.shape[2]))
+        nb = N if bias_samples is None else int(bias_samples)
+        self._ck(self.lib.pctts_conv2d_wgrad_multi(ctypes.cast(arr, ctypes.c_void_p), n, nb, ws.data_ptr(), N, T, F, float(scale),
+                                                   int(accumulate), self._stream()), 'pctts_conv2d_wgrad_multi')
 
     # -- batch normalisation ---------------------------------------------------------------------------------
     def bn_stats(self, x, final=True):

@@ -63,7 +63,7 @@ class CpuOpsDouble(object):
     def release_shape(self, tag):
         pass
 
-    def side_lane(self):
+    def side_lane(self, second=False):
         import contextlib
         return contextlib.nullcontext(self)
 

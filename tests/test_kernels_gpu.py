@@ -136,6 +136,43 @@ def test_conv2d_fwd_flip_wgrad(cuda_ops, CIN, COUT, KH, KW, N, T, F):
     close(db, db_want, 3e-5, 'fused bias gradient')
 
 
+@pytest.mark.parametrize('N,T,F,L', [(2, 37, 129, 8), (1, 5, 17, 3), (3, 16, 65, 1), (5, 100, 130, 9), (2, 33, 9, 4)])
+def test_conv2d_wgrad_multi(cuda_ops, N, T, F, L):
+    """Weight + bias gradients of a whole 5x5 stack in one launch (pctts_conv2d_wgrad_multi): first layer 1 -> 4 channels read from
+    a strided feature view, the others 4 -> 4; write form with the bias over the first samples, then the accumulate form."""
+    feats = rnd(N, T, F + 3, seed=1)
+    xs = [feats[:, :, 1:1 + F].unsqueeze(-1)] + [rnd(N, T, F, 4, seed=10 + i) for i in range(1, L)]
+    dys = [rnd(N, T, F, 4, seed=30 + i) for i in range(L)]
+    nb = max(N - 1, 1)
+    fd = dev(feats)
+    xd = [fd[:, :, 1:1 + F].unsqueeze(-1)] + [dev(x) for x in xs[1:]]
+    dyd = [dev(d) for d in dys]
+    dws = [torch.full((5, 5, x.shape[3], 4), 7.0, device='cuda') for x in xs]
+    dbs = [torch.full((4,), 7.0, device='cuda') for _ in xs]
+    layers = [dict(x=xd[i], dy=dyd[i], dw=dws[i], dbias=dbs[i]) for i in range(L)]
+    assert cuda_ops.conv2d_wgrad_multi_ok(layers)
+    cuda_ops.conv2d_wgrad_multi(layers, bias_samples=nb)
+    want = []
+    for i in range(L):
+        dw_want, db_want = torch.zeros(5, 5, xs[i].shape[3], 4, dtype=torch.float64), torch.zeros(4, dtype=torch.float64)
+        REF.conv2d_wgrad(xs[i], dys[i], dw_want, dbias=db_want, bias_samples=nb)
+        close(dws[i], dw_want, 3e-5, ('multi wgrad', i))
+        close(dbs[i], db_want, 3e-5, ('multi bias', i))
+        want.append(dw_want)
+    # accumulate form without biases (the gradient-penalty rows of the critic step)
+    before = [b.clone() for b in dbs]
+    cuda_ops.conv2d_wgrad_multi([dict(x=xd[i], dy=dyd[i], dw=dws[i]) for i in range(L)], scale=0.5, accumulate=True)
+    for i in range(L):
+        close(dws[i], 1.5 * want[i], 3e-5, ('multi wgrad accumulate', i))
+        assert torch.equal(dbs[i], before[i])
+    # run-to-run determinism
+    again = [torch.zeros_like(d) for d in dws]
+    cuda_ops.conv2d_wgrad_multi([dict(x=xd[i], dy=dyd[i], dw=again[i]) for i in range(L)])
+    again2 = [torch.zeros_like(d) for d in dws]
+    cuda_ops.conv2d_wgrad_multi([dict(x=xd[i], dy=dyd[i], dw=again2[i]) for i in range(L)])
+    assert all(torch.equal(a, b) for a, b in zip(again, again2))
+
+
 def test_conv2d_strided_feature_views(cuda_ops):
     """First critic layer reads / last generator layer writes the spectral columns of a [B,T,O] tensor in place."""
     B, T, S, O = 2, 21, 17, 23
