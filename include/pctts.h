@@ -28,6 +28,8 @@ extern "C" {
 #define PCTTS_EPI_DLRELU_AUX 8  /* * LeakyReLU'(aux) with aux = the layer's stored OUTPUT (y>0 <=> x>0)               */
 #define PCTTS_EPI_ACCUM 16      /* C += result                                                                        */
 #define PCTTS_EPI_ATOMIC 32     /* atomicAdd(C, result) (overlapping virtual rows: Conv1D data gradient)              */
+#define PCTTS_EPI_WFLIP 128     /* Conv2D (tensor-core kernel): w is the FORWARD kernel [KH][KW][cout][cin]; the data-gradient
+                                   kernel w[KH-1-kt][KW-1-kf][co][ci] is formed on the fly                             */
 #define PCTTS_EPI_ADDMOD 64     /* + addmod[m % addrows, n]  (critic: ctx-branch term shared by the 3 applications)   */
 
 int pctts_abi_version(void);
@@ -220,6 +222,7 @@ int pctts_adam(float* p, const float* g, float* m, float* v, long n, float lr, f
                void* stream);
 
 /* ---- small movers -------------------------------------------------------------------------------------------------------- */
+int pctts_stamp(unsigned long long* slot, void* stream);   /* developer probe: %globaltimer (ns) at this point of the stream */
 int pctts_add(float* out, const float* a, const float* b, long n, void* stream);
 int pctts_sigmoid_bwd(const float* dy, long lddy, const float* y, long ldy, float* dz, long lddz, long rows, int cols, void* stream);
 int pctts_copy2d(float* dst, long ldd, const float* src, long lds, long rows, int cols, int accumulate, void* stream);

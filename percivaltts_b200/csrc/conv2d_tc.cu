@@ -184,7 +184,14 @@ __global__ void __launch_bounds__(C2_THREADS, 1) conv2d_tc_kernel(const C2Params
     if (warp >= C2_PW) {
         constexpr int NB_THREADS = C2_THREADS - C2_PROD;
         const int bt = tid - C2_PROD;
-        for (int i = bt; i < KT * KW5 * 16; i += NB_THREADS) wsm[i] = __ldg(p.w + i);
+        if (p.flags & PCTTS_EPI_WFLIP) {     // data-gradient kernel of the forward kernel w [5][5][co][ci]
+            for (int i = bt; i < KT * KW5 * 16; i += NB_THREADS) {
+                const int co = i & 3, ci = (i >> 2) & 3, tap = i >> 4;
+                wsm[i] = __ldg(p.w + ((KT * KW5 - 1 - tap) * 4 + co) * 4 + ci);
+            }
+        } else {
+            for (int i = bt; i < KT * KW5 * 16; i += NB_THREADS) wsm[i] = __ldg(p.w + i);
+        }
         asm volatile("bar.sync 2, %0;" ::"n"(NB_THREADS) : "memory");
         for (int e = bt; e < NMMA * 2 * 16; e += NB_THREADS) {
             const int n16 = e & 15, c = (e >> 4) & 1, j = e >> 5;
@@ -484,7 +491,7 @@ static int conv2d_tc_run(const float* x, const float* w, const float* bias, cons
     if (nterms != 1 && nterms != 3 && nterms != 6) return PCTTS_EINVAL;
     if ((flags & PCTTS_EPI_BIAS) && !bias) return PCTTS_EINVAL;
     if ((flags & PCTTS_EPI_DLRELU_AUX) && !aux) return PCTTS_EINVAL;
-    if (flags & ~(PCTTS_EPI_BIAS | PCTTS_EPI_LRELU | PCTTS_EPI_DLRELU_AUX | PCTTS_EPI_ACCUM)) return PCTTS_EUNSUPPORTED;
+    if (flags & ~(PCTTS_EPI_BIAS | PCTTS_EPI_LRELU | PCTTS_EPI_DLRELU_AUX | PCTTS_EPI_ACCUM | PCTTS_EPI_WFLIP)) return PCTTS_EUNSUPPORTED;
     // float4 accesses: 16-byte aligned bases and row / sample pitches
     if ((((uintptr_t)x | (uintptr_t)y | (uintptr_t)aux) & 15) || ((xpitch | ypitch | xbatch | ybatch) & 3) ||
         (aux && ((auxpitch | auxbatch) & 3)))

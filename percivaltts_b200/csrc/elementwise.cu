@@ -191,6 +191,14 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
 __global__ void incr_kernel(int* step) {
     pdl_entry(); if (threadIdx.x == 0 && blockIdx.x == 0) *step += 1; }
 
+__global__ void stamp_kernel(unsigned long long* slot) {
+    if (threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        *slot = t;
+    }
+}
+
 __global__ void add_kernel(float* __restrict__ out, const float* __restrict__ a, const float* __restrict__ b, long n) {
     pdl_entry();
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) out[i] = a[i] + b[i];
@@ -354,6 +362,14 @@ extern "C" int pctts_adam(float* p, const float* g, float* m, float* v, long n, 
         PCTTS_LAUNCH_CHECK();
     }
     pctts_launch(incr_kernel, 1, 32, 0, st, step);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
+/* developer probe: writes %globaltimer (ns) into *slot when the stream reaches this point (tools/timeline.py) */
+extern "C" int pctts_stamp(unsigned long long* slot, void* stream) {
+    if (!slot) return PCTTS_EINVAL;
+    stamp_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(slot);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

@@ -273,6 +273,8 @@ class Generator(_BNNet):
             pl['df0'] = o.empty(M, 1)
             pl['dmapA'] = o.empty(B, T, S, Fl)
             pl['dmapB'] = o.empty(B, T, S, Fl)
+            pl['cv_dz'] = [o.empty(B, T, S, Fl) for _ in range(L)]     # kept per layer: the weight gradients of the stack are one launch
+            pl['d_lctx_nm'] = o.empty(M, H)
             pl['ds'] = o.empty(M, S)
             pl['dhout'] = o.empty(B, T, 2 * H)
             pl['dzl'] = [o.empty(B, T, 4 * H) for _ in range(2)]
@@ -282,6 +284,13 @@ class Generator(_BNNet):
                 pl['ctx_dzp'] = o.zeros(B, T + W - 1, H)
                 pl['ctx_kflip'] = o.empty(W, 1, H, H)
         return pl
+
+    def _nm_lane(self, sync, training=True):
+        """The noise-mask branch may run on the second side lane: always on a single replica; with replicas its BatchNorm
+        exchanges need their own peer-memory channel (DistSync.bn_handle2)."""
+        if not training or sync.world == 1:
+            return True
+        return self._fused_sync(sync) and getattr(sync, 'bn_handle2', None) is not None
 
     # ---- forward ----------------------------------------------------------------------------------------------
     def forward(self, pl, ctx, out, training=True, update_stats=False, sync=None, spec_only=False, materialize=True):
@@ -320,6 +329,20 @@ class Generator(_BNNet):
                 o.lstm_fwd(pl['zx'], [p['g.f0.blstm.fw.recurrent'], p['g.f0.blstm.bw.recurrent']], pl['hout'], pl['gates'],
                            pl['cstate'])
                 o.gemm(pl['hout'].view(M, 2 * H), p['g.f0.out.kernel'], out2[:, 0:1], bias=p['g.f0.out.bias'])
+        # NM: pFC x (L//2), Dense(sigmoid)   (modeltts_common.py:117-121): a chain of small GEMM + BatchNorm launches that shares
+        # nothing but lctx with the spectral branch -- second side lane (with replicas: only when the sync-BN exchange has a
+        # channel of its own for that lane, the ranks must meet the exchanges of a channel in one order)
+        def nm_branch():
+            n2 = lctx
+            for i in range(a.gen_nbcnnlayers // 2):
+                o.gemm(n2, p['g.nm.fc%d.kernel' % i], pl['nm_z'][i])
+                self._bn_fwd(pl['nm_z'][i], pl['nm_y'][i], pl['nm_bn'][i], training, update_stats, sync)
+                n2 = pl['nm_y'][i]
+            o.gemm(n2, p['g.nm.out.kernel'], out2[:, 1 + S:], bias=p['g.nm.out.bias'], flags=EPI_SIGMOID)
+        nm_lane = not spec_only and self._nm_lane(sync, training)
+        if nm_lane:
+            with o.side_lane(lane=2):
+                nm_branch()
         # Spec: Dense projection, [B,T,S,1] map, pCNN2D stack, Conv2D(1)   (modeltts_common.py:95-101)
         o.gemm(lctx, p['g.spec.proj.kernel'], pl['s'], bias=p['g.spec.proj.bias'])
         amap = pl['s'].view(B, T, S, 1)
@@ -340,14 +363,8 @@ class Generator(_BNNet):
                 pending = (bn.mean, bn.invstd, p[bn.prefix + '.gamma'], p[bn.prefix + '.beta'], pl['cv_a'][i])
                 amap = pl['cv_z'][i]
         o.conv2d(amap, p['g.spec.out.kernel'], out[:, :, 1:1 + S].unsqueeze(-1), bias=p['g.spec.out.bias'])
-        # NM: pFC x (L//2), Dense(sigmoid)   (modeltts_common.py:117-121)
-        n2 = lctx
-        for i in range(0 if spec_only else a.gen_nbcnnlayers // 2):
-            o.gemm(n2, p['g.nm.fc%d.kernel' % i], pl['nm_z'][i])
-            self._bn_fwd(pl['nm_z'][i], pl['nm_y'][i], pl['nm_bn'][i], training, update_stats, sync)
-            n2 = pl['nm_y'][i]
-        if not spec_only:
-            o.gemm(n2, p['g.nm.out.kernel'], out2[:, 1 + S:], bias=p['g.nm.out.bias'], flags=EPI_SIGMOID)
+        if not spec_only and not nm_lane:
+            nm_branch()
         if not spec_only:
             o.join_lanes()
         pl['lctx'], pl['ctx_in'] = lctx, ctx
@@ -387,21 +404,29 @@ class Generator(_BNNet):
                 else:
                     o.fill_segments(gU.view(-1), gU.numel(), 0.0)
                 o.gemm(dz2, p['g.f0.blstm.%s.kernel' % dn], pl['d_lctx_f0'], transB=True, flags=EPI_ACCUM if d > 0 else 0)
-        # ---- NM branch
-        nlast = pl['nm_y'][Ln - 1] if Ln > 0 else lctx
-        o.sigmoid_bwd(dout2[:, 1 + S:], out2[:, 1 + S:], pl['dz_nm'])
-        o.gemm(nlast, pl['dz_nm'], g['g.nm.out.kernel'], transA=True)
-        o.colsum(pl['dz_nm'], g['g.nm.out.bias'])
-        dcur = dl if Ln == 0 else pl['dA']
-        o.gemm(pl['dz_nm'], p['g.nm.out.kernel'], dcur, transB=True)
-        for i in range(Ln - 1, -1, -1):
-            xin = pl['nm_y'][i - 1] if i > 0 else lctx
-            dz = pl['dB'] if dcur is pl['dA'] else pl['dA']
-            self._bn_bwd(pl['nm_z'][i], dcur, dz, pl['nm_bn'][i], sync)
-            o.gemm(xin, dz, g['g.nm.fc%d.kernel' % i], transA=True)
-            dnext = dl if i == 0 else dcur
-            o.gemm(dz, p['g.nm.fc%d.kernel' % i], dnext, transB=True)
-            dcur = dnext
+        # ---- NM branch: shares nothing but lctx with the spectral branch -> second side lane, its share of d(lctx) in its own buffer
+        dl_nm = pl['d_lctx_nm']
+
+        def nm_branch():
+            nlast = pl['nm_y'][Ln - 1] if Ln > 0 else lctx
+            o.sigmoid_bwd(dout2[:, 1 + S:], out2[:, 1 + S:], pl['dz_nm'])
+            o.gemm(nlast, pl['dz_nm'], g['g.nm.out.kernel'], transA=True)
+            o.colsum(pl['dz_nm'], g['g.nm.out.bias'])
+            dcur = dl_nm if Ln == 0 else pl['dA']
+            o.gemm(pl['dz_nm'], p['g.nm.out.kernel'], dcur, transB=True)
+            for i in range(Ln - 1, -1, -1):
+                xin = pl['nm_y'][i - 1] if i > 0 else lctx
+                dz = pl['dB'] if dcur is pl['dA'] else pl['dA']
+                self._bn_bwd(pl['nm_z'][i], dcur, dz, pl['nm_bn'][i], sync)
+                o.gemm(xin, dz, g['g.nm.fc%d.kernel' % i], transA=True)
+                dnext = dl_nm if i == 0 else dcur
+                o.gemm(dz, p['g.nm.fc%d.kernel' % i], dnext, transB=True)
+                dcur = dnext
+        nm_lane, nm_ev = self._nm_lane(sync), None
+        if nm_lane:
+            with o.side_lane(lane=2):
+                nm_branch()
+                nm_ev = o.lane_event()
         # ---- Spec branch
         o.copy2d(pl['dspec'], dout2[:, 1:1 + S])
         dmap = pl['dspec'].view(B, T, S, 1)
@@ -410,20 +435,33 @@ class Generator(_BNNet):
         o.conv2d_flip(p['g.spec.out.kernel'], pl['wflip_out'])
         da = pl['dmapA']
         o.conv2d(dmap, pl['wflip_out'], da)
+        wlayers = []        # weight gradients of the stack: one launch after the data-gradient chain (every dz is kept)
         for i in range(L - 1, -1, -1):
-            dz = pl['dmapB'] if da is pl['dmapA'] else pl['dmapA']
+            dz = pl['cv_dz'][i]
             self._bn_bwd(pl['cv_z'][i].view(M * S, Fl), da.view(M * S, Fl), dz.view(M * S, Fl), pl['cv_bn'][i], sync)
             ain = pl['cv_a'][i - 1] if i > 0 else pl['s'].view(B, T, S, 1)
-            o.conv2d_wgrad(ain, dz, g['g.spec.cnn%d.kernel' % i])
-            o.conv2d_flip(p['g.spec.cnn%d.kernel' % i], pl['wflip'][i])
-            dnext = (pl['dmapB'] if dz is pl['dmapA'] else pl['dmapA']) if i > 0 else pl['ds'].view(B, T, S, 1)
-            o.conv2d(dz, pl['wflip'][i], dnext)
+            wlayers.append(dict(x=ain, dy=dz, dw=g['g.spec.cnn%d.kernel' % i]))
+            dnext = (pl['dmapB'] if da is pl['dmapA'] else pl['dmapA']) if i > 0 else pl['ds'].view(B, T, S, 1)
+            o.conv2d_dgrad(dz, p['g.spec.cnn%d.kernel' % i], dnext, pl['wflip'][i])
             da = dnext
+        multi = hasattr(o, 'conv2d_wgrad_multi_ok') and o.conv2d_wgrad_multi_ok(wlayers)
+        if multi:       # beside the rest of the backward pass (second side lane, behind the noise-mask branch)
+            with o.side_lane(lane=2):
+                o.conv2d_wgrad_multi(wlayers)
+        else:
+            for Lw in wlayers:
+                o.conv2d_wgrad(Lw['x'], Lw['dy'], Lw['dw'])
         o.gemm(lctx, pl['ds'], g['g.spec.proj.kernel'], transA=True)
         o.colsum(pl['ds'], g['g.spec.proj.bias'])
-        o.gemm(pl['ds'], p['g.spec.proj.kernel'], dl, transB=True, flags=EPI_ACCUM)
-        o.join_lanes()
+        o.gemm(pl['ds'], p['g.spec.proj.kernel'], dl, transB=True)
+        if not nm_lane:
+            nm_branch()
+        # the ctx trunk needs the branches' shares of d(lctx): the F0 lane as a whole, of lane 2 only the noise-mask branch (the
+        # weight gradients queued behind it are joined at the end)
+        o.join_lanes(1)
+        o.wait_lane_event(nm_ev)
         o.add(dl, dl, pl['d_lctx_f0'])
+        o.add(dl, dl, dl_nm)
         # ---- ctx trunk: pFC x2 then pCNN1D stack
         dcur = dl
         for i in (1, 0):
@@ -451,6 +489,7 @@ class Generator(_BNNet):
                 dnext = pl['dA'] if dz is pl['dB'] else pl['dB']
                 o.gemm(_im2col_view(pl['ctx_dzp'], T, W), pl['ctx_kflip'].view(W * H, H), dnext)
                 dcur = dnext
+        o.join_lanes()
 
 
 class Critic(object):

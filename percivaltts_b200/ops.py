@@ -17,7 +17,7 @@ import torch
 
 from . import _lib
 
-EPI_BIAS, EPI_LRELU, EPI_SIGMOID, EPI_DLRELU_AUX, EPI_ACCUM, EPI_ATOMIC, EPI_ADDMOD = 1, 2, 4, 8, 16, 32, 64
+EPI_BIAS, EPI_LRELU, EPI_SIGMOID, EPI_DLRELU_AUX, EPI_ACCUM, EPI_ATOMIC, EPI_ADDMOD, EPI_WFLIP = 1, 2, 4, 8, 16, 32, 64, 128
 
 
 def _mat(t):
@@ -189,6 +189,7 @@ class CudaOps(object):
         self.fuse_bn_stats = os.environ.get('PCTTS_FUSE_BN_STATS', '1') != '0'   # BN sums in the Conv2D epilogue
         self.bn_single_launch = os.environ.get('PCTTS_BN_SINGLE_LAUNCH', '1') != '0'   # second stage inside bn_finalize (1 replica)
         self.conv2d_tc = os.environ.get('PCTTS_CONV2D_TC', '1') != '0'   # tcgen05 implicit-GEMM Conv2D (4->4, 5x5)
+        self.tc_wflip = os.environ.get('PCTTS_TC_WFLIP', '1') != '0'     # Conv2D data gradients read the forward kernels (no flip launch)
         self.wgrad_multi = os.environ.get('PCTTS_WGRAD_MULTI', '1') != '0'   # weight gradients of a whole Conv2D stack in one launch
         self.conv_chain = os.environ.get('PCTTS_CONV_CHAIN', '1') != '0'   # the critic's BN-free Conv2D stack as ONE launch per chain
         self._shadows = {}         # view key -> Shadow
@@ -211,6 +212,7 @@ class CudaOps(object):
         self._side2_open = False
         self.lane3 = os.environ.get('PCTTS_LANE3', '1') != '0'
         self.lanes = os.environ.get('PCTTS_LANES', '1') != '0'   # run independent branches of a step on two streams
+        self.timeline = None
         self.launches = 0          # number of C-ABI kernel-launching calls (reset by the caller)
 
     # -- helpers ---------------------------------------------------------------------------------------------
@@ -220,6 +222,29 @@ class CudaOps(object):
     def _ck(self, rc, what):
         self.launches += 1
         _lib.check(rc, what)
+        if self.timeline is not None:      # developer probe (tools/timeline.py): a time stamp behind every call, per lane
+            i = len(self.timeline)
+            if i < self._stamps.numel():
+                self.lib.pctts_stamp(self._stamps.data_ptr() + 8 * i, self._stream())
+                self.timeline.append((what, self._lane))
+
+    def timeline_start(self, n=4096):
+        self._stamps = torch.zeros(n, dtype=torch.int64, device=self.device)
+        self.timeline = []
+        self.stamp('start')
+
+    def stamp(self, what):
+        if self.timeline is not None:
+            self.lib.pctts_stamp(self._stamps.data_ptr() + 8 * len(self.timeline), self._stream())
+            self.timeline.append((what, self._lane))
+
+    def timeline_stop(self):
+        """-> [(what, lane, ns since start)]"""
+        torch.cuda.synchronize(self.device)
+        t = self._stamps.cpu().tolist()
+        out = [(w, l, t[i] - t[0]) for i, (w, l) in enumerate(self.timeline)]
+        self.timeline = None
+        return out
 
     def reduce_ws(self, rows, C):
         key = (self._tag, self._lane, int(rows), int(C))
@@ -256,26 +281,27 @@ class CudaOps(object):
 
     # -- two-lane execution: independent branches of a step on two streams (fork / join, capturable) ------------------
     @contextlib.contextmanager
-    def side_lane(self, second=False):
+    def side_lane(self, second=False, lane=None):
         """Kernels issued inside run on a side stream, ordered after everything issued so far on the caller's stream, and
         concurrently with what the caller issues afterwards until join_lanes().  Scratch workspaces are per lane; operands
-        shared by lanes must have their bf16 shadows taken BEFORE the fork (shadow()).  second=True inside a side lane forks
-        a SECOND side stream off the first (three concurrent branches; PCTTS_LANE3=0: runs in line on the first side lane).
-        With PCTTS_LANES=0 the body simply runs in line."""
-        nest = second and self._lane == 1 and self.lane3
-        if not self.lanes or (self._lane != 0 and not nest):
+        shared by lanes must have their bf16 shadows taken BEFORE the fork (shadow()).  Two side streams exist: lane 1 (default,
+        forked from the caller's stream) and lane 2 (lane=2 from anywhere, or second=True inside lane 1: a branch off the first
+        side lane; PCTTS_LANE3=0 runs it in line).  With PCTTS_LANES=0 the body simply runs in line."""
+        if lane is None:
+            lane = 2 if (second and self._lane == 1) else 1
+        if not self.lanes or lane == self._lane or (lane == 1 and self._lane != 0) or (lane == 2 and not self.lane3):
             yield self
             return
         cur = torch.cuda.current_stream(self.device)
-        if nest:
+        if lane == 2:
             if self._side2 is None:
                 self._side2 = torch.cuda.Stream(device=self.device)
-            side, lane = self._side2, 2
+            side = self._side2
             self._side2_open = True
         else:
             if self._side is None:
                 self._side = torch.cuda.Stream(device=self.device)
-            side, lane = self._side, 1
+            side = self._side
         side.wait_stream(cur)
         outer, self._lane = self._lane, lane
         try:
@@ -290,8 +316,8 @@ class CudaOps(object):
             self.shadow(t)
 
     def lane_event(self):
-        """Inside side_lane(): marks the point reached there; the main lane can wait for it without a full join."""
-        if not self.lanes or self._lane != 1:
+        """Inside a side lane: marks the point reached there; another lane can wait for it without a full join."""
+        if not self.lanes or self._lane == 0:
             return None
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(self.device))
@@ -301,10 +327,11 @@ class CudaOps(object):
         if ev is not None:
             torch.cuda.current_stream(self.device).wait_event(ev)
 
-    def join_lanes(self):
+    def join_lanes(self, which=None):
+        """The caller's stream waits for the side lanes (which = 1: for the first one only)."""
         if self.lanes and self._side is not None:
             torch.cuda.current_stream(self.device).wait_stream(self._side)
-        if self._side2_open:
+        if self._side2_open and which is None:
             torch.cuda.current_stream(self.device).wait_stream(self._side2)
             self._side2_open = False
 
@@ -536,6 +563,27 @@ class CudaOps(object):
         self.gemm(xp.as_strided((B, T, W * CIN), (Tp * CIN, CIN, 1)), dz, dw.view(W * CIN, COUT), transA=True)
 
     # -- 2-D convolutions ------------------------------------------------------------------------------------
+    def conv2d_dgrad(self, dy, w, dx, scratch, aux=None, flags=0):
+        """dx = epilogue(conv2d_same(dy, flip(w))): the data gradient of y = conv2d_same(x, w), w the FORWARD kernel
+        [KH,KW,Cin,Cout].  The tensor-core kernel forms the flipped kernel on the fly; otherwise it goes to `scratch` [KH,KW,Cout,Cin]."""
+        N, T, F, COUT = dy.shape
+        KH, KW, CIN, co = w.shape
+        assert co == COUT and tuple(dx.shape) == (N, T, F, CIN) and w.is_contiguous()
+        px, xb, xp = _map4(dy)
+        py, yb, yp = _map4(dx)
+        pa, ab, ap = _map4(aux) if aux is not None else (0, 0, 0)
+        if (self.nterms > 0 and self.conv2d_tc and self.tc_wflip and self.lib.pctts_conv2d_tc_supported(F, COUT, CIN, KH, KW, (KH - 1) // 2, (KW - 1) // 2)
+                and not ((px | py | pa) & 15) and not ((xp | yp | ap | xb | yb | ab) & 3)):
+            if aux is not None:
+                flags |= EPI_DLRELU_AUX
+            self._wrote(dx)
+            self._ck(self.lib.pctts_conv2d_tc_fwd_fused(px, w.data_ptr(), None, pa or None, py, N, T, F, COUT, CIN, KH, KW, (KH - 1) // 2,
+                                                        (KW - 1) // 2, xp, yp, ap, xb, yb, ab, flags | EPI_WFLIP, self.nterms, None, None,
+                                                        None, None, None, 1, self._stream()), 'pctts_conv2d_tc_fwd_fused')
+            return
+        self.conv2d_flip(w, scratch)
+        self.conv2d(dy, scratch, dx, aux=aux, flags=flags)
+
     def conv2d(self, x, w, y, bias=None, aux=None, pad=None, flags=0, stats=False, in_bn=None, stats_final=True):
         """y = epilogue(conv2d_same(x, w)); x [N,T,F,Cin], w [KH,KW,Cin,Cout] contiguous, y/aux [N,T,F,Cout] views.
         stats=True also returns the ReduceWorkspace holding the BatchNorm sums [sum y, sum y^2] of the (contiguous) output:
@@ -749,9 +797,8 @@ class CudaOps(object):
     # -- BatchNorm second stage + replica exchange + finalize in ONE launch (csrc/peer.cu: bn_sync_kernel) --------------------
     bn_sync = True
 
-    @staticmethod
-    def _peer_args(sync):
-        h = getattr(sync, 'bn_handle', None)
+    def _peer_args(self, sync):
+        h = getattr(sync, 'bn_handle2' if self._lane == 2 else 'bn_handle', None)
         if h is None or sync.world == 1:
             return None, 0, 1, None
         bases, err = h

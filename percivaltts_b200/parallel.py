@@ -30,6 +30,7 @@ class DistSync(object):
         self.peer_calls = 0
         self._peer = None
         self._bn = None            # (bases, err) of the sliced sync-BatchNorm protocol (second symmetric buffer)
+        self._bn2 = None           # the same for the exchanges issued on the step's second side lane
         self.peer_error = None
 
     def allreduce(self, t):
@@ -69,12 +70,19 @@ class DistSync(object):
             hdl2 = symm_mem.rendezvous(buf2, group.group_name)
             buf2.zero_()
             bases2 = (ctypes.c_ulonglong * self.world)(*[int(p) for p in hdl2.buffer_ptrs])
-            self._peer_keep = (buf, hdl, buf2, hdl2)
+            # a second channel of the same protocol for the step's second side lane (engine.Generator: the noise-mask branch beside
+            # the spectral branch): every rank meets the exchanges of ONE channel in the same order, two lanes need two channels
+            buf3 = symm_mem.empty((nb2 + 7) // 8, dtype=torch.float64, device=device)
+            hdl3 = symm_mem.rendezvous(buf3, group.group_name)
+            buf3.zero_()
+            bases3 = (ctypes.c_ulonglong * self.world)(*[int(p) for p in hdl3.buffer_ptrs])
+            self._peer_keep = (buf, hdl, buf2, hdl2, buf3, hdl3)
             peer = (lib, bases, err)
             bn = (bases2, err)
+            bn2 = (bases3, err)
             ok.fill_(1.0)
         except Exception as e:      # noqa: BLE001 -- any failure here means "use NCCL"
-            peer = bn = None
+            peer = bn = bn2 = None
             self.peer_error = repr(e)
         torch.cuda.synchronize(device)
         dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)      # all ranks or none (also the barrier after zeroing)
@@ -93,6 +101,7 @@ class DistSync(object):
             return False
         if os.environ.get('PCTTS_BN_SYNC_FUSED', '1') != '0':
             self._bn = bn
+            self._bn2 = bn2
         return True
 
     def broadcast_scalar(self, x, src=0):
@@ -109,6 +118,11 @@ class DistSync(object):
     def bn_handle(self):
         """(peer bases, err flag) of the fused sync-BatchNorm launches, or None (exchange as separate launches)."""
         return self._bn
+
+    @property
+    def bn_handle2(self):
+        """The channel of the fused sync-BatchNorm launches issued on the step's second side lane, or None."""
+        return self._bn2
 
     @property
     def peer_err(self):

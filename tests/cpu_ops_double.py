@@ -63,11 +63,11 @@ class CpuOpsDouble(object):
     def release_shape(self, tag):
         pass
 
-    def side_lane(self, second=False):
+    def side_lane(self, second=False, lane=None):
         import contextlib
         return contextlib.nullcontext(self)
 
-    def join_lanes(self):
+    def join_lanes(self, which=None):
         pass
 
     def share_rows(self, t):
@@ -177,6 +177,10 @@ class CpuOpsDouble(object):
     def conv2d_flip(self, w, wt):
         self.launches += 1
         wt.copy_(torch.flip(w, dims=(0, 1)).permute(0, 1, 3, 2))
+
+    def conv2d_dgrad(self, dy, w, dx, scratch, aux=None, flags=0):
+        self.conv2d_flip(w, scratch)
+        self.conv2d(dy, scratch, dx, aux=aux, flags=flags)
 
     def conv2d_wgrad(self, x, dy, dw, scale=1.0, accumulate=False, pad=None, dbias=None, bias_samples=None):
         self.launches += 1

@@ -84,6 +84,20 @@ def main():
         dw = torch.empty(5, 5, 4, 4, device=dev)
         dbias = torch.empty(4, device=dev)
         report("conv2d_wgrad 4->4 %s (+bias)" % tag, lambda: ops.conv2d_wgrad(x, y, dw, dbias=dbias), nbytes=2 * mapb, note="%.2f GFLOP, CUDA cores" % (fl / 1e9))
+    # ---- weight + bias gradients of the critic's whole stack (1->4 and 7 x 4->4) in one launch: bound by the fp32 FMA pipe
+    #      (148 SMs x 128 FMA/clk x 1.965 GHz = 37.2 T FMA/s), 400 FMA per pixel and layer
+    for nb, tag in ((2 * B, '2B'), (B, 'B')):
+        xs = [rnd(nb, T, S, 1)] + [rnd(nb, T, S, 4) for _ in range(7)]
+        dys = [rnd(nb, T, S, 4) for _ in range(8)]
+        dws = [torch.empty(5, 5, xx.shape[3], 4, device=dev) for xx in xs]
+        dbs = [torch.empty(4, device=dev) for _ in xs]
+        lay = [dict(x=xs[i], dy=dys[i], dw=dws[i], dbias=dbs[i]) for i in range(8)]
+        if (not args.only or 'wgrad_multi' in args.only) and ops.conv2d_wgrad_multi_ok(lay):
+            ms = timeit(lambda: ops.conv2d_wgrad_multi(lay))
+            fma = 8.0 * nb * T * S * 400
+            print(json.dumps({'kernel': 'conv2d_wgrad_multi 8 layers %s' % tag, 'ms': round(ms, 5), 'bound': 'fma', 'achieved': round(fma / ms / 1e9, 2),
+                              'unit': 'TFMA/s', 'peak': 37.2, 'frac': round(fma / ms / 1e9 / 37.2, 4),
+                              'work': '%.3f GFMA issued (the 1->4 layer runs as 4->4 with three zero channels)' % (fma / 1e9)}), flush=True)
     x1, y4, w14 = rnd(3 * B, T, S, 1), torch.empty(3 * B, T, S, 4, device=dev), rnd(5, 5, 1, 4)
     report('conv2d_simt_fwd 1->4 3B', lambda: ops.conv2d(x1, w14, y4), nbytes=3 * B * T * S * 4 * 5)
     w41 = rnd(5, 5, 4, 1)
