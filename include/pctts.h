@@ -65,6 +65,15 @@ int pctts_gemm_splitk_f32(int transA, int transB, int M, int N, int K, float alp
  * A shadow is `parts` planes of [rows, ld_dst] bf16 (ld_dst % 8 == 0, plane pitch part_stride elements, 16-byte aligned). */
 int pctts_split_bf16(const float* src, long ld, int seg, long segstride, long rows, int cols, void* dst, long ld_dst,
                      long part_stride, int parts, void* stream);
+/* up to PCTTS_SPLIT_MAX_JOBS plain matrices (no segments) in ONE launch: the weight shadows of a network after its Adam update */
+#define PCTTS_SPLIT_MAX_JOBS 24
+typedef struct pctts_split_job {
+    const float* src;
+    void* dst;
+    long ld, rows, ld_dst, part_stride;
+    int cols;
+} pctts_split_job;
+int pctts_split_bf16_multi(const pctts_split_job* jobs, int njobs, int parts, void* stream);
 int pctts_gemm_tc_splits(int M, int N, int K);                 /* host call: recommended split-K factor (1 = none) */
 long pctts_gemm_tc_workspace(int M, int N, int splits);        /* host call: floats of split-K workspace */
 long pctts_gemm_tc_tail_workspace(int M, int N, int K);        /* host call: floats with which a splits = 1 call cuts the m-tiles of a
@@ -181,6 +190,15 @@ int pctts_bn_finalize(void* workspace, long rows, int C, double count, float eps
                       float* moving_mean, float* moving_var, void* stream);          /* moving_* may be NULL (frozen) */
 int pctts_bn_apply(const float* x, float* y, const float* mean, const float* invstd_or_var, const float* gamma,
                    const float* beta, long rows, int C, float eps, int use_var, int lrelu, void* stream);
+/* pctts_bn_apply / pctts_bn_bwd_apply that also write the bf16 operand planes of their output (what pctts_split_bf16 would write:
+ * [parts][rows][ld_dst] bf16, plane stride part_stride elements) when the consumer is a tensor-core GEMM.  C % 4 == 0, C <= 1024 and
+ * 16-byte aligned maps only (PCTTS_EUNSUPPORTED otherwise). */
+int pctts_bn_apply_planes(const float* x, float* y, const float* mean, const float* invstd_or_var, const float* gamma,
+                          const float* beta, long rows, int C, float eps, int use_var, int lrelu, void* planes, long ld_dst,
+                          long part_stride, int parts, void* stream);
+int pctts_bn_bwd_apply_planes(const float* x, const float* dy, float* dx, const float* mean, const float* invstd,
+                              const float* gamma, const float* beta, long rows, int C, double count, int lrelu, void* workspace,
+                              void* planes, long ld_dst, long part_stride, int parts, void* stream);
 int pctts_bn_bwd_reduce(const float* x, const float* dy, const float* mean, const float* invstd, const float* gamma,
                         const float* beta, long rows, int C, int lrelu, void* workspace, void* stream);
 int pctts_bn_bwd_reduce_partial(const float* x, const float* dy, const float* mean, const float* invstd, const float* gamma,

@@ -502,6 +502,55 @@ __global__ void __launch_bounds__(256) split_bf16_vec8_kernel(const float* __res
     }
 }
 
+// several matrices in ONE launch (the weight shadows of a network after its Adam update): blockIdx.y = job
+constexpr int SPLIT_MAXJOBS = PCTTS_SPLIT_MAX_JOBS;
+struct SplitJob {
+    const float* src;
+    __nv_bfloat16* dst;
+    long ld, ld_dst, part_stride;
+    int rows, cols, vec;
+};
+struct SplitJobs {
+    SplitJob j[SPLIT_MAXJOBS];
+    int parts;
+};
+__global__ void __launch_bounds__(256) split_bf16_multi_kernel(const SplitJobs P) {
+    pdl_entry();
+    const SplitJob& J = P.j[blockIdx.y];
+    if (J.vec) {
+        const int groups = (int)(J.ld_dst >> 3);
+        const int total = J.rows * groups;
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+            const int r = i / groups;
+            const int c = (i - r * groups) * 8;
+            const long off = (long)r * J.ld;
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+            if (c < J.cols) a = *reinterpret_cast<const float4*>(J.src + off + c);
+            if (c + 4 < J.cols) b = *reinterpret_cast<const float4*>(J.src + off + c + 4);
+            float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+            __nv_bfloat16* d = J.dst + (long)r * J.ld_dst + c;
+            for (int pl = 0; pl < P.parts; ++pl) {
+                uint32_t w[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) w[q] = bf16x2_rn(v[2 * q], v[2 * q + 1], v[2 * q], v[2 * q + 1]);
+                *reinterpret_cast<uint4*>(d + (long)pl * J.part_stride) = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+        }
+    } else {
+        const long pairs = J.ld_dst / 2;
+        const long total = (long)J.rows * pairs;
+        for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+            const long r = i / pairs;
+            const int c = (int)(i - r * pairs) * 2;
+            float x0 = c < J.cols ? J.src[r * J.ld + c] : 0.f, x1 = c + 1 < J.cols ? J.src[r * J.ld + c + 1] : 0.f;
+            for (int pl = 0; pl < P.parts; ++pl) {
+                const uint32_t w = bf16x2_rn(x0, x1, x0, x1);
+                *reinterpret_cast<uint32_t*>(J.dst + (long)pl * J.part_stride + r * J.ld_dst + c) = w;
+            }
+        }
+    }
+}
+
 long long* g_trace = nullptr;
 
 struct Launch {
@@ -666,6 +715,30 @@ extern "C" int pctts_split_bf16(const float* src, long ld, int seg, long segstri
     int blocks = pctts_div_up(total, 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
     pctts_launch(split_bf16_kernel, blocks, 256, 0, (cudaStream_t)stream, src, ld, seg, segstride, rows, cols, (__nv_bfloat16*)dst, ld_dst, part_stride, parts);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
+extern "C" int pctts_split_bf16_multi(const pctts_split_job* jobs, int njobs, int parts, void* stream) {
+    if (!jobs || njobs < 1 || njobs > SPLIT_MAXJOBS || parts < 1 || parts > 3) return PCTTS_EINVAL;
+    SplitJobs P;
+    P.parts = parts;
+    long most = 0;
+    for (int i = 0; i < njobs; ++i) {
+        const pctts_split_job& s = jobs[i];
+        if (!s.src || !s.dst || s.rows < 0 || s.cols <= 0 || s.ld_dst < s.cols || (s.ld_dst & 7) || s.rows * (s.ld_dst / 2) >= (1L << 31))
+            return PCTTS_EINVAL;
+        SplitJob& d = P.j[i];
+        d.src = s.src, d.dst = (__nv_bfloat16*)s.dst, d.ld = s.ld, d.ld_dst = s.ld_dst, d.part_stride = s.part_stride;
+        d.rows = (int)s.rows, d.cols = s.cols;
+        d.vec = ((s.cols & 3) == 0 && (s.ld & 3) == 0 && !((uintptr_t)s.src & 15) && !((uintptr_t)s.dst & 15) && (s.part_stride & 7) == 0) ? 1 : 0;
+        const long work = d.vec ? s.rows * (s.ld_dst / 8) : s.rows * (s.ld_dst / 2);
+        if (work > most) most = work;
+    }
+    if (most == 0) return PCTTS_OK;
+    int bx = pctts_div_up(most, 256);
+    if (bx > 148 * 4) bx = 148 * 4;
+    pctts_launch(split_bf16_multi_kernel, dim3(bx, njobs), 256, 0, (cudaStream_t)stream, P);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

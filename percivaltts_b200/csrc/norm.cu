@@ -5,6 +5,7 @@
 // Data are [rows, C] with channels innermost.  Reductions are two-stage and deterministic: every CTA writes a
 // double partial, the last CTA to finish (ticket counter) sums the partials in index order.
 #include "common.cuh"
+#include <cuda_bf16.h>
 #include "pctts.h"
 
 namespace {
@@ -238,10 +239,32 @@ __global__ void bn_apply_kernel(const float* __restrict__ x, float* __restrict__
 // The same for C % 4 == 0 and 16-byte aligned maps: one float4 per thread and iteration (the scalar loop above keeps ~1.2 MB
 // in flight on the whole GPU and runs at load latency).  Per-element expression unchanged: bit-identical output.
 constexpr int NORM_SMEM_C = 1024;
+
+// bf16 operand planes of four consecutive values (the format and the rounding steps of pctts_split_bf16, gemm_tc.cu: bit-identical
+// planes), written by the kernel that produces the values when their consumer is a tensor-core GEMM
+struct PlaneOut {
+    __nv_bfloat16* dst;      // NULL: none
+    long ld, part_stride;    // elements
+    int parts;
+};
+__device__ __forceinline__ void emit_planes4(const PlaneOut& po, long row, int c, float (&v)[4]) {
+    __nv_bfloat16* d = po.dst + row * po.ld + c;
+    for (int pl = 0; pl < po.parts; ++pl) {
+        uint32_t w[2];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const __nv_bfloat16 ha = __float2bfloat16_rn(v[2 * j]), hb = __float2bfloat16_rn(v[2 * j + 1]);
+            v[2 * j] -= __bfloat162float(ha), v[2 * j + 1] -= __bfloat162float(hb);
+            w[j] = (uint32_t)__bfloat16_as_ushort(ha) | ((uint32_t)__bfloat16_as_ushort(hb) << 16);
+        }
+        *reinterpret_cast<uint2*>(d + (long)pl * po.part_stride) = make_uint2(w[0], w[1]);
+    }
+}
+
 __global__ void __launch_bounds__(256) bn_apply_vec4_kernel(const float4* __restrict__ x, float4* __restrict__ y,
                                                             const float* __restrict__ mean, const float* __restrict__ invstd_or_var,
                                                             const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                            long total4, int C, float eps, int use_var, int lrelu) {
+                                                            long total4, int C, float eps, int use_var, int lrelu, const PlaneOut po) {
     pdl_entry();
     __shared__ float s_m[NORM_SMEM_C], s_i[NORM_SMEM_C], s_g[NORM_SMEM_C], s_b[NORM_SMEM_C];
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
@@ -261,6 +284,7 @@ __global__ void __launch_bounds__(256) bn_apply_vec4_kernel(const float4* __rest
             o[j] = t;
         }
         y[i] = make_float4(o[0], o[1], o[2], o[3]);
+        if (po.dst) emit_planes4(po, i / C4, c, o);
     }
 }
 
@@ -268,7 +292,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_vec4_kernel(const float4* __
                                                                 float4* __restrict__ dx, const float* __restrict__ mean,
                                                                 const float* __restrict__ invstd, const float* __restrict__ gamma,
                                                                 const float* __restrict__ beta, const double* __restrict__ sums,
-                                                                double count, long total4, int C, int lrelu) {
+                                                                double count, long total4, int C, int lrelu, const PlaneOut po) {
     pdl_entry();
     __shared__ float s_m[NORM_SMEM_C], s_i[NORM_SMEM_C], s_g[NORM_SMEM_C], s_b[NORM_SMEM_C], s_1[NORM_SMEM_C], s_2[NORM_SMEM_C];
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
@@ -293,6 +317,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_vec4_kernel(const float4* __
             o[j] = s_g[c + j] * s_i[c + j] * (dz - s_1[c + j] - xh * s_2[c + j]);
         }
         dx[i] = make_float4(o[0], o[1], o[2], o[3]);
+        if (po.dst) emit_planes4(po, i / C4, c, o);
     }
 }
 
@@ -433,6 +458,29 @@ extern "C" int pctts_bn_finalize(void* workspace, long rows, int C, double count
     return PCTTS_OK;
 }
 
+static bool planes_ok(const void* planes, long ld_dst, long part_stride, int parts, int C) {
+    return planes && parts >= 1 && parts <= 3 && ld_dst >= C && (ld_dst & 3) == 0 && (part_stride & 3) == 0 && !(((uintptr_t)planes) & 7);
+}
+
+/* y = LeakyReLU?(BN(x)) and, in the same pass, the bf16 operand planes of y (what pctts_split_bf16(y) would write): planes
+ * [parts][rows][ld_dst] bf16 with plane stride part_stride (elements).  C % 4 == 0, 16-byte aligned x / y only, else PCTTS_EUNSUPPORTED. */
+extern "C" int pctts_bn_apply_planes(const float* x, float* y, const float* mean, const float* invstd_or_var, const float* gamma,
+                                     const float* beta, long rows, int C, float eps, int use_var, int lrelu, void* planes, long ld_dst,
+                                     long part_stride, int parts, void* stream) {
+    if (!x || !y || !mean || !invstd_or_var || !gamma || !beta) return PCTTS_EINVAL;
+    if (!planes_ok(planes, ld_dst, part_stride, parts, C)) return PCTTS_EINVAL;
+    if (!norm_vec() || (C & 3) || C > NORM_SMEM_C || (((uintptr_t)x | (uintptr_t)y) & 15)) return PCTTS_EUNSUPPORTED;
+    const long total = rows * C;
+    if (total == 0) return PCTTS_OK;
+    int blocks = pctts_div_up(total / 4, 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    PlaneOut po{(__nv_bfloat16*)planes, ld_dst, part_stride, parts};
+    pctts_launch(bn_apply_vec4_kernel, blocks, 256, 0, (cudaStream_t)stream, (const float4*)x, (float4*)y, mean, invstd_or_var, gamma,
+                 beta, total / 4, C, eps, use_var, lrelu, po);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
 extern "C" int pctts_bn_apply(const float* x, float* y, const float* mean, const float* invstd_or_var, const float* gamma,
                               const float* beta, long rows, int C, float eps, int use_var, int lrelu, void* stream) {
     if (!x || !y || !mean || !invstd_or_var || !gamma || !beta) return PCTTS_EINVAL;
@@ -444,7 +492,7 @@ extern "C" int pctts_bn_apply(const float* x, float* y, const float* mean, const
         blocks = pctts_div_up(total / 4, 256);
         if (blocks > 148 * 8) blocks = 148 * 8;
         pctts_launch(bn_apply_vec4_kernel, blocks, 256, 0, (cudaStream_t)stream, (const float4*)x, (float4*)y, mean, invstd_or_var, gamma,
-                     beta, total / 4, C, eps, use_var, lrelu);
+                     beta, total / 4, C, eps, use_var, lrelu, PlaneOut{nullptr, 0, 0, 0});
     } else
         pctts_launch(bn_apply_kernel, blocks, 256, 0, (cudaStream_t)stream, x, y, mean, invstd_or_var, gamma, beta, total, C, eps, use_var, lrelu);
     PCTTS_LAUNCH_CHECK();
@@ -488,7 +536,7 @@ extern "C" int pctts_bn_bwd_apply(const float* x, const float* dy, float* dx, co
         blocks = pctts_div_up(total / 4, 256);
         if (blocks > 148 * 8) blocks = 148 * 8;
         pctts_launch(bn_bwd_apply_vec4_kernel, blocks, 256, 0, st, (const float4*)x, (const float4*)dy, (float4*)dx, mean, invstd, gamma,
-                     beta, w.sums, count, total / 4, C, lrelu);
+                     beta, w.sums, count, total / 4, C, lrelu, PlaneOut{nullptr, 0, 0, 0});
     } else
         pctts_launch(bn_bwd_apply_kernel, blocks, 256, 0, st, x, dy, dx, mean, invstd, gamma, beta, w.sums, count, total, C, lrelu);
     PCTTS_LAUNCH_CHECK();
@@ -496,6 +544,25 @@ extern "C" int pctts_bn_bwd_apply(const float* x, const float* dy, float* dx, co
         pctts_launch(sums_to_grads_kernel, pctts_div_up(C, 128), 128, 0, st, w.sums, C, dbeta, dgamma, accumulate, (double)grad_scale);
         PCTTS_LAUNCH_CHECK();
     }
+    return PCTTS_OK;
+}
+
+/* phase 2 with the bf16 operand planes of dx written in the same pass (see pctts_bn_apply_planes); no dgamma / dbeta here */
+extern "C" int pctts_bn_bwd_apply_planes(const float* x, const float* dy, float* dx, const float* mean, const float* invstd,
+                                         const float* gamma, const float* beta, long rows, int C, double count, int lrelu,
+                                         void* workspace, void* planes, long ld_dst, long part_stride, int parts, void* stream) {
+    if (!x || !dy || !dx || !workspace) return PCTTS_EINVAL;
+    if (!planes_ok(planes, ld_dst, part_stride, parts, C)) return PCTTS_EINVAL;
+    if (!norm_vec() || (C & 3) || C > NORM_SMEM_C || (((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dx) & 15)) return PCTTS_EUNSUPPORTED;
+    Ws w = carve(workspace, rows, C);
+    const long total = rows * C;
+    if (total == 0) return PCTTS_OK;
+    int blocks = pctts_div_up(total / 4, 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    PlaneOut po{(__nv_bfloat16*)planes, ld_dst, part_stride, parts};
+    pctts_launch(bn_bwd_apply_vec4_kernel, blocks, 256, 0, (cudaStream_t)stream, (const float4*)x, (const float4*)dy, (float4*)dx, mean,
+                 invstd, gamma, beta, w.sums, count, total / 4, C, lrelu, po);
+    PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }
 

@@ -117,12 +117,13 @@ class _BNNet(object):
             return False
         return sync.world == 1 or getattr(sync, 'bn_handle', None) is not None
 
-    def _bn_fwd(self, z2, y2, bn, training, update_stats, sync, ws=None, apply=True):
+    def _bn_fwd(self, z2, y2, bn, training, update_stats, sync, ws=None, apply=True, planes=False):
         """ws: the batch sums when the producer of z2 already reduced them (Conv2D epilogue).  apply=False: only the
         statistics (bn.mean / bn.invstd) -- the consumer applies BatchNorm + LeakyReLU on load."""
         o, p = self.ops, self.params.p
         g, b = p[bn.prefix + '.gamma'], p[bn.prefix + '.beta']
         mm, mv = p[bn.prefix + '.moving_mean'], p[bn.prefix + '.moving_var']
+        pk = dict(planes=True) if planes else {}      # y2 feeds a GEMM: its bf16 operand planes come out of the same kernel
         if training:
             fused = self._fused_sync(sync)
             if ws is None:
@@ -135,19 +136,20 @@ class _BNNet(object):
                 o.bn_finalize(ws, bn.rows * sync.world, A.BN_EPS, A.BN_MOMENTUM, bn.mean, bn.invstd,
                               mm if update_stats else None, mv if update_stats else None)
             if apply:
-                o.bn_apply(z2, y2, bn.mean, bn.invstd, g, b, A.BN_EPS, 0, 1)
+                o.bn_apply(z2, y2, bn.mean, bn.invstd, g, b, A.BN_EPS, 0, 1, **pk)
         else:
-            o.bn_apply(z2, y2, mm, mv, g, b, A.BN_EPS, 1, 1)
+            o.bn_apply(z2, y2, mm, mv, g, b, A.BN_EPS, 1, 1, **pk)
 
-    def _bn_bwd(self, z2, dy2, dz2, bn, sync):
+    def _bn_bwd(self, z2, dy2, dz2, bn, sync, planes=False):
         o, p, g = self.ops, self.params.p, self.params.g
+        pk = dict(planes=True) if planes else {}
         gam, bet = p[bn.prefix + '.gamma'], p[bn.prefix + '.beta']
         # dgamma / dbeta come from the all-reduced sums, i.e. every rank holds the global value: pre-divide by world so
         # that the all-reduce(sum) of the flat gradient buffer does not count them `world` times
         if self._fused_sync(sync):
             ws = o.bn_bwd_reduce(z2, dy2, bn.mean, bn.invstd, gam, bet, 1, final=False)
             o.bn_sync_bwd(ws, g[bn.prefix + '.gamma'], g[bn.prefix + '.beta'], 1.0 / sync.world, False, sync)
-            o.bn_bwd_apply(ws, z2, dy2, dz2, bn.mean, bn.invstd, gam, bet, bn.rows * sync.world, 1, None, None)
+            o.bn_bwd_apply(ws, z2, dy2, dz2, bn.mean, bn.invstd, gam, bet, bn.rows * sync.world, 1, None, None, **pk)
             return
         ws = o.bn_bwd_reduce(z2, dy2, bn.mean, bn.invstd, gam, bet, 1)
         sync.allreduce(ws.sums)
@@ -186,7 +188,7 @@ class GenericFC(_BNNet):
         x2 = ctx.reshape(M, a.ctxsize)
         for i in range(len(a.layertypes)):
             o.gemm(x2, p['g.fc%d.kernel' % i], pl['z'][i])
-            self._bn_fwd(pl['z'][i], pl['y'][i], pl['bn'][i], training, update_stats, sync)
+            self._bn_fwd(pl['z'][i], pl['y'][i], pl['bn'][i], training, update_stats, sync, planes=True)
             x2 = pl['y'][i]
         out2 = out.view(M, a.outsize)
         o.gemm(x2, p['g.f0spec.kernel'], out2[:, 0:1 + S], bias=p['g.f0spec.bias'])
@@ -215,7 +217,7 @@ class GenericFC(_BNNet):
         for i in range(L - 1, -1, -1):
             xin = pl['y'][i - 1] if i > 0 else pl['ctx_in'].reshape(M, a.ctxsize)
             dz = pl['dB'] if dcur is pl['dA'] else pl['dA']
-            self._bn_bwd(pl['z'][i], dcur, dz, pl['bn'][i], sync)
+            self._bn_bwd(pl['z'][i], dcur, dz, pl['bn'][i], sync, planes=True)
             o.gemm(xin, dz, g['g.fc%d.kernel' % i], transA=True)
             if i > 0:
                 dnext = pl['dA'] if dz is pl['dB'] else pl['dB']
@@ -309,12 +311,12 @@ class Generator(_BNNet):
             xp = pl['ctx_xp'][i]
             o.pad_time(xp, x, left, W - 1 - left)
             o.conv1d(xp, p['g.ctx.cnn%d.kernel' % i], pl['ctx_z'][i], T)
-            self._bn_fwd(pl['ctx_z'][i], pl['ctx_y'][i], pl['ctx_bn'][i], training, update_stats, sync)
+            self._bn_fwd(pl['ctx_z'][i], pl['ctx_y'][i], pl['ctx_bn'][i], training, update_stats, sync, planes=True)
             x = pl['ctx_y'][i].view(B, T, H)
         x2 = x.reshape(M, -1)
         for i in range(2):                                                   # pFC (networktts.py:59-63)
             o.gemm(x2, p['g.ctx.fc%d.kernel' % i], pl['fc_z'][i])
-            self._bn_fwd(pl['fc_z'][i], pl['fc_y'][i], pl['fc_bn'][i], training, update_stats, sync)
+            self._bn_fwd(pl['fc_z'][i], pl['fc_y'][i], pl['fc_bn'][i], training, update_stats, sync, planes=True)
             x2 = pl['fc_y'][i]
         lctx = x2
         out2 = out.view(M, O)
@@ -336,7 +338,7 @@ class Generator(_BNNet):
             n2 = lctx
             for i in range(a.gen_nbcnnlayers // 2):
                 o.gemm(n2, p['g.nm.fc%d.kernel' % i], pl['nm_z'][i])
-                self._bn_fwd(pl['nm_z'][i], pl['nm_y'][i], pl['nm_bn'][i], training, update_stats, sync)
+                self._bn_fwd(pl['nm_z'][i], pl['nm_y'][i], pl['nm_bn'][i], training, update_stats, sync, planes=True)
                 n2 = pl['nm_y'][i]
             o.gemm(n2, p['g.nm.out.kernel'], out2[:, 1 + S:], bias=p['g.nm.out.bias'], flags=EPI_SIGMOID)
         nm_lane = not spec_only and self._nm_lane(sync, training)
@@ -417,7 +419,7 @@ class Generator(_BNNet):
             for i in range(Ln - 1, -1, -1):
                 xin = pl['nm_y'][i - 1] if i > 0 else lctx
                 dz = pl['dB'] if dcur is pl['dA'] else pl['dA']
-                self._bn_bwd(pl['nm_z'][i], dcur, dz, pl['nm_bn'][i], sync)
+                self._bn_bwd(pl['nm_z'][i], dcur, dz, pl['nm_bn'][i], sync, planes=True)
                 o.gemm(xin, dz, g['g.nm.fc%d.kernel' % i], transA=True)
                 dnext = dl_nm if i == 0 else dcur
                 o.gemm(dz, p['g.nm.fc%d.kernel' % i], dnext, transB=True)
@@ -470,7 +472,7 @@ class Generator(_BNNet):
             else:
                 xin = pl['ctx_y'][-1] if a.ctx_nbcnnlayers > 0 else pl['ctx_in'].view(M, -1)
             dz = pl['dB'] if dcur is not pl['dB'] else pl['dA']
-            self._bn_bwd(pl['fc_z'][i], dcur, dz, pl['fc_bn'][i], sync)
+            self._bn_bwd(pl['fc_z'][i], dcur, dz, pl['fc_bn'][i], sync, planes=True)
             o.gemm(xin, dz, g['g.ctx.fc%d.kernel' % i], transA=True)
             if i > 0 or a.ctx_nbcnnlayers > 0:
                 dnext = pl['dA'] if dz is pl['dB'] else pl['dB']
@@ -479,7 +481,7 @@ class Generator(_BNNet):
         left = (W - 1) // 2
         for i in range(a.ctx_nbcnnlayers - 1, -1, -1):
             dz = pl['dB'] if dcur is not pl['dB'] else pl['dA']
-            self._bn_bwd(pl['ctx_z'][i], dcur, dz, pl['ctx_bn'][i], sync)
+            self._bn_bwd(pl['ctx_z'][i], dcur, dz, pl['ctx_bn'][i], sync, planes=True)
             k = p['g.ctx.cnn%d.kernel' % i]
             o.conv1d_wgrad(pl['ctx_xp'][i], dz, g['g.ctx.cnn%d.kernel' % i], T)
             if i > 0:

@@ -154,6 +154,12 @@ class ChainLayerStruct(ctypes.Structure):
                 ('cin', ctypes.c_int), ('cout', ctypes.c_int), ('flags', ctypes.c_int), ('flip', ctypes.c_int)]
 
 
+class SplitJobStruct(ctypes.Structure):
+    """pctts_split_job of include/pctts.h"""
+    _fields_ = [('src', ctypes.c_void_p), ('dst', ctypes.c_void_p), ('ld', ctypes.c_long), ('rows', ctypes.c_long),
+                ('ld_dst', ctypes.c_long), ('part_stride', ctypes.c_long), ('cols', ctypes.c_int)]
+
+
 class WgradLayerStruct(ctypes.Structure):
     """pctts_wgrad_layer of include/pctts.h"""
     _fields_ = [('x', ctypes.c_void_p), ('dy', ctypes.c_void_p), ('dw', ctypes.c_void_p), ('dbias', ctypes.c_void_p),
@@ -189,6 +195,8 @@ class CudaOps(object):
         self.fuse_bn_stats = os.environ.get('PCTTS_FUSE_BN_STATS', '1') != '0'   # BN sums in the Conv2D epilogue
         self.bn_single_launch = os.environ.get('PCTTS_BN_SINGLE_LAUNCH', '1') != '0'   # second stage inside bn_finalize (1 replica)
         self.conv2d_tc = os.environ.get('PCTTS_CONV2D_TC', '1') != '0'   # tcgen05 implicit-GEMM Conv2D (4->4, 5x5)
+        self.split_multi = os.environ.get('PCTTS_SPLIT_MULTI', '1') != '0'   # weight shadows after Adam in one launch
+        self.fuse_planes = os.environ.get('PCTTS_FUSE_PLANES', '1') != '0'   # BatchNorm apply kernels write the bf16 operand planes of their output
         self.tc_wflip = os.environ.get('PCTTS_TC_WFLIP', '1') != '0'     # Conv2D data gradients read the forward kernels (no flip launch)
         self.wgrad_multi = os.environ.get('PCTTS_WGRAD_MULTI', '1') != '0'   # weight gradients of a whole Conv2D stack in one launch
         self.conv_chain = os.environ.get('PCTTS_CONV_CHAIN', '1') != '0'   # the critic's BN-free Conv2D stack as ONE launch per chain
@@ -377,9 +385,19 @@ class CudaOps(object):
     def refresh_persistent(self, flat):
         """Re-split every shadow taken from views of `flat` (after Adam or a weight load)."""
         lo, hi = _extent(flat)
+        jobs = []
         for key, (sh, view) in self._persist.items():
             if lo <= key[0] < hi:
-                self._split(view, sh)
+                p, ld, seg, ss, rows, cols = _mat(view)
+                if seg > 0 or not self.split_multi:
+                    self._split(view, sh)
+                else:
+                    jobs.append(SplitJobStruct(p, sh.ptr, ld, rows, sh.ld, sh.part_stride, cols))
+        for i in range(0, len(jobs), 24):       # the plain matrices in one launch per 24
+            chunk = jobs[i:i + 24]
+            arr = (SplitJobStruct * len(chunk))(*chunk)
+            self._ck(self.lib.pctts_split_bf16_multi(ctypes.cast(arr, ctypes.c_void_p), len(chunk), PLANES[self.nterms], self._stream()),
+                     'pctts_split_bf16_multi')
 
     def _clear_fresh(self):
         self._fresh.clear()
@@ -775,10 +793,43 @@ class CudaOps(object):
                                             invstd.data_ptr(), _ptr(moving_mean), _ptr(moving_var), self._stream()),
                  'pctts_bn_finalize')
 
-    def bn_apply(self, x, y, mean, invstd_or_var, gamma, beta, eps, use_var, lrelu):
+    def _plane_target(self, y):
+        """Where the kernel that produces the contiguous [rows, C] matrix y may write y's bf16 operand planes itself (saving the
+        pctts_split_bf16 launch in front of the consuming GEMM): (shadow, mark_fresh) or (None, None)."""
+        if not (self.nterms > 0 and self._tracking and self.fuse_planes and y.dim() == 2 and y.is_contiguous()
+                and y.shape[1] % 8 == 0 and y.shape[1] <= 1024 and y.data_ptr() % 16 == 0):
+            return None, None
+        par, r0 = self._row_parent(y)
+        if par is not None:
+            r1 = r0 + y.shape[0]
+            return ShadowRows(par.shadow, r0, y.shape[0]), (lambda: par.add(r0, r1))
+        key = (y.data_ptr(), tuple(y.shape), tuple(y.stride()))
+        if self._is_persistent(key[0]):
+            return None, None
+        sh = self._shadows.get(key)
+        if sh is None:
+            sh = self._shadows[key] = Shadow(self.device, y.shape[0], y.shape[1], PLANES[self.nterms])
+            self._note(self._shadows, key)
+        ext = _extent(y)
+
+        def mark():
+            self._fresh[key] = ext
+        return sh, mark
+
+    def bn_apply(self, x, y, mean, invstd_or_var, gamma, beta, eps, use_var, lrelu, planes=False):
+        """planes=True: y feeds a tensor-core GEMM -- its bf16 operand planes are written by the same kernel where possible."""
         rows, C = x.shape
         assert x.is_contiguous() and y.is_contiguous()
         self._wrote(y)
+        sh, mark = self._plane_target(y) if planes else (None, None)
+        if sh is not None:
+            rc = self.lib.pctts_bn_apply_planes(x.data_ptr(), y.data_ptr(), mean.data_ptr(), invstd_or_var.data_ptr(),
+                                                gamma.data_ptr(), beta.data_ptr(), rows, C, float(eps), int(use_var), int(lrelu),
+                                                sh.ptr, sh.ld, sh.part_stride, sh.parts, self._stream())
+            if rc != -2:
+                self._ck(rc, 'pctts_bn_apply_planes')
+                mark()
+                return
         self._ck(self.lib.pctts_bn_apply(x.data_ptr(), y.data_ptr(), mean.data_ptr(), invstd_or_var.data_ptr(),
                                          gamma.data_ptr(), beta.data_ptr(), rows, C, float(eps), int(use_var), int(lrelu),
                                          self._stream()), 'pctts_bn_apply')
@@ -820,10 +871,20 @@ class CudaOps(object):
         ws.pending = 0
 
     def bn_bwd_apply(self, ws, x, dy, dx, mean, invstd, gamma, beta, count, lrelu, dgamma, dbeta, grad_scale=1.0,
-                     accumulate=False):
+                     accumulate=False, planes=False):
+        """planes=True: dx feeds tensor-core GEMMs -- its bf16 operand planes are written by the same kernel where possible."""
         rows, C = x.shape
         assert dx.is_contiguous()
         self._wrote(dx)
+        sh, mark = self._plane_target(dx) if (planes and dgamma is None and dbeta is None) else (None, None)
+        if sh is not None:
+            rc = self.lib.pctts_bn_bwd_apply_planes(x.data_ptr(), dy.data_ptr(), dx.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                                                    gamma.data_ptr(), beta.data_ptr(), rows, C, float(count), int(lrelu), ws.ptr,
+                                                    sh.ptr, sh.ld, sh.part_stride, sh.parts, self._stream())
+            if rc != -2:
+                self._ck(rc, 'pctts_bn_bwd_apply_planes')
+                mark()
+                return
         self._ck(self.lib.pctts_bn_bwd_apply(x.data_ptr(), dy.data_ptr(), dx.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
                                              gamma.data_ptr(), beta.data_ptr(), rows, C, float(count), int(lrelu),
                                              _ptr(dgamma), _ptr(dbeta), float(grad_scale), int(accumulate), ws.ptr,

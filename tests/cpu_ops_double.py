@@ -220,7 +220,7 @@ class CpuOpsDouble(object):
             moving_mean.copy_(momentum * moving_mean + (1.0 - momentum) * m.to(mean.dtype))
             moving_var.copy_(momentum * moving_var + (1.0 - momentum) * v.to(mean.dtype))
 
-    def bn_apply(self, x, y, mean, invstd_or_var, gamma, beta, eps, use_var, lrelu):
+    def bn_apply(self, x, y, mean, invstd_or_var, gamma, beta, eps, use_var, lrelu, planes=False):
         self.launches += 1
         istd = torch.rsqrt(invstd_or_var + eps) if use_var else invstd_or_var
         v = (x - mean) * istd * gamma + beta
@@ -243,7 +243,7 @@ class CpuOpsDouble(object):
         return ws
 
     def bn_bwd_apply(self, ws, x, dy, dx, mean, invstd, gamma, beta, count, lrelu, dgamma, dbeta, grad_scale=1.0,
-                     accumulate=False):
+                     accumulate=False, planes=False):
         self.launches += 1
         xh, dz = self._bn_dz(x, dy, mean, invstd, gamma, beta, lrelu)
         m1 = (ws.sums[0] / count).to(x.dtype)

@@ -173,6 +173,71 @@ def test_conv2d_wgrad_multi(cuda_ops, N, T, F, L):
     assert all(torch.equal(a, b) for a, b in zip(again, again2))
 
 
+@pytest.mark.parametrize('rows,C', [(4000, 256), (517, 64), (33, 8)])
+def test_batchnorm_apply_kernels_write_operand_planes(rows, C):
+    """bn_apply / bn_bwd_apply(planes=True) write y / dx and, in the same launch, the bf16 operand planes the consuming GEMM would
+    otherwise get from pctts_split_bf16: same fp32 output as the plain kernels and bit-identical planes, and the GEMM that follows
+    inside the step scope launches no split."""
+    ops = OPS.CudaOps(precision='fp32')
+    x, dy = dev(rnd(rows, C) * 2 + 0.3), dev(rnd(rows, C, seed=1))
+    gamma, beta = dev(rnd(C, seed=2) + 1.5), dev(rnd(C, seed=3) * 0.1)
+    mean, istd = dev(rnd(C, seed=4) * 0.1), dev(rnd(C, seed=5).abs() + 0.5)
+    y0, y1 = torch.zeros(rows, C, device='cuda'), torch.zeros(rows, C, device='cuda')
+    ops.bn_apply(x, y0, mean, istd, gamma, beta, 1e-3, 0, 1)
+    w = dev(rnd(C, 16, seed=6))
+    out0, out1 = torch.zeros(rows, 16, device='cuda'), torch.zeros(rows, 16, device='cuda')
+    with ops.step_scope():
+        ops.bn_apply(x, y1, mean, istd, gamma, beta, 1e-3, 0, 1, planes=True)
+        assert torch.equal(y0, y1)
+        got = ops.shadow(y1)                       # fresh: no launch
+        n0 = ops.launches
+        assert ops.shadow(y1) is got and ops.launches == n0
+        want = OPS.Shadow(ops.device, rows, C, 3)
+        ops._split(y1, want)
+        assert torch.equal(got.buf, want.buf)
+        n0 = ops.launches
+        ops.gemm(y1, w, out1)
+        n_gemm = ops.launches - n0
+    ops.gemm(y0, w, out0)
+    assert torch.equal(out0, out1)
+    # backward apply
+    ws = ops.bn_bwd_reduce(x, dy, mean, istd, gamma, beta, 1)
+    dx0, dx1 = torch.zeros(rows, C, device='cuda'), torch.zeros(rows, C, device='cuda')
+    ops.bn_bwd_apply(ws, x, dy, dx0, mean, istd, gamma, beta, rows, 1, None, None)
+    with ops.step_scope():
+        ops.bn_bwd_apply(ws, x, dy, dx1, mean, istd, gamma, beta, rows, 1, None, None, planes=True)
+        assert torch.equal(dx0, dx1)
+        got = ops.shadow(dx1)
+        want = OPS.Shadow(ops.device, rows, C, 3)
+        ops._split(dx1, want)
+        assert torch.equal(got.buf, want.buf)
+        # a later writer invalidates the planes again
+        ops.bn_apply(x, dx1, mean, istd, gamma, beta, 1e-3, 0, 1)
+        n0 = ops.launches
+        ops.shadow(dx1)
+        assert ops.launches == n0 + 1
+
+
+def test_split_bf16_multi_matches_single_splits():
+    """The weight shadows of a network after Adam are refreshed by ONE launch (pctts_split_bf16_multi): bit-identical planes."""
+    import ctypes
+    ops = OPS.CudaOps(precision='fp32')
+    shapes = [(516, 256), (256, 256), (21 * 425, 256), (256, 129), (256, 1024), (33, 7), (8, 8)]
+    mats = [dev(rnd(r, c, seed=i)) for i, (r, c) in enumerate(shapes)]
+    want = [OPS.Shadow(ops.device, r, c, 3) for r, c in shapes]
+    got = [OPS.Shadow(ops.device, r, c, 3) for r, c in shapes]
+    for m, sh in zip(mats, want):
+        sh.buf.zero_()
+        ops._split(m, sh)
+    for sh in got:
+        sh.buf.zero_()
+    jobs = (OPS.SplitJobStruct * len(mats))(*[OPS.SplitJobStruct(m.data_ptr(), sh.ptr, m.stride(0), m.shape[0], sh.ld, sh.part_stride, m.shape[1])
+                                             for m, sh in zip(mats, got)])
+    OPS._lib.check(ops.lib.pctts_split_bf16_multi(ctypes.cast(jobs, ctypes.c_void_p), len(mats), 3, ops._stream()), 'multi')
+    for a, b in zip(got, want):
+        assert torch.equal(a.buf, b.buf)
+
+
 def test_conv2d_strided_feature_views(cuda_ops):
     """First critic layer reads / last generator layer writes the spectral columns of a [B,T,O] tensor in place."""
     B, T, S, O = 2, 21, 17, 23
