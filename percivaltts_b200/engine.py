@@ -616,7 +616,11 @@ class Critic(object):
         pl['s0'] = s0
         return pl['d']
 
-    def backward_to_input(self, pl, g_out, g_rows=None, accumulate=False, ctx_grads_apps=0):
+    def backward_to_input(self, *args, **kw):
+        with self.ops.backward_terms():      # gradient passes: linear in their seeds (ops.bwd_nterms)
+            return self._backward_to_input(*args, **kw)
+
+    def _backward_to_input(self, pl, g_out, g_rows=None, accumulate=False, ctx_grads_apps=0):
         """Back-propagate pl['dd'] (d objective / d critic output, [nM,1]) to the spectral input.  The per-layer
         pre-activation gradients stay in pl['dp'] / pl['da'] for param_grads().  g_out: [n,T,S,1] view receiving the
         input gradient of the applications `g_rows` (slice over the napp*B sample axis; default all)."""
@@ -628,8 +632,7 @@ class Critic(object):
         if not chain:      # the chain kernel forms the data-gradient kernels on the fly
             for i in range(L - 1, -1, -1):
                 o.conv2d_flip(p['c.spec.cnn%d.kernel' % i], pl['wflip'][i])
-        if g_rows is not None and ctx_grads_apps and getattr(o, 'lanes', False) and g_rows.start > 0 \
-                and g_rows.stop == pl['nB']:
+        if g_rows is not None and ctx_grads_apps and g_rows.start > 0 and g_rows.stop == pl['nB']:
             # critic step.  Only the interpolated applications' input gradient is on the critical path (norm -> penalty ->
             # tangent sweep); the other applications' pre-activation gradients are needed by the weight gradients only:
             # side lane, followed there by everything else that hangs off them (ctx branch, bias sums).
@@ -644,18 +647,23 @@ class Critic(object):
                 self._conv_wgrads(pl, slice(0, g_rows.start), first=True)
                 pl['conv_wgrads_apps'] = g_rows.start // pl['B']
                 pl['side_event'] = o.lane_event()
-            self._dgrad_chain(pl, g_rows, final=(g_out, accumulate) if chain else None)
+            # the interpolated rows' input gradient feeds 1 - ||g|| (a difference of nearly equal numbers once the critic is
+            # trained): forward precision.  Everything else on the gradient passes is summed, never differenced.
+            with o.full_terms():
+                self._dgrad_chain(pl, g_rows, final=(g_out, accumulate) if chain else None)
         elif chain and (g_rows is None or (g_rows.start == 0 and g_rows.stop == pl['nB'])):
             self._dgrad_chain(pl, slice(0, pl['nB']), final=(g_out, accumulate))
             if ctx_grads_apps:
                 self.param_grads_ctx(pl, ctx_grads_apps)
         else:
-            self._dgrad_chain(pl, slice(0, pl['nB']))
+            with o.full_terms():      # in-line schedule of the critic step / validation pass: the penalty rows are among these
+                self._dgrad_chain(pl, slice(0, pl['nB']))
             if ctx_grads_apps:
                 self.param_grads_ctx(pl, ctx_grads_apps)
             if chain:
-                o.conv2d_chain(pl['da'][0][g_rows], [dict(w=p['c.spec.cnn0.kernel'], flip=True, y=g_out,
-                                                          flags=EPI_ACCUM if accumulate else 0)])
+                with o.full_terms():
+                    o.conv2d_chain(pl['da'][0][g_rows], [dict(w=p['c.spec.cnn0.kernel'], flip=True, y=g_out,
+                                                              flags=EPI_ACCUM if accumulate else 0)])
                 return
         if chain:
             return
@@ -693,7 +701,11 @@ class Critic(object):
         for i in range(L - 1, 0, -1):
             o.conv2d(pl['da'][i][sm], pl['wflip'][i], pl['da'][i - 1][sm], aux=pl['a'][i - 1][sm])
 
-    def tangent_forward(self, pl, rows):
+    def tangent_forward(self, *args, **kw):
+        with self.ops.backward_terms():      # gradient passes: linear in their seeds (ops.bwd_nterms)
+            return self._tangent_forward(*args, **kw)
+
+    def _tangent_forward(self, pl, rows):
         """Forward-mode sweep of the linearised critic (LeakyReLU masks frozen) on the applications `rows`, whose
         input tangent has been written over pl['s0'][rows].  The tangents overwrite the stored activations of those
         rows in place, so that param_grads() sees [a | a | tangent] as one batched layer input."""
@@ -716,7 +728,11 @@ class Critic(object):
         for i in (1, 2):
             o.gemm(pl['p'][i - 1][r2], p['c.post.fc%d.kernel' % i], pl['p'][i][r2], aux=pl['p'][i][r2])
 
-    def param_grads_ctx(self, pl, first_order_apps=2):
+    def param_grads_ctx(self, *args, **kw):
+        with self.ops.backward_terms():      # gradient passes: linear in their seeds (ops.bwd_nterms)
+            return self._param_grads_ctx(*args, **kw)
+
+    def _param_grads_ctx(self, pl, first_order_apps=2):
         """Gradients of the ctx branch and of its rows of the first post layer, on the side lane.  They depend on pl['dp'][0]
         only, so the critic step forks them as soon as backward_to_input() has produced it (ctx_grads_apps), long before the
         gradient-penalty sweep that the spectral weight gradients wait for; param_grads() joins."""
@@ -777,7 +793,11 @@ class Critic(object):
         for L in layers:
             o.conv2d_wgrad(L['x'], L['dy'], L['dw'], dbias=L['dbias'], accumulate=not first)
 
-    def param_grads(self, pl, first_order_apps=2):
+    def param_grads(self, *args, **kw):
+        with self.ops.backward_terms():      # gradient passes: linear in their seeds (ops.bwd_nterms)
+            return self._param_grads(*args, **kw)
+
+    def _param_grads(self, pl, first_order_apps=2):
         """Gradients of every critic parameter from the stored layer inputs (activations, or tangents on the GP rows)
         and pre-activation gradients.  Kernels use all napp applications; biases and the ctx branch only the first
         `first_order_apps` (the gradient penalty reaches neither: optimizertts_wgan.py:57-68 differentiates through

@@ -192,6 +192,11 @@ class CudaOps(object):
             raise ValueError('unknown precision %r (one of %s)' % (precision, sorted(PRECISIONS)))
         self.precision = precision
         self.nterms = PRECISIONS[precision]
+        # products per k-slice inside backward_terms(): the gradient passes of the critic are LINEAR in their seeds (LeakyReLU masks come
+        # from the stored fp32 activations), so two planes / three products (2^-17 per product) leave the gradients ~1e-5 from the fp32
+        # result; the forward passes, which decide the masks, keep the six products.  PCTTS_BWD_TERMS=6 switches it off.
+        self.bwd_nterms = 3 if (self.nterms == 6 and os.environ.get('PCTTS_BWD_TERMS', '3') == '3') else self.nterms
+        self._nt = self.nterms
         self.fuse_bn_stats = os.environ.get('PCTTS_FUSE_BN_STATS', '1') != '0'   # BN sums in the Conv2D epilogue
         self.bn_single_launch = os.environ.get('PCTTS_BN_SINGLE_LAUNCH', '1') != '0'   # second stage inside bn_finalize (1 replica)
         self.conv2d_tc = os.environ.get('PCTTS_CONV2D_TC', '1') != '0'   # tcgen05 implicit-GEMM Conv2D (4->4, 5x5)
@@ -317,6 +322,26 @@ class CudaOps(object):
                 yield self
         finally:
             self._lane = outer
+
+    @contextlib.contextmanager
+    def backward_terms(self):
+        """Tensor-core contractions issued inside use the gradient-pass precision (see bwd_nterms); operand planes are unchanged
+        (the two-plane products read the first two of the three planes)."""
+        outer, self._nt = self._nt, self.bwd_nterms
+        try:
+            yield self
+        finally:
+            self._nt = outer
+
+    @contextlib.contextmanager
+    def full_terms(self):
+        """Inside backward_terms(): back to the forward precision for a pass whose result is differenced afterwards (the input
+        gradient of the interpolated rows feeds 1 - ||g||)."""
+        outer, self._nt = self._nt, self.nterms
+        try:
+            yield self
+        finally:
+            self._nt = outer
 
     def preshare(self, t):
         """Take the bf16 shadow of an operand both lanes are going to read (no-op for the CUDA-core GEMM mode)."""
@@ -512,7 +537,7 @@ class CudaOps(object):
                     self.launches += 1
             self._ck(self.lib.pctts_gemm_tc(int(transA), int(transB), M, N, K, float(alpha), sha.ptr, sha.ld, sha.part_stride,
                                             shb.ptr, shb.ld, shb.part_stride, pc, ldc, _ptr(bias), _ptr(aux), _ptr(addmod),
-                                            addrows, flags, self.nterms, splits, _ptr(ws), self._stream()), 'pctts_gemm_tc')
+                                            addrows, flags, self._nt, splits, _ptr(ws), self._stream()), 'pctts_gemm_tc')
             return
         self._wrote(C)
         if (flags & ~EPI_ACCUM) == 0 and K >= 1024:
@@ -557,7 +582,7 @@ class CudaOps(object):
             if ws is not None:
                 self.launches += 1
             self._ck(self.lib.pctts_conv1d_tc_fwd(shx.ptr, shx.ld, shx.part_stride, shw.ptr, shw.ld, shw.part_stride, y.data_ptr(),
-                                                  y.stride(0), B, T, W, CIN, COUT, _ptr(bias), _ptr(aux), flags, self.nterms,
+                                                  y.stride(0), B, T, W, CIN, COUT, _ptr(bias), _ptr(aux), flags, self._nt,
                                                   _ptr(ws), self._stream()), 'pctts_conv1d_tc_fwd')
             return
         self.gemm(xp.as_strided((B, T, W * CIN), (Tp * CIN, CIN, 1)), kernel.view(W * CIN, COUT), y, bias=bias, aux=aux, flags=flags)
@@ -575,7 +600,7 @@ class CudaOps(object):
             if ws is not None:
                 self.launches += 1
             self._ck(self.lib.pctts_conv1d_tc_wgrad(shx.ptr, shx.ld, shx.part_stride, shz.ptr, shz.ld, shz.part_stride,
-                                                    dw.data_ptr(), B, T, W, CIN, COUT, 0, self.nterms, _ptr(ws), self._stream()),
+                                                    dw.data_ptr(), B, T, W, CIN, COUT, 0, self._nt, _ptr(ws), self._stream()),
                      'pctts_conv1d_tc_wgrad')
             return
         self.gemm(xp.as_strided((B, T, W * CIN), (Tp * CIN, CIN, 1)), dz, dw.view(W * CIN, COUT), transA=True)
@@ -596,7 +621,7 @@ class CudaOps(object):
                 flags |= EPI_DLRELU_AUX
             self._wrote(dx)
             self._ck(self.lib.pctts_conv2d_tc_fwd_fused(px, w.data_ptr(), None, pa or None, py, N, T, F, COUT, CIN, KH, KW, (KH - 1) // 2,
-                                                        (KW - 1) // 2, xp, yp, ap, xb, yb, ab, flags | EPI_WFLIP, self.nterms, None, None,
+                                                        (KW - 1) // 2, xp, yp, ap, xb, yb, ab, flags | EPI_WFLIP, self._nt, None, None,
                                                         None, None, None, 1, self._stream()), 'pctts_conv2d_tc_fwd_fused')
             return
         self.conv2d_flip(w, scratch)
@@ -640,7 +665,7 @@ class CudaOps(object):
             if stats and self.fuse_bn_stats and y.is_contiguous():
                 ws = self.reduce_ws(N * T * F, COUT)
                 rc = self.lib.pctts_conv2d_tc_fwd_fused(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t,
-                                                        pad_f, xp, yp, ap, xb, yb, ab, flags, self.nterms, bnp[0], bnp[1], bnp[2],
+                                                        pad_f, xp, yp, ap, xb, yb, ab, flags, self._nt, bnp[0], bnp[1], bnp[2],
                                                         bnp[3], ws.ptr, int(stats_final), self._stream())
                 if rc != -2:      # PCTTS_EUNSUPPORTED: map too small for 148 partial slots
                     self.launches += int(stats_final)      # conv + the second reduction stage
@@ -648,7 +673,7 @@ class CudaOps(object):
                     ws.pending = 0 if stats_final else self.lib.pctts_conv2d_tc_stat_partials(N, T, F)
                     return ws
             self._ck(self.lib.pctts_conv2d_tc_fwd_fused(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
-                                                        xp, yp, ap, xb, yb, ab, flags, self.nterms, bnp[0], bnp[1], bnp[2], bnp[3],
+                                                        xp, yp, ap, xb, yb, ab, flags, self._nt, bnp[0], bnp[1], bnp[2], bnp[3],
                                                         None, 1, self._stream()), 'pctts_conv2d_tc_fwd_fused')
         else:
             self._ck(self.lib.pctts_conv2d_fwd(px, w.data_ptr(), _ptr(bias), pa, py, N, T, F, CIN, COUT, KH, KW, pad_t, pad_f,
@@ -692,7 +717,7 @@ class CudaOps(object):
             arr[i] = ChainLayerStruct(w.data_ptr(), _ptr(bias), pa, py, yb, yp, ab, ap, cin, cout, flags, int(flip))
             cin = cout
         self._ck(self.lib.pctts_conv2d_chain(x.data_ptr(), x.stride(0), x.stride(1), cin0, N, T, F, len(layers),
-                                             ctypes.cast(arr, ctypes.c_void_p), self.nterms, self._stream()), 'pctts_conv2d_chain')
+                                             ctypes.cast(arr, ctypes.c_void_p), self._nt, self._stream()), 'pctts_conv2d_chain')
 
     def conv2d_flip(self, w, wt):
         KH, KW, CIN, COUT = w.shape

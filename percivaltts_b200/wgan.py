@@ -197,7 +197,7 @@ class WGANStepper(object):
         o.sum_scaled(d[M:2 * M], -1.0 / ng, self.losses, L_GW)
         o.fill_segments(cpl['dd'].view(-1), M, 0.0, M, 0.0, M, 1.0)
         rows = slice(2 * B, 3 * B)
-        self.C.backward_to_input(cpl, bf['g'], g_rows=rows, ctx_grads_apps=2)
+        self.C.backward_to_input(cpl, bf['g'], g_rows=rows)       # no parameter gradients in a validation pass
         o.gp_norms(bf['g'].view(B, T * S), bf['ss'])
         o.gp_scale(bf['g'].view(B, T * S), bf['ss'], bf['s0'][rows].view(B, T * S), self.lam, B, self.losses, L_GP)
         o.loss_combine(self.losses, L_CRITIC, L_REAL, 1.0, L_FAKE, 1.0, L_GP, self.lam)
