@@ -269,15 +269,38 @@ def kernel_rooflines(st, ops, B, T, device, peak_tf, peak_hbm, critic_ms, gen_ms
                         'share_of_critic_step': t / critic_ms, 'layers_per_launch': L, 'us_per_layer': 1e3 * t / L,
                         'algorithmic': 'input map (1 ch) read + %d output maps (4 ch) written once: (1 + 4 x %d) x 3B x T x %d x 4 B; tiles stay in shared memory between layers' % (L, L, S)})
             rows = slice(2 * B, 3 * B)
+            limiter = ('tcgen05 operand reads from shared memory in the block-Toeplitz form: ~52 cycles per 128x(48|32|16)x16 MMA, 390 MMAs '
+                       'per layer and CTA + ~5 k cycles of halo hand-over per layer (clock trace: profiles/r02_b_chain_trace.txt)')
+            out[-1]['limiter'] = limiter
             dg_layers = [dict(w=cp['c.spec.cnn%d.kernel' % i], flip=True, aux=cpl['a'][i - 1][rows], y=cpl['da'][i - 1][rows]) for i in range(L - 1, 0, -1)]
             dg_layers.append(dict(w=cp['c.spec.cnn0.kernel'], flip=True, y=bf['g']))
             t = timed(lambda: ops.conv2d_chain(cpl['da'][L - 1][rows], dg_layers))
             nb = px * (4 + 8 * (L - 1) + 1)
-            out.append({'name': 'conv2d_chain_dgrad_B', 'kernel': 'conv2d_chain_kernel<3>: data-gradient chain (%d layers 4->4 with LeakyReLU\' masks + 4->1 input gradient) on [B,T,%d,.]' % (L - 1, S),
+            out.append({'name': 'conv2d_chain_dgrad_B', 'kernel': 'conv2d_chain_kernel<3>: data-gradient chain of the interpolated rows (%d layers 4->4 with LeakyReLU\' masks + 4->1 input gradient) on [B,T,%d,.], six products' % (L - 1, S),
                         'bound': 'hbm', 'achieved': nb / (t * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s', 'frac': nb / (t * 1e-3) / 1e9 / peak_hbm,
-                        'kernel_ms': t, 'bytes_per_launch': nb, 'traffic': None, 'launches_per_critic_step': 2,
-                        'share_of_critic_step': 3 * t / critic_ms, 'layers_per_launch': L, 'us_per_layer': 1e3 * t / L,
-                        'algorithmic': 'top gradient map + %d mask maps read, %d gradient maps + the 1-ch input gradient written (the second launch per step covers 2B samples on the side lane)' % (L - 1, L - 1)})
+                        'kernel_ms': t, 'bytes_per_launch': nb, 'traffic': None, 'launches_per_critic_step': 1,
+                        'share_of_critic_step': t / critic_ms, 'layers_per_launch': L, 'us_per_layer': 1e3 * t / L, 'limiter': limiter,
+                        'algorithmic': 'top gradient map + %d mask maps read, %d gradient maps + the 1-ch input gradient written' % (L - 1, L - 1)})
+            # the first-order applications' data-gradient chain [2B] and the tangent sweep [B]: gradient-pass precision (three products)
+            r2 = slice(0, 2 * B)
+            dg2 = [dict(w=cp['c.spec.cnn%d.kernel' % i], flip=True, aux=cpl['a'][i - 1][r2], y=cpl['da'][i - 1][r2]) for i in range(L - 1, 0, -1)]
+            tg = [dict(w=cp['c.spec.cnn%d.kernel' % i], aux=cpl['a'][i][rows], y=cpl['a'][i][rows]) for i in range(L)]
+            with ops.backward_terms():
+                t2 = timed(lambda: ops.conv2d_chain(cpl['da'][L - 1][r2], dg2))
+                t3 = timed(lambda: ops.conv2d_chain(s0[rows], tg))
+            nb2, nb3 = 2 * px * (4 + 8 * (L - 1)), px * (1 + 8 * L)
+            parts_b = {6: 3, 3: 2, 1: 1}.get(ops.bwd_nterms, 0)
+            out.append({'name': 'conv2d_chain_dgrad_2B', 'kernel': 'conv2d_chain_kernel<%d>: data-gradient chain of the real + fake rows on [2B,T,%d,4], side lane' % (parts_b, S),
+                        'bound': 'hbm', 'achieved': nb2 / (t2 * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s', 'frac': nb2 / (t2 * 1e-3) / 1e9 / peak_hbm,
+                        'kernel_ms': t2, 'bytes_per_launch': nb2, 'traffic': None, 'launches_per_critic_step': 1, 'share_of_critic_step': t2 / critic_ms,
+                        'algorithmic': 'top gradient map + %d mask maps read, %d gradient maps written, 2B samples' % (L - 1, L - 1)})
+            out.append({'name': 'conv2d_chain_tangent_B', 'kernel': 'conv2d_chain_kernel<%d>: forward-mode sweep of the gradient penalty, in place over the stored activations of the interpolated rows' % parts_b,
+                        'bound': 'hbm', 'achieved': nb3 / (t3 * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s', 'frac': nb3 / (t3 * 1e-3) / 1e9 / peak_hbm,
+                        'kernel_ms': t3, 'bytes_per_launch': nb3, 'traffic': None, 'launches_per_critic_step': 1, 'share_of_critic_step': t3 / critic_ms,
+                        'algorithmic': 'seed map (1 ch) + %d activation maps read (masks), %d tangent maps written over them' % (L, L)})
+            fam = [r for r in out if r['name'].startswith('conv2d_chain')]
+            for r in fam:
+                r['family_share_of_critic_step'] = sum(q['share_of_critic_step'] for q in fam)
         # -- one 4->4 layer on a B-sized map (the generator's stack: BatchNorm between the layers, one launch per layer)
         x1, y1 = gpl['cv_a'][1], gpl['cv_z'][2]
         t = timed(lambda: ops.conv2d(x1, gp['g.spec.cnn2.kernel'], y1))
@@ -287,16 +310,24 @@ def kernel_rooflines(st, ops, B, T, device, peak_tf, peak_hbm, critic_ms, gen_ms
                     'kernel_ms': t, 'bytes_per_launch': nb1, 'traffic': None, 'launches_per_critic_step': (L - 1) if st.C._chain(T) else 3 * (L - 1),
                     'share_of_critic_step': t * ((L - 1) if st.C._chain(T) else 3 * (L - 1)) / critic_ms,
                     'algorithmic': 'one fp32 map read + one written: 2 x B x T x %d x 4 ch x 4 B' % S})
-        # -- Conv2D 4->4 weight gradient over the first-order applications [2B,T,S,4]
-        xa, da = cpl['a'][1][:2 * B], cpl['da'][2][:2 * B]
-        gk, gb = st.C.params.g['c.spec.cnn2.kernel'], st.C.params.g['c.spec.cnn2.bias']
-        t = timed(lambda: ops.conv2d_wgrad(xa, da, gk, dbias=gb))
-        nbw = 2.0 * xa.numel() * 4
-        out.append({'name': 'conv2d_wgrad_4to4_2B', 'kernel': 'Conv2D 4->4 weight (+ bias) gradient on [2B,T,%d,4]' % S, 'bound': 'hbm',
-                    'achieved': nbw / (t * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s', 'frac': nbw / (t * 1e-3) / 1e9 / peak_hbm,
-                    'kernel_ms': t, 'bytes_per_launch': nbw, 'traffic': None, 'launches_per_critic_step': L - 1,
-                    'share_of_critic_step': t * 1.5 * (L - 1) / critic_ms,
-                    'algorithmic': 'activation map + gradient map read once: 2 x 2B x T x %d x 4 ch x 4 B (the B tangent rows are a second launch of half the size)' % S})
+        # -- weight + bias gradients of the critic's whole Conv2D stack in ONE launch (conv2d_wgrad44.cu): [2B] first-order rows on the
+        #    side lane, [B] tangent rows accumulated on the main lane.  50 flop per byte read: bound by the fp32 FMA pipe, not by HBM
+        #    (both fractions are given; `bound` keeps the contract's vocabulary)
+        fma_peak = 148 * 128 * 1.965e9
+        for tag, rws, nsm, first in (('2B', slice(0, 2 * B), 2 * B, True), ('B', slice(2 * B, 3 * B), B, False)):
+            lay = [dict(x=(cpl['a'][i - 1] if i > 0 else bf['s0'].view(3 * B, T, S, 1))[rws], dy=cpl['da'][i][rws], dw=st.C.params.g['c.spec.cnn%d.kernel' % i],
+                        dbias=st.C.params.g['c.spec.cnn%d.bias' % i] if first else None) for i in range(L)]
+            if not ops.conv2d_wgrad_multi_ok(lay):
+                continue
+            t = timed(lambda: ops.conv2d_wgrad_multi(lay, accumulate=not first))
+            nbw = nsm * T * S * 4.0 * (1 + 4 + (L - 1) * 8)
+            fma = nsm * T * S * 400.0 * L
+            out.append({'name': 'conv2d_wgrad_stack_%s' % tag, 'kernel': 'conv2d_wgrad44_kernel: weight (+ bias) gradients of all %d Conv2D layers on [%s,T,%d,.] in one launch' % (L, tag, S),
+                        'bound': 'hbm', 'achieved': nbw / (t * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s', 'frac': nbw / (t * 1e-3) / 1e9 / peak_hbm,
+                        'kernel_ms': t, 'bytes_per_launch': nbw, 'traffic': None, 'launches_per_critic_step': 1, 'share_of_critic_step': t / critic_ms,
+                        'fma_per_launch': fma, 'fma_frac_of_fp32_peak': fma / (t * 1e-3) / fma_peak,
+                        'limiter': 'fp32 FMA pipe (CUDA cores): 400 FMA per pixel and layer against 32 bytes read; peak = 148 SMs x 128 FMA/clk x 1.965 GHz',
+                        'algorithmic': 'every layer input map + every gradient map read once (1-ch input of the first layer)'})
         # -- Conv1D k=21 425->256 forward: virtual-im2col tcgen05 GEMM -- tensor bound
         kern, xp, z = gp['g.ctx.cnn0.kernel'], gpl['ctx_xp'][0], gpl['ctx_z'][0]
         t = timed(lambda: ops.conv1d(xp, kern, z, T), iters=20)
@@ -313,11 +344,14 @@ def kernel_rooflines(st, ops, B, T, device, peak_tf, peak_hbm, critic_ms, gen_ms
         dz = gpl['dB']
         gkern = st.G.params.g['g.ctx.cnn0.kernel']
         t = timed(lambda: ops.conv1d_wgrad(xp, dz, gkern, T))
+        with ops.backward_terms():      # the critic's ctx-branch weight gradient runs at the gradient-pass precision
+            t_b = timed(lambda: ops.conv1d_wgrad(xp, dz, gkern, T))
         ach = fl / (t * 1e-3) / 1e12
         out.append({'name': 'conv1d_wgrad', 'kernel': 'gemm_tc_kernel<128,PARTS> tail-split (Conv1D weight gradient, M=%d N=%d K=%d)' % (W * a.ctxsize, H, B * T),
                     'bound': 'tensor', 'achieved': ach, 'peak': peak_tf, 'unit': 'TFLOP/s', 'frac': ach / peak_tf, 'kernel_ms': t,
                     'flop_per_launch': fl, 'traffic': None, 'tensor_pipe_frac': products * ach / peak_tf, 'launches_per_critic_step': 1,
-                    'share_of_critic_step': t / critic_ms})
+                    'kernel_ms_gradient_pass_precision': t_b, 'gradient_pass_products': max(ops.bwd_nterms, 1),
+                    'share_of_critic_step': t_b / critic_ms})
     del flush
     return out
 

@@ -255,3 +255,152 @@ extern "C" int pctts_bn_sync_bwd(const double* partial, double* sums, int nblk, 
     a.rank = rank, a.world = world, a.err = err;
     return bn_sync_launch(a, peer_bases, (cudaStream_t)stream);
 }
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// Gradient all-reduce FUSED with the Adam update ("gradients are reduced after each critic and generator step").
+//
+// The flat fp32 gradient buffer of a network lives in symmetric memory (mapped into every peer over NVLink).  One launch per
+// network and step does a two-shot all-reduce and the optimiser update:
+//   1. ready barrier    every rank raises its flag in every peer (its local gradients are complete: stream order);
+//   2. reduce-scatter   rank r sums slice r of all the ranks' buffers in RANK ORDER (16-byte peer loads) ...
+//   3. all-gather       ... and writes the sum back into slice r of every rank's buffer (16-byte peer stores), in place: slice r is
+//                       touched by nobody else;
+//   4. done barrier     last CTA of the grid raises the rank's second flag in every peer; everybody waits for all of them;
+//   5. Adam             over the whole (now identical on every rank) gradient, Keras form as in adam_kernel (elementwise.cu),
+//                       step counter advanced by the last CTA.
+// No NCCL launch, no separate Adam launch; flags carry a sequence number that lives in device memory, so the launch is
+// capturable and replays stay in lock step.  Control block per rank (symmetric, zeroed once):
+//   [0] seq u64 | [8] cnt1 u32 | [12] cnt2 u32 | [64] ready u64[16] | [192] done u64[16]
+namespace {
+
+constexpr int GS_THREADS = 512;
+constexpr long GS_READY = 64, GS_DONE = 192, GS_BYTES = 512;
+
+struct GradSyncArgs {
+    uint64_t grad[PEER_MAX_WORLD];
+    uint64_t ctl[PEER_MAX_WORLD];
+    float *p, *m, *v;
+    int* step;
+    long n, n4;            // parameters; float4 vectors of the (zero-padded) gradient buffer
+    float lr, b1, b2, eps;
+    int rank, world;
+    int* err;
+};
+
+__device__ __forceinline__ float4 ld_relaxed_sys_v4(const float4* p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_sys_v4(float4* p, const float4& v) {
+    asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+__device__ __forceinline__ void gs_wait(const uint64_t* flag, uint64_t seq, int* err) {
+    const long long t0 = clock64();
+    while (ld_acquire_sys(flag) < seq) {
+        if (clock64() - t0 > PEER_SPIN_LIMIT) {
+            *err = 1;
+            break;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(GS_THREADS) grad_sync_adam_kernel(const GradSyncArgs a) {
+    pdl_entry();
+    __shared__ uint64_t s_seq;
+    __shared__ float s_lr;
+    __shared__ int s_last;
+    const int tid = threadIdx.x, W = a.world, R = a.rank;
+    uint8_t* const ctl = reinterpret_cast<uint8_t*>(a.ctl[R]);
+    if (tid == 0) {
+        s_seq = *reinterpret_cast<volatile uint64_t*>(ctl) + 1;
+        const double t = (double)(*a.step + 1);
+        s_lr = (float)((double)a.lr * sqrt(1.0 - pow((double)a.b2, t)) / (1.0 - pow((double)a.b1, t)));
+    }
+    __syncthreads();
+    const uint64_t seq = s_seq;
+    if (W > 1) {
+        // 1. ready: the local gradients were written by earlier launches of this stream
+        if (blockIdx.x == 0 && tid < W) st_release_sys(reinterpret_cast<uint64_t*>(a.ctl[tid] + GS_READY) + R, seq);
+        if (tid < W) gs_wait(reinterpret_cast<const uint64_t*>(ctl + GS_READY) + tid, seq, a.err);
+        __syncthreads();
+        // 2 + 3. slice R: rank-ordered sum of every rank's values, written back to every rank
+        const long lo = a.n4 * R / W, hi = a.n4 * (R + 1) / W;
+        for (long i = lo + (long)blockIdx.x * GS_THREADS + tid; i < hi; i += (long)gridDim.x * GS_THREADS) {
+            float4 s = ld_relaxed_sys_v4(reinterpret_cast<const float4*>(a.grad[0]) + i);
+            for (int q = 1; q < W; ++q) {
+                const float4 g = ld_relaxed_sys_v4(reinterpret_cast<const float4*>(a.grad[q]) + i);
+                s.x += g.x, s.y += g.y, s.z += g.z, s.w += g.w;
+            }
+            for (int q = 0; q < W; ++q) st_relaxed_sys_v4(reinterpret_cast<float4*>(a.grad[q]) + i, s);
+        }
+        __threadfence_system();
+        __syncthreads();
+        // 4. done: the last CTA of this rank tells every peer; then wait for every peer's slice
+        if (tid == 0) {
+            const unsigned old = atomicAdd(reinterpret_cast<unsigned*>(ctl + 8), 1u);
+            s_last = (old == gridDim.x - 1);
+        }
+        __syncthreads();
+        if (s_last) {
+            __threadfence_system();
+            if (tid < W) st_release_sys(reinterpret_cast<uint64_t*>(a.ctl[tid] + GS_DONE) + R, seq);
+            if (tid == 0) *reinterpret_cast<volatile unsigned*>(ctl + 8) = 0u;
+        }
+        if (tid < W) gs_wait(reinterpret_cast<const uint64_t*>(ctl + GS_DONE) + tid, seq, a.err);
+        __syncthreads();
+    }
+    // 5. Adam (Keras 2.2 form, see adam_kernel) on the summed gradient; the sums were stored by peers: read at L2
+    const float lr_t = s_lr;
+    const float* g = reinterpret_cast<const float*>(a.grad[R]);
+    for (long i = (long)blockIdx.x * GS_THREADS + tid; i < a.n; i += (long)gridDim.x * GS_THREADS) {
+        const float gi = __ldcg(g + i);
+        const float mi = a.b1 * a.m[i] + (1.f - a.b1) * gi;
+        const float vi = a.b2 * a.v[i] + (1.f - a.b2) * gi * gi;
+        a.m[i] = mi;
+        a.v[i] = vi;
+        a.p[i] -= lr_t * mi / (sqrtf(vi) + a.eps);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        const unsigned old = atomicAdd(reinterpret_cast<unsigned*>(ctl + 12), 1u);
+        if (old == gridDim.x - 1) {
+            *reinterpret_cast<volatile unsigned*>(ctl + 12) = 0u;
+            *reinterpret_cast<volatile uint64_t*>(ctl) = seq;
+            *a.step += 1;
+        }
+    }
+}
+
+}  // namespace
+
+/* bytes of the symmetric control block of pctts_grad_sync_adam (zeroed once, then a barrier, before the first call) */
+extern "C" long pctts_grad_sync_ctl_bytes(void) { return GS_BYTES; }
+
+/* In place: grad (this rank's flat fp32 gradient buffer in symmetric memory, npad floats, npad % 4 == 0, zero padded beyond n)
+ * <- sum over the ranks in rank order, then the Keras Adam update of p / m / v [n] with it and *step += 1 -- one launch.
+ * grad_bases / ctl_bases: HOST arrays of `world` addresses (the buffers of rank r as mapped into this process).  world == 1:
+ * plain Adam.  err: device int set to 1 if a peer did not show up. */
+extern "C" int pctts_grad_sync_adam(const unsigned long long* grad_bases, const unsigned long long* ctl_bases, int rank, int world,
+                                    float* p, float* m, float* v, long n, long npad, float lr, float beta1, float beta2, float eps,
+                                    int* step, int* err, void* stream) {
+    if (!grad_bases || !ctl_bases || !p || !m || !v || !step || !err || world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world ||
+        n < 0 || npad < n || (npad & 3))
+        return PCTTS_EINVAL;
+    GradSyncArgs a;
+    for (int r = 0; r < PEER_MAX_WORLD; ++r) {
+        a.grad[r] = r < world ? grad_bases[r] : 0;
+        a.ctl[r] = r < world ? ctl_bases[r] : 0;
+        if (r < world && ((a.grad[r] & 15) || (a.ctl[r] & 15))) return PCTTS_EINVAL;
+    }
+    a.p = p, a.m = m, a.v = v, a.step = step, a.n = n, a.n4 = npad / 4;
+    a.lr = lr, a.b1 = beta1, a.b2 = beta2, a.eps = eps, a.rank = rank, a.world = world, a.err = err;
+    // every CTA spins on peers' flags: the grid must be resident as a whole (one CTA per SM at most)
+    long want = (n + GS_THREADS * 8 - 1) / (GS_THREADS * 8);
+    int grid = (int)(want < 1 ? 1 : (want > 132 ? 132 : want));
+    pctts_launch(grad_sync_adam_kernel, grid, GS_THREADS, 0, (cudaStream_t)stream, a);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}

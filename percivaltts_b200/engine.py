@@ -25,6 +25,9 @@ class LocalSync(object):
     def allreduce(self, t):
         return t
 
+    def grad_adam(self, store, lr, beta1, beta2, eps):
+        store.adam(lr, beta1, beta2, eps)
+
 
 class ParamStore(object):
     """Flat fp32 buffers (parameters, gradients, Adam slots) with named views; non-trainable BN moving
@@ -54,6 +57,18 @@ class ParamStore(object):
             else:
                 self.p[name] = self.state[os_:os_ + n].view(*shape)
                 os_ += n
+
+    def use_grad_buffer(self, buf):
+        """Re-home the flat gradient buffer (data parallel: into NVLink symmetric memory, parallel.DistSync.enable_grad_sync) and
+        rebuild the named views.  Before any plan or CUDA graph has captured the old addresses."""
+        assert buf.dtype == self.grad.dtype and buf.numel() >= max(self.ntrain, 1) and buf.is_contiguous()
+        self.grad = buf[:max(self.ntrain, 1)]
+        ot = 0
+        for name, shape, trainable in self.shapes:
+            n = int(np.prod(shape))
+            if trainable:
+                self.g[name] = self.grad[ot:ot + n].view(*shape)
+                ot += n
 
     def count_params(self):
         return self.ntrain + self.nstate

@@ -31,6 +31,9 @@ class DistSync(object):
         self._peer = None
         self._bn = None            # (bases, err) of the sliced sync-BatchNorm protocol (second symmetric buffer)
         self._bn2 = None           # the same for the exchanges issued on the step's second side lane
+        self._gs = {}              # id(ParamStore) -> (grad bases, npad): flat gradient buffers in symmetric memory
+        self._gs_ctl = None        # control blocks of the fused all-reduce + Adam launch
+        self.fused_adam_calls = 0
         self.peer_error = None
 
     def allreduce(self, t):
@@ -103,6 +106,66 @@ class DistSync(object):
             self._bn = bn
             self._bn2 = bn2
         return True
+
+    def enable_grad_sync(self, stores, device):
+        """Move the flat gradient buffers of `stores` (engine.ParamStore) into symmetric memory so that the gradient all-reduce and
+        the Adam update run as ONE launch over NVLink peer memory (csrc/peer.cu: pctts_grad_sync_adam) instead of an NCCL
+        all-reduce followed by adam_kernel.  Collective; needs enable_peer() to have succeeded.  Returns False (NCCL + Adam stay)
+        when the platform cannot or PCTTS_FUSED_ADAM=0."""
+        if self.world < 2 or self._peer is None or getattr(device, 'type', 'cpu') != 'cuda' or os.environ.get('PCTTS_FUSED_ADAM', '1') == '0':
+            return False
+        ok = torch.zeros(1, device=device)
+        made = None
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            lib = self._peer[0]
+            group = self.group if self.group is not None else dist.group.WORLD
+            keep, table = [], {}
+            for st in stores:
+                npad = max((st.ntrain + 3) // 4 * 4, 4)
+                buf = symm_mem.empty(npad, dtype=torch.float32, device=device)
+                hdl = symm_mem.rendezvous(buf, group.group_name)
+                buf.zero_()
+                keep.append((buf, hdl))
+                table[id(st)] = ((ctypes.c_ulonglong * self.world)(*[int(p) for p in hdl.buffer_ptrs]), npad, buf)
+            nctl = int(lib.pctts_grad_sync_ctl_bytes())
+            ctl = symm_mem.empty((nctl + 7) // 8, dtype=torch.float64, device=device)
+            hctl = symm_mem.rendezvous(ctl, group.group_name)
+            ctl.zero_()
+            keep.append((ctl, hctl))
+            made = (table, (ctypes.c_ulonglong * self.world)(*[int(p) for p in hctl.buffer_ptrs]), keep)
+            ok.fill_(1.0)
+        except Exception as e:      # noqa: BLE001 -- any failure here means "NCCL + separate Adam"
+            self.peer_error = repr(e)
+        torch.cuda.synchronize(device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)      # all ranks or none (also the barrier after zeroing)
+        if float(ok) < 1.0:
+            return False
+        table, ctl_bases, keep = made
+        for st in stores:
+            st.use_grad_buffer(table[id(st)][2])
+        self._gs, self._gs_ctl, self._gs_keep = table, ctl_bases, keep
+        return True
+
+    def grad_adam(self, store, lr, beta1, beta2, eps):
+        """All-reduce(sum) of store.grad over the replicas followed by store's Adam update: one fused launch over peer memory where
+        enable_grad_sync() set it up, NCCL all-reduce + adam_kernel otherwise."""
+        ent = self._gs.get(id(store))
+        if ent is None or store.ntrain == 0:
+            self.allreduce(store.grad)
+            store.adam(lr, beta1, beta2, eps)
+            return
+        bases, npad, _ = ent
+        lib, _, err = self._peer
+        n = store.ntrain
+        _lib.check(lib.pctts_grad_sync_adam(ctypes.cast(bases, ctypes.c_void_p), ctypes.cast(self._gs_ctl, ctypes.c_void_p), self.rank,
+                                            self.world, store.flat.data_ptr(), store.m.data_ptr(), store.v.data_ptr(), n, npad,
+                                            float(lr), float(beta1), float(beta2), float(eps), store.step.data_ptr(), err.data_ptr(),
+                                            torch.cuda.current_stream(store.flat.device).cuda_stream), 'pctts_grad_sync_adam')
+        store.ops.launches += 1
+        self.fused_adam_calls += 1
+        self.calls += 1
+        store.ops.refresh_persistent(store.flat)
 
     def broadcast_scalar(self, x, src=0):
         """The python float of rank `src` on every rank (model-selection decisions must agree across the replicas)."""

@@ -39,6 +39,8 @@ class WGANStepper(object):
         self.sync = sync or LocalSync()
         self.G = generator or Generator(ops, arch)
         self.C = critic or Critic(ops, arch)
+        if hasattr(self.sync, 'enable_grad_sync'):      # replicas: flat gradient buffers into NVLink symmetric memory (collective)
+            self.sync.enable_grad_sync([self.G.params, self.C.params], ops.device)
         self.copt = (critic_lr, critic_beta1, critic_beta2)
         self.gopt = (gen_lr, gen_beta1, gen_beta2)
         self.adam_eps = adam_eps
@@ -129,9 +131,8 @@ class WGANStepper(object):
         o.loss_combine(self.losses, L_CRITIC, L_REAL, 1.0, L_FAKE, 1.0, L_GP, self.lam)   # loss_weights [1,1,lambda] (:150)
         if sync.world > 1:
             sync.allreduce(self.losses[L_REAL:L_CRITIC + 1])       # local shares -> global means (logging only)
-        if apply:
-            sync.allreduce(self.C.params.grad)
-            self.C.params.adam(*self.copt, eps=self.adam_eps)
+        if apply:       # gradient all-reduce over the replicas + Adam (one fused peer-memory launch where available)
+            sync.grad_adam(self.C.params, *self.copt, eps=self.adam_eps)
 
     def generator_step(self, X, *args, **kw):
         return self._scoped(self._generator_step, X, *args, **kw)
@@ -168,8 +169,7 @@ class WGANStepper(object):
         if sync.world > 1:
             sync.allreduce(self.losses[L_GW:L_GEN + 1])
         if apply:
-            sync.allreduce(self.G.params.grad)
-            self.G.params.adam(*self.gopt, eps=self.adam_eps)
+            sync.grad_adam(self.G.params, *self.gopt, eps=self.adam_eps)
 
     def evaluate_losses(self, X, *args, **kw):
         return self._scoped(self._evaluate_losses, X, *args, **kw)

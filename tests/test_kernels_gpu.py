@@ -238,6 +238,32 @@ def test_split_bf16_multi_matches_single_splits():
         assert torch.equal(a.buf, b.buf)
 
 
+def test_grad_sync_adam_single_rank_equals_adam_kernel(cuda_ops):
+    """pctts_grad_sync_adam with world = 1 (no exchange): the fused launch's optimiser half is bit-identical to pctts_adam, the step
+    counter and the control block's sequence number advance per call (the multi-rank half runs in tests/test_dp_gpu.py)."""
+    import ctypes
+    n = 100003
+    npad = (n + 3) // 4 * 4
+    g = torch.Generator(device='cuda').manual_seed(3)
+    grad = torch.zeros(npad, device='cuda')
+    p = torch.randn(n, device='cuda', generator=g)
+    m, v = torch.zeros(n, device='cuda'), torch.zeros(n, device='cuda')
+    step = torch.zeros(1, dtype=torch.int32, device='cuda')
+    p2, m2, v2, step2 = p.clone(), m.clone(), v.clone(), step.clone()
+    ctl = torch.zeros(int(cuda_ops.lib.pctts_grad_sync_ctl_bytes()) // 8, dtype=torch.int64, device='cuda')
+    err = torch.zeros(1, dtype=torch.int32, device='cuda')
+    gb, cb = (ctypes.c_ulonglong * 1)(grad.data_ptr()), (ctypes.c_ulonglong * 1)(ctl.data_ptr())
+    for it in range(3):
+        grad[:n].copy_(torch.randn(n, device='cuda', generator=g) * 0.1)
+        cuda_ops.adam(p2, grad[:n], m2, v2, 1e-3, 0.5, 0.9, 1e-7, step2)
+        OPS._lib.check(cuda_ops.lib.pctts_grad_sync_adam(ctypes.cast(gb, ctypes.c_void_p), ctypes.cast(cb, ctypes.c_void_p), 0, 1,
+                                                         p.data_ptr(), m.data_ptr(), v.data_ptr(), n, npad, 1e-3, 0.5, 0.9, 1e-7,
+                                                         step.data_ptr(), err.data_ptr(), cuda_ops._stream()), 'grad_sync_adam')
+    torch.cuda.synchronize()
+    assert torch.equal(p, p2) and torch.equal(m, m2) and torch.equal(v, v2)
+    assert int(step) == int(step2) == 3 and int(ctl[0]) == 3 and int(err) == 0
+
+
 def test_conv2d_strided_feature_views(cuda_ops):
     """First critic layer reads / last generator layer writes the spectral columns of a [B,T,O] tensor in place."""
     B, T, S, O = 2, 21, 17, 23

@@ -93,6 +93,36 @@ def main():
         print('rank %d: peer all-reduce soak (200 graph replays x %d exchanges) %s, err flag %d'
               % (rank, len(sizes), 'ok' if soak_ok else 'FAILED', int(sync.peer_err)), flush=True)
     ok = ok and soak_ok
+    # fused gradient all-reduce + Adam over peer memory (csrc/peer.cu) against NCCL all-reduce + adam_kernel on copies
+    fused_ok = True
+    if world > 1 and sync._gs:
+        for store in (st.C.params, st.G.params):
+            n = store.ntrain
+            gen = torch.Generator(device=device).manual_seed(100 + rank)
+            store.grad.copy_(torch.randn(n, device=device, generator=gen) * 0.01)
+            want_g = store.grad.clone()
+            dist.all_reduce(want_g)
+            p0, m0, v0, s0 = store.flat.clone(), store.m.clone(), store.v.clone(), store.step.clone()
+            ops.adam(p0[:n], want_g, m0[:n], v0[:n], 1e-3, 0.5, 0.9, 1e-7, s0)
+            before = sync.fused_adam_calls
+            for rep in range(3):          # replays: sequence numbers / flags advance
+                if rep:
+                    store.grad.copy_(torch.randn(n, device=device, generator=gen) * 0.01)
+                    want_g = store.grad.clone()
+                    dist.all_reduce(want_g)
+                    ops.adam(p0[:n], want_g, m0[:n], v0[:n], 1e-3, 0.5, 0.9, 1e-7, s0)
+                sync.grad_adam(store, 1e-3, 0.5, 0.9, 1e-7)
+            torch.cuda.synchronize()
+            err_p = float((store.flat[:n] - p0[:n]).abs().max() / (p0[:n].abs().max() + 1e-30))
+            err_g = float((store.grad - want_g).abs().max() / (want_g.abs().max() + 1e-30))
+            good = (sync.fused_adam_calls == before + 3 and err_p < 1e-6 and err_g < 1e-6 and int(store.step) == int(s0)
+                    and not sync.peer_failed())
+            fused_ok = fused_ok and good
+            print('rank %d: fused all-reduce + Adam (%d params, 3 calls): rel err params %.1e, summed gradient %.1e, step %d/%d %s'
+                  % (rank, n, err_p, err_g, int(store.step), int(s0), 'ok' if good else 'FAILED'), flush=True)
+    elif world > 1:
+        print('rank %d: fused all-reduce + Adam not set up (%s)' % (rank, sync.peer_error), flush=True)
+    ok = ok and fused_ok
     flat = torch.cat([st.C.params.flat, st.G.params.flat, st.G.params.state])
     ref = flat.clone()
     if world > 1:
