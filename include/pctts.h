@@ -283,12 +283,12 @@ int pctts_bn_sync_bwd(const double* partial, double* sums, int nblk, int C, floa
 
 /* Gradient all-reduce fused with the Adam update (peer.cu): the flat gradient buffer of a network lives in symmetric memory; one
  * launch = ready barrier, rank-ordered reduce-scatter over peer loads, all-gather over peer stores (in place), done barrier, Keras
- * Adam on the summed gradient, *step += 1.  grad_bases / ctl_bases: HOST arrays of `world` mapped addresses (gradient buffers of
+ * Adam on the summed gradient, *step += 1; losses [nloss <= 8] (or NULL) are summed over the ranks on the way.  grad_bases / ctl_bases: HOST arrays of `world` mapped addresses (gradient buffers of
  * npad floats, npad % 4 == 0, zero beyond n; control blocks of pctts_grad_sync_ctl_bytes() bytes, zeroed once).  world == 1: Adam only. */
 long pctts_grad_sync_ctl_bytes(void);
 int pctts_grad_sync_adam(const unsigned long long* grad_bases, const unsigned long long* ctl_bases, int rank, int world, float* p,
-                         float* m, float* v, long n, long npad, float lr, float beta1, float beta2, float eps, int* step, int* err,
-                         void* stream);
+                         float* m, float* v, long n, long npad, float lr, float beta1, float beta2, float eps, int* step,
+                         float* losses, int nloss, int* err, void* stream);
 
 #ifdef __cplusplus
 }

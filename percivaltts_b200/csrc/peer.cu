@@ -270,11 +270,14 @@ extern "C" int pctts_bn_sync_bwd(const double* partial, double* sums, int nblk, 
 //                       step counter advanced by the last CTA.
 // No NCCL launch, no separate Adam launch; flags carry a sequence number that lives in device memory, so the launch is
 // capturable and replays stay in lock step.  Control block per rank (symmetric, zeroed once):
-//   [0] seq u64 | [8] cnt1 u32 | [12] cnt2 u32 | [64] ready u64[16] | [192] done u64[16]
+//   [0] seq u64 | [8] cnt1 u32 | [12] cnt2 u32 | [64] ready u64[16] | [192] done u64[16] | [320] loss f32 [2][GS_NLOSS]
+// The step's loss scalars (local shares of the global means, logging only) ride on the ready barrier: published in the control
+// block in front of the flag, summed in rank order behind it -- no separate small all-reduce.
 namespace {
 
-constexpr int GS_THREADS = 512;
-constexpr long GS_READY = 64, GS_DONE = 192, GS_BYTES = 512;
+constexpr int GS_THREADS = 256;      // 2 x 16 peer vectors in flight per thread: registers, not threads, carry the NVLink latency
+constexpr int GS_NLOSS = 8;
+constexpr long GS_READY = 64, GS_DONE = 192, GS_LOSS = 320, GS_BYTES = 512;
 
 struct GradSyncArgs {
     uint64_t grad[PEER_MAX_WORLD];
@@ -285,7 +288,14 @@ struct GradSyncArgs {
     float lr, b1, b2, eps;
     int rank, world;
     int* err;
+    float* losses;         // nloss scalars summed over the ranks in place (or NULL)
+    int nloss;
 };
+__device__ __forceinline__ float ld_relaxed_sys_f32(const float* p) {
+    float v;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
 
 __device__ __forceinline__ float4 ld_relaxed_sys_v4(const float4* p) {
     float4 v;
@@ -321,19 +331,48 @@ __global__ void __launch_bounds__(GS_THREADS) grad_sync_adam_kernel(const GradSy
     __syncthreads();
     const uint64_t seq = s_seq;
     if (W > 1) {
-        // 1. ready: the local gradients were written by earlier launches of this stream
-        if (blockIdx.x == 0 && tid < W) st_release_sys(reinterpret_cast<uint64_t*>(a.ctl[tid] + GS_READY) + R, seq);
+        // 1. ready: the local gradients were written by earlier launches of this stream; CTA 0 also publishes the loss scalars
+        const int par = (int)(seq & 1);
+        if (blockIdx.x == 0) {
+            if (tid < a.nloss) reinterpret_cast<float*>(ctl + GS_LOSS)[par * GS_NLOSS + tid] = a.losses[tid];
+            __threadfence_system();
+            __syncthreads();
+            if (tid < W) st_release_sys(reinterpret_cast<uint64_t*>(a.ctl[tid] + GS_READY) + R, seq);
+        }
         if (tid < W) gs_wait(reinterpret_cast<const uint64_t*>(ctl + GS_READY) + tid, seq, a.err);
         __syncthreads();
+        if (blockIdx.x == 0 && tid < a.nloss) {
+            float s = 0.f;
+            for (int q = 0; q < W; ++q) s += ld_relaxed_sys_f32(reinterpret_cast<const float*>(a.ctl[q] + GS_LOSS) + par * GS_NLOSS + tid);
+            a.losses[tid] = s;
+        }
         // 2 + 3. slice R: rank-ordered sum of every rank's values, written back to every rank
         const long lo = a.n4 * R / W, hi = a.n4 * (R + 1) / W;
-        for (long i = lo + (long)blockIdx.x * GS_THREADS + tid; i < hi; i += (long)gridDim.x * GS_THREADS) {
-            float4 s = ld_relaxed_sys_v4(reinterpret_cast<const float4*>(a.grad[0]) + i);
-            for (int q = 1; q < W; ++q) {
-                const float4 g = ld_relaxed_sys_v4(reinterpret_cast<const float4*>(a.grad[q]) + i);
-                s.x += g.x, s.y += g.y, s.z += g.z, s.w += g.w;
-            }
-            for (int q = 0; q < W; ++q) st_relaxed_sys_v4(reinterpret_cast<float4*>(a.grad[q]) + i, s);
+        // (two vectors per thread and trip: the peer loads of both are in flight together -- the loop runs at NVLink latency)
+        const long stride = (long)gridDim.x * GS_THREADS;
+        for (long i = lo + (long)blockIdx.x * GS_THREADS + tid; i < hi; i += 2 * stride) {
+            const long j = i + stride;
+            const bool two = j < hi;
+            float4 g0[PEER_MAX_WORLD], g1[PEER_MAX_WORLD];
+#pragma unroll
+            for (int q = 0; q < PEER_MAX_WORLD; ++q)
+                if (q < W) {
+                    g0[q] = ld_relaxed_sys_v4(reinterpret_cast<const float4*>(a.grad[q]) + i);
+                    if (two) g1[q] = ld_relaxed_sys_v4(reinterpret_cast<const float4*>(a.grad[q]) + j);
+                }
+            float4 s0 = g0[0], s1 = two ? g1[0] : g0[0];
+#pragma unroll
+            for (int q = 1; q < PEER_MAX_WORLD; ++q)
+                if (q < W) {
+                    s0.x += g0[q].x, s0.y += g0[q].y, s0.z += g0[q].z, s0.w += g0[q].w;
+                    if (two) s1.x += g1[q].x, s1.y += g1[q].y, s1.z += g1[q].z, s1.w += g1[q].w;
+                }
+#pragma unroll
+            for (int q = 0; q < PEER_MAX_WORLD; ++q)
+                if (q < W) {
+                    st_relaxed_sys_v4(reinterpret_cast<float4*>(a.grad[q]) + i, s0);
+                    if (two) st_relaxed_sys_v4(reinterpret_cast<float4*>(a.grad[q]) + j, s1);
+                }
         }
         __threadfence_system();
         __syncthreads();
@@ -354,7 +393,24 @@ __global__ void __launch_bounds__(GS_THREADS) grad_sync_adam_kernel(const GradSy
     // 5. Adam (Keras 2.2 form, see adam_kernel) on the summed gradient; the sums were stored by peers: read at L2
     const float lr_t = s_lr;
     const float* g = reinterpret_cast<const float*>(a.grad[R]);
-    for (long i = (long)blockIdx.x * GS_THREADS + tid; i < a.n; i += (long)gridDim.x * GS_THREADS) {
+    const bool vec = !((reinterpret_cast<uintptr_t>(a.p) | reinterpret_cast<uintptr_t>(a.m) | reinterpret_cast<uintptr_t>(a.v)) & 15);
+    const long nv = vec ? a.n / 4 : 0;
+    for (long i = (long)blockIdx.x * GS_THREADS + tid; i < nv; i += (long)gridDim.x * GS_THREADS) {
+        const float4 g4 = __ldcg(reinterpret_cast<const float4*>(g) + i);
+        float4 m4 = reinterpret_cast<float4*>(a.m)[i], v4 = reinterpret_cast<float4*>(a.v)[i], p4 = reinterpret_cast<float4*>(a.p)[i];
+        const float gg[4] = {g4.x, g4.y, g4.z, g4.w};
+        float mm[4] = {m4.x, m4.y, m4.z, m4.w}, vv[4] = {v4.x, v4.y, v4.z, v4.w}, pp[4] = {p4.x, p4.y, p4.z, p4.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            mm[k] = a.b1 * mm[k] + (1.f - a.b1) * gg[k];
+            vv[k] = a.b2 * vv[k] + (1.f - a.b2) * gg[k] * gg[k];
+            pp[k] -= lr_t * mm[k] / (sqrtf(vv[k]) + a.eps);
+        }
+        reinterpret_cast<float4*>(a.m)[i] = make_float4(mm[0], mm[1], mm[2], mm[3]);
+        reinterpret_cast<float4*>(a.v)[i] = make_float4(vv[0], vv[1], vv[2], vv[3]);
+        reinterpret_cast<float4*>(a.p)[i] = make_float4(pp[0], pp[1], pp[2], pp[3]);
+    }
+    for (long i = nv * 4 + (long)blockIdx.x * GS_THREADS + tid; i < a.n; i += (long)gridDim.x * GS_THREADS) {
         const float gi = __ldcg(g + i);
         const float mi = a.b1 * a.m[i] + (1.f - a.b1) * gi;
         const float vi = a.b2 * a.v[i] + (1.f - a.b2) * gi * gi;
@@ -382,12 +438,13 @@ extern "C" long pctts_grad_sync_ctl_bytes(void) { return GS_BYTES; }
 /* In place: grad (this rank's flat fp32 gradient buffer in symmetric memory, npad floats, npad % 4 == 0, zero padded beyond n)
  * <- sum over the ranks in rank order, then the Keras Adam update of p / m / v [n] with it and *step += 1 -- one launch.
  * grad_bases / ctl_bases: HOST arrays of `world` addresses (the buffers of rank r as mapped into this process).  world == 1:
- * plain Adam.  err: device int set to 1 if a peer did not show up. */
+ * plain Adam.  losses [nloss <= 8] (or NULL): scalars summed over the ranks in place on the way (the step's loss shares).
+ * err: device int set to 1 if a peer did not show up. */
 extern "C" int pctts_grad_sync_adam(const unsigned long long* grad_bases, const unsigned long long* ctl_bases, int rank, int world,
                                     float* p, float* m, float* v, long n, long npad, float lr, float beta1, float beta2, float eps,
-                                    int* step, int* err, void* stream) {
+                                    int* step, float* losses, int nloss, int* err, void* stream) {
     if (!grad_bases || !ctl_bases || !p || !m || !v || !step || !err || world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world ||
-        n < 0 || npad < n || (npad & 3))
+        n < 0 || npad < n || (npad & 3) || nloss < 0 || nloss > GS_NLOSS || (nloss > 0 && !losses))
         return PCTTS_EINVAL;
     GradSyncArgs a;
     for (int r = 0; r < PEER_MAX_WORLD; ++r) {
@@ -397,6 +454,7 @@ extern "C" int pctts_grad_sync_adam(const unsigned long long* grad_bases, const 
     }
     a.p = p, a.m = m, a.v = v, a.step = step, a.n = n, a.n4 = npad / 4;
     a.lr = lr, a.b1 = beta1, a.b2 = beta2, a.eps = eps, a.rank = rank, a.world = world, a.err = err;
+    a.losses = losses, a.nloss = nloss;
     // every CTA spins on peers' flags: the grid must be resident as a whole (one CTA per SM at most)
     long want = (n + GS_THREADS * 8 - 1) / (GS_THREADS * 8);
     int grid = (int)(want < 1 ? 1 : (want > 132 ? 132 : want));

@@ -25,7 +25,7 @@ class LocalSync(object):
     def allreduce(self, t):
         return t
 
-    def grad_adam(self, store, lr, beta1, beta2, eps):
+    def grad_adam(self, store, lr, beta1, beta2, eps, losses=None):
         store.adam(lr, beta1, beta2, eps)
 
 
@@ -310,7 +310,8 @@ class Generator(_BNNet):
         return self._fused_sync(sync) and getattr(sync, 'bn_handle2', None) is not None
 
     # ---- forward ----------------------------------------------------------------------------------------------
-    def forward(self, pl, ctx, out, training=True, update_stats=False, sync=None, spec_only=False, materialize=True):
+    def forward(self, pl, ctx, out, training=True, update_stats=False, sync=None, spec_only=False, materialize=True,
+                after_first_conv=None):
         """ctx [B,T,ctxsize] -> out [B,T,O] (both contiguous device tensors).  training: BN uses batch statistics
         (all-reduced through `sync`); update_stats: also move the BN moving averages (generator step only).
         spec_only: evaluate the ctx trunk and the spectral branch only and leave the F0 / noise-mask columns of `out`
@@ -326,8 +327,15 @@ class Generator(_BNNet):
             xp = pl['ctx_xp'][i]
             o.pad_time(xp, x, left, W - 1 - left)
             o.conv1d(xp, p['g.ctx.cnn%d.kernel' % i], pl['ctx_z'][i], T)
+            if i == 0 and after_first_conv is not None:
+                # the caller's independent branch (the critic's ctx branch: another machine-filling Conv1D) is forked HERE, behind
+                # this Conv1D: two 132-CTA GEMMs launched together only slow each other down on the lane that has no slack
+                after_first_conv()
+                after_first_conv = None
             self._bn_fwd(pl['ctx_z'][i], pl['ctx_y'][i], pl['ctx_bn'][i], training, update_stats, sync, planes=True)
             x = pl['ctx_y'][i].view(B, T, H)
+        if after_first_conv is not None:
+            after_first_conv()
         x2 = x.reshape(M, -1)
         for i in range(2):                                                   # pFC (networktts.py:59-63)
             o.gemm(x2, p['g.ctx.fc%d.kernel' % i], pl['fc_z'][i])

@@ -147,22 +147,29 @@ class DistSync(object):
         self._gs, self._gs_ctl, self._gs_keep = table, ctl_bases, keep
         return True
 
-    def grad_adam(self, store, lr, beta1, beta2, eps):
+    def grad_adam(self, store, lr, beta1, beta2, eps, losses=None):
         """All-reduce(sum) of store.grad over the replicas followed by store's Adam update: one fused launch over peer memory where
-        enable_grad_sync() set it up, NCCL all-reduce + adam_kernel otherwise."""
+        enable_grad_sync() set it up, NCCL all-reduce + adam_kernel otherwise.  losses: a slice of the step's loss vector (local
+        shares of the global means) summed over the replicas on the way."""
         ent = self._gs.get(id(store))
         if ent is None or store.ntrain == 0:
+            if losses is not None:
+                self.allreduce(losses)       # local shares -> global means (logging only)
             self.allreduce(store.grad)
             store.adam(lr, beta1, beta2, eps)
             return
+        assert losses is None or (losses.dtype == torch.float32 and losses.is_contiguous() and losses.numel() <= 8)
         bases, npad, _ = ent
         lib, _, err = self._peer
         n = store.ntrain
         _lib.check(lib.pctts_grad_sync_adam(ctypes.cast(bases, ctypes.c_void_p), ctypes.cast(self._gs_ctl, ctypes.c_void_p), self.rank,
                                             self.world, store.flat.data_ptr(), store.m.data_ptr(), store.v.data_ptr(), n, npad,
-                                            float(lr), float(beta1), float(beta2), float(eps), store.step.data_ptr(), err.data_ptr(),
+                                            float(lr), float(beta1), float(beta2), float(eps), store.step.data_ptr(),
+                                            losses.data_ptr() if losses is not None else None, losses.numel() if losses is not None else 0,
+                                            err.data_ptr(),
                                             torch.cuda.current_stream(store.flat.device).cuda_stream), 'pctts_grad_sync_adam')
         store.ops.launches += 1
+        store.ops.stamp('grad_sync_adam')
         self.fused_adam_calls += 1
         self.calls += 1
         store.ops.refresh_persistent(store.flat)

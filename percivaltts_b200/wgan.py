@@ -50,6 +50,9 @@ class WGANStepper(object):
         # PCTTS_REAL_EARLY=1: D(real) on the side lane beside the frozen generator instead of batched with the two other
         # applications -- measured on B200: 16 more launches, same step time (2.729 vs 2.722 ms), so it stays off
         self.real_rows_early = os.environ.get('PCTTS_REAL_EARLY', '0') != '0'
+        # PCTTS_STAGGER_CONV1D=1: the critic's ctx branch (side lane) forked behind the generator's first Conv1D instead of beside it
+        # -- measured on B200: critic step 1.962 -> 1.995 ms (the side lane then ends later than the frozen generator), so it stays off
+        self.stagger_conv1d = os.environ.get('PCTTS_STAGGER_CONV1D', '0') != '0'
         self.wbar = float(w_wgan_mean)
         self.w_ls = None
         if errtype == 'WLSWGAN':
@@ -100,15 +103,21 @@ class WGANStepper(object):
         # the critic's ctx branch reads the labels and the critic weights only: side lane, beside the frozen generator
         s0 = bf['s0'].view(3 * B, T, S, 1)
         early = self.real_rows_early
-        with o.side_lane():
-            self.C.forward_ctx(cpl, X)
-            if early:
-                # D(real) needs nothing from the generator either: real block of the packed input, then its forward pass
-                o.copy2d(bf['s0'][:B].view(M, S), Y.view(M, a.outsize)[:, 1:1 + S])
-                self.C.forward_spec(cpl, s0, samples=slice(0, B))
+
+        def critic_ctx_branch():
+            with o.side_lane():
+                self.C.forward_ctx(cpl, X)
+                if early:
+                    # D(real) needs nothing from the generator either: real block of the packed input, then its forward pass
+                    o.copy2d(bf['s0'][:B].view(M, S), Y.view(M, a.outsize)[:, 1:1 + S])
+                    self.C.forward_spec(cpl, s0, samples=slice(0, B))
+        stagger = self.stagger_conv1d
+        if not stagger:
+            critic_ctx_branch()
         # frozen generator, learning phase 1: batch statistics, no moving-average update (:121-128)
         self.G.forward(gpl, X, bf['fake'], training=True, update_stats=False, sync=sync,
-                       spec_only=not self.critic_step_full_generator, materialize=False)
+                       spec_only=not self.critic_step_full_generator, materialize=False,
+                       after_first_conv=critic_ctx_branch if stagger else None)
         if alpha is None:
             o.uniform(bf['alpha'], self.seed, self.counter)
             alpha = bf['alpha']
@@ -129,10 +138,11 @@ class WGANStepper(object):
         self.C.tangent_forward(cpl, rows)
         self.C.param_grads(cpl, first_order_apps=2)
         o.loss_combine(self.losses, L_CRITIC, L_REAL, 1.0, L_FAKE, 1.0, L_GP, self.lam)   # loss_weights [1,1,lambda] (:150)
-        if sync.world > 1:
-            sync.allreduce(self.losses[L_REAL:L_CRITIC + 1])       # local shares -> global means (logging only)
+        lv = self.losses[L_REAL:L_CRITIC + 1]      # local shares -> global means (logging only)
         if apply:       # gradient all-reduce over the replicas + Adam (one fused peer-memory launch where available)
-            sync.grad_adam(self.C.params, *self.copt, eps=self.adam_eps)
+            sync.grad_adam(self.C.params, *self.copt, eps=self.adam_eps, losses=lv if sync.world > 1 else None)
+        elif sync.world > 1:
+            sync.allreduce(lv)
 
     def generator_step(self, X, *args, **kw):
         return self._scoped(self._generator_step, X, *args, **kw)
@@ -146,9 +156,13 @@ class WGANStepper(object):
         gpl = self.G.plan(B, T)
         pred = bf['fake']
         cpl = self.C.plan(1, B, T)
-        with o.side_lane():
-            self.C.forward_ctx(cpl, X)
-        self.G.forward(gpl, X, pred, training=True, update_stats=True, sync=sync)      # joins the lanes
+        def critic_ctx_branch():
+            with o.side_lane():
+                self.C.forward_ctx(cpl, X)
+        if not self.stagger_conv1d:
+            critic_ctx_branch()
+        self.G.forward(gpl, X, pred, training=True, update_stats=True, sync=sync,      # joins the lanes
+                       after_first_conv=critic_ctx_branch if self.stagger_conv1d else None)
         o.join_lanes()
         d = self.C.forward_spec(cpl, pred[:, :, 1:1 + S].unsqueeze(-1))
         ng = float(M * sync.world)
@@ -166,10 +180,11 @@ class WGANStepper(object):
         o.fill_segments(cpl['dd'].view(-1), M, seed)
         self.C.backward_to_input(cpl, dpred[:, :, 1:1 + S].unsqueeze(-1), accumulate=True)
         self.G.backward(gpl, pred, dpred, sync=sync)
-        if sync.world > 1:
-            sync.allreduce(self.losses[L_GW:L_GEN + 1])
+        lv = self.losses[L_GW:L_GEN + 1]
         if apply:
-            sync.grad_adam(self.G.params, *self.gopt, eps=self.adam_eps)
+            sync.grad_adam(self.G.params, *self.gopt, eps=self.adam_eps, losses=lv if sync.world > 1 else None)
+        elif sync.world > 1:
+            sync.allreduce(lv)
 
     def evaluate_losses(self, X, *args, **kw):
         return self._scoped(self._evaluate_losses, X, *args, **kw)

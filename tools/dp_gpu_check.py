@@ -111,7 +111,10 @@ def main():
                     want_g = store.grad.clone()
                     dist.all_reduce(want_g)
                     ops.adam(p0[:n], want_g, m0[:n], v0[:n], 1e-3, 0.5, 0.9, 1e-7, s0)
-                sync.grad_adam(store, 1e-3, 0.5, 0.9, 1e-7)
+                lv = torch.arange(4, dtype=torch.float32, device=device) + rank
+                sync.grad_adam(store, 1e-3, 0.5, 0.9, 1e-7, losses=lv)
+                good_l = bool(torch.equal(lv, torch.arange(4, dtype=torch.float32, device=device) * world + world * (world - 1) / 2.0))
+                fused_ok = fused_ok and good_l
             torch.cuda.synchronize()
             err_p = float((store.flat[:n] - p0[:n]).abs().max() / (p0[:n].abs().max() + 1e-30))
             err_g = float((store.grad - want_g).abs().max() / (want_g.abs().max() + 1e-30))

@@ -11,9 +11,13 @@ from percivaltts_b200.wgan import WGANStepper
 
 which = sys.argv[1] if len(sys.argv) > 1 else 'critic'
 B, T = int(os.environ.get('B', 10)), int(os.environ.get('T', 400))
+sync = None
+if int(os.environ.get('WORLD_SIZE', '1')) > 1:       # torchrun: the data-parallel step (rank 0 prints)
+    from percivaltts_b200 import parallel
+    sync, _ = parallel.init_from_env()
 ops = CudaOps()
 a = A.Arch()
-st = WGANStepper(ops, a, w_ls=np.ones(a.outsize), w_wgan_mean=0.5)
+st = WGANStepper(ops, a, w_ls=np.ones(a.outsize), w_wgan_mean=0.5, sync=sync)
 st.G.params.load(A.init_params(A.generator_param_shapes(a), 1))
 st.C.params.load(A.init_params(A.critic_param_shapes(a), 2))
 rng = np.random.RandomState(0)
@@ -30,6 +34,9 @@ torch.cuda._sleep(int(4e7))          # ~20 ms of spin on the main stream while t
 step(X, Y)
 ops.stamp('end')
 tl = ops.timeline_stop()
+if sync is not None and sync.rank != 0:
+    sys.stdout.flush()
+    os._exit(0)
 t0 = min(t for w, l, t in tl[1:])
 last = {}
 print('%-4s %-26s %4s %9s %8s' % ('#', 'call', 'lane', 'end us', 'dur us'))
@@ -38,3 +45,6 @@ for i, (w, l, t) in enumerate(tl[1:]):
     d = e - last.get(l, 0.0)
     last[l] = e
     print('%-4d %-26s %4d %9.1f %8.1f' % (i, w.replace('pctts_', ''), l, e, d))
+if sync is not None:
+    sys.stdout.flush()
+    os._exit(0)
