@@ -9,7 +9,7 @@
 // register-resident accumulators.  The CTAs of the grid are divided between the layers (148 / nlayers each), so a stack of 7 layers
 // is one launch with ~24 tiles per CTA instead of 7 launches of 3-7 tiles each with their fill, drain and partial-sum passes.
 // A CTA (15 warps) walks over tiles of 16 frame rows x F bins of its layer, staged in shared memory by cp.async (zero-filled halo,
-// double-buffered).  Warp (kt, part) owns one kernel row; lane (row r, segment) slides along its run of SEG pixels with
+// double-buffered).  Warp (kt, part) owns one kernel row; lane (row r, segment) slides along its run of SEG = 22 pixels with
 // the 5-pixel input window held in registers, so that a pixel costs 2 LDS.128 (one new window pixel, one dy pixel) for
 // 80 FMAs.  The 80 (+4) accumulators stay in registers over all the tiles of the CTA; one warp reduction at the end, then the
 // deterministic partial sum over the CTAs of the layer (wgrad_multi_reduce_kernel, one launch for all layers).
@@ -18,8 +18,8 @@
 
 namespace {
 
-constexpr int W4_TT = 16;                // output rows per tile (a lane takes rows r and r + 8)
-constexpr int W4_PARTS = 3;              // a kernel row is shared by 3 warps = 96 (row, segment) units
+constexpr int W4_TT = 16;                // output rows per tile (one per lane & 15)
+constexpr int W4_PARTS = 3;              // a kernel row is shared by 3 warps = 96 (row, segment) units: 16 rows x 6 segments
 constexpr int W4_WARPS = 5 * W4_PARTS;   // 15 warps, one CTA per SM (112 registers per thread: 80 accumulators + window)
 constexpr int W4_THREADS = W4_WARPS * 32;
 constexpr int W4_NW = 400;
@@ -84,8 +84,10 @@ __global__ void __launch_bounds__(W4_THREADS, 1) conv2d_wgrad44_kernel(const W4P
     const int stage_n = xs_n + dys_n;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int kt = warp % 5, half = warp / 5;
-    const int r = lane & 7, seg = (lane >> 3) + 4 * half;
-    constexpr int NSEG = 4 * W4_PARTS;
+    // a lane owns one of the tile's 16 rows and one of 6 segments of the frequency axis (22 pixels at F = 129): long runs keep the
+    // per-run set-up (addresses, the first four window pixels) and the run's tail small against the 80 FMAs per pixel
+    const int r = lane & 15, seg = (lane >> 4) + 2 * half;
+    constexpr int NSEG = 2 * W4_PARTS;
     const int SEG = (F + NSEG - 1) / NSEG;
     const int f0 = seg * SEG;
     const int len = max(0, min(SEG, F - f0));
@@ -157,39 +159,38 @@ __global__ void __launch_bounds__(W4_THREADS, 1) conv2d_wgrad44_kernel(const W4P
         __syncthreads();
         const bool with_bias = kt == 0 && (ti / p.tiles_per_sample) < p.nb_bias;
         if (len > 0) {
-#pragma unroll 1
-            for (int rh = 0; rh < W4_TT; rh += 8) {
-                const float4* xs = smem4 + (size_t)s * stage_n + (size_t)(r + rh + kt) * FW + f0;
-                const float4* dys = smem4 + (size_t)s * stage_n + xs_n + (size_t)(r + rh) * F + f0;
-                float4 w0 = xs[0], w1 = xs[1], w2 = xs[2], w3 = xs[3], w4;
-                int i = 0;
-                // five pixels per trip: the window rotates through the registers without moves
-                for (; i + 5 <= len; i += 5) {
-                    float4 d;
-                    w4 = xs[i + 4], d = dys[i];
-                    fma_px(acc, w0, w1, w2, w3, w4, d);
-                    if (with_bias) bsum.x += d.x, bsum.y += d.y, bsum.z += d.z, bsum.w += d.w;
-                    w0 = xs[i + 5], d = dys[i + 1];
-                    fma_px(acc, w1, w2, w3, w4, w0, d);
-                    if (with_bias) bsum.x += d.x, bsum.y += d.y, bsum.z += d.z, bsum.w += d.w;
-                    w1 = xs[i + 6], d = dys[i + 2];
-                    fma_px(acc, w2, w3, w4, w0, w1, d);
-                    if (with_bias) bsum.x += d.x, bsum.y += d.y, bsum.z += d.z, bsum.w += d.w;
-                    w2 = xs[i + 7], d = dys[i + 3];
-                    fma_px(acc, w3, w4, w0, w1, w2, d);
-                    if (with_bias) bsum.x += d.x, bsum.y += d.y, bsum.z += d.z, bsum.w += d.w;
-                    w3 = xs[i + 8], d = dys[i + 4];
-                    fma_px(acc, w4, w0, w1, w2, w3, d);
-                    if (with_bias) bsum.x += d.x, bsum.y += d.y, bsum.z += d.z, bsum.w += d.w;
-                }
-                for (; i < len; ++i) {
-                    w4 = xs[i + 4];
-                    const float4 d = dys[i];
-                    fma_px(acc, w0, w1, w2, w3, w4, d);
-                    if (with_bias) bsum.x += d.x, bsum.y += d.y, bsum.z += d.z, bsum.w += d.w;
-                    w0 = w1, w1 = w2, w2 = w3, w3 = w4;
+            const float4* xs = smem4 + (size_t)s * stage_n + (size_t)(r + kt) * FW + f0;
+            const float4* dys = smem4 + (size_t)s * stage_n + xs_n + (size_t)r * F + f0;
+            float4 w0 = xs[0], w1 = xs[1], w2 = xs[2], w3 = xs[3], w4;
+            float4 d;
+#define W4_PX(WA, WB, WC, WD, WE, OFF)                                                     \
+    WE = xs[i + (OFF) + 4], d = dys[i + (OFF)];                                            \
+    fma_px(acc, WA, WB, WC, WD, WE, d);                                                    \
+    if (with_bias) bsum.x += d.x, bsum.y += d.y, bsum.z += d.z, bsum.w += d.w;
+            int i = 0;
+            // five pixels per trip: the window rotates through the registers without moves
+            for (; i + 5 <= len; i += 5) {
+                W4_PX(w0, w1, w2, w3, w4, 0)
+                W4_PX(w1, w2, w3, w4, w0, 1)
+                W4_PX(w2, w3, w4, w0, w1, 2)
+                W4_PX(w3, w4, w0, w1, w2, 3)
+                W4_PX(w4, w0, w1, w2, w3, 4)
+            }
+            // the run's last len % 5 pixels: the same rotation, cut short (no register moves)
+            const int rem = len - i;
+            if (rem > 0) {
+                W4_PX(w0, w1, w2, w3, w4, 0)
+                if (rem > 1) {
+                    W4_PX(w1, w2, w3, w4, w0, 1)
+                    if (rem > 2) {
+                        W4_PX(w2, w3, w4, w0, w1, 2)
+                        if (rem > 3) {
+                            W4_PX(w3, w4, w0, w1, w2, 3)
+                        }
+                    }
                 }
             }
+#undef W4_PX
         }
         __syncthreads();      // every warp is done with stage s before the next trip refills it
     }

@@ -154,6 +154,19 @@ class ChainLayerStruct(ctypes.Structure):
                 ('cin', ctypes.c_int), ('cout', ctypes.c_int), ('flags', ctypes.c_int), ('flip', ctypes.c_int)]
 
 
+class _AblatedLib(object):
+    """libpctts.so with some entry points stubbed out (PCTTS_ABLATE=pctts_conv2d_chain,...): how much of a step's time a kernel
+    family is responsible for, measured by leaving it out.  Never on in a run whose results are used."""
+
+    def __init__(self, lib, names):
+        self._lib, self._names = lib, set(n.strip() for n in names if n.strip())
+
+    def __getattr__(self, name):
+        if name in self._names:
+            return lambda *a, **k: 0
+        return getattr(self._lib, name)
+
+
 class SplitJobStruct(ctypes.Structure):
     """pctts_split_job of include/pctts.h"""
     _fields_ = [('src', ctypes.c_void_p), ('dst', ctypes.c_void_p), ('ld', ctypes.c_long), ('rows', ctypes.c_long),
@@ -185,6 +198,8 @@ class CudaOps(object):
         if not torch.cuda.is_available():
             raise _lib.PcttsError('percivaltts_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback')
         self.lib = _lib.load()
+        if os.environ.get('PCTTS_ABLATE'):      # developer probe: named C-ABI calls become no-ops (timing ablations; results are wrong)
+            self.lib = _AblatedLib(self.lib, os.environ['PCTTS_ABLATE'].split(','))
         self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
         _lib.check(self.lib.pctts_device_check(self.device.index or 0), 'pctts_device_check')
         precision = precision or os.environ.get('PCTTS_PRECISION', 'fp32')
