@@ -125,6 +125,20 @@ constexpr int SL_COLS = 32;
 
 __host__ __device__ inline long sl_flags_off() { return (long)SL_MAX * 8; }
 __host__ __device__ inline long sl_data_off(int world) { return sl_flags_off() + ((2L * SL_MAX * world * 8 + 127) / 128) * 128; }
+// Low-latency variant of the exchange (the default): every 32-bit half of a double travels as ONE 8-byte store {data, seq} straight
+// into every peer's receive area, and a rank polls its OWN memory until the word carries the current sequence number -- one one-way
+// NVLink write per word, no system-scope fence, no flag round, no remote load (the pull protocol above pays fence + flag + a remote
+// read round trip, ~4 us more per exchange).  Receive area per rank: u64 [2][SL_MAX][world][128] behind the pull protocol's slots.
+__host__ __device__ inline long sl_ll_off(int world) { return sl_data_off(world) + 2L * SL_MAX * 64 * 8; }
+__host__ __device__ inline long sl_ll_bytes(int world) { return 2L * SL_MAX * world * 128 * 8; }
+__device__ __forceinline__ void st_relaxed_sys_u64(uint64_t* p, uint64_t v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t ld_relaxed_sys_u64(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
 
 struct BnSyncArgs {
     const double* partial;   // [nblk][2][C]
@@ -139,6 +153,7 @@ struct BnSyncArgs {
     int accumulate;
     int rank, world;
     int* err;
+    int ll;                  // 1: low-latency push protocol, 0: publish / flag / pull
 };
 
 __global__ void __launch_bounds__(256) bn_sync_kernel(BnSyncArgs a, PeerBases bases) {
@@ -165,6 +180,40 @@ __global__ void __launch_bounds__(256) bn_sync_kernel(BnSyncArgs a, PeerBases ba
         __syncthreads();
         const uint64_t seq = s_seq;
         const int par = (int)(seq & 1);
+        if (a.ll) {
+            const uint32_t tag = (uint32_t)seq;
+            const long base = sl_ll_off(a.world) + (((long)par * SL_MAX + s) * a.world) * 128 * 8;
+            if (tid < 128) {      // word tid = half (tid & 1) of double tid >> 1, to every peer's area for this rank
+                const uint64_t bits = (uint64_t)__double_as_longlong(loc[tid >> 1]);
+                const uint64_t word = ((uint64_t)tag << 32) | (uint32_t)(bits >> (32 * (tid & 1)));
+                for (int r = 0; r < a.world; ++r)
+                    if (r != a.rank) st_relaxed_sys_u64(reinterpret_cast<uint64_t*>(bases.b[r] + base) + (long)a.rank * 128 + tid, word);
+            }
+            double q = 0.0;
+            if (tid < 64) {
+                const long long t0 = clock64();
+                for (int r = 0; r < a.world; ++r) {       // rank order: bit-identical sums on every rank
+                    if (r == a.rank) {
+                        q += loc[tid];
+                        continue;
+                    }
+                    const uint64_t* w = reinterpret_cast<const uint64_t*>(mine + base) + (long)r * 128 + 2 * tid;
+                    uint64_t lo, hi;
+                    while ((uint32_t)((lo = ld_relaxed_sys_u64(w)) >> 32) != tag || (uint32_t)((hi = ld_relaxed_sys_u64(w + 1)) >> 32) != tag) {
+                        if (clock64() - t0 > PEER_SPIN_LIMIT) {
+                            *a.err = 1;
+                            lo = hi = 0;
+                            break;
+                        }
+                    }
+                    q += __longlong_as_double((long long)(((hi & 0xffffffffull) << 32) | (lo & 0xffffffffull)));
+                }
+            }
+            __syncthreads();
+            if (tid < 64) loc[tid] = q;
+            __syncthreads();
+            if (tid == 0) reinterpret_cast<volatile uint64_t*>(mine)[s] = seq;
+        } else {
         const long doff = sl_data_off(a.world) + ((long)par * SL_MAX + s) * 64 * 8;
         if (tid < 64) reinterpret_cast<double*>(mine + doff)[tid] = loc[tid];
         __threadfence_system();
@@ -189,6 +238,7 @@ __global__ void __launch_bounds__(256) bn_sync_kernel(BnSyncArgs a, PeerBases ba
         }
         __syncthreads();
         if (tid == 0) reinterpret_cast<volatile uint64_t*>(mine)[s] = seq;
+        }
     }
     if (tid < 64) {
         const int m = tid >> 5, j = tid & 31;
@@ -218,6 +268,8 @@ int bn_sync_launch(BnSyncArgs& a, const unsigned long long* peer_bases, cudaStre
     if (a.world > 1 && (!peer_bases || !a.err || a.world > PEER_MAX_WORLD || a.rank < 0 || a.rank >= a.world)) return PCTTS_EINVAL;
     PeerBases b;
     for (int r = 0; r < PEER_MAX_WORLD; ++r) b.b[r] = (a.world > 1 && r < a.world) ? peer_bases[r] : 0;
+    static const int ll = getenv("PCTTS_BN_LL") ? atoi(getenv("PCTTS_BN_LL")) : 1;
+    a.ll = ll;
     pctts_launch(bn_sync_kernel, pctts_div_up(a.C, SL_COLS), 256, 0, st, a, b);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
@@ -228,7 +280,7 @@ int bn_sync_launch(BnSyncArgs& a, const unsigned long long* peer_bases, cudaStre
 /* bytes of the symmetric buffer of the sliced protocol (zeroed, then a barrier, before the first call) */
 extern "C" long pctts_bn_sync_bytes(int world) {
     if (world < 1 || world > PEER_MAX_WORLD) return -1;
-    return sl_data_off(world) + 2L * SL_MAX * 64 * 8;
+    return sl_ll_off(world) + sl_ll_bytes(world);
 }
 
 /* Forward BatchNorm statistics: second reduction stage over the nblk first-stage partials [nblk][2][C] (doubles) at `partial`,
