@@ -407,6 +407,7 @@ class Generator(_BNNet):
         out2, dout2 = out.view(M, O), dout.view(M, O)
         # ---- F0 branch on the side lane (BPTT is latency-bound); its share of d(lctx) goes to its own buffer
         o.preshare(lctx)
+        f0_ev = None
         with o.side_lane():
             o.copy2d(pl['df0'], dout2[:, 0:1])
             hout2 = pl['hout'].view(M, 2 * H)
@@ -415,6 +416,11 @@ class Generator(_BNNet):
             o.gemm(pl['df0'], p['g.f0.out.kernel'], pl['dhout'].view(M, 2 * H), transB=True)
             U = [p['g.f0.blstm.fw.recurrent'], p['g.f0.blstm.bw.recurrent']]
             o.lstm_bwd(pl['dhout'], U, pl['gates'], pl['cstate'], pl['dzl'])
+            # the branch's share of d(lctx) first: it is all the ctx trunk waits for; the weight gradients follow behind the event
+            for d, dn in enumerate(('fw', 'bw')):
+                o.gemm(pl['dzl'][d].view(M, 4 * H), p['g.f0.blstm.%s.kernel' % dn], pl['d_lctx_f0'], transB=True,
+                       flags=EPI_ACCUM if d > 0 else 0)
+            f0_ev = o.lane_event()
             for d, dn in enumerate(('fw', 'bw')):
                 dz2 = pl['dzl'][d].view(M, 4 * H)
                 o.gemm(lctx, dz2, g['g.f0.blstm.%s.kernel' % dn], transA=True)
@@ -428,7 +434,6 @@ class Generator(_BNNet):
                         o.gemm(hd[:, 1:T], pl['dzl'][d][:, 0:T - 1], gU, transA=True)
                 else:
                     o.fill_segments(gU.view(-1), gU.numel(), 0.0)
-                o.gemm(dz2, p['g.f0.blstm.%s.kernel' % dn], pl['d_lctx_f0'], transB=True, flags=EPI_ACCUM if d > 0 else 0)
         # ---- NM branch: shares nothing but lctx with the spectral branch -> second side lane, its share of d(lctx) in its own buffer
         dl_nm = pl['d_lctx_nm']
 
@@ -483,7 +488,10 @@ class Generator(_BNNet):
             nm_branch()
         # the ctx trunk needs the branches' shares of d(lctx): the F0 lane as a whole, of lane 2 only the noise-mask branch (the
         # weight gradients queued behind it are joined at the end)
-        o.join_lanes(1)
+        if f0_ev is not None:
+            o.wait_lane_event(f0_ev)
+        else:
+            o.join_lanes(1)
         o.wait_lane_event(nm_ev)
         o.add(dl, dl, pl['d_lctx_f0'])
         o.add(dl, dl, dl_nm)
