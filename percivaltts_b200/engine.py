@@ -570,7 +570,10 @@ class Critic(object):
             pl['ctx_y'].append(o.empty(M, H))
             cin = H
         pl['fc_y'] = [o.empty(M, H) for _ in range(2)]
-        pl['ctxterm'] = o.empty(M, H)
+        # the ctx branch's term of the first post layer: rows [0, M) are computed, the copies behind them let a row range that
+        # starts inside an application (split forward) address its addend without a modulo
+        pl['ctxterm_rep'] = o.empty(napp * M, H)
+        pl['ctxterm'] = pl['ctxterm_rep'][:M]
         pl['a'] = [o.empty(nB, T, S, Fl) for _ in range(L)]
         pl['p'] = [o.empty(nM, H) for _ in range(3)]
         pl['d'] = o.empty(nM, 1)
@@ -615,7 +618,53 @@ class Critic(object):
             x2 = pl['fc_y'][i]
         w0 = p['c.post.fc0.kernel']
         o.gemm(x2, w0[SF:], pl['ctxterm'], bias=p['c.post.fc0.bias'])
+        if self._split_forward(pl) is not None:
+            for k in range(1, pl['napp']):
+                o.copy2d(pl['ctxterm_rep'][k * M:(k + 1) * M], pl['ctxterm'])
         pl['ctx_in'], pl['ctx_last'] = ctx, x2
+
+    def _split_forward(self, pl):
+        """Samples of the first chain launch when the batched forward needs two rounds of clusters (None: one launch)."""
+        o = self.ops
+        if not (getattr(o, 'split_fwd', False) and self._chain(pl['T'])):      # (lanes off: the same launches, in line)
+            return None
+        nc = o.lib.pctts_conv2d_chain_supported(int(pl['T']), int(self.a.spec_size), o.nterms)
+        per_round = 148 // nc if nc > 0 else 0
+        if per_round < 1 or not (per_round < pl['nB'] <= 2 * per_round):
+            return None
+        return per_round
+
+    def _spec_chain(self, pl, s0, sm):
+        """The spectral Conv2D stack (networks_critic.py:58-70) on the samples `sm` (slice over the napp*B axis)."""
+        o, a, p = self.ops, self.a, self.params.p
+        L = a.gen_nbcnnlayers
+        amap = s0[sm]
+        if self._chain(pl['T']):
+            # the BatchNorm-free stack (networks_critic.py:66-68) as ONE launch: tiles stay in shared memory from layer to layer
+            o.conv2d_chain(amap, [dict(w=p['c.spec.cnn%d.kernel' % i], bias=p['c.spec.cnn%d.bias' % i], y=pl['a'][i][sm],
+                                       flags=EPI_LRELU) for i in range(L)])
+        else:
+            for i in range(L):
+                o.conv2d(amap, p['c.spec.cnn%d.kernel' % i], pl['a'][i][sm], bias=p['c.spec.cnn%d.bias' % i], flags=EPI_LRELU)
+                amap = pl['a'][i][sm]
+
+    def _post_layers(self, pl, r):
+        """Post layers (networks_critic.py:89-96) on the rows `r` of the batched matrices; concat([spec, ctx]) . W0 =
+        spec . W0[:SF] + ctx . W0[SF:], the second term being pl['ctxterm'] of the row's frame."""
+        o, a, p = self.ops, self.a, self.params.p
+        M, nM = pl['M'], pl['nM']
+        S, Fl, L = a.spec_size, a.gen_nbfilters, a.gen_nbcnnlayers
+        SF = S * Fl
+        w0 = p['c.post.fc0.kernel']
+        if r == slice(None) or (r.start % M == 0):
+            addmod = pl['ctxterm']                              # row m of the range uses ctxterm[m % M]
+        else:
+            off, n = r.start % M, r.stop - r.start
+            addmod = pl['ctxterm_rep'][off:off + n]             # replicated rows: no modulo needed
+        o.gemm(pl['a'][L - 1].view(nM, SF)[r], w0[:SF], pl['p'][0][r], addmod=addmod, flags=EPI_LRELU)
+        for i in (1, 2):
+            o.gemm(pl['p'][i - 1][r], p['c.post.fc%d.kernel' % i], pl['p'][i][r], bias=p['c.post.fc%d.bias' % i], flags=EPI_LRELU)
+        o.gemm(pl['p'][2][r], p['c.out.kernel'], pl['d'][r], bias=p['c.out.bias'])
 
     def forward_spec(self, pl, s0, samples=None):
         """Spectral branch (networks_critic.py:58-70) and the post layers on the applications `samples` (a slice over the
@@ -630,20 +679,20 @@ class Critic(object):
         else:
             assert samples.start % pl['B'] == 0 and samples.stop % pl['B'] == 0
             sm, r = samples, slice(samples.start * T, samples.stop * T)
-        amap = s0[sm]
-        if self._chain(T):
-            # the BatchNorm-free stack (networks_critic.py:66-68) as ONE launch: tiles stay in shared memory from layer to layer
-            o.conv2d_chain(amap, [dict(w=p['c.spec.cnn%d.kernel' % i], bias=p['c.spec.cnn%d.bias' % i], y=pl['a'][i][sm],
-                                       flags=EPI_LRELU) for i in range(L)])
+        split = self._split_forward(pl) if (sm == slice(None)) else None
+        if split is not None:
+            # More clusters than the machine holds at once (30 samples x 8 CTAs on 148 SMs = two rounds): the first round's samples go
+            # first, and their post layers run on the side lane UNDER the second round's chain launch instead of behind it.
+            n1 = split
+            self._spec_chain(pl, s0, slice(0, n1))
+            with o.side_lane():
+                self._post_layers(pl, slice(0, n1 * T))
+            self._spec_chain(pl, s0, slice(n1, pl['nB']))
+            self._post_layers(pl, slice(n1 * T, nM))
+            o.join_lanes(1)
         else:
-            for i in range(L):
-                o.conv2d(amap, p['c.spec.cnn%d.kernel' % i], pl['a'][i][sm], bias=p['c.spec.cnn%d.bias' % i], flags=EPI_LRELU)
-                amap = pl['a'][i][sm]
-        # post layers (networks_critic.py:89-96); concat([spec, ctx]) . W0 = spec . W0[:SF] + ctx . W0[SF:]
-        o.gemm(pl['a'][L - 1].view(nM, SF)[r], w0[:SF], pl['p'][0][r], addmod=pl['ctxterm'], flags=EPI_LRELU)
-        for i in (1, 2):
-            o.gemm(pl['p'][i - 1][r], p['c.post.fc%d.kernel' % i], pl['p'][i][r], bias=p['c.post.fc%d.bias' % i], flags=EPI_LRELU)
-        o.gemm(pl['p'][2][r], p['c.out.kernel'], pl['d'][r], bias=p['c.out.bias'])
+            self._spec_chain(pl, s0, sm)
+            self._post_layers(pl, r)
         pl['s0'] = s0
         return pl['d']
 

@@ -218,6 +218,9 @@ class CudaOps(object):
         self.split_multi = os.environ.get('PCTTS_SPLIT_MULTI', '1') != '0'   # weight shadows after Adam in one launch
         self.fuse_planes = os.environ.get('PCTTS_FUSE_PLANES', '1') != '0'   # BatchNorm apply kernels write the bf16 operand planes of their output
         self.tc_wflip = os.environ.get('PCTTS_TC_WFLIP', '1') != '0'     # Conv2D data gradients read the forward kernels (no flip launch)
+        # PCTTS_SPLIT_FWD=1: batched critic forward as two chain launches (18 + 12 samples), the post layers of the first under the second.
+        # Measured on B200: critic step 1.930 -> 2.007 ms (GEMM CTAs on the free SMs delay the second launch's 8-CTA clusters) -- off
+        self.split_fwd = os.environ.get('PCTTS_SPLIT_FWD', '0') != '0'
         self.wgrad_multi = os.environ.get('PCTTS_WGRAD_MULTI', '1') != '0'   # weight gradients of a whole Conv2D stack in one launch
         self.conv_chain = os.environ.get('PCTTS_CONV_CHAIN', '1') != '0'   # the critic's BN-free Conv2D stack as ONE launch per chain
         self._shadows = {}         # view key -> Shadow
