@@ -234,7 +234,11 @@ int pctts_gp_scale(const float* g, const float* ss, float* r0, int B, long per_s
 int pctts_loss_combine(float* losses, int out, int a, float ca, int b, float cb, int c, float cc, void* stream);
 long pctts_lse_workspace_bytes(void);  /* host call; zero once */
 int pctts_lse_loss_grad(const float* pred, const float* real, const float* w, float* dpred, long rows, int O,
-                        double scale_loss, float scale_grad, float* losses, int slot, void* workspace, void* stream); /* :73-79 */
+                        double scale_loss, float scale_grad, float* losses, int slot, void* workspace, void* stream);
+/* ... restricted to the columns [c0, c0 + nc) (w indexed by the absolute column): the generator step evaluates the F0 column on the
+ * F0 lane, behind the LSTM; give concurrent calls their own workspace */
+int pctts_lse_loss_grad_cols(const float* pred, const float* real, const float* w, float* dpred, long rows, int O, int c0, int nc,
+                             double scale_loss, float scale_grad, float* losses, int slot, void* workspace, void* stream); /* :73-79 */
 /* Keras Adam (:145,172): reads *step, uses t=*step+1, then increments *step (device int) */
 int pctts_adam(float* p, const float* g, float* m, float* v, long n, float lr, float beta1, float beta2, float eps, int* step,
                void* stream);

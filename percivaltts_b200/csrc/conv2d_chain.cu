@@ -67,6 +67,7 @@ struct ChainParams {
     int D;                 // slide between the two origins, in entries
     int nlayers;
     long long* trace;      // developer probe (pctts_conv2d_chain_set_trace): clock64() stamps of CTA 0, 16 per layer
+    int debug;             // developer probe (PCTTS_CHAIN_DEBUG): 1 = epilogue without the next layer's operand stores, 2 = empty epilogue (results wrong)
     ChainLayer L[CH_MAXL];
 };
 
@@ -321,6 +322,11 @@ __global__ void __launch_bounds__(CH_THREADS, 1) conv2d_chain_kernel(const Chain
                     const uint32_t ph = (bc / NSLOT) & 1u;
                     mbar_wait(smem_u32(&acc_full[s]), ph);
                     tc_fence_after();
+                    if (p.debug & 2) {
+                        tc_fence_before();
+                        mbar_arrive(smem_u32(&acc_empty[s]));
+                        continue;
+                    }
                     const int blk = asc ? pos : nblk - 1 - pos;
                     const uint32_t col = tmem_base + lane_addr + (uint32_t)(s * BLKCOLS);
                     uint32_t c0[16];
@@ -391,7 +397,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) conv2d_chain_kernel(const Chain
                                 }
                             }
                         }
-                        if (!last) {
+                        if (!last && !(p.debug & 1)) {
                             // this row as input of the next layer: tile frame to + 2, pairs 2g and 2g + 1 -> entry 1 + r + 2G of
                             // the even and of the odd array of the layout with origin Oout
                             const float va[8] = {o[0], o[1], o[2], o[3], o[4], o[5], o[6], o[7]};
@@ -561,6 +567,8 @@ extern "C" int pctts_conv2d_chain(const float* x, long xbatch, long xpitch, int 
     p.E = p.D + p.nblk * 128 + 4 * p.G + 8;
     p.nlayers = nlayers;
     p.trace = g_chain_trace;
+    static const int dbg = getenv("PCTTS_CHAIN_DEBUG") ? atoi(getenv("PCTTS_CHAIN_DEBUG")) : 0;
+    p.debug = dbg;
     int cin = cin0;
     for (int l = 0; l < nlayers; ++l) {
         const pctts_chain_layer& s = layers[l];

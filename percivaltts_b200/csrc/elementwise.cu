@@ -168,6 +168,41 @@ __global__ void lse_kernel(const float* __restrict__ pred, const float* __restri
     }
 }
 
+// the same over the column window [c0, c0 + nc) of the [rows, O] matrices (the generator step evaluates the F0 column on its own
+// lane, behind the LSTM, and the other columns without waiting for it)
+__global__ void lse_cols_kernel(const float* __restrict__ pred, const float* __restrict__ real, const float* __restrict__ w,
+                                float* __restrict__ dpred, long rows, int O, int c0, int nc, double scale_loss, float scale_grad,
+                                double* __restrict__ partial, unsigned int* __restrict__ counter, float* __restrict__ losses, int slot) {
+    pdl_entry();
+    __shared__ double scratch[32];
+    __shared__ bool is_last;
+    const long n = rows * nc;
+    double s = 0.0;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        const long r = i / nc;
+        const int c = c0 + (int)(i - r * nc);
+        const long k = r * O + c;
+        const float wv = w ? w[c] : 1.f;
+        const float d = pred[k] - real[k];
+        s += (double)(d * d * wv);
+        if (dpred) dpred[k] = scale_grad * 2.f * d * wv;
+    }
+    s = block_sum_d(s, scratch);
+    if (threadIdx.x == 0) {
+        partial[blockIdx.x] = s;
+        __threadfence();
+        is_last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (is_last && threadIdx.x == 0) {
+        __threadfence();
+        double t = 0.0;
+        for (unsigned int b = 0; b < gridDim.x; ++b) t += __ldcg(partial + b);
+        losses[slot] = (float)(t * scale_loss);
+        *counter = 0u;
+    }
+}
+
 // Keras-2.2 Adam: t = step+1; lr_t = lr*sqrt(1-b2^t)/(1-b1^t); m,v updated; p -= lr_t*m/(sqrt(v)+eps)
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                             long n, float lr, float b1, float b2, float eps, const int* __restrict__ step) {
@@ -349,6 +384,20 @@ extern "C" int pctts_lse_loss_grad(const float* pred, const float* real, const f
     double* partial = (double*)workspace;
     unsigned int* counter = (unsigned int*)(partial + 148 * 8);
     pctts_launch(lse_kernel, ew_blocks(rows * O), ET, 0, (cudaStream_t)stream, pred, real, w, dpred, rows, O, scale_loss, scale_grad, partial, counter, losses, slot);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
+/* the same restricted to the columns [c0, c0 + nc) of the [rows, O] matrices (w indexed by the absolute column); the workspace must
+ * not be shared with a call that may run concurrently on another stream */
+extern "C" int pctts_lse_loss_grad_cols(const float* pred, const float* real, const float* w, float* dpred, long rows, int O, int c0,
+                                        int nc, double scale_loss, float scale_grad, float* losses, int slot, void* workspace,
+                                        void* stream) {
+    if (!pred || !real || !losses || !workspace || rows <= 0 || O <= 0 || c0 < 0 || nc <= 0 || c0 + nc > O) return PCTTS_EINVAL;
+    double* partial = (double*)workspace;
+    unsigned int* counter = (unsigned int*)(partial + 148 * 8);
+    pctts_launch(lse_cols_kernel, ew_blocks(rows * nc), ET, 0, (cudaStream_t)stream, pred, real, w, dpred, rows, O, c0, nc, scale_loss,
+                 scale_grad, partial, counter, losses, slot);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

@@ -311,7 +311,7 @@ class Generator(_BNNet):
 
     # ---- forward ----------------------------------------------------------------------------------------------
     def forward(self, pl, ctx, out, training=True, update_stats=False, sync=None, spec_only=False, materialize=True,
-                after_first_conv=None):
+                after_first_conv=None, join_f0=True):
         """ctx [B,T,ctxsize] -> out [B,T,O] (both contiguous device tensors).  training: BN uses batch statistics
         (all-reduced through `sync`); update_stats: also move the BN moving averages (generator step only).
         spec_only: evaluate the ctx trunk and the spectral branch only and leave the F0 / noise-mask columns of `out`
@@ -391,12 +391,50 @@ class Generator(_BNNet):
         if not spec_only and not nm_lane:
             nm_branch()
         if not spec_only:
-            o.join_lanes()
+            # join_f0=False (generator step): the F0 lane is left running -- only out[:, :, 0] comes from it, and the caller keeps
+            # everything that reads that column (its LSE term, the F0 backward) on that lane
+            o.join_lanes(None if join_f0 else 2)
         pl['lctx'], pl['ctx_in'] = lctx, ctx
         return out
 
     # ---- backward ---------------------------------------------------------------------------------------------
-    def backward(self, pl, out, dout, sync=None):
+    def backward_f0(self, pl, out, dout):
+        """Backward of the F0 branch (Dense(1), BLSTM) on the CURRENT lane: needs dout[:, :, 0] only; leaves its share of d(lctx) in
+        pl['d_lctx_f0'] and returns the lane event behind it (None in line); the branch's weight gradients follow the event."""
+        o, a, p, g = self.ops, self.a, self.params.p, self.params.g
+        B, T, M = pl['B'], pl['T'], pl['M']
+        H, O = a.hiddenwidth, a.outsize
+        lctx = pl['lctx']
+        out2, dout2 = out.view(M, O), dout.view(M, O)
+        f0_ev = None
+        o.copy2d(pl['df0'], dout2[:, 0:1])
+        hout2 = pl['hout'].view(M, 2 * H)
+        o.gemm(hout2, pl['df0'], g['g.f0.out.kernel'], transA=True)
+        o.colsum(pl['df0'], g['g.f0.out.bias'])
+        o.gemm(pl['df0'], p['g.f0.out.kernel'], pl['dhout'].view(M, 2 * H), transB=True)
+        U = [p['g.f0.blstm.fw.recurrent'], p['g.f0.blstm.bw.recurrent']]
+        o.lstm_bwd(pl['dhout'], U, pl['gates'], pl['cstate'], pl['dzl'])
+        # the branch's share of d(lctx) first: it is all the ctx trunk waits for; the weight gradients follow behind the event
+        for d, dn in enumerate(('fw', 'bw')):
+            o.gemm(pl['dzl'][d].view(M, 4 * H), p['g.f0.blstm.%s.kernel' % dn], pl['d_lctx_f0'], transB=True,
+                   flags=EPI_ACCUM if d > 0 else 0)
+        f0_ev = o.lane_event()
+        for d, dn in enumerate(('fw', 'bw')):
+            dz2 = pl['dzl'][d].view(M, 4 * H)
+            o.gemm(lctx, dz2, g['g.f0.blstm.%s.kernel' % dn], transA=True)
+            o.colsum(dz2, g['g.f0.blstm.%s.bias' % dn])
+            gU = g['g.f0.blstm.%s.recurrent' % dn]
+            if T > 1:
+                hd = pl['hout'][:, :, d * H:(d + 1) * H]
+                if d == 0:      # forward direction: the state feeding step t is h[t-1]
+                    o.gemm(hd[:, 0:T - 1], pl['dzl'][d][:, 1:T], gU, transA=True)
+                else:           # backward direction: the state feeding step t is h[t+1]
+                    o.gemm(hd[:, 1:T], pl['dzl'][d][:, 0:T - 1], gU, transA=True)
+            else:
+                o.fill_segments(gU.view(-1), gU.numel(), 0.0)
+        return f0_ev
+
+    def backward(self, pl, out, dout, sync=None, f0_issued=None):
         """dout = d(loss)/d(out) [B,T,O]; fills params.g for every trainable generator parameter."""
         o, a, p, g = self.ops, self.a, self.params.p, self.params.g
         sync = sync or LocalSync()
@@ -405,35 +443,14 @@ class Generator(_BNNet):
         L, Ln = a.gen_nbcnnlayers, a.gen_nbcnnlayers // 2
         lctx, dl = pl['lctx'], pl['d_lctx']
         out2, dout2 = out.view(M, O), dout.view(M, O)
-        # ---- F0 branch on the side lane (BPTT is latency-bound); its share of d(lctx) goes to its own buffer
+        # ---- F0 branch on the side lane (BPTT is latency-bound); its share of d(lctx) goes to its own buffer.  f0_issued: the caller
+        # has already queued backward_f0() on that lane (generator step: behind the F0 column's loss term, without a fork)
         o.preshare(lctx)
-        f0_ev = None
-        with o.side_lane():
-            o.copy2d(pl['df0'], dout2[:, 0:1])
-            hout2 = pl['hout'].view(M, 2 * H)
-            o.gemm(hout2, pl['df0'], g['g.f0.out.kernel'], transA=True)
-            o.colsum(pl['df0'], g['g.f0.out.bias'])
-            o.gemm(pl['df0'], p['g.f0.out.kernel'], pl['dhout'].view(M, 2 * H), transB=True)
-            U = [p['g.f0.blstm.fw.recurrent'], p['g.f0.blstm.bw.recurrent']]
-            o.lstm_bwd(pl['dhout'], U, pl['gates'], pl['cstate'], pl['dzl'])
-            # the branch's share of d(lctx) first: it is all the ctx trunk waits for; the weight gradients follow behind the event
-            for d, dn in enumerate(('fw', 'bw')):
-                o.gemm(pl['dzl'][d].view(M, 4 * H), p['g.f0.blstm.%s.kernel' % dn], pl['d_lctx_f0'], transB=True,
-                       flags=EPI_ACCUM if d > 0 else 0)
-            f0_ev = o.lane_event()
-            for d, dn in enumerate(('fw', 'bw')):
-                dz2 = pl['dzl'][d].view(M, 4 * H)
-                o.gemm(lctx, dz2, g['g.f0.blstm.%s.kernel' % dn], transA=True)
-                o.colsum(dz2, g['g.f0.blstm.%s.bias' % dn])
-                gU = g['g.f0.blstm.%s.recurrent' % dn]
-                if T > 1:
-                    hd = pl['hout'][:, :, d * H:(d + 1) * H]
-                    if d == 0:      # forward direction: the state feeding step t is h[t-1]
-                        o.gemm(hd[:, 0:T - 1], pl['dzl'][d][:, 1:T], gU, transA=True)
-                    else:           # backward direction: the state feeding step t is h[t+1]
-                        o.gemm(hd[:, 1:T], pl['dzl'][d][:, 0:T - 1], gU, transA=True)
-                else:
-                    o.fill_segments(gU.view(-1), gU.numel(), 0.0)
+        if f0_issued is not None:
+            f0_ev = f0_issued[0]
+        else:
+            with o.side_lane():
+                f0_ev = self.backward_f0(pl, out, dout)
         # ---- NM branch: shares nothing but lctx with the spectral branch -> second side lane, its share of d(lctx) in its own buffer
         dl_nm = pl['d_lctx_nm']
 

@@ -233,6 +233,7 @@ class CudaOps(object):
         self._red = {}
         self._wg = {}
         self._lse_ws = None
+        self._lse_ws_lane = {}     # lane -> workspace of the column-window LSE (calls on different lanes may overlap)
         self._splitk_ws = {}       # lane -> split-K workspace
         self._ws_keep = []
         self._tag = None           # batch-shape tag (shape_scope): per-shape scratch is recorded under it and freed by release_shape()
@@ -312,7 +313,7 @@ class CudaOps(object):
 
     # -- two-lane execution: independent branches of a step on two streams (fork / join, capturable) ------------------
     @contextlib.contextmanager
-    def side_lane(self, second=False, lane=None):
+    def side_lane(self, second=False, lane=None, nowait=False):
         """Kernels issued inside run on a side stream, ordered after everything issued so far on the caller's stream, and
         concurrently with what the caller issues afterwards until join_lanes().  Scratch workspaces are per lane; operands
         shared by lanes must have their bf16 shadows taken BEFORE the fork (shadow()).  Two side streams exist: lane 1 (default,
@@ -333,7 +334,8 @@ class CudaOps(object):
             if self._side is None:
                 self._side = torch.cuda.Stream(device=self.device)
             side = self._side
-        side.wait_stream(cur)
+        if not nowait:      # nowait: continue an already forked lane where it stands (what is queued needs nothing newer of the caller's lane)
+            side.wait_stream(cur)
         outer, self._lane = self._lane, lane
         try:
             with torch.cuda.stream(side):
@@ -379,10 +381,10 @@ class CudaOps(object):
             torch.cuda.current_stream(self.device).wait_event(ev)
 
     def join_lanes(self, which=None):
-        """The caller's stream waits for the side lanes (which = 1: for the first one only)."""
-        if self.lanes and self._side is not None:
+        """The caller's stream waits for the side lanes (which = 1 / 2: for that one only)."""
+        if self.lanes and self._side is not None and which != 2:
             torch.cuda.current_stream(self.device).wait_stream(self._side)
-        if self._side2_open and which is None:
+        if self._side2_open and which != 1:
             torch.cuda.current_stream(self.device).wait_stream(self._side2)
             self._side2_open = False
 
@@ -1015,6 +1017,20 @@ class CudaOps(object):
         self._ck(self.lib.pctts_lse_loss_grad(pred.data_ptr(), real.data_ptr(), _ptr(w), _ptr(dpred), rows, O, float(scale_loss),
                                               float(scale_grad), losses.data_ptr(), slot, self._lse_ws.data_ptr(),
                                               self._stream()), 'pctts_lse_loss_grad')
+
+    def lse_loss_grad_cols(self, pred, real, w, dpred, c0, nc, scale_loss, scale_grad, losses, slot):
+        """lse_loss_grad over the columns [c0, c0 + nc) only (loss sum -> losses[slot], gradient -> those columns of dpred)."""
+        O = pred.shape[-1]
+        rows = pred.numel() // O
+        assert pred.is_contiguous() and real.is_contiguous() and (dpred is None or dpred.is_contiguous())
+        ws = self._lse_ws_lane.get(self._lane)
+        if ws is None:
+            ws = self._lse_ws_lane[self._lane] = torch.zeros(self.lib.pctts_lse_workspace_bytes(), dtype=torch.uint8, device=self.device)
+        if dpred is not None:
+            self._wrote(dpred)
+        self._ck(self.lib.pctts_lse_loss_grad_cols(pred.data_ptr(), real.data_ptr(), _ptr(w), _ptr(dpred), rows, O, int(c0), int(nc),
+                                                   float(scale_loss), float(scale_grad), losses.data_ptr(), slot, ws.data_ptr(),
+                                                   self._stream()), 'pctts_lse_loss_grad_cols')
 
     def adam(self, p, g, m, v, lr, beta1, beta2, eps, step):
         assert p.is_contiguous() and g.is_contiguous() and step.dtype == torch.int32

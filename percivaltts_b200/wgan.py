@@ -19,8 +19,8 @@ from . import arch as A
 from .engine import Generator, Critic, LocalSync
 
 # slots of the device loss vector
-L_REAL, L_FAKE, L_GP, L_CRITIC, L_GW, L_GLS, L_GEN, L_SSE = 0, 1, 2, 3, 4, 5, 6, 7
-NLOSS = 8
+L_REAL, L_FAKE, L_GP, L_CRITIC, L_GW, L_GLS, L_GEN, L_SSE, L_GLS_F0 = 0, 1, 2, 3, 4, 5, 6, 7, 8
+NLOSS = 9
 
 
 def critic_runs(generator_updates):
@@ -53,6 +53,10 @@ class WGANStepper(object):
         # PCTTS_STAGGER_CONV1D=1: the critic's ctx branch (side lane) forked behind the generator's first Conv1D instead of beside it
         # -- measured on B200: critic step 1.962 -> 1.995 ms (the side lane then ends later than the frozen generator), so it stays off
         self.stagger_conv1d = os.environ.get('PCTTS_STAGGER_CONV1D', '0') != '0'
+        # PCTTS_F0_FREE=1: generator step with the F0 lane (LSTM forward, its LSE column, BPTT) never joined between forward and backward
+        # -- measured on B200: generator step 2.45-2.48 vs 2.43-2.50 ms, inside the noise (what the LSTM pair costs the step is the 80 SMs
+        # it holds for 1 ms, not the position of its join), so it stays off
+        self.f0_free = os.environ.get('PCTTS_F0_FREE', '0') != '0'
         self.wbar = float(w_wgan_mean)
         self.w_ls = None
         if errtype == 'WLSWGAN':
@@ -156,19 +160,37 @@ class WGANStepper(object):
         gpl = self.G.plan(B, T)
         pred = bf['fake']
         cpl = self.C.plan(1, B, T)
+        pl_ctx_ev = [None]
+
         def critic_ctx_branch():
             with o.side_lane():
                 self.C.forward_ctx(cpl, X)
+                pl_ctx_ev[0] = o.lane_event()
         if not self.stagger_conv1d:
             critic_ctx_branch()
-        self.G.forward(gpl, X, pred, training=True, update_stats=True, sync=sync,      # joins the lanes
-                       after_first_conv=critic_ctx_branch if self.stagger_conv1d else None)
-        o.join_lanes()
+        # The F0 lane (LSTM) is not joined here: the critic reads the spectral columns only, so the recurrence and, behind it, the
+        # F0 column's loss term and the BPTT run beside the critic's forward / backward and the other branches' backward.
+        f0_free = self.f0_free and self.errtype == 'WLSWGAN'
+        f0_issued = None
+        self.G.forward(gpl, X, pred, training=True, update_stats=True, sync=sync,
+                       after_first_conv=critic_ctx_branch if self.stagger_conv1d else None, join_f0=not f0_free)
+        if f0_free:
+            o.join_lanes(2)         # (the critic's ctx branch ran on lane 1 in FRONT of the F0 branch; forward_spec needs it)
+            o.wait_lane_event(pl_ctx_ev[0])
+        else:
+            o.join_lanes()
         d = self.C.forward_spec(cpl, pred[:, :, 1:1 + S].unsqueeze(-1))
         ng = float(M * sync.world)
         o.sum_scaled(d, -1.0 / ng, self.losses, L_GW)
         dpred = bf['dpred']
-        if self.errtype == 'WLSWGAN':
+        if self.errtype == 'WLSWGAN' and f0_free:
+            # specweighted_lse_loss (:73-79) in two parts: every column but F0 here, the F0 column on the F0 lane behind the LSTM
+            o.lse_loss_grad_cols(pred, Y, self.w_ls, dpred, 1, O - 1, 1.0 / (ng * O), 1.0 / (ng * O), self.losses, L_GLS)
+            with o.side_lane(nowait=True):      # behind the LSTM forward on its own lane; nothing here needs the main lane
+                o.lse_loss_grad_cols(pred, Y, self.w_ls, dpred, 0, 1, 1.0 / (ng * O), 1.0 / (ng * O), self.losses, L_GLS_F0)
+                f0_issued = (self.G.backward_f0(gpl, pred, dpred),)
+            seed = -self.wbar / ng
+        elif self.errtype == 'WLSWGAN':
             o.lse_loss_grad(pred, Y, self.w_ls, dpred, 1.0 / (ng * O), 1.0 / (ng * O), self.losses, L_GLS)   # (:73-79)
             o.loss_combine(self.losses, L_GEN, L_GW, self.wbar, L_GLS, 1.0)                                  # (:213)
             seed = -self.wbar / ng
@@ -179,7 +201,10 @@ class WGANStepper(object):
             seed = -1.0 / ng
         o.fill_segments(cpl['dd'].view(-1), M, seed)
         self.C.backward_to_input(cpl, dpred[:, :, 1:1 + S].unsqueeze(-1), accumulate=True)
-        self.G.backward(gpl, pred, dpred, sync=sync)
+        self.G.backward(gpl, pred, dpred, sync=sync, f0_issued=f0_issued)
+        if self.errtype == 'WLSWGAN' and f0_free:      # the two parts of the LSE term (backward joined the lanes), then (:213)
+            o.loss_combine(self.losses, L_GLS, L_GLS, 1.0, L_GLS_F0, 1.0)
+            o.loss_combine(self.losses, L_GEN, L_GW, self.wbar, L_GLS, 1.0)
         lv = self.losses[L_GW:L_GEN + 1]
         if apply:
             sync.grad_adam(self.G.params, *self.gopt, eps=self.adam_eps, losses=lv if sync.world > 1 else None)

@@ -63,7 +63,7 @@ class CpuOpsDouble(object):
     def release_shape(self, tag):
         pass
 
-    def side_lane(self, second=False, lane=None):
+    def side_lane(self, second=False, lane=None, nowait=False):
         import contextlib
         return contextlib.nullcontext(self)
 
@@ -367,6 +367,14 @@ class CpuOpsDouble(object):
         losses[slot] = float((d * d * wv).double().sum() * scale_loss)
         if dpred is not None:
             dpred.copy_(scale_grad * 2.0 * d * wv)
+
+    def lse_loss_grad_cols(self, pred, real, w, dpred, c0, nc, scale_loss, scale_grad, losses, slot):
+        self.launches += 1
+        d = (pred - real)[..., c0:c0 + nc]
+        wv = (w if w is not None else torch.ones(pred.shape[-1], dtype=pred.dtype))[c0:c0 + nc]
+        losses[slot] = float((d * d * wv).double().sum() * scale_loss)
+        if dpred is not None:
+            dpred[..., c0:c0 + nc] = scale_grad * 2.0 * d * wv
 
     def adam(self, p, g, m, v, lr, beta1, beta2, eps, step):
         self.launches += 1
