@@ -244,6 +244,7 @@ int pctts_adam(float* p, const float* g, float* m, float* v, long n, float lr, f
                void* stream);
 
 /* ---- small movers -------------------------------------------------------------------------------------------------------- */
+int pctts_umma_probe(int layout, int N, int nmma, int shift_rows, long long* out, void* stream);   /* developer probe: tcgen05.mma issue rate per operand layout (umma_probe.cu) */
 int pctts_stamp(unsigned long long* slot, void* stream);   /* developer probe: %globaltimer (ns) at this point of the stream */
 int pctts_add(float* out, const float* a, const float* b, long n, void* stream);
 int pctts_sigmoid_bwd(const float* dy, long lddy, const float* y, long ldy, float* dz, long lddz, long rows, int cols, void* stream);
