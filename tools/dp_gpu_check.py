@@ -63,6 +63,18 @@ def main():
     for i in range(6):
         Xb, Yb, _ = O.synthetic_batch(ao, Bg, T, seed=20 + i)
         tr.train_on_batch(i * 5, parallel.shard_batch(Xb, rank, world), parallel.shard_batch(Yb, rank, world))
+    # a rank that arrives late (a host pause of 3 s before one step) is waited for, not timed out on: the exchange's spin limit is ~60 s
+    # and its time-out flag is read back with the losses of every step (DistSync.check_peer)
+    if world > 1 and sync._peer is not None:
+        import time
+        if rank == world - 1:
+            time.sleep(3.0)
+        Xb, Yb, _ = O.synthetic_batch(ao, Bg, T, seed=40)
+        tr.train_on_batch(30, parallel.shard_batch(Xb, rank, world), parallel.shard_batch(Yb, rank, world))
+        torch.cuda.synchronize()
+        late_ok = not sync.peer_failed()
+        print('rank %d: step with rank %d arriving 3 s late: %s' % (rank, world - 1, 'ok' if late_ok else 'FAILED (time-out flag set)'), flush=True)
+        ok = ok and late_ok
     # soak of the peer-memory exchange: 200 replays of a captured graph holding 8 exchanges of different sizes (the parity
     # double-buffering of slots / flags under replay at this world size), results checked, time-out flag must stay 0
     soak_ok = True
