@@ -247,6 +247,7 @@ int pctts_adam(float* p, const float* g, float* m, float* v, long n, float lr, f
 int pctts_umma_probe(int layout, int N, int nmma, int shift_rows, long long* out, void* stream);   /* developer probe: tcgen05.mma issue rate per operand layout (umma_probe.cu) */
 int pctts_stamp(unsigned long long* slot, void* stream);   /* developer probe: %globaltimer (ns) at this point of the stream */
 int pctts_add(float* out, const float* a, const float* b, long n, void* stream);
+int pctts_add3(float* out, const float* a, const float* b, const float* c, long n, void* stream);   /* out = (a + b) + c */
 int pctts_sigmoid_bwd(const float* dy, long lddy, const float* y, long ldy, float* dz, long lddz, long rows, int cols, void* stream);
 int pctts_copy2d(float* dst, long ldd, const float* src, long lds, long rows, int cols, int accumulate, void* stream);
 int pctts_pad_time(float* dst, const float* src, int B, int T, int C, int left, int right, void* stream);

@@ -234,6 +234,12 @@ __global__ void stamp_kernel(unsigned long long* slot) {
     }
 }
 
+__global__ void add3_kernel(float* __restrict__ out, const float* __restrict__ a, const float* __restrict__ b,
+                            const float* __restrict__ c, long n) {
+    pdl_entry();
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) out[i] = (a[i] + b[i]) + c[i];
+}
+
 __global__ void add_kernel(float* __restrict__ out, const float* __restrict__ a, const float* __restrict__ b, long n) {
     pdl_entry();
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) out[i] = a[i] + b[i];
@@ -427,6 +433,15 @@ extern "C" int pctts_add(float* out, const float* a, const float* b, long n, voi
     if (!out || !a || !b || n < 0) return PCTTS_EINVAL;
     if (n == 0) return PCTTS_OK;
     pctts_launch(add_kernel, ew_blocks(n), ET, 0, (cudaStream_t)stream, out, a, b, n);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
+/* out = (a + b) + c  (the generator's three branch shares of d(lctx)) */
+extern "C" int pctts_add3(float* out, const float* a, const float* b, const float* c, long n, void* stream) {
+    if (!out || !a || !b || !c || n < 0) return PCTTS_EINVAL;
+    if (n == 0) return PCTTS_OK;
+    pctts_launch(add3_kernel, ew_blocks(n), ET, 0, (cudaStream_t)stream, out, a, b, c, n);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

@@ -1,3 +1,6 @@
+// GENERAL-SHAPE FALLBACK of the recurrence: used only where lstm_fast.cu does not apply (H not a multiple of 32 up to 256, the tiny
+// test configurations) or with PCTTS_LSTM_FAST=0 for A/B runs.  The demo shape (H = 256) runs lstm_fast.cu.
+//
 // Persistent LSTM recurrence (forward and BPTT) for pLSTM / pBLSTM (networktts.py:72-96): Keras LSTM with tanh /
 // sigmoid, gate order i,f,c,o, return_sequences; Bidirectional = two directions concatenated [fwd, bwd].
 //

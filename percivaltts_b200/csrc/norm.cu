@@ -173,6 +173,23 @@ __global__ void __launch_bounds__(RT) colreduce_final_kernel(const double* __res
     if (lane == 0) sums[e] = q;
 }
 
+// Stage 2 of a plain column sum with the hand-over to the gradient buffer in the same launch (bias gradients): the order of
+// colreduce_final_kernel, then out[c] (+)= (float)sum -- what colreduce_final_kernel + sums_to_grads_kernel did in two launches.
+__global__ void __launch_bounds__(RT) colsum_final_kernel(const double* __restrict__ partial, double* __restrict__ sums, int nblk, int C,
+                                                          float* __restrict__ out, int accumulate) {
+    pdl_entry();
+    const int c = blockIdx.x * (RT / 32) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (c >= C) return;
+    double q = 0.0;
+    for (int b = lane; b < nblk; b += 32) q += partial[(long)b * 2 * C + c];
+    q = warp_sum_d(q);
+    if (lane == 0) {
+        sums[c] = q;
+        out[c] = (accumulate ? out[c] : 0.f) + (float)(q * 1.0);
+    }
+}
+
 // STATS finalize: mean / invstd from (possibly all-reduced) sums; optional moving-average update.
 __global__ void bn_finalize_kernel(const double* __restrict__ sums, double count, int C, float eps, float momentum,
                                    float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ moving_mean,
@@ -572,8 +589,8 @@ extern "C" int pctts_colsum(const float* x, long rows, int C, float* out, int ac
     Ws w = carve(workspace, rows, C);
     cudaStream_t st = (cudaStream_t)stream;
     RedArgs a{x, nullptr, nullptr, nullptr, nullptr, nullptr, rows, C, 0};
-    PCTTS_CUDA_RC(run_colreduce<MODE_COLSUM>(a, w, st));
-    pctts_launch(sums_to_grads_kernel, pctts_div_up(C, 128), 128, 0, st, w.sums, C, out, nullptr, accumulate, 1.0);
+    PCTTS_CUDA_RC(run_colreduce<MODE_COLSUM>(a, w, st, false));
+    pctts_launch(colsum_final_kernel, pctts_div_up(C, RT / 32), RT, 0, st, w.partial, w.sums, reduce_grid(rows, C), C, out, accumulate);
     PCTTS_LAUNCH_CHECK();
     return PCTTS_OK;
 }

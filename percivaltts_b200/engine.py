@@ -510,8 +510,7 @@ class Generator(_BNNet):
         else:
             o.join_lanes(1)
         o.wait_lane_event(nm_ev)
-        o.add(dl, dl, pl['d_lctx_f0'])
-        o.add(dl, dl, dl_nm)
+        o.add3(dl, dl, pl['d_lctx_f0'], dl_nm)
         # ---- ctx trunk: pFC x2 then pCNN1D stack
         dcur = dl
         for i in (1, 0):

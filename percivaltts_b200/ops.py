@@ -1039,6 +1039,11 @@ class CudaOps(object):
                                      float(beta2), float(eps), step.data_ptr(), self._stream()), 'pctts_adam')
 
     # -- small movers ----------------------------------------------------------------------------------------
+    def add3(self, out, a, b, c):
+        assert out.is_contiguous() and a.is_contiguous() and b.is_contiguous() and c.is_contiguous()
+        self._wrote(out)
+        self._ck(self.lib.pctts_add3(out.data_ptr(), a.data_ptr(), b.data_ptr(), c.data_ptr(), out.numel(), self._stream()), 'pctts_add3')
+
     def add(self, out, a, b):
         assert out.is_contiguous() and a.is_contiguous() and b.is_contiguous()
         self._wrote(out)

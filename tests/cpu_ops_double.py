@@ -386,6 +386,10 @@ class CpuOpsDouble(object):
         step += 1
 
     # ---- small movers ----------------------------------------------------------------------------------------
+    def add3(self, out, a, b, c):
+        self.launches += 1
+        out.copy_((a + b) + c)
+
     def add(self, out, a, b):
         self.launches += 1
         out.copy_(a + b)
