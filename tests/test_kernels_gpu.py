@@ -265,6 +265,45 @@ def test_grad_sync_adam_single_rank_equals_adam_kernel(cuda_ops):
     assert int(step) == int(step2) == 3 and int(ctl[0]) == 3 and int(err) == 0
 
 
+@pytest.mark.parametrize('N,T,F', [(2, 37, 129), (1, 5, 17), (3, 40, 65)])
+def test_conv2d_dgrad_reads_forward_kernel(N, T, F):
+    """conv2d_dgrad (tensor-core kernel with PCTTS_EPI_WFLIP: the flipped kernel is formed while the weight operand is built)
+    against an explicit flip + convolution; with a LeakyReLU' mask and accumulate."""
+    ops = OPS.CudaOps(precision='fp32')
+    w = rnd(5, 5, 4, 4, seed=1)
+    dy, aux, acc0 = rnd(N, T, F, 4, seed=2), rnd(N, T, F, 4, seed=3), rnd(N, T, F, 4, seed=4)
+    wt = torch.zeros(5, 5, 4, 4, dtype=torch.float64)
+    REF.conv2d_flip(w, wt)
+    for flags, kw in ((0, {}), (0, dict(aux=aux)), (OPS.EPI_ACCUM, {})):
+        want = acc0.clone()
+        REF.conv2d(dy, wt, want, flags=flags, **kw)
+        got = dev(acc0)
+        scratch = torch.zeros(5, 5, 4, 4, device='cuda')
+        n0 = ops.launches
+        ops.conv2d_dgrad(dev(dy), dev(w), got, scratch, flags=flags, **dict((k, dev(v)) for k, v in kw.items()))
+        assert ops.launches == n0 + 1          # no flip launch
+        close(got, want, 2e-5, ('conv2d_dgrad', flags, list(kw)))
+
+
+def test_lse_column_window_and_add3(cuda_ops):
+    """pctts_lse_loss_grad_cols over two column windows = pctts_lse_loss_grad over all columns (loss sums add up, gradients are the
+    same elements); pctts_add3."""
+    M, O = 777, 163
+    pred, real, w = dev(rnd(M, O)), dev(rnd(M, O, seed=1)), dev(rnd(O, seed=2).abs())
+    losses = torch.zeros(9, device='cuda')
+    d_all, d_win = torch.zeros(M, O, device='cuda'), torch.full((M, O), 7.0, device='cuda')
+    cuda_ops.lse_loss_grad(pred, real, w, d_all, 0.5, 0.25, losses, 0)
+    cuda_ops.lse_loss_grad_cols(pred, real, w, d_win, 1, O - 1, 0.5, 0.25, losses, 1)
+    cuda_ops.lse_loss_grad_cols(pred, real, w, d_win, 0, 1, 0.5, 0.25, losses, 2)
+    torch.cuda.synchronize()
+    assert torch.equal(d_all, d_win)
+    assert abs(float(losses[0]) - float(losses[1] + losses[2])) < 1e-5 * abs(float(losses[0]))
+    a, b, c = dev(rnd(1000, 16)), dev(rnd(1000, 16, seed=1)), dev(rnd(1000, 16, seed=2))
+    out = torch.zeros(1000, 16, device='cuda')
+    cuda_ops.add3(out, a, b, c)
+    assert torch.equal(out, (a + b) + c)
+
+
 def test_conv2d_strided_feature_views(cuda_ops):
     """First critic layer reads / last generator layer writes the spectral columns of a [B,T,O] tensor in place."""
     B, T, S, O = 2, 21, 17, 23
