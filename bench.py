@@ -393,15 +393,17 @@ def run_b200(args):
     n2 = lib.pctts_launch_count()
     st.generator_step(s.X, s.Y, apply=True)
     n_gen = lib.pctts_launch_count() - n2
+    n3 = lib.pctts_launch_count()
+    if tr.fuse_steps:
+        st.critic_generator_step(s.X, s.Y)
+    n_both = (lib.pctts_launch_count() - n3) if tr.fuse_steps else n_critic + n_gen
     torch.cuda.synchronize(device)
 
     def resident_step(i):
         x, y = dev[i % R]
         s.X.copy_(x, non_blocking=True)
         s.Y.copy_(y, non_blocking=True)
-        tr.critic_step_device(s)
-        if i % 5 == 0:
-            tr.generator_step_device(s)
+        tr.step_device(s, i % 5 == 0)       # what train_on_batch runs: critic update, + generator update on the same batch every 5th step
 
     # ---- value: device-resident loop ---------------------------------------------------------------------------------
     # the sampler starts in front of the warm-up: nvidia-smi's own start-up (NVML initialisation takes driver locks and was seen
@@ -438,6 +440,7 @@ def run_b200(args):
         return a0.elapsed_time(a1) / n
     critic_ms = max_over_ranks(loop_ms(lambda: tr.critic_step_device(s), 10), device)
     gen_ms = max_over_ranks(loop_ms(lambda: tr.generator_step_device(s), 5), device)
+    both_ms = max_over_ranks(loop_ms(lambda: tr.step_device(s, True), 5), device)      # critic + generator update of one batch, one graph
     tr.generator_updates = 25
 
     # ---- e2e: the public API with host buffers --------------------------------------------------------------------------
@@ -494,7 +497,8 @@ def run_b200(args):
 
     if rank != 0:
         return
-    launches = args.steps * n_critic + ((args.steps + 4) // 5) * n_gen
+    ngen_steps = (args.steps + 4) // 5
+    launches = (args.steps - ngen_steps) * n_critic + ngen_steps * n_both
     out = {
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'strong' if args.global_batch else 'weak', 'vs_baseline': None,
@@ -503,11 +507,12 @@ def run_b200(args):
         'config': {'workload': WORKLOAD if (ops.precision == 'fp32' and not args.global_batch) else
                    WORKLOAD.replace('fp32', ops.precision).replace('B=10/GPU', 'B=%d/GPU' % B).replace('config #2', 'config #3' if ops.precision == 'bf16' else 'config #2 variant'),
                    'global_batch_utterances': B * world, 'frames_per_step': B * T * world,
-                   'schedule': '1 critic update per step + 1 generator update every 5th step (generator_updates>=25)',
+                   'schedule': '1 critic update per step + 1 generator update every 5th step (generator_updates>=25); on those steps both updates '
+                               'run as one graph sharing the generator forward pass of the batch',
                    'l2': 'per-step working set (activations of 3x batched critic + generator, ~0.6 GB) exceeds the 126 MB L2; '
                          'inputs cycle over 4 resident batches',
                    'parallelism': 'dp%d sync-BN + flat-gradient all-reduce' % world if world > 1 else 'single GPU'},
-        'critic_step_ms': critic_ms, 'generator_step_ms': gen_ms,
+        'critic_step_ms': critic_ms, 'generator_step_ms': gen_ms, 'critic_plus_generator_step_ms': both_ms,
         'conv_tc_util_pct': 100.0 * conv1d['tensor_pipe_frac'] if conv1d else None, 'gemm_precision': ops.precision,
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': e2e_h2d,
                 'd2h_bytes_per_step': e2e_d2h, 'ms_per_step': 1e3 * e2e_s / args.steps,
@@ -515,6 +520,7 @@ def run_b200(args):
         'e2e_sync': {'value': frames / e2e_sync_s, 'unit': UNIT, 'ms_per_step': 1e3 * e2e_sync_s / args.steps,
                      'call': 'OptimizerTTSWGAN.train_on_batch(batchid, X, Y) -- the reference\'s 3-argument hook, synchronous staging'},
         'gpu_launches': int(launches), 'kernels_per_critic_step': int(n_critic), 'kernels_per_generator_step': int(n_gen),
+        'kernels_per_critic_plus_generator_step': int(n_both),
         'clocks': clk, 'roofline': roofline, 'rooflines': rooflines, 'whole_step': whole,
     }
     if world == 1 and not args.no_cpu_baseline:

@@ -27,7 +27,7 @@ class _ShapeState(object):
         self.Yh = torch.empty(B, T, a.outsize, dtype=torch.float32, pin_memory=cuda)
         self.lossh = torch.zeros(W.NLOSS, dtype=torch.float32, pin_memory=cuda)
         self.errh = torch.zeros(1, dtype=torch.int32, pin_memory=cuda)       # peer-exchange time-out flag, read with the losses
-        self.g_critic = self.g_critic_alpha = self.g_gen = None
+        self.g_critic = self.g_critic_alpha = self.g_gen = self.g_both = None
 
 
 class DeviceTrainer(object):
@@ -45,6 +45,8 @@ class DeviceTrainer(object):
         self.max_shapes = int(max_shapes if max_shapes is not None else os.environ.get('PCTTS_SHAPE_CACHE', '128'))
         self.max_bytes = int(max_bytes if max_bytes is not None else float(os.environ.get('PCTTS_SHAPE_CACHE_GB', '32')) * 2 ** 30)
         self.graph_after = int(graph_after)
+        # critic + generator update of one batch share the generator's forward pass (wgan.critic_generator_step); PCTTS_FUSE_STEPS=0: two graphs
+        self.fuse_steps = os.environ.get('PCTTS_FUSE_STEPS', '1') != '0'
         self._shapes = OrderedDict()
         self._seen = {}
         self.evictions = 0
@@ -70,7 +72,7 @@ class DeviceTrainer(object):
             old = self._shapes.pop(key)
             if self._pf_placed is old:
                 self._pf_placed = None
-            old.g_critic = old.g_critic_alpha = old.g_gen = None      # the graphs (and their private pools) go first
+            old.g_critic = old.g_critic_alpha = old.g_gen = old.g_both = None      # the graphs (and their private pools) go first
             del old
             self.st.release(*key)
             self.evictions += 1
@@ -121,6 +123,11 @@ class DeviceTrainer(object):
         s.g_gen = torch.cuda.CUDAGraph()
         with torch.cuda.graph(s.g_gen):
             st.generator_step(s.X, s.Y, apply=True)
+        s.g_both = None
+        if self.fuse_steps:       # critic + generator update of one batch as ONE graph sharing the generator's forward pass
+            s.g_both = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(s.g_both):
+                st.critic_generator_step(s.X, s.Y)
 
     # ---- steps on resident device data ---------------------------------------------------------------------------
     def critic_step_device(self, s, explicit_alpha=False):
@@ -129,6 +136,20 @@ class DeviceTrainer(object):
         else:
             self.st.critic_step(s.X, s.Y, alpha=s.alpha if explicit_alpha else None, apply=True)
             self._account(s)
+
+    def step_device(self, s, with_generator, explicit_alpha=False):
+        """One train_on_batch on resident data: the critic update and, when due, the generator update on the same batch."""
+        if with_generator and self.fuse_steps and not explicit_alpha:
+            if getattr(s, 'g_both', None) is not None:
+                s.g_both.replay()
+            else:
+                self.st.critic_generator_step(s.X, s.Y)
+                self._account(s)
+            self.generator_updates += 1
+            return
+        self.critic_step_device(s, explicit_alpha=explicit_alpha)
+        if with_generator:
+            self.generator_step_device(s)
 
     def generator_step_device(self, s):
         if s.g_gen is not None:
@@ -210,11 +231,8 @@ class DeviceTrainer(object):
             self.stage(s, X, Y, alpha)
         self._pf = None
         self._pf_placed = None
-        self.critic_step_device(s, explicit_alpha=alpha is not None)
-        trained_gen = False
-        if batchid % W.critic_runs(self.generator_updates) == 0:
-            self.generator_step_device(s)
-            trained_gen = True
+        trained_gen = batchid % W.critic_runs(self.generator_updates) == 0
+        self.step_device(s, trained_gen, explicit_alpha=alpha is not None)
         s.lossh.copy_(self.st.losses, non_blocking=True)
         self.d2h_bytes += W.NLOSS * 4
         perr = getattr(self.st.sync, 'peer_err', None)

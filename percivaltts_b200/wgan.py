@@ -95,7 +95,19 @@ class WGANStepper(object):
     def critic_step(self, X, *args, **kw):
         return self._scoped(self._critic_step, X, *args, **kw)
 
-    def _critic_step(self, X, Y, alpha=None, apply=True):
+    def critic_generator_step(self, X, *args, **kw):
+        return self._scoped(self._critic_generator_step, X, *args, **kw)
+
+    def _critic_generator_step(self, X, Y, alpha=None):
+        """One critic update followed by one generator update on the SAME batch (what train_on_batch does whenever the generator is
+        due, optimizertts_wgan.py:216-241).  The generator's weights do not move in the critic step, so G(ctx) and every activation
+        of its forward pass are the same in both graphs of the reference: the critic step evaluates the whole generator once
+        (materialised, moving statistics updated) and the generator step starts from it instead of repeating the forward pass --
+        same values, one forward pass and one round of sync-BatchNorm exchanges less."""
+        self._critic_step(X, Y, alpha=alpha, apply=True, for_generator=True)
+        self._generator_step(X, Y, apply=True, reuse_forward=True)
+
+    def _critic_step(self, X, Y, alpha=None, apply=True, for_generator=False):
         """One critic update on device tensors X [B,T,ctx], Y [B,T,O].  alpha [B] overrides the random
         interpolation weights (RandomWeightedAverage, optimizertts_wgan.py:44-51)."""
         o, a, sync = self.ops, self.a, self.sync
@@ -119,9 +131,13 @@ class WGANStepper(object):
         if not stagger:
             critic_ctx_branch()
         # frozen generator, learning phase 1: batch statistics, no moving-average update (:121-128)
-        self.G.forward(gpl, X, bf['fake'], training=True, update_stats=False, sync=sync,
-                       spec_only=not self.critic_step_full_generator, materialize=False,
-                       after_first_conv=critic_ctx_branch if stagger else None)
+        if for_generator:       # the generator step that follows on this batch starts from this forward pass (critic_generator_step)
+            self.G.forward(gpl, X, bf['fake'], training=True, update_stats=True, sync=sync, spec_only=False, materialize=True,
+                           after_first_conv=critic_ctx_branch if stagger else None)
+        else:
+            self.G.forward(gpl, X, bf['fake'], training=True, update_stats=False, sync=sync,
+                           spec_only=not self.critic_step_full_generator, materialize=False,
+                           after_first_conv=critic_ctx_branch if stagger else None)
         if alpha is None:
             o.uniform(bf['alpha'], self.seed, self.counter)
             alpha = bf['alpha']
@@ -151,8 +167,9 @@ class WGANStepper(object):
     def generator_step(self, X, *args, **kw):
         return self._scoped(self._generator_step, X, *args, **kw)
 
-    def _generator_step(self, X, Y, apply=True):
-        """One generator update (BN moving statistics move here, like in the reference's generator_model)."""
+    def _generator_step(self, X, Y, apply=True, reuse_forward=False):
+        """One generator update (BN moving statistics move here, like in the reference's generator_model).  reuse_forward: the
+        generator's forward pass on this batch is the one the preceding critic step left in the plan (critic_generator_step)."""
         o, a, sync = self.ops, self.a, self.sync
         B, T, _ = X.shape
         M, S, O = B * T, a.spec_size, a.outsize
@@ -170,10 +187,14 @@ class WGANStepper(object):
             critic_ctx_branch()
         # The F0 lane (LSTM) is not joined here: the critic reads the spectral columns only, so the recurrence and, behind it, the
         # F0 column's loss term and the BPTT run beside the critic's forward / backward and the other branches' backward.
-        f0_free = self.f0_free and self.errtype == 'WLSWGAN'
+        f0_free = self.f0_free and self.errtype == 'WLSWGAN' and not reuse_forward
         f0_issued = None
-        self.G.forward(gpl, X, pred, training=True, update_stats=True, sync=sync,
-                       after_first_conv=critic_ctx_branch if self.stagger_conv1d else None, join_f0=not f0_free)
+        if reuse_forward:
+            if self.stagger_conv1d:
+                critic_ctx_branch()
+        else:
+            self.G.forward(gpl, X, pred, training=True, update_stats=True, sync=sync,
+                           after_first_conv=critic_ctx_branch if self.stagger_conv1d else None, join_f0=not f0_free)
         if f0_free:
             o.join_lanes(2)         # (the critic's ctx branch ran on lane 1 in FRONT of the F0 branch; forward_spec needs it)
             o.wait_lane_event(pl_ctx_ev[0])

@@ -271,3 +271,37 @@ def test_two_lane_execution_is_bit_identical_to_inline(cuda_ops, kw, B, T):
                 assert torch.equal(a, b)
     finally:
         cuda_ops.lanes = keep
+
+
+@pytest.mark.parametrize('kw,B,T', [(MID, 3, 57), (DEMO, 4, 96), (DEMO, 10, 400)])
+def test_critic_plus_generator_step_shares_the_generator_forward(cuda_ops, kw, B, T):
+    """train_on_batch runs the critic update and, when due, the generator update on the SAME batch; the generator's weights do not
+    move in between, so the fused step (wgan.critic_generator_step) evaluates the generator once -- materialised, moving statistics
+    updated -- and the generator update starts from that forward pass.  Weights, Adam slots, BatchNorm moving statistics and losses
+    must come out exactly as from the two separate steps."""
+    ao, wg, wc, wgt, wct, X, Y, alpha, st = setup(cuda_ops, kw, B, T)
+    Xd, Yd, ad = torch.tensor(X).cuda(), torch.tensor(Y).cuda(), torch.tensor(alpha).cuda()
+    snap = [t.clone() for t in (st.G.params.flat, st.G.params.state, st.G.params.m, st.G.params.v, st.G.params.step,
+                                st.C.params.flat, st.C.params.m, st.C.params.v, st.C.params.step)]
+
+    def restore():
+        for dst, src in zip((st.G.params.flat, st.G.params.state, st.G.params.m, st.G.params.v, st.G.params.step,
+                             st.C.params.flat, st.C.params.m, st.C.params.v, st.C.params.step), snap):
+            dst.copy_(src)
+        cuda_ops.refresh_persistent(st.G.params.flat)
+        cuda_ops.refresh_persistent(st.C.params.flat)
+
+    def state():
+        torch.cuda.synchronize()
+        return [t.clone() for t in (st.G.params.flat, st.G.params.state, st.G.params.m, st.G.params.v, st.C.params.flat, st.C.params.m,
+                                    st.C.params.v, st.losses[:W.L_SSE])]
+
+    st.critic_step(Xd, Yd, alpha=ad, apply=True)
+    st.generator_step(Xd, Yd, apply=True)
+    want = state()
+    restore()
+    st.critic_generator_step(Xd, Yd, alpha=ad)
+    got = state()
+    for a, b in zip(want, got):
+        assert torch.equal(a, b)
+
