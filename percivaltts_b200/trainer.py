@@ -27,7 +27,7 @@ class _ShapeState(object):
         self.Yh = torch.empty(B, T, a.outsize, dtype=torch.float32, pin_memory=cuda)
         self.lossh = torch.zeros(W.NLOSS, dtype=torch.float32, pin_memory=cuda)
         self.errh = torch.zeros(1, dtype=torch.int32, pin_memory=cuda)       # peer-exchange time-out flag, read with the losses
-        self.g_critic = self.g_critic_alpha = self.g_gen = self.g_both = None
+        self.g_critic = self.g_critic_alpha = self.g_gen = self.g_both = self.g_both_alpha = None
 
 
 class DeviceTrainer(object):
@@ -72,7 +72,7 @@ class DeviceTrainer(object):
             old = self._shapes.pop(key)
             if self._pf_placed is old:
                 self._pf_placed = None
-            old.g_critic = old.g_critic_alpha = old.g_gen = old.g_both = None      # the graphs (and their private pools) go first
+            old.g_critic = old.g_critic_alpha = old.g_gen = old.g_both = old.g_both_alpha = None      # the graphs (and their private pools) go first
             del old
             self.st.release(*key)
             self.evictions += 1
@@ -123,11 +123,14 @@ class DeviceTrainer(object):
         s.g_gen = torch.cuda.CUDAGraph()
         with torch.cuda.graph(s.g_gen):
             st.generator_step(s.X, s.Y, apply=True)
-        s.g_both = None
+        s.g_both = s.g_both_alpha = None
         if self.fuse_steps:       # critic + generator update of one batch as ONE graph sharing the generator's forward pass
             s.g_both = torch.cuda.CUDAGraph()
             with torch.cuda.graph(s.g_both):
                 st.critic_generator_step(s.X, s.Y)
+            s.g_both_alpha = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(s.g_both_alpha):
+                st.critic_generator_step(s.X, s.Y, alpha=s.alpha)
 
     # ---- steps on resident device data ---------------------------------------------------------------------------
     def critic_step_device(self, s, explicit_alpha=False):
@@ -139,11 +142,11 @@ class DeviceTrainer(object):
 
     def step_device(self, s, with_generator, explicit_alpha=False):
         """One train_on_batch on resident data: the critic update and, when due, the generator update on the same batch."""
-        if with_generator and self.fuse_steps and not explicit_alpha:
+        if with_generator and self.fuse_steps:
             if getattr(s, 'g_both', None) is not None:
-                s.g_both.replay()
+                (s.g_both_alpha if explicit_alpha else s.g_both).replay()
             else:
-                self.st.critic_generator_step(s.X, s.Y)
+                self.st.critic_generator_step(s.X, s.Y, alpha=s.alpha if explicit_alpha else None)
                 self._account(s)
             self.generator_updates += 1
             return
