@@ -75,3 +75,15 @@ def test_host_planning_calls_need_no_gpu():
     assert 0 < lib.pctts_conv2d_tc_stat_partials(2, 40, 33) < 148
     assert lib.pctts_conv2d_tc_supported(129, 4, 4, 5, 5, 2, 2) == 1 and lib.pctts_conv2d_tc_supported(129, 1, 4, 5, 5, 2, 2) == 0
     assert lib.pctts_peer_allreduce_bytes(8, 1024) > 2 * 1024 * 8 and lib.pctts_peer_allreduce_bytes(17, 1024) == -1
+    # round 2: the chain kernel's cluster size per sample (demo: 8 CTAs of 50 frames; two operand planes fit 80 frames per CTA; a
+    # sequence too long for 16 CTAs of shared memory is refused), the one-launch stack weight gradient's partial-sum workspace
+    # (CTAs divided between the layers), the control block of the fused all-reduce + Adam, the sync-BN buffers incl. the push areas
+    assert lib.pctts_conv2d_chain_supported(400, 129, 6) == 8 and lib.pctts_conv2d_chain_supported(50, 129, 6) == 1
+    assert lib.pctts_conv2d_chain_supported(54, 129, 6) == 1 and lib.pctts_conv2d_chain_supported(55, 129, 6) == 2
+    assert lib.pctts_conv2d_chain_supported(400, 129, 3) == 8 and lib.pctts_conv2d_chain_supported(4000, 129, 6) == 0
+    assert lib.pctts_conv2d_chain_supported(0, 129, 6) == 0 and lib.pctts_conv2d_chain_supported(400, 129, 0) == 0
+    assert lib.pctts_conv2d_wgrad_multi_workspace(8) == 8 * 18 * 404 and lib.pctts_conv2d_wgrad_multi_workspace(1) == 148 * 404
+    assert lib.pctts_conv2d_wgrad_multi_workspace(0) == 0 and lib.pctts_conv2d_wgrad_multi_workspace(10) == 0
+    assert lib.pctts_grad_sync_ctl_bytes() == 512
+    assert lib.pctts_bn_sync_bytes(8) > 2 * 32 * 8 * 128 * 8 and lib.pctts_bn_sync_bytes(17) == -1
+
