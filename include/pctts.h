@@ -209,6 +209,24 @@ int pctts_bn_bwd_apply(const float* x, const float* dy, float* dx, const float* 
                        (1/world when the sums were all-reduced and the flat gradient is summed over ranks afterwards) */
 int pctts_colsum(const float* x, long rows, int C, float* out, int accumulate, void* workspace, void* stream);
 
+/* pctts_colsum without a workspace argument.  No counterpart in the reference; it exists for hosts that are not allowed to
+ * create device buffers of their own beyond the tensors they were handed: a plugin running inside another framework's
+ * allocator (which may forbid cudaMalloc while it owns the device or while a stream capture is open), a real-time or
+ * embedded caller whose memory budget was fixed at start-up, or a binding from a language runtime that can pass pointers but
+ * has no CUDA allocator.  The scratch pctts_colsum asks its caller for sits instead in a fixed array inside libpctts.so:
+ * about 4.9 MB of device memory on every GPU that loads the library, held until the process exits.
+ *   - x [rows, C] and out [C] are still the caller's device buffers; same result as pctts_colsum, bit for bit.
+ *   - Limit: C <= PCTTS_COLSUM_STATIC_MAX_C (any number of rows).  A wider matrix returns PCTTS_ELIMIT (-3) and launches nothing.
+ *   - The call runs on the CURRENT device; `stream` must belong to it.  The first call on each device looks the array's device
+ *     address up (cudaGetSymbolAddress); make that first call outside any stream capture.  Neither it nor any later call
+ *     calls cudaMalloc / cudaFree or any other allocating routine.
+ *   - All calls on one GPU share the one array, and it keeps whatever the previous call left in it.  Nothing in it has to start
+ *     at zero (each call overwrites every slot it later reads), but two calls whose kernels can overlap on the GPU -- different
+ *     streams, or different host threads on different streams -- race on it: order them (same stream, or an event). */
+#define PCTTS_COLSUM_STATIC_MAX_C 1024
+#define PCTTS_ELIMIT (-3)
+int pctts_colsum_static(const float* x, long rows, int C, float* out, int accumulate, void* stream);
+
 /* ---- LSTM / Bidirectional(LSTM) recurrence (networktts.py:72-96): persistent cluster kernel, U resident in smem -------- */
 /* zx* = x.W + b  [B,T,4H] (gate order i,f,c,o); U* [H,4H]; hout [B,T,ldh] (direction d -> columns d*H..); the gates and c buffers are
  * written when non-NULL (needed by the backward).  ndir = 1 (LSTM) or 2 (Bidirectional: direction 1 runs time-reversed).

@@ -18,7 +18,8 @@ _CTYPES = {
     'unsigned long long': ctypes.c_ulonglong, 'void': None,
 }
 
-ERRORS = {-1: 'PCTTS_EINVAL (bad argument)', -2: 'PCTTS_EUNSUPPORTED (shape or device not supported)'}
+ERRORS = {-1: 'PCTTS_EINVAL (bad argument)', -2: 'PCTTS_EUNSUPPORTED (shape or device not supported)',
+          -3: 'PCTTS_ELIMIT (size beyond the fixed capacity of a *_static entry point)'}
 
 
 class PcttsError(RuntimeError):

@@ -7,6 +7,7 @@
 #include "common.cuh"
 #include <cuda_bf16.h>
 #include "pctts.h"
+#include <mutex>
 
 namespace {
 
@@ -587,6 +588,59 @@ extern "C" int pctts_bn_bwd_apply_planes(const float* x, const float* dy, float*
 extern "C" int pctts_colsum(const float* x, long rows, int C, float* out, int accumulate, void* workspace, void* stream) {
     if (!x || !out || !workspace || rows <= 0 || C <= 0) return PCTTS_EINVAL;
     Ws w = carve(workspace, rows, C);
+    cudaStream_t st = (cudaStream_t)stream;
+    RedArgs a{x, nullptr, nullptr, nullptr, nullptr, nullptr, rows, C, 0};
+    PCTTS_CUDA_RC(run_colreduce<MODE_COLSUM>(a, w, st, false));
+    pctts_launch(colsum_final_kernel, pctts_div_up(C, RT / 32), RT, 0, st, w.partial, w.sums, reduce_grid(rows, C), C, out, accumulate);
+    PCTTS_LAUNCH_CHECK();
+    return PCTTS_OK;
+}
+
+// ---- pctts_colsum for callers that may not allocate device memory -------------------------------------------------------
+// Same two launches as pctts_colsum; the per-CTA partials and the double sums live in a fixed array that is part of the
+// library image instead of in a caller-provided workspace.  See include/pctts.h for who needs this and for the rules of use.
+namespace {
+constexpr int STATIC_MAX_C = PCTTS_COLSUM_STATIC_MAX_C;
+// the largest layout carve() can ask for: reduce_grid() never exceeds 2 * 148 CTAs, each owning [2][C] doubles
+constexpr long STATIC_SCRATCH_BYTES = ((long)(148 * 2) * 2 * STATIC_MAX_C + 2 * STATIC_MAX_C) * (long)sizeof(double) + 16;
+constexpr int STATIC_MAX_DEVICES = 64;
+}  // namespace
+
+// One copy per GPU that loads the library (about 4.9 MB each), alive until the process exits.
+static __device__ __align__(256) unsigned char g_colsum_static_scratch[STATIC_SCRATCH_BYTES];
+
+namespace {
+// In host code `g_colsum_static_scratch` is only a handle for the runtime's symbol table, never a device address: the address a
+// kernel may use is looked up per device, once, with that device current.
+std::mutex g_static_mu;
+void* g_static_ptr[STATIC_MAX_DEVICES] = {};
+
+int static_scratch_for_current_device(void** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= STATIC_MAX_DEVICES) return PCTTS_EUNSUPPORTED;
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_colsum_static_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (!p) return (int)cudaErrorInvalidSymbol;
+        g_static_ptr[dev] = p;
+    }
+    *out = g_static_ptr[dev];
+    return PCTTS_OK;
+}
+}  // namespace
+
+extern "C" int pctts_colsum_static(const float* x, long rows, int C, float* out, int accumulate, void* stream) {
+    if (!x || !out || rows <= 0 || C <= 0) return PCTTS_EINVAL;
+    // the fixed array has no room for wider matrices (the second test guards the layout against a future change of reduce_grid)
+    if (C > STATIC_MAX_C || pctts_colreduce_workspace_bytes(rows, C) > STATIC_SCRATCH_BYTES) return PCTTS_ELIMIT;
+    void* scratch = nullptr;
+    PCTTS_CUDA_RC(static_scratch_for_current_device(&scratch));
+    // Stage 1 overwrites every partial that stage 2 reads, so nothing left in the array by an earlier call needs clearing.
+    Ws w = carve(scratch, rows, C);
     cudaStream_t st = (cudaStream_t)stream;
     RedArgs a{x, nullptr, nullptr, nullptr, nullptr, nullptr, rows, C, 0};
     PCTTS_CUDA_RC(run_colreduce<MODE_COLSUM>(a, w, st, false));
