@@ -10,7 +10,9 @@ import time
 
 import numpy as np
 
-from .percivaltts import is_int, print_tty
+from .percivaltts import is_int, numpy_force_random_seed, print_tty
+
+numpy_force_random_seed()      # reference data.py:32: repeatable shuffles / crops, and the SAME draws on every replica
 
 _SHAPE_SUFFIX = re.compile(r'^(.*):\((.*)\)$')
 

@@ -21,7 +21,11 @@ import numpy as np
 
 from . import data
 from .backend_b200 import gpu_memused
-from .percivaltts import configuration, print_log, print_tty, time2str
+from .percivaltts import configuration, numpy_force_random_seed, print_log, print_tty, time2str
+
+numpy_force_random_seed()      # reference optimizertts.py:37
+
+_DP_CHECK = os.environ.get('PCTTS_DP_CHECK', '0') not in ('', '0')   # compare the local (B,T) across the replicas before EVERY batch
 
 
 def proc_memresident():
@@ -204,6 +208,10 @@ class OptimizerTTS(object):
         epoch = -1
         for epoch in range(epochstart, 1 + cfg.train_max_nbepochs):
             timeepochstart = time.time()
+            if world > 1:
+                # the replicas must draw the same global batches (shuffle, crop offsets) or their (B,T) and their sync-BN counts
+                # diverge: rank 0's numpy RNG state is authoritative at every epoch start (which also covers a resume)
+                np.random.set_state(sync.broadcast_rng_state(np.random.get_state()))
             rndidx = np.arange(int(nbbatches * cfg.train_batch_size))
             np.random.shuffle(rndidx)
             rndidxb = np.split(rndidx, nbbatches)
@@ -221,6 +229,8 @@ class OptimizerTTS(object):
             for batchid in range(nbbatches):
                 print_tty('\r    Training batch {}/{}'.format(1 + batchid, nbbatches))
                 X_trab, Y_trab, W_trab = nxt
+                if world > 1 and (batchid == 0 or _DP_CHECK):
+                    sync.assert_same_shape(X_trab.shape[:2], 'batch %d of epoch %d' % (batchid, epoch))
                 nxt = load_batch(batchid + 1) if batchid + 1 < nbbatches else None
                 load_times.append(time.time() - t0)
                 t1 = time.time()

@@ -181,6 +181,34 @@ class DistSync(object):
         dist.broadcast(t, src=src, group=self.group)
         return float(t.item())
 
+    def _host_device(self):
+        return torch.device('cuda', torch.cuda.current_device()) if dist.get_backend(self.group) == 'nccl' else torch.device('cpu')
+
+    def broadcast_rng_state(self, state, src=0):
+        """numpy's global MT19937 state (np.random.get_state()) of rank `src`, on every rank: the replicas draw the same shuffles
+        and crop offsets, as the single process of the reference does (seed 123, data.py:32)."""
+        import numpy as np
+        name, keys, pos, has_gauss, cached = state
+        assert name == 'MT19937' and len(keys) == 624
+        t = torch.empty(627, dtype=torch.float64)                  # uint32 words are exact in a double
+        t[:624] = torch.from_numpy(np.asarray(keys, dtype=np.float64))
+        t[624], t[625], t[626] = float(pos), float(has_gauss), float(cached)
+        t = t.to(self._host_device())
+        dist.broadcast(t, src=src, group=self.group)
+        t = t.cpu()
+        return ('MT19937', t[:624].numpy().astype(np.uint32), int(t[624]), int(t[625]), float(t[626]))
+
+    def assert_same_shape(self, shape, what=''):
+        """Raise on EVERY rank when the replicas disagree on `shape` (sync-BN divides by rows * world and the peer exchanges run in
+        lock-step, so unequal local shapes are silently wrong first and a time-out later)."""
+        v = torch.tensor([float(d) for d in shape], dtype=torch.float64, device=self._host_device())
+        lo, hi = v.clone(), v.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=self.group)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=self.group)
+        if not torch.equal(lo, hi):
+            raise RuntimeError('replicas disagree on the shape of %s: rank %d has %s, min %s, max %s'
+                               % (what, self.rank, tuple(shape), lo.tolist(), hi.tolist()))
+
     def barrier(self):
         dist.barrier(group=self.group)
 

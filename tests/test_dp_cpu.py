@@ -96,3 +96,26 @@ def test_two_rank_train_through_the_public_api(tmp_path):
            '--master-port', str(_free_port()), os.path.join(ROOT, 'tools', 'dp_api_check.py')]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
     assert r.returncode == 0 and 'DP API OK' in r.stdout, (r.stdout[-3000:], r.stderr[-3000:])
+
+
+def test_two_rank_train_with_mixed_lengths_and_unsynchronised_rngs(tmp_path):
+    """lengthmax=None: T is the shortest utterance of each global batch, so replicas whose numpy RNGs differ would shuffle and
+    crop differently and disagree on (B,T).  The ranks start from different seeds; rank 0's state, broadcast at every epoch start,
+    must keep them on the same batches (the reference is one process seeded with 123, data.py:32)."""
+    import subprocess
+    env = dict(os.environ, PCTTS_DP_WORKDIR=str(tmp_path / 'work'), CUDA_VISIBLE_DEVICES='', PCTTS_DP_MIXED_LENGTHS='1',
+               PCTTS_DP_CHECK='1')
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr', '127.0.0.1',
+           '--master-port', str(_free_port()), os.path.join(ROOT, 'tools', 'dp_api_check.py')]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
+    assert r.returncode == 0 and 'DP API OK' in r.stdout, (r.stdout[-3000:], r.stderr[-3000:])
+
+
+def test_import_seeds_numpy_like_the_reference():
+    """reference data.py:32 / optimizertts.py:37: importing the package leaves numpy's global RNG at seed 123."""
+    import subprocess
+    code = ("import numpy as np; np.random.seed(5); import percivaltts_b200.data, percivaltts_b200.optimizertts; a = np.random.rand(3);"
+            "np.random.seed(123); assert (a == np.random.rand(3)).all(); print('SEEDED')")
+    r = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, timeout=300, cwd=ROOT,
+                       env=dict(os.environ, CUDA_VISIBLE_DEVICES=''))
+    assert 'SEEDED' in r.stdout, r.stderr[-2000:]

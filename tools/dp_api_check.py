@@ -58,6 +58,11 @@ def main():
     cfg.train_max_nbepochs = 2
     cfg.train_cancel_nodecepochs = 2
     cfg.train_batch_lengthmax = 32
+    if os.environ.get('PCTTS_DP_MIXED_LENGTHS'):
+        # T = the shortest utterance of each global batch (lengthmax None), and the ranks' numpy RNGs deliberately apart: only
+        # the epoch-start broadcast of rank 0's state keeps the replicas on the same batches
+        cfg.train_batch_lengthmax = None
+        np.random.seed(1000 + rank)
     cfg.train_nbepochs_scalewdata = False
     voc = vocoders.VocoderPML(16000, 0.005, 65, 17)
     quiet = open(os.devnull, 'w') if rank else None
