@@ -477,8 +477,11 @@ int chain_pick_nc(int T, int fmax) {
     if (fmax < 1) return 0;
     for (int nc = 1; nc <= 16; nc *= 2)
         if ((long)nc * fmax >= T) {
-            // (nc-1) * ceil(T/nc) < T always holds for T >= nc; shorter sequences take fewer CTAs by construction
-            return nc;
+            // every CTA of the cluster must own at least one frame: with Fc = ceil(T / nc) the last rank starts at (nc-1) * Fc,
+            // which can reach or pass T when fmax is small against T (wide maps: F = 227, T = 225 -> nc = 16, Fc = 15); such
+            // shapes are refused here (the callers then run the stack layer by layer) instead of launching an empty CTA
+            const long fc = ((long)T + nc - 1) / nc;
+            return (long)(nc - 1) * fc < T ? nc : 0;
         }
     return 0;
 }

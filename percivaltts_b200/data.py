@@ -167,14 +167,34 @@ def batching(xs, length=None, lengthmax=None, padtype='randshift', outmask=False
     return outs, MB
 
 
+def addstop(X, value=1.0):
+    """A copy of the list with one more column (zeros) on every matrix and one more row [0, ..., 0, value] behind it: the stop
+    symbol of sequences whose input and output lengths differ (data.py:286-295).  float64, as numpy promotes in the reference."""
+    out = []
+    for x in X:
+        y = np.zeros((x.shape[0] + 1, x.shape[1] + 1), dtype=np.float64)
+        y[:-1, :-1] = x
+        y[-1, -1] = value
+        out.append(y)
+    return out
+
+
 def load_inoutset(indir, outdir, outwdir, fid_lst, inouttimesync=True, length=None, lengthmax=None, maskpadtype='padright',
                   cropmode='begend', verbose=0):
     """Load inputs, outputs and time weights of the given ids, crop silences, and batch them."""
-    if not inouttimesync:
-        raise NotImplementedError('only time-synchronous input/output sets are supported')
     X = load(indir, fid_lst, verbose=verbose, label='Context labels: ')
     Y = load(outdir, fid_lst, verbose=verbose, label='Output features: ')
     Wt = load(outwdir, fid_lst, verbose=verbose, label='Time weights: ')
+    if not inouttimesync:
+        # inputs and outputs of different lengths (data.py:309-313,319-321): a stop frame behind each, batched separately (two
+        # rounds of window draws), the time weights stay a list of cropped matrices
+        X = addstop(X)
+        Y, Wt = croplen([Y, Wt])
+        [Y], Wt = croplen_weight([Y], Wt, cropmode=cropmode)
+        Y = addstop(Y)
+        [X], _ = batching([X], length=length, lengthmax=lengthmax, padtype=maskpadtype)
+        [Y], _ = batching([Y], length=length, lengthmax=lengthmax, padtype=maskpadtype)
+        return X, Y, Wt
     X, Y, Wt = croplen([X, Y, Wt])
     [X, Y], Wt = croplen_weight([X, Y], Wt, cropmode=cropmode)
     [X, Y, Wt], _ = batching([X, Y, Wt], length=length, lengthmax=lengthmax, padtype=maskpadtype)

@@ -82,8 +82,12 @@ def print_tty(txt, end=''):
 
 
 def is_int(v):
-    try:
-        int(v)
+    """True for text that reads as a whole number (percivaltts.py:131-135) -- including, as in the reference, an integral decimal
+    such as '1.0' or '100.': signs are dropped from the left, then zeros and one dot from the right, and what remains must be
+    digits only; a text holding '..' is tested as it stands."""
+    v = str(v).strip()
+    if v == '0':
         return True
-    except (TypeError, ValueError):
-        return False
+    if '..' not in v:
+        v = v.lstrip('-+').rstrip('0').rstrip('.')
+    return v.isdigit()

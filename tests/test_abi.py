@@ -82,6 +82,14 @@ def test_host_planning_calls_need_no_gpu():
     assert lib.pctts_conv2d_chain_supported(54, 129, 6) == 1 and lib.pctts_conv2d_chain_supported(55, 129, 6) == 2
     assert lib.pctts_conv2d_chain_supported(400, 129, 3) == 8 and lib.pctts_conv2d_chain_supported(4000, 129, 6) == 0
     assert lib.pctts_conv2d_chain_supported(0, 129, 6) == 0 and lib.pctts_conv2d_chain_supported(400, 129, 0) == 0
+    # no cluster CTA may be left without frames: wide maps that would need 16 CTAs with an empty last one are refused
+    assert lib.pctts_conv2d_chain_supported(225, 227, 6) == 0 and lib.pctts_conv2d_chain_supported(209, 243, 6) == 0
+    assert lib.pctts_conv2d_chain_supported(224, 227, 6) == 8 and lib.pctts_conv2d_chain_supported(226, 227, 6) == 16
+    for nterms in (6, 3, 1):
+        for Fq in range(1, 520, 3):
+            for T in range(1, 800, 7):
+                nc = lib.pctts_conv2d_chain_supported(T, Fq, nterms)
+                assert nc == 0 or (nc - 1) * ((T + nc - 1) // nc) < T, (T, Fq, nterms, nc)
     assert lib.pctts_conv2d_wgrad_multi_workspace(8) == 8 * 18 * 404 and lib.pctts_conv2d_wgrad_multi_workspace(1) == 148 * 404
     assert lib.pctts_conv2d_wgrad_multi_workspace(0) == 0 and lib.pctts_conv2d_wgrad_multi_workspace(10) == 0
     assert lib.pctts_grad_sync_ctl_bytes() == 512

@@ -46,7 +46,8 @@ def make_weights(L, seed, scale=0.25):
 
 
 SHAPES = [(3, 1, 129, 8), (2, 7, 129, 8), (2, 50, 129, 8), (2, 55, 129, 3), (3, 130, 129, 8), (1, 293, 129, 8), (3, 400, 129, 8),
-          (1, 747, 129, 8), (2, 61, 33, 4), (2, 90, 65, 2), (2, 37, 30, 1)]
+          (1, 747, 129, 8), (2, 61, 33, 4), (2, 90, 65, 2), (2, 37, 30, 1),
+          (1, 226, 227, 2), (1, 211, 243, 2), (1, 225, 227, 2)]   # wide maps: 16 CTAs, the last one owning a single frame / refused (skipped)
 
 
 @pytest.mark.parametrize('N,T,Fq,L', SHAPES)
