@@ -157,6 +157,19 @@ def cpu_baseline_cycle(threads):
     return 5 * B_PER_GPU * T_FRAMES / dt, dt
 
 
+def bench_config(world, B, precision='fp32', global_batch=None):
+    """The `config` object of the JSON line -- the same function, hence the same dict, for both arms."""
+    wl = WORKLOAD
+    if precision != 'fp32' or global_batch:
+        wl = WORKLOAD.replace('fp32', precision).replace('B=10/GPU', 'B=%d/GPU' % B).replace(
+            'config #2', 'config #3' if precision == 'bf16' else 'config #2 variant')
+    return {'workload': wl, 'global_batch_utterances': B * world, 'frames_per_step': B * T_FRAMES * world,
+            'schedule': '1 critic update per step + 1 generator update every 5th step (generator_updates>=25)',
+            'l2': 'per-step working set (activations of 3x batched critic + generator, ~0.6 GB) exceeds the 126 MB L2; '
+                  'inputs cycle over 4 resident batches',
+            'parallelism': 'dp%d sync-BN + flat-gradient all-reduce' % world if world > 1 else 'single GPU'}
+
+
 def run_reference(args):
     """--impl reference: the reference's TensorFlow-1.9 / python-2 step cannot run here, so the timed CPU arm
     is the oracle port with all host threads.  A step is one train_on_batch on the full B=10 batch (~0.7 s on 16 cores), the
@@ -185,7 +198,8 @@ def run_reference(args):
     print(json.dumps({
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': 1e3 * dt / args.steps, 'higher_is_better': True, 'scaling': 'weak',
-        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': {'workload': WORKLOAD},
+        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': bench_config(args.gpus, B_PER_GPU),
+        'arm_note': 'CPU port of the reference graph on rank 0: one replica\'s batch per step whatever --gpus says',
         'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': threads, 'kind': 'port', 'sample': sample},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}))
 
@@ -504,14 +518,13 @@ def run_b200(args):
         'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'strong' if args.global_batch else 'weak', 'vs_baseline': None,
         'dtype': 'bf16' if ops.precision == 'bf16' else 'f32',
         'data': 'synthetic',
-        'config': {'workload': WORKLOAD if (ops.precision == 'fp32' and not args.global_batch) else
-                   WORKLOAD.replace('fp32', ops.precision).replace('B=10/GPU', 'B=%d/GPU' % B).replace('config #2', 'config #3' if ops.precision == 'bf16' else 'config #2 variant'),
-                   'global_batch_utterances': B * world, 'frames_per_step': B * T * world,
-                   'schedule': '1 critic update per step + 1 generator update every 5th step (generator_updates>=25); on those steps both updates '
-                               'run as one graph sharing the generator forward pass of the batch',
-                   'l2': 'per-step working set (activations of 3x batched critic + generator, ~0.6 GB) exceeds the 126 MB L2; '
-                         'inputs cycle over 4 resident batches',
-                   'parallelism': 'dp%d sync-BN + flat-gradient all-reduce' % world if world > 1 else 'single GPU'},
+        'config': bench_config(world, B, ops.precision, args.global_batch),
+        'schedule_note': 'on the steps with a generator update both updates run as one graph sharing the generator forward pass of the batch',
+        # disclosure: what "f32" means here -- forward contractions and the penalty's input gradient use three bf16 planes / six
+        # products (fp32-grade); the critic's other gradient passes two planes / three products
+        'gradient_pass_products': int(max(ops.bwd_nterms, 1)), 'forward_products': int(max(ops.nterms, 1)),
+        'precision_note': 'PCTTS_BWD_TERMS=6 restores six products in every pass; worst gradient error against the fp64 oracle is '
+                          'printed by __graft_entry__.smoke() (2.4e-5 at three products, bar 1e-3)',
         'critic_step_ms': critic_ms, 'generator_step_ms': gen_ms, 'critic_plus_generator_step_ms': both_ms,
         'conv_tc_util_pct': 100.0 * conv1d['tensor_pipe_frac'] if conv1d else None, 'gemm_precision': ops.precision,
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': e2e_h2d,

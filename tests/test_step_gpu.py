@@ -305,3 +305,39 @@ def test_critic_plus_generator_step_shares_the_generator_forward(cuda_ops, kw, B
     for a, b in zip(want, got):
         assert torch.equal(a, b)
 
+
+
+# the reference's other step variants: its own smoke test trains errtype 'WGAN' as well as 'WLSWGAN'
+# (tests/test_smoke_tensorflowkeras.py:183-203), and prepare() has two more branches for the LSE weight vector
+# (optimizertts_wgan.py:190-205): LScoef == 0 (flat weights) and use_WGAN_incnoisefeature (the noise columns join the critic side)
+@pytest.mark.parametrize('variant', [dict(errtype='WGAN'), dict(LScoef=0.0), dict(incnoise=True), dict(LScoef=0.0, incnoise=True),
+                                     dict(LScoef=0.6, incnoise=True)])
+@pytest.mark.parametrize('kw,B,T', [(MID, 3, 57), (DEMO, 2, 48)])
+def test_generator_step_variants_vs_oracle(cuda_ops, variant, kw, B, T):
+    errtype = variant.get('errtype', 'WLSWGAN')
+    okw = {k: v for k, v in variant.items() if k != 'errtype'}
+    ao, a = O.Arch(**kw), A.Arch(**kw)
+    wg = O.perturb_params(O.init_params(O.generator_param_shapes(ao), seed=1))
+    wc = O.perturb_params(O.init_params(O.critic_param_shapes(ao), seed=2))
+    X, Y, _ = O.synthetic_batch(ao, B, T, seed=5)
+    wgan_w, wls, wbar = O.wlswgan_weights(ao, **okw)
+    if 'LScoef' in okw and okw['LScoef'] == 0.0:
+        assert np.all(wgan_w[1:1 + ao.spec_size] == 1.0) and np.all(wls[1:1 + ao.spec_size] == 0.0)
+    if okw.get('incnoise'):
+        assert np.all(wgan_w[1 + ao.spec_size:] > 0.0)
+    st = WGANStepper(cuda_ops, a, errtype=errtype, w_ls=wls if errtype == 'WLSWGAN' else None, w_wgan_mean=wbar)
+    st.G.params.load(wg)
+    st.C.params.load(wc)
+    dt = torch.float64
+    wgt, wct = O.to_torch(wg, dt, requires_grad=True), O.to_torch(wc, dt, requires_grad=True)
+    rg = O.generator_step(ao, wgt, wct, torch.tensor(X, dtype=dt), torch.tensor(Y, dtype=dt), errtype=errtype, **okw)
+    rg32 = O.generator_step(ao, O.to_torch(wg, torch.float32, True), O.to_torch(wc, torch.float32, True), torch.tensor(X),
+                            torch.tensor(Y), errtype=errtype, **okw)
+    st.generator_step(torch.tensor(X).cuda(), torch.tensor(Y).cuda(), apply=False)
+    torch.cuda.synchronize()
+    losses = st.losses.cpu()
+    assert relerr(st.buffers(B, T)['fake'], rg['pred']) < TOL
+    assert abs(float(losses[W.L_GEN]) - float(rg['loss'])) < TOL * max(abs(float(rg['loss'])), 1e-2), (losses, rg['loss'])
+    check_grads(st.G.params, rg['grads'], rg32['grads'])
+    for k, v in rg['new_stats'].items():
+        assert relerr(st.G.params.p[k], v) < TOL, k

@@ -57,6 +57,11 @@ def run(ops=None, total=1000000, chunk=250000, cpu_frames=10000):
     PO.fwbnd2linbnd(c, fs, dftlen, smooth=True)
     t2 = time.perf_counter()
     out['cpu_oracle'] = {'frames': cpu_frames, 'cores': 1, 'compress_frames_per_s': round(cpu_frames / (t1 - t0)), 'decompress_frames_per_s': round(cpu_frames / (t2 - t1))}
+    out['operator'] = ('builder-defined (the reference delegates to the sigproc submodule, absent from /root/reference): mel-warped point '
+                       'sampling by linear interpolation, Catmull-Rom on the way back -- parity unpinned; GBps / frac count the WHOLE input row, '
+                       'of which point sampling needs only the sectors around the band centres (compress: 127 of 257 sectors at 129 bands, 36 '
+                       'of 257 at 33), so compress_frac is an upper reading, not an algorithmic one')
+    out['frames'] = '%d frames = one resident chunk of %d frames (%.1f GB in, well beyond L2) processed %d times' % (total, chunk, chunk * NB * 4 / 1e9, total // chunk)
     out.update(config='pml_1M_frames', hbm_peak_GBps=hbm, bytes_per_frame={'compress_spec': (NB + 129) * 4, 'compress_nm': (NB + 33) * 4})
     del spec, nm
     torch.cuda.empty_cache()
