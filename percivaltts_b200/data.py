@@ -112,26 +112,30 @@ def _speech_mask(w, thresh):
     return (w[:, 0] if w.ndim > 1 else w) > thresh
 
 
+def _crop_selection(wk, thresh, cropmode, cropsize):
+    """What croplen_weight keeps of one utterance with time weights wk: a slice or an index array."""
+    keep = _speech_mask(wk, thresh)
+    idx = np.where(keep)[0]
+    if cropmode == 'begend':
+        return slice(int(idx.min()), int(idx.max()))
+    if cropmode == 'begendbigger':
+        gaps = np.diff(idx)
+        for g in np.where(gaps > 1)[0]:
+            if gaps[g] < int(cropsize):
+                keep[idx[g]:idx[g + 1]] = True
+        return np.where(keep)[0]
+    if cropmode == 'all':
+        return idx
+    raise ValueError('unknown cropmode ' + str(cropmode))
+
+
 def croplen_weight(xs, w, thresh=0.5, cropmode='begend', cropsize=int(0.750 / 0.005)):
     """Remove silences according to the time weights w (threshold `thresh`):
     'begend' keeps [first speech frame, last speech frame); 'begendbigger' also drops inner pauses of at least
     `cropsize` frames; 'all' keeps speech frames only."""
     _same_count([w] + list(xs))
     for k in range(len(w)):
-        keep = _speech_mask(w[k], thresh)
-        idx = np.where(keep)[0]
-        if cropmode == 'begend':
-            sel = slice(int(idx.min()), int(idx.max()))
-        elif cropmode == 'begendbigger':
-            gaps = np.diff(idx)
-            for g in np.where(gaps > 1)[0]:
-                if gaps[g] < int(cropsize):
-                    keep[idx[g]:idx[g + 1]] = True
-            sel = np.where(keep)[0]
-        elif cropmode == 'all':
-            sel = idx
-        else:
-            raise ValueError('unknown cropmode ' + str(cropmode))
+        sel = _crop_selection(w[k], thresh, cropmode, cropsize)
         for x in xs:
             x[k] = x[k][sel]
         w[k] = w[k][sel]
@@ -199,6 +203,64 @@ def load_inoutset(indir, outdir, outwdir, fid_lst, inouttimesync=True, length=No
     [X, Y], Wt = croplen_weight([X, Y], Wt, cropmode=cropmode)
     [X, Y, Wt], _ = batching([X, Y, Wt], length=length, lengthmax=lengthmax, padtype=maskpadtype)
     return X, Y, Wt
+
+
+def _rows_on_disk(path, fbase):
+    """Frames of one raw float32 file whose selector is ':(-1,D)', from its size alone; None when the selector has another form."""
+    fpath, shape = getpathandshape(path)
+    if shape is None or len(shape) != 2 or shape[0] != -1 or shape[1] < 1:
+        return None
+    fpath = fpath.replace('*', fbase)
+    if not os.path.isfile(fpath):
+        raise ValueError('{} does not exists'.format(fpath))
+    return os.path.getsize(fpath) // (4 * shape[1])
+
+
+def load_inoutset_shard(indir, outdir, outwdir, fid_lst, rank, world, length=None, lengthmax=None, maskpadtype='padright',
+                        cropmode='begend', verbose=0):
+    """Utterances [rank*B/world, (rank+1)*B/world) of load_inoutset(...)'s batch -- the same arrays, the same draws from numpy's
+    global RNG -- reading the input and output files of THOSE utterances only.  What has to be known of the whole batch (its
+    common length and one window draw per utterance, in utterance order) follows from the file sizes and the time weights, which
+    are one float per frame and are read for every utterance.  No reference counterpart (the reference is one process)."""
+    nb = len(fid_lst)
+    if nb % world:
+        raise ValueError('batch of {} utterances does not split over {} ranks'.format(nb, world))
+    nx = [_rows_on_disk(indir, f) for f in fid_lst]
+    ny = [_rows_on_disk(outdir, f) for f in fid_lst]
+    if any(n is None for n in nx + ny):           # a selector the sizes cannot be read from: load everything, keep the shard
+        X, Y, Wt = load_inoutset(indir, outdir, outwdir, fid_lst, length=length, lengthmax=lengthmax, maskpadtype=maskpadtype,
+                                 cropmode=cropmode, verbose=verbose)
+        n = nb // world
+        return X[rank * n:(rank + 1) * n], Y[rank * n:(rank + 1) * n], Wt[rank * n:(rank + 1) * n]
+    Wt = load(outwdir, fid_lst, verbose=verbose, label='Time weights: ')
+    sels, lens = [], []
+    for k in range(nb):
+        n = min(nx[k], ny[k], Wt[k].shape[0])                                     # croplen
+        Wt[k] = Wt[k][:n]
+        sel = _crop_selection(Wt[k], 0.5, cropmode, int(0.750 / 0.005))           # croplen_weight
+        Wt[k] = Wt[k][sel]
+        sels.append((n, sel))
+        lens.append(Wt[k].shape[0])
+    if length is None:                                                            # batching
+        length = max(lens) if maskpadtype == 'padright' else min(lens)
+    if lengthmax is not None and length > lengthmax:
+        length = lengthmax
+    length = int(length)
+    per = nb // world
+    mine = range(rank * per, (rank + 1) * per)
+    outs = None
+    for b in range(nb):
+        shift = np.random.randint(0, (lens[b] - length) + 1) if maskpadtype == 'randshift' else 0
+        if b not in mine:
+            continue
+        n, sel = sels[b]
+        mats = [loadfile(indir, fid_lst[b])[:n][sel], loadfile(outdir, fid_lst[b])[:n][sel], Wt[b]]
+        if outs is None:
+            outs = [np.zeros((per, length, 1 if m.ndim == 1 else m.shape[1]), dtype='float32') for m in mats]
+        m = min(lens[b], length)
+        for x, out in zip(mats, outs):
+            out[b - mine[0], :m, :] = x[shift:shift + m].reshape(m, -1)
+    return outs[0], outs[1], outs[2]
 
 
 # ---- evaluation helpers ---------------------------------------------------------------------------------------------

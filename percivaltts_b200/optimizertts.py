@@ -9,6 +9,8 @@ The loop stays host python (it is the caller of the hot path, not part of it); p
 The base class itself is the reference's plain least-squares ('LSE') optimizer (:378-436): its step runs on the GPU through
 lse.LSEStepper (forward, loss + gradient, backward, Adam: the same kernels as the WGAN-GP path).
 """
+import collections
+import concurrent.futures
 import copy
 import glob
 import os
@@ -206,6 +208,7 @@ class OptimizerTTS(object):
 
         print_log('    start training ...')
         epoch = -1
+        loader = concurrent.futures.ThreadPoolExecutor(max_workers=1, thread_name_prefix='pctts-loader')
         for epoch in range(epochstart, 1 + cfg.train_max_nbepochs):
             timeepochstart = time.time()
             if world > 1:
@@ -218,21 +221,27 @@ class OptimizerTTS(object):
             costs_tra_batches, load_times, train_times = [], [], []
             def load_batch(bid):
                 fid_lst_trab = [fid_lst_tra[bidx] for bidx in rndidxb[bid]]
-                Xb, Yb, Wb = data.load_inoutset(indir, outdir, wdir, fid_lst_trab, length=cfg.train_batch_length,
-                                                lengthmax=cfg.train_batch_lengthmax,
-                                                maskpadtype=cfg.train_batch_padtype, cropmode=cfg.train_batch_cropmode)
-                return (shard(Xb), shard(Yb), shard(Wb)) if world > 1 else (Xb, Yb, Wb)
-            # one batch of look-ahead: batch i+1 is read (same order of numpy RNG draws as the reference, which loads batch by
-            # batch, optimizertts.py:231-232) before batch i trains, so that its host->device copy overlaps the kernels of batch i
+                kw = dict(length=cfg.train_batch_length, lengthmax=cfg.train_batch_lengthmax, maskpadtype=cfg.train_batch_padtype,
+                          cropmode=cfg.train_batch_cropmode)
+                if world > 1:       # this rank's utterances only: same arrays and RNG draws as the whole batch, 1/world of the reads
+                    return data.load_inoutset_shard(indir, outdir, wdir, fid_lst_trab, rank, world, **kw)
+                return data.load_inoutset(indir, outdir, wdir, fid_lst_trab, **kw)
+            # The reference loads batch by batch on the main thread (optimizertts.py:231-232) and the GPU waits for the disk.  Here a
+            # single loader thread runs two batches ahead: batch i+2 is read and cropped while batch i trains and the copy of batch
+            # i+1 to the device overlaps its kernels.  One thread, batches in order, and nobody else draws from numpy's global RNG
+            # during the epoch: the sequence of window draws is the reference's.
+            pending = collections.deque(loader.submit(load_batch, b) for b in range(min(2, nbbatches)))
             t0 = time.time()
-            nxt = load_batch(0) if nbbatches > 0 else None
+            nxt = pending.popleft().result() if nbbatches > 0 else None
             for batchid in range(nbbatches):
                 print_tty('\r    Training batch {}/{}'.format(1 + batchid, nbbatches))
                 X_trab, Y_trab, W_trab = nxt
                 if world > 1 and (batchid == 0 or _DP_CHECK):
                     sync.assert_same_shape(X_trab.shape[:2], 'batch %d of epoch %d' % (batchid, epoch))
-                nxt = load_batch(batchid + 1) if batchid + 1 < nbbatches else None
-                load_times.append(time.time() - t0)
+                if batchid + 2 < nbbatches:
+                    pending.append(loader.submit(load_batch, batchid + 2))
+                nxt = pending.popleft().result() if batchid + 1 < nbbatches else None
+                load_times.append(time.time() - t0)          # time the step loop WAITED for data, not the loader's own time
                 t1 = time.time()
                 if self.supports_prefetch and nxt is not None:
                     cost_tra = self.train_on_batch(batchid, X_trab, Y_trab, next_batch=(nxt[0], nxt[1]))
@@ -285,6 +294,7 @@ class OptimizerTTS(object):
                 print_log('WARNING: validation error did not decrease for {} epochs. Early stop!'.format(cfg.train_cancel_nodecepochs))
                 break
 
+        loader.shutdown(wait=False)
         if best_val is None:
             raise ValueError('No model has been saved during training!')
         return {'epoch_stopped': epoch, 'worst_val': worst_val,
