@@ -547,6 +547,8 @@ def run_b200(args):
         sys.path.insert(0, os.path.join(ROOT, 'tools'))
         import bench_gp
         import bench_pml
+        import bench_files
+        out['e2e_files'] = bench_files.run(demo_cfg())     # the same step driven by train() on files (loader thread + prefetch)
         out['config4_gp_microbench'] = bench_gp.run(ops, iters=6)
         out['config5_pml_1M_frames'] = bench_pml.run(ops, cpu_frames=4000)
     print(json.dumps(out))

@@ -5,6 +5,7 @@ OptimizerTTSWGAN.train_on_batch (reference percivaltts/optimizertts_wgan.py:216-
 
 One process drives one GPU; under torch.distributed every rank runs the same code on its shard of the batch.
 """
+import concurrent.futures
 import os
 from collections import OrderedDict
 
@@ -12,6 +13,8 @@ import numpy as np
 import torch
 
 from . import wgan as W
+
+STAGE_THREADS = 4     # host threads that fill the pinned staging buffer of a synchronously staged batch (Trainer.stage)
 
 
 class _ShapeState(object):
@@ -59,6 +62,7 @@ class DeviceTrainer(object):
         self._pf_slot = 0
         self._pf_bufs = [None, None]
         self._copy_stream = None
+        self._stage_pool = None
 
     # ---- shape state / graph capture ---------------------------------------------------------------------------
     def _mem(self):
@@ -174,11 +178,30 @@ class DeviceTrainer(object):
 
     # ---- the reference's per-batch entry point ---------------------------------------------------------------------
     def stage(self, s, X, Y, alpha=None):
-        """numpy [B,T,*] float32 -> pinned -> device (async on the current stream)."""
-        np.copyto(s.Xh.numpy(), np.asarray(X, dtype=np.float32).reshape(s.Xh.shape))
-        np.copyto(s.Yh.numpy(), np.asarray(Y, dtype=np.float32).reshape(s.Yh.shape))
-        s.X.copy_(s.Xh, non_blocking=True)
-        s.Y.copy_(s.Yh, non_blocking=True)
+        """numpy [B,T,*] float32 -> pinned -> device (async on the current stream).  A batch of a megabyte or more is cut into
+        groups of utterances: a small pool of threads fills the pinned buffer (numpy's copy releases the GIL) while this thread
+        sends each group to the device as soon as it is in place, so the host copy runs on several cores and the PCIe transfer
+        hides behind it -- this is the synchronous path of the reference's 3-argument train_on_batch(batchid, X, Y)."""
+        X = np.asarray(X, dtype=np.float32).reshape(s.Xh.shape)
+        Y = np.asarray(Y, dtype=np.float32).reshape(s.Yh.shape)
+        Xh, Yh = s.Xh.numpy(), s.Yh.numpy()
+        B = int(X.shape[0])
+        if self.ops.device.type != 'cuda' or B < 2 or X.nbytes + Y.nbytes < (1 << 20):
+            np.copyto(Xh, X)
+            np.copyto(Yh, Y)
+            s.X.copy_(s.Xh, non_blocking=True)
+            s.Y.copy_(s.Yh, non_blocking=True)
+        else:
+            if self._stage_pool is None:
+                self._stage_pool = concurrent.futures.ThreadPoolExecutor(max_workers=STAGE_THREADS, thread_name_prefix='pctts-stage')
+            jobs = []
+            for host, src, dev_t, host_t, parts in ((Xh, X, s.X, s.Xh, min(B, STAGE_THREADS)), (Yh, Y, s.Y, s.Yh, min(B, 2))):
+                edges = np.linspace(0, B, parts + 1).astype(int)
+                for a, b in zip(edges[:-1], edges[1:]):
+                    jobs.append((self._stage_pool.submit(np.copyto, host[a:b], src[a:b]), dev_t, host_t, int(a), int(b)))
+            for fut, dev_t, host_t, a, b in jobs:
+                fut.result()
+                dev_t[a:b].copy_(host_t[a:b], non_blocking=True)
         s.filled = True
         self.h2d_bytes += s.Xh.numel() * 4 + s.Yh.numel() * 4
         if alpha is not None:

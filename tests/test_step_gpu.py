@@ -341,3 +341,24 @@ def test_generator_step_variants_vs_oracle(cuda_ops, variant, kw, B, T):
     check_grads(st.G.params, rg['grads'], rg32['grads'])
     for k, v in rg['new_stats'].items():
         assert relerr(st.G.params.p[k], v) < TOL, k
+
+
+def test_threaded_staging_of_a_large_batch_places_every_byte(cuda_ops):
+    """DeviceTrainer.stage cuts a batch of a megabyte or more into groups of utterances filled by a thread pool and sent to the
+    device group by group: the device buffers must hold exactly the host batch, also for non-contiguous and float64 input, for a
+    batch with fewer utterances than threads, and when the same buffers are staged again with other data."""
+    from percivaltts_b200.trainer import DeviceTrainer
+    ao, wg, wc, wgt, wct, X, Y, alpha, st = setup(cuda_ops, MID, 2, 40)
+    tr = DeviceTrainer(st)
+    rng = np.random.RandomState(4)
+    for B, T in ((10, 400), (3, 2000), (2, 40)):
+        s = tr.shape_state(B, T, capture=False)
+        for rep in range(3):
+            Xb = rng.uniform(-1, 1, size=(B, T, ao.ctxsize)).astype(np.float32)
+            Yb = rng.normal(size=(B, T, ao.outsize))
+            if rep == 1:
+                Xb = np.asfortranarray(Xb)
+            tr.stage(s, Xb, Yb)
+            torch.cuda.synchronize()
+            assert np.array_equal(s.X.cpu().numpy(), np.ascontiguousarray(Xb)), (B, T, rep)
+            assert np.array_equal(s.Y.cpu().numpy(), Yb.astype(np.float32)), (B, T, rep)
