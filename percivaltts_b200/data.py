@@ -233,13 +233,14 @@ def load_inoutset_shard(indir, outdir, outwdir, fid_lst, rank, world, length=Non
         n = nb // world
         return X[rank * n:(rank + 1) * n], Y[rank * n:(rank + 1) * n], Wt[rank * n:(rank + 1) * n]
     Wt = load(outwdir, fid_lst, verbose=verbose, label='Time weights: ')
+    xpat, ypat = [(fp, sh[1]) for fp, sh in (getpathandshape(indir), getpathandshape(outdir))]
     sels, lens = [], []
     for k in range(nb):
         n = min(nx[k], ny[k], Wt[k].shape[0])                                     # croplen
         Wt[k] = Wt[k][:n]
         sel = _crop_selection(Wt[k], 0.5, cropmode, int(0.750 / 0.005))           # croplen_weight
         Wt[k] = Wt[k][sel]
-        sels.append((n, sel))
+        sels.append((n, sel))                                                     # sel indexes the first n frames
         lens.append(Wt[k].shape[0])
     if length is None:                                                            # batching
         length = max(lens) if maskpadtype == 'padright' else min(lens)
@@ -253,14 +254,47 @@ def load_inoutset_shard(indir, outdir, outwdir, fid_lst, rank, world, length=Non
         shift = np.random.randint(0, (lens[b] - length) + 1) if maskpadtype == 'randshift' else 0
         if b not in mine:
             continue
-        n, sel = sels[b]
-        mats = [loadfile(indir, fid_lst[b])[:n][sel], loadfile(outdir, fid_lst[b])[:n][sel], Wt[b]]
-        if outs is None:
-            outs = [np.zeros((per, length, 1 if m.ndim == 1 else m.shape[1]), dtype='float32') for m in mats]
         m = min(lens[b], length)
-        for x, out in zip(mats, outs):
-            out[b - mine[0], :m, :] = x[shift:shift + m].reshape(m, -1)
+        sel = sels[b][1]
+        if outs is None:      # every frame of every row is written below (window, then zeros behind a short utterance): no zero fill
+            outs = [np.empty((per, length, d), dtype='float32') for d in (xpat[1], ypat[1], 1 if Wt[b].ndim == 1 else Wt[b].shape[1])]
+        r = b - mine[0]
+        # only the window's frames leave the page cache, read straight into the batch: rows [shift, shift + m) of the cropped
+        # utterance (the whole-file read, crop copy and window copy of load_inoutset are three passes more)
+        _read_window_into(outs[0][r, :m], xpat, fid_lst[b], sel, shift, m)
+        _read_window_into(outs[1][r, :m], ypat, fid_lst[b], sel, shift, m)
+        outs[2][r, :m] = Wt[b][shift:shift + m].reshape(m, -1)
+        for out in outs:
+            out[r, m:] = 0
+    for out, path in zip(outs, (indir, outdir, outwdir)):
+        # a NaN or an Inf anywhere makes the plain sum non-finite; so can an overflow of finite values, hence the exact second look
+        if not np.isfinite(out.sum()) and not np.isfinite(out).all():
+            raise ValueError('ERROR: There are nan or inf in a file of {}'.format(getpath(path)))
     return outs[0], outs[1], outs[2]
+
+
+def _read_window_into(dst, pat, fbase, sel, shift, m):
+    """Frames [shift, shift + m) of what the crop selection `sel` keeps of one ':(-1,D)' file -> dst [m, D] (C-contiguous view of
+    the batch).  Consecutive frames (always for 'begend'; for the other modes unless a dropped pause falls inside the window) are one
+    seek + one read into dst; otherwise the span is read once and the kept frames gathered."""
+    fpath, D = pat
+    if m <= 0:
+        return
+    if isinstance(sel, slice):
+        first, idx = sel.start + shift, None
+    else:
+        idx = sel[shift:shift + m]
+        first = int(idx[0])
+        if int(idx[-1]) - first + 1 == m:
+            idx = None
+    with open(fpath.replace('*', fbase), 'rb', buffering=0) as f:
+        f.seek(first * D * 4)
+        if idx is None:
+            if f.readinto(memoryview(dst).cast('B')) != m * D * 4:
+                raise ValueError('{} is shorter than its time weights say'.format(fpath.replace('*', fbase)))
+        else:
+            span = int(idx[-1]) - first + 1
+            dst[...] = np.fromfile(f, dtype=np.float32, count=span * D).reshape(span, D)[idx - first]
 
 
 # ---- evaluation helpers ---------------------------------------------------------------------------------------------

@@ -225,9 +225,9 @@ class OptimizerTTS(object):
                 fid_lst_trab = [fid_lst_tra[bidx] for bidx in rndidxb[bid]]
                 kw = dict(length=cfg.train_batch_length, lengthmax=cfg.train_batch_lengthmax, maskpadtype=cfg.train_batch_padtype,
                           cropmode=cfg.train_batch_cropmode)
-                if world > 1:       # this rank's utterances only: same arrays and RNG draws as the whole batch, 1/world of the reads
-                    return data.load_inoutset_shard(indir, outdir, wdir, fid_lst_trab, rank, world, **kw)
-                return data.load_inoutset(indir, outdir, wdir, fid_lst_trab, **kw)
+                # same arrays and the same RNG draws as data.load_inoutset(...) (tests/test_loader_cpu.py), but only the window's
+                # frames of this rank's utterances are copied out of the files: one pass instead of four, 1/world of the reads
+                return data.load_inoutset_shard(indir, outdir, wdir, fid_lst_trab, rank, world, **kw)
             # The reference loads batch by batch on the main thread (optimizertts.py:231-232) and the GPU waits for the disk.  Here a
             # single loader thread runs two batches ahead: batch i+2 is read and cropped while batch i trains and the copy of batch
             # i+1 to the device overlaps its kernels.  One thread, batches in order, and nobody else draws from numpy's global RNG

@@ -106,3 +106,17 @@ def test_epoch_loop_feeds_the_batches_of_the_sequential_loop(tmp_path, monkeypat
     finally:
         np.random.set_state(state)
         backend_b200.set_ops(None)
+
+
+def test_shard_loader_refuses_nan_in_a_window(tmp_path):
+    import data_scenarios as S
+    fids = S.make_files(str(tmp_path))
+    indir = os.path.join(str(tmp_path), 'lab', '*.lab') + ':(-1,%d)' % S.CTX
+    outdir = os.path.join(str(tmp_path), 'cmp', '*.cmp') + ':(-1,%d)' % S.OUT
+    wdir = os.path.join(str(tmp_path), 'w', '*.w') + ':(-1,1)'
+    f = os.path.join(str(tmp_path), 'cmp', fids[1] + '.cmp')
+    Y = np.fromfile(f, dtype=np.float32)
+    Y[S.OUT * 30 + 2] = np.nan
+    Y.tofile(f)
+    with pytest.raises(ValueError):
+        data.load_inoutset_shard(indir, outdir, wdir, fids[:2], 0, 1)       # padright: every kept frame is in the window
