@@ -282,6 +282,14 @@ def kernel_rooflines(st, ops, B, T, device, peak_tf, peak_hbm, critic_ms, gen_ms
                         'kernel_ms': t, 'bytes_per_launch': nb, 'traffic': None, 'launches_per_critic_step': 1,
                         'share_of_critic_step': t / critic_ms, 'layers_per_launch': L, 'us_per_layer': 1e3 * t / L,
                         'algorithmic': 'input map (1 ch) read + %d output maps (4 ch) written once: (1 + 4 x %d) x 3B x T x %d x 4 B; tiles stay in shared memory between layers' % (L, L, S)})
+            if (B, T, S, L) == (10, 400, 129, 8):
+                # one `ncu --set full` capture of this launch (grid 240 = 3B x 8 CTAs) inside the step at the same shape:
+                # dram__bytes_read.sum 6 287 872 + dram__bytes_write.sum 140 961 280 (profiles/r03/r03_d_ncu_full_chain_raw.csv);
+                # below the algorithmic 204.3 MB because the rest of the maps is still in the 126 MB L2 when the launch ends
+                out[-1]['traffic'] = 6287872 + 140961280
+                out[-1]['traffic_source'] = 'profiles/r03/r03_d_ncu_full_chain_raw.csv (ncu --set full, round 3, same shape, launch inside the critic step)'
+                out[-1]['bound_note'] = ('per byte the kernel is HBM-class (25 flop/B) and is reported against HBM as the contract asks, but DRAM '
+                                         'traffic is 147 MB in 0.24 ms = 0.6 TB/s: what limits it is the tcgen05.mma issue floor named in `limiter`')
             rows = slice(2 * B, 3 * B)
             limiter = ('tcgen05 operand reads from shared memory in the block-Toeplitz form: ~52 cycles per 128x(48|32|16)x16 MMA, 390 MMAs '
                        'per layer and CTA + ~5 k cycles of halo hand-over per layer (clock trace: profiles/r02_b_chain_trace.txt)')

@@ -249,7 +249,7 @@ def load_inoutset_shard(indir, outdir, outwdir, fid_lst, rank, world, length=Non
     length = int(length)
     per = nb // world
     mine = range(rank * per, (rank + 1) * per)
-    outs = None
+    outs, reads = None, []
     for b in range(nb):
         shift = np.random.randint(0, (lens[b] - length) + 1) if maskpadtype == 'randshift' else 0
         if b not in mine:
@@ -261,16 +261,34 @@ def load_inoutset_shard(indir, outdir, outwdir, fid_lst, rank, world, length=Non
         r = b - mine[0]
         # only the window's frames leave the page cache, read straight into the batch: rows [shift, shift + m) of the cropped
         # utterance (the whole-file read, crop copy and window copy of load_inoutset are three passes more)
-        _read_window_into(outs[0][r, :m], xpat, fid_lst[b], sel, shift, m)
-        _read_window_into(outs[1][r, :m], ypat, fid_lst[b], sel, shift, m)
+        reads.append((outs[0][r, :m], xpat, fid_lst[b], sel, shift, m))
+        reads.append((outs[1][r, :m], ypat, fid_lst[b], sel, shift, m))
         outs[2][r, :m] = Wt[b][shift:shift + m].reshape(m, -1)
         for out in outs:
             out[r, m:] = 0
+    # every window draw is made (in utterance order, above); the reads themselves are independent and release the GIL
+    if len(reads) > 2:
+        list(_read_pool().map(lambda a: _read_window_into(*a), reads))
+    else:
+        for a in reads:
+            _read_window_into(*a)
     for out, path in zip(outs, (indir, outdir, outwdir)):
         # a NaN or an Inf anywhere makes the plain sum non-finite; so can an overflow of finite values, hence the exact second look
         if not np.isfinite(out.sum()) and not np.isfinite(out).all():
             raise ValueError('ERROR: There are nan or inf in a file of {}'.format(getpath(path)))
     return outs[0], outs[1], outs[2]
+
+
+_READ_POOL = None
+
+
+def _read_pool():
+    """Four threads shared by every batch assembly of the process (file reads into disjoint rows of a batch)."""
+    global _READ_POOL
+    if _READ_POOL is None:
+        import concurrent.futures
+        _READ_POOL = concurrent.futures.ThreadPoolExecutor(max_workers=4, thread_name_prefix='pctts-read')
+    return _READ_POOL
 
 
 def _read_window_into(dst, pat, fbase, sel, shift, m):
